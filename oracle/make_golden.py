@@ -1,0 +1,94 @@
+"""TEST INFRASTRUCTURE ONLY -- generates tests/golden/*.npz by running the REAL reference
+(/root/reference, imported through oracle/ref_import.py) in the build container.
+
+    PYTHONDONTWRITEBYTECODE=1 python oracle/make_golden.py
+
+The vectors hold inputs and the reference's outputs; tests/test_oracle_golden.py pins the numpy
+restatement (oracle/xcorr_oracle.py) to them and the -m gpu tests pin the CUDA library to them.
+Known-answer cases of the reference's own unit tests are restated in tests/ directly
+(xcorrRoutines.py:2130-2241, filterRoutines.py:1326-1335, cupyExtensions.py:697-712).
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+sys.path.insert(0, HERE)
+sys.path.insert(0, ROOT)
+
+import ref_import  # noqa: E402
+from pydsproutines_b200 import signals  # noqa: E402
+
+OUT = os.path.join(ROOT, "tests", "golden")
+
+
+def fastxcorr_cases(ref):
+    cases = {}
+    # (name, seed, N, rxlen, p0, k0, shifts or None)
+    specs = [
+        ("n64", 11, 64, 400, 123, 5, None),
+        ("n100_nonpow2", 12, 100, 350, 77, 9, None),
+        ("n256_step7", 13, 256, 2000, 704, 200, np.arange(4, 1500, 7)),
+        ("n1024", 14, 1024, 1024 + 96, 40, 1000, None),
+        ("n4096_win", 15, 4096, 4096 + 600, 300, 4000, np.arange(280, 320)),
+        ("n8192_win", 16, 8192, 8192 + 700, 345, 1234, np.arange(337, 353)),
+    ]
+    for name, seed, N, rxlen, p0, k0, shifts in specs:
+        cutout, rx = signals.make_fastxcorr_case(seed, N, rxlen, p0, k0, amp=0.7)
+        d = dict(cutout=cutout, rx=rx, p0=p0, k0=k0)
+        if shifts is not None:
+            d["shifts"] = shifts
+        d["qf2_nofreq"] = ref.fastXcorr(cutout, rx, shifts=shifts)
+        q, f = ref.fastXcorr(cutout, rx, freqsearch=True, shifts=shifts)
+        d["qf2_freq"], d["fidx_freq"] = q, f
+        if N <= 256:
+            d["cplx_nofreq"] = ref.fastXcorr(cutout, rx, shifts=shifts, absResult=False)
+            q, f = ref.fastXcorr(cutout, rx, freqsearch=True, shifts=shifts, absResult=False)
+            d["cplx_freq"], d["cplx_fidx"] = q, f
+            d["caf"] = ref.fastXcorr(cutout, rx, freqsearch=True, outputCAF=True, shifts=shifts)
+            d["caf_cplx"] = ref.fastXcorr(cutout, rx, freqsearch=True, outputCAF=True,
+                                          shifts=shifts, absResult=False)
+        cases[name] = d
+    return cases
+
+
+def group_cases(ref):
+    cases = {}
+    rng = np.random.default_rng(21)
+    specs = [
+        # name, G, L, F, starts, K, p0, k0
+        ("g4_l16_f64", 4, 16, 64, np.array([0, 40, 80, 120]), 60, 17, 5),
+        ("g8_l32_f256_ragged", 8, 32, 256, np.array([10, 47, 99, 140, 300, 333, 420, 511]), 48, 30, 200),
+        ("g64_l128_f4096_win", 64, 128, 4096, np.arange(64) * 1024, 12, 5, 777),
+        ("g6_l20_f32_wrap", 6, 20, 32, np.array([0, 25, 50, 77, 100, 131]), 40, 11, 3),
+    ]
+    for name, G, L, F, starts, K, p0, k0 in specs:
+        ygroups = signals.qpsk(rng, G * L).reshape(G, L)
+        z = starts - starts[0]
+        rx = signals.cnoise(rng, K + int(z[-1]) + F + 1)
+        for g in range(G):
+            a = p0 + int(z[g])
+            rx[a:a + L] += np.complex64(0.8) * ygroups[g] * signals.tone(L, k0, F, offset=int(z[g]))
+        obj = ref.GroupXcorrFFT(ygroups, starts, 1, fftlen=F)
+        shifts = np.arange(K)
+        xc, fi = obj.xcorr(rx, shifts)
+        caf = obj.xcorr(rx, shifts, flattenToTime=False)
+        cases[name] = dict(ygroups=ygroups, starts=starts, rx=rx, F=F, shifts=shifts,
+                           xc=xc, fi=fi, caf=caf, p0=p0, k0=k0)
+    return cases
+
+
+def main():
+    ref = ref_import.load()
+    os.makedirs(OUT, exist_ok=True)
+    for fam, cases in (("fastxcorr", fastxcorr_cases(ref)), ("groupxcorr", group_cases(ref))):
+        for name, d in cases.items():
+            path = os.path.join(OUT, "%s_%s.npz" % (fam, name))
+            np.savez_compressed(path, **d)
+            print(path, os.path.getsize(path))
+
+
+if __name__ == "__main__":
+    main()

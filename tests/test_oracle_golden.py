@@ -1,0 +1,109 @@
+"""Pins the numpy restatement (oracle/xcorr_oracle.py) to vectors produced by the REAL reference
+(oracle/make_golden.py, run in the build container) and to the reference's own known-answer tests."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import scipy.signal as sps
+
+from oracle import xcorr_oracle as orc
+from pydsproutines_b200 import signals
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _load(pattern):
+    files = sorted(glob.glob(os.path.join(GOLDEN, pattern)))
+    assert files, "golden vectors missing: %s" % pattern
+    return [(os.path.basename(f)[:-4], np.load(f)) for f in files]
+
+
+@pytest.mark.parametrize("name,d", _load("fastxcorr_*.npz"), ids=lambda v: v if isinstance(v, str) else "")
+def test_fastxcorr_restatement_is_bit_exact(name, d):
+    cutout, rx = d["cutout"], d["rx"]
+    shifts = d["shifts"] if "shifts" in d.files else None
+    assert np.array_equal(orc.fastXcorr(cutout, rx, shifts=shifts), d["qf2_nofreq"])
+    q, f = orc.fastXcorr(cutout, rx, freqsearch=True, shifts=shifts)
+    assert q.dtype == np.float64 and f.dtype == np.uint32
+    assert np.array_equal(q, d["qf2_freq"]) and np.array_equal(f, d["fidx_freq"])
+    # planted peak is where the generator put it
+    sh = np.arange(len(rx) - len(cutout) + 1) if shifts is None else shifts
+    assert sh[np.argmax(q)] == int(d["p0"]) and f[np.argmax(q)] == int(d["k0"])
+    if "caf" in d.files:
+        assert np.array_equal(orc.fastXcorr(cutout, rx, shifts=shifts, absResult=False), d["cplx_nofreq"])
+        q, f = orc.fastXcorr(cutout, rx, freqsearch=True, shifts=shifts, absResult=False)
+        assert np.array_equal(q, d["cplx_freq"]) and np.array_equal(f, d["cplx_fidx"])
+        assert np.array_equal(orc.fastXcorr(cutout, rx, True, True, shifts), d["caf"])
+        assert np.array_equal(orc.fastXcorr(cutout, rx, True, True, shifts, False), d["caf_cplx"])
+
+
+@pytest.mark.parametrize("name,d", _load("groupxcorr_*.npz"), ids=lambda v: v if isinstance(v, str) else "")
+def test_groupxcorr_restatement_is_bit_exact(name, d):
+    o = orc.GroupXcorrFFT(d["ygroups"], d["starts"], 1, fftlen=int(d["F"]))
+    xc, fi = o.xcorr(d["rx"], d["shifts"])
+    assert xc.dtype == np.float64 and fi.dtype == np.uint32
+    assert np.array_equal(xc, d["xc"]) and np.array_equal(fi, d["fi"])
+    assert np.array_equal(o.xcorr(d["rx"], d["shifts"], flattenToTime=False), d["caf"])
+    assert d["shifts"][np.argmax(xc)] == int(d["p0"]) and fi[np.argmax(xc)] == int(d["k0"])
+
+
+def test_cyipp_conventions():
+    c, rx = signals.make_fastxcorr_case(5, 32, 200, 60, 3)
+    p, b = orc.cyIppXcorrFFT(c, rx, -4, 190, 2)
+    assert p.dtype == np.float32 and b.dtype == np.int32 and p.size == len(range(-4, 190, 2))
+    assert p[0] == 0 and p[1] == 0 and p[-1] == 0 and b[-1] == 0      # out of range -> 0 (IppXcorrFFT.cpp:125-130)
+    assert np.argmax(p) == (60 + 4) // 2 and b[np.argmax(p)] == 3
+
+
+# ---- reference known-answer tests restated (xcorrRoutines.py:2130-2241) --------------------------
+def _qpsk_templates():
+    rng = np.random.default_rng(7)
+    x = signals.qpsk(rng, 100).astype(np.complex64)
+    templates = np.vstack((x[20:40] * 1.234, x[40:60] * 2.345)).astype(np.complex64)
+    return x, templates
+
+
+def test_template_correlator_known_answers():
+    x, templates = _qpsk_templates()
+    tc = orc.TemplateCrossCorrelator(templates, x.size)
+    out = tc.correlate(x)
+    assert out.shape == (2, 100 - 20 + 1)
+    np.testing.assert_almost_equal(np.abs(out[0, 20]), 1.0, 5)       # :2237-2241
+    np.testing.assert_almost_equal(np.abs(out[1, 40]), 1.0, 5)
+    qf, tidx = tc.correlate(x, returnMax=True)
+    assert tidx[20] == 0 and tidx[40] == 1
+    assert np.array_equal(qf, np.abs(out).max(axis=0)) and np.array_equal(tidx, np.abs(out).argmax(axis=0))
+    # single template equals sqrt(fastXcorr) to 6 dp (:2180-2200)
+    for i in range(2):
+        ref = orc.fastXcorr(templates[i], x) ** 0.5
+        np.testing.assert_almost_equal(np.abs(out[i]), ref, 5)
+    with pytest.raises(ValueError):
+        orc.TemplateCrossCorrelator(templates[0], 100)
+
+
+def test_multitemplate_dot_matches_template_correlator():
+    rng = np.random.default_rng(8)
+    T, L, n = 5, 24, 300
+    templates = signals.qpsk(rng, T * L).reshape(T, L)
+    x = signals.cnoise(rng, n)
+    x[100:100 + L] += templates[3]
+    tidx, qf2 = orc.multiTemplateSlidingDotProduct(x, templates.conj(), 0, n - L + 1)
+    qf, tidx2 = orc.TemplateCrossCorrelator(templates, n).correlate(x, returnMax=True)
+    assert np.array_equal(tidx, tidx2.astype(np.int32))
+    np.testing.assert_allclose(qf2, qf ** 2, rtol=2e-4)
+    assert np.argmax(qf2) == 100 and tidx[100] == 3
+
+
+def test_moving_average_known_answer():
+    x = np.random.default_rng(9).random(100).astype(np.float32)        # filterRoutines.py:1326-1335
+    np.testing.assert_almost_equal(orc.movingAverage(x, 20, sumInstead=True), sps.lfilter(np.ones(20), 1, x), 5)
+    np.testing.assert_almost_equal(orc.movingAverage(x, 20), sps.lfilter(np.ones(20) / 20, 1, x), 5)
+
+
+def test_find_local_maxima_known_answer():
+    x = np.zeros(50, np.float32)                                       # cupyExtensions.py:697-712
+    x[5], x[8], x[9], x[37], x[41] = 1.0, 0.5, 0.6, 0.9, 0.7
+    assert list(orc.findLocalMaxima(x, 0.4)) == [5, 9, 37, 41]
+    idx, val = orc.argmaxAbsRows(np.array([[1, 3j, -3, 0], [0, 0, 0, 0]], np.complex64))
+    assert list(idx) == [1, 0] and list(val) == [3.0, 0.0]
