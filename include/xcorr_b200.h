@@ -1,0 +1,158 @@
+/* xcorr_b200.h -- C-ABI of libxcorr_b200.so: B200 (sm_100a) kernels for the cross-correlation
+ * detection hot path of icyveins7/pydsproutines.
+ *
+ * Conventions (they follow the reference's own ctypes-DLL convention, cpuWola.py:38-66 and
+ * cython_ext/compareIntPreambles/compareIntPreambles.py:7-30):
+ *   - every buffer is caller-owned; outputs are caller-allocated;
+ *   - complex64 data is passed as `const void*` to interleaved (re, im) float32 pairs;
+ *   - `where` tells whether the data pointers are host (XC_HOST) or device (XC_DEVICE) memory;
+ *     with XC_HOST the library stages through its own cached device workspace (H2D, kernels, D2H)
+ *     and returns when the outputs are host-visible; with XC_DEVICE it only enqueues on `stream`
+ *     (a cudaStream_t, NULL = default stream) and does NOT synchronise;
+ *   - every function returns an int32 status (XC_OK == 0, negative on error) and leaves a
+ *     thread-local message readable through xc_last_error(); no C++ exception crosses the ABI;
+ *   - there is no CPU fallback: without a CUDA device every compute call returns XC_ERR_CUDA.
+ *
+ * Each entry point cites the reference interface it replaces (file:line in pydsproutines @ e005737).
+ */
+#ifndef XCORR_B200_H
+#define XCORR_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define XC_OK 0
+#define XC_ERR_ARG (-1)         /* bad argument value (maps to ValueError)                       */
+#define XC_ERR_RANGE (-2)       /* shift / index outside the input (maps to ValueError)          */
+#define XC_ERR_UNSUPPORTED (-3) /* size not supported by the kernels (maps to NotImplementedError)*/
+#define XC_ERR_NOMEM (-4)       /* device allocation failed (maps to MemoryError)                */
+#define XC_ERR_CUDA (-5)        /* CUDA runtime / launch failure (maps to RuntimeError)          */
+
+#define XC_HOST 0
+#define XC_DEVICE 1
+
+/* flags of xc_fastxcorr_c64 */
+#define XC_FLAG_ZERO_OOB 1 /* shifts with s<0 or s+N>rxlen give 0.0 / 0 (IppXcorrFFT.cpp:125-130) */
+
+/* The peak tuple (QF^2, frequency index, peak position) of one call; what ranks exchange in the
+ * shift-sharded multi-GPU run (one allgather of world_size of these). 32 bytes. */
+typedef struct xc_peak {
+    float qf2;     /* largest QF^2 of the call                                     */
+    uint32_t fidx; /* its frequency bin (0 when no frequency search)               */
+    int64_t index; /* position in the call's shift list (lowest on ties)           */
+    int64_t shift; /* the shift value itself (shift0 + index*step, or shifts[index])*/
+    int32_t aux;   /* template index for the multi-template correlator, else 0     */
+    int32_t rank;  /* filled by the host side when peaks of several ranks are merged*/
+} xc_peak;
+
+/* ---- library / device ------------------------------------------------------------------ */
+int32_t xc_version(void);
+const char* xc_last_error(void);
+int32_t xc_device_count(void);
+int32_t xc_set_device(int32_t device);
+/* frees the cached device workspace of the current device */
+int32_t xc_release_workspace(void);
+/* device properties the bench reports: out[0]=SM count, out[1]=max smem/block (opt-in), out[2]=clock kHz,
+ * out[3]=compute capability major*10+minor */
+int32_t xc_device_info(int32_t* out4);
+/* number of kernels launched by this library in this process so far (bench.py's gpu_launches) */
+int64_t xc_launch_count(void);
+/* CUDA-event timing of the dominant (fused FFT) kernel: when enabled, every launch of it is bracketed
+ * by two events on its own stream; xc_profile_last_ms() waits for the latest one and returns its
+ * duration in milliseconds (-1 when nothing was recorded).  Used by bench.py for the roofline. */
+int32_t xc_profile_enable(int32_t on);
+double xc_profile_last_ms(void);
+/* sustained FP32 FMA rate of the device in TFLOP/s measured with a register-resident FFMA loop
+ * for `ms` milliseconds (roofline denominator of the FFT kernels; not a reference function) */
+int32_t xc_measure_fp32_tflops(double ms, double* tflops);
+
+/* ---- a11: sliding energy primitives ------------------------------------------------------ */
+/* valid-mode windowed energy out[s] = sum_{n<L} |x[s+n]|^2, s in [0, n-L+1)
+ * (what xcorrRoutines.py:342-355 slices out of cupyComplexMagnSq + cupyMovingAverage(sumInstead)) */
+int32_t xc_sliding_energy_c64(const void* x, int64_t n, int32_t L, float* out, int32_t where,
+                              void* stream);
+/* cupyMovingAverage (filterRoutines.py:1167-1203 -> filter.cu:291-347): causal length-L window,
+ * zero padded front, out has n elements; sum_instead != 0 gives the moving sum */
+int32_t xc_moving_average_f32(const float* x, int64_t n, int32_t L, int32_t sum_instead, float* out,
+                              int32_t where, void* stream);
+/* cupyComplexMagnSq (cupyExtensions.py:337-387 -> complex_magn.cu:8-20): out[i] = re^2 + im^2
+ * evaluated in the output type; out_f64 != 0 writes float64 */
+int32_t xc_complex_magnsq_c64(const void* x, int64_t n, void* out, int32_t out_f64, int32_t where,
+                              void* stream);
+
+/* ---- a1, a2, a4, a5, a6: fastXcorr --------------------------------------------------------
+ * xcorrRoutines.fastXcorr (xcorrRoutines.py:460-531), cp_fastXcorr (29-167), cp_fastXcorr_v2
+ * (169-274), IppXcorrFFT_32fc::xcorr_array (IppXcorrFFT.cpp:94-178).
+ * Shift list: shift0 + i*step, i in [0, K), or the explicit list `shifts` (int64[K], same memory
+ * space as `rx`) when non-NULL.  The cutout is conjugated inside (pass it as the reference does).
+ *   freqsearch == 0: qf2[i] = |sum_n conj(rx[s+n]) cutout[n]|^2 / ||cutout||^2 / ||rx[s:s+N]||^2
+ *   freqsearch != 0: X = FFT_N(rx[s:s+N] * conj(cutout)); fidx[i] = argmax |X|^2 (lowest index on
+ *                    ties); qf2[i] = |X[fidx]|^2 / ||cutout||^2 / ||rx[s:s+N]||^2
+ * qf2: float32[K]; fidx: uint32[K] (may be NULL when freqsearch == 0); cplx: optional
+ * complex64[K] receiving the un-squared complex QF of the absResult=False variants
+ * (xcorrRoutines.py:497-509, 533-548); peak: optional, HOST pointer, filled with the call's
+ * largest QF^2 (forces a stream synchronisation). */
+int32_t xc_fastxcorr_c64(const void* cutout, int32_t N, const void* rx, int64_t rxlen, int64_t shift0,
+                         int64_t step, int64_t K, const int64_t* shifts, int32_t freqsearch,
+                         int32_t flags, float* qf2, uint32_t* fidx, void* cplx, xc_peak* peak,
+                         int32_t where, void* stream);
+/* a3: full CAF rows (xcorrRoutines.py:550-580): caf is float32 (K, N) QF^2 when complex_out == 0,
+ * complex64 (K, N) un-squared QF when complex_out != 0. Bins are in natural FFT order. */
+int32_t xc_fastxcorr_caf_c64(const void* cutout, int32_t N, const void* rx, int64_t rxlen,
+                             int64_t shift0, int64_t step, int64_t K, const int64_t* shifts,
+                             void* caf, int32_t complex_out, int32_t where, void* stream);
+/* 1 when the fused frequency-search kernel has an instantiation for this cutout length */
+int32_t xc_fastxcorr_supported(int32_t N);
+
+/* ---- a7, a8: GroupXcorrFFT ----------------------------------------------------------------
+ * xcorrRoutines.GroupXcorrFFT (xcorrRoutines.py:1047-1262), GroupXcorrFFT.cpp:3-199.
+ * ygroups: complex64 (G, L) HOST memory, conjugated inside when auto_conj != 0; starts: int64[G]
+ * used as given (the Python side applies autoZeroStarts); F = fftlen >= L. */
+typedef struct xc_group xc_group;
+int32_t xc_group_create(const void* ygroups, int32_t G, int32_t L, const int64_t* starts, int32_t F,
+                        int32_t auto_conj, xc_group** handle);
+/* per shift s: Z[k] = sum_g exp(-j2pi k starts[g]/F) FFT_F(ygroups[g] * rx[s+starts[g] : +L])[k];
+ * caf[k] = |Z[k]|^2 / sum_g ||rx_g||^2 / ||ygroups||^2.  qf2/fidx (float32[K], uint32[K]) receive
+ * the max / argmax over k when non-NULL; caf (float32 (K, F)) the full rows when non-NULL. */
+int32_t xc_group_xcorr(xc_group* handle, const void* rx, int64_t rxlen, int64_t shift0, int64_t step,
+                       int64_t K, const int64_t* shifts, float* qf2, uint32_t* fidx, float* caf,
+                       xc_peak* peak, int32_t where, void* stream);
+int32_t xc_group_destroy(xc_group* handle);
+
+/* ---- a9, a10: (multi-)template correlator -------------------------------------------------
+ * xcorrRoutines.TemplateCrossCorrelator (xcorrRoutines.py:277-371) and
+ * cupyExtensions.multiTemplateSlidingDotProduct (cupyExtensions.py:563-642 -> multiplySlices.cu:251-399).
+ * templates: complex64 (T, L) HOST memory; conj != 0 conjugates them inside (TemplateCrossCorrelator
+ * semantics), conj == 0 uses them as given (multiTemplateSlidingDotProduct semantics).
+ * energies: optional float32[T] template energies (NULL = computed inside). */
+typedef struct xc_mt xc_mt;
+int32_t xc_mt_create(const void* templates, int32_t T, int32_t L, int32_t conj, const float* energies,
+                     xc_mt** handle);
+/* for s = start + i, i in [0, K): d_t = sum_n tmpl_t[n] x[s+n];
+ *   best[i] = max_t |d_t|^2 / E_t / E_x[s]  (sqrt of it when sqrt_out != 0), tidx[i] = argmax_t
+ *   (lowest t on ties; index 0 when nothing is > 0, multiplySlices.cu:313-316,382-386);
+ *   full (optional complex64 (T, K)) = d_t / sqrt(E_t) / sqrt(E_x[s])  (xcorrRoutines.py:352-357) */
+int32_t xc_mt_correlate(xc_mt* handle, const void* x, int64_t xlen, int64_t start, int64_t K,
+                        float* best, int32_t* tidx, void* full, int32_t sqrt_out, xc_peak* peak,
+                        int32_t where, void* stream);
+int32_t xc_mt_destroy(xc_mt* handle);
+
+/* ---- a12: row argmax (cupyExtensions.py:268-319 -> argmax.cu:93-152) ------------------------ */
+/* per row of the complex64 (rows, cols) matrix: index of the largest abs(x) (use_normsq == 0) or
+ * abs(x)^2 (use_normsq != 0), lowest index on ties; val (optional) receives that value */
+int32_t xc_row_argmax_c64(const void* x, int64_t rows, int64_t cols, int32_t use_normsq, uint32_t* idx,
+                          float* val, int32_t where, void* stream);
+
+/* ---- a13: local maxima (cupyExtensions.py:651-686 -> peakfinding.cu:14-58) ------------------ */
+/* indices i with x[i] > min_height, x[i] > x[i-1], x[i] > x[i+1] (outside = 0); at most `cap` are
+ * stored (count still reports how many exist); sorted != 0 returns them in ascending order */
+int32_t xc_find_local_maxima_f32(const float* x, int64_t n, float min_height, int32_t* idx, int32_t cap,
+                                 int32_t* count, int32_t sorted, int32_t where, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* XCORR_B200_H */

@@ -1,0 +1,394 @@
+// api.cu -- the C-ABI of libxcorr_b200 (include/xcorr_b200.h): argument checks, host<->device
+// staging for XC_HOST callers, error strings.  All arithmetic is in the kernels; nothing here
+// computes on the CPU.
+#include <stdarg.h>
+
+#include <atomic>
+
+#include "internal.cuh"
+
+namespace xc {
+
+static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+int32_t fail(int32_t code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+void count_launch(int n) { g_launches += n; }
+
+static bool g_prof_on = false, g_prof_valid = false;
+static cudaEvent_t g_prof_e0 = nullptr, g_prof_e1 = nullptr;
+void profile_begin(cudaStream_t st) {
+    if (!g_prof_on) return;
+    if (!g_prof_e0) {
+        cudaEventCreate(&g_prof_e0);
+        cudaEventCreate(&g_prof_e1);
+    }
+    cudaEventRecord(g_prof_e0, st);
+}
+void profile_end(cudaStream_t st) {
+    if (!g_prof_on) return;
+    cudaEventRecord(g_prof_e1, st);
+    g_prof_valid = true;
+}
+
+// ---- workspace -----------------------------------------------------------------------------------
+struct SlotBuf {
+    void* ptr = nullptr;
+    size_t bytes = 0;
+};
+static SlotBuf g_slots[SLOT_COUNT];
+static int g_sm_count = 0, g_smem_optin = 0, g_dev = -1;
+
+static void refresh_device() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return;
+    if (dev == g_dev && g_sm_count) return;
+    if (g_dev != -1 && dev != g_dev) release_workspace();
+    g_dev = dev;
+    cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
+    cudaDeviceGetAttribute(&g_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+}
+int sm_count() {
+    refresh_device();
+    return g_sm_count > 0 ? g_sm_count : 1;
+}
+int max_smem_optin() {
+    refresh_device();
+    return g_smem_optin;
+}
+void* workspace(Slot slot, size_t bytes) {
+    refresh_device();
+    SlotBuf& s = g_slots[slot];
+    if (bytes == 0) bytes = 256;
+    if (s.bytes >= bytes) return s.ptr;
+    if (s.ptr) {
+        cudaDeviceSynchronize();   // the old block may still be in use by enqueued work
+        cudaFree(s.ptr);
+        s.ptr = nullptr;
+        s.bytes = 0;
+    }
+    size_t want = bytes + bytes / 8;
+    want = (want + 255) & ~(size_t)255;
+    cudaError_t e = cudaMalloc(&s.ptr, want);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        e = cudaMalloc(&s.ptr, bytes);
+        want = bytes;
+    }
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        s.ptr = nullptr;
+        fail(XC_ERR_NOMEM, "device allocation of %zu bytes failed: %s", bytes, cudaGetErrorString(e));
+        return nullptr;
+    }
+    s.bytes = want;
+    return s.ptr;
+}
+int32_t release_workspace() {
+    for (int i = 0; i < SLOT_COUNT; ++i) {
+        if (g_slots[i].ptr) cudaFree(g_slots[i].ptr);
+        g_slots[i] = SlotBuf();
+    }
+    return XC_OK;
+}
+
+// ---- staging helpers -------------------------------------------------------------------------------
+// Input: returns a device pointer holding `bytes` bytes of `p` (p itself in device mode).
+static const void* stage_in(Slot slot, const void* p, size_t bytes, int where, cudaStream_t st, int32_t* status) {
+    if (where == XC_DEVICE || p == nullptr) return p;
+    void* d = workspace(slot, bytes);
+    if (!d) {
+        *status = XC_ERR_NOMEM;
+        return nullptr;
+    }
+    if (bytes) {
+        cudaError_t e = cudaMemcpyAsync(d, p, bytes, cudaMemcpyHostToDevice, st);
+        if (e != cudaSuccess) *status = fail(XC_ERR_CUDA, "H2D copy failed: %s", cudaGetErrorString(e));
+    }
+    return d;
+}
+static void* stage_out(Slot slot, void* p, size_t bytes, int where, int32_t* status) {
+    if (where == XC_DEVICE || p == nullptr) return p;
+    void* d = workspace(slot, bytes);
+    if (!d) *status = XC_ERR_NOMEM;
+    return d;
+}
+static int32_t fetch_out(void* host, const void* dev, size_t bytes, int where, cudaStream_t st) {
+    if (where == XC_DEVICE || host == nullptr || bytes == 0) return XC_OK;
+    XC_CUDA_TRY(cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, st));
+    return XC_OK;
+}
+static int32_t finish(int where, cudaStream_t st) {
+    if (where == XC_HOST) XC_CUDA_TRY(cudaStreamSynchronize(st));
+    return XC_OK;
+}
+static int32_t check_where(int where) {
+    if (where != XC_HOST && where != XC_DEVICE) return fail(XC_ERR_ARG, "where must be XC_HOST (0) or XC_DEVICE (1)");
+    return XC_OK;
+}
+static int32_t require_device() {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        return fail(XC_ERR_CUDA, "no CUDA device available (%s); libxcorr_b200 has no CPU fallback",
+                    e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    }
+    return XC_OK;
+}
+
+// Fills *peak from the device arrays of one call (synchronises the stream).
+int32_t collect_peak(const float* d_qf2, const uint32_t* d_fidx, const int32_t* d_aux, int64_t K, int64_t shift0,
+                     int64_t step, const int64_t* d_shifts, xc_peak* peak, cudaStream_t st) {
+    memset(peak, 0, sizeof(*peak));
+    peak->index = -1;
+    if (K <= 0) return XC_OK;
+    unsigned long long* d_packed = reinterpret_cast<unsigned long long*>(workspace(SLOT_TMP3, 256));
+    if (!d_packed) return XC_ERR_NOMEM;
+    XC_TRY(peak_reduce_device(d_qf2, d_fidx, d_aux, K, d_packed, st));
+    unsigned long long packed = 0;
+    XC_CUDA_TRY(cudaMemcpyAsync(&packed, d_packed, sizeof(packed), cudaMemcpyDeviceToHost, st));
+    XC_CUDA_TRY(cudaStreamSynchronize(st));
+    const uint32_t vb = (uint32_t)(packed >> 32);
+    memcpy(&peak->qf2, &vb, 4);
+    peak->index = (int64_t)(0xffffffffu - (uint32_t)(packed & 0xffffffffull));
+    if (d_fidx) XC_CUDA_TRY(cudaMemcpy(&peak->fidx, d_fidx + peak->index, 4, cudaMemcpyDeviceToHost));
+    if (d_aux) XC_CUDA_TRY(cudaMemcpy(&peak->aux, d_aux + peak->index, 4, cudaMemcpyDeviceToHost));
+    if (d_shifts)
+        XC_CUDA_TRY(cudaMemcpy(&peak->shift, d_shifts + peak->index, 8, cudaMemcpyDeviceToHost));
+    else
+        peak->shift = shift0 + peak->index * step;
+    return XC_OK;
+}
+
+}  // namespace xc
+
+using namespace xc;
+
+extern "C" {
+
+int32_t xc_version(void) { return 100; }
+const char* xc_last_error(void) { return g_err; }
+int32_t xc_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+int32_t xc_set_device(int32_t device) {
+    XC_TRY(require_device());
+    XC_CUDA_TRY(cudaSetDevice(device));
+    return XC_OK;
+}
+int32_t xc_release_workspace(void) { return release_workspace(); }
+int32_t xc_device_info(int32_t* out4) {
+    if (!out4) return fail(XC_ERR_ARG, "out4 is NULL");
+    XC_TRY(require_device());
+    int dev = 0, clock = 0, major = 0, minor = 0;
+    XC_CUDA_TRY(cudaGetDevice(&dev));
+    cudaDeviceGetAttribute(&clock, cudaDevAttrClockRate, dev);
+    cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+    cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, dev);
+    out4[0] = sm_count();
+    out4[1] = max_smem_optin();
+    out4[2] = clock;
+    out4[3] = major * 10 + minor;
+    return XC_OK;
+}
+int64_t xc_launch_count(void) { return g_launches.load(); }
+int32_t xc_profile_enable(int32_t on) {
+    g_prof_on = on != 0;
+    g_prof_valid = false;
+    return XC_OK;
+}
+double xc_profile_last_ms(void) {
+    if (!g_prof_valid) return -1.0;
+    if (cudaEventSynchronize(g_prof_e1) != cudaSuccess) return -1.0;
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, g_prof_e0, g_prof_e1) != cudaSuccess) return -1.0;
+    return (double)ms;
+}
+
+int32_t xc_sliding_energy_c64(const void* x, int64_t n, int32_t L, float* out, int32_t where, void* stream) {
+    XC_TRY(check_where(where));
+    if (!x || !out) return fail(XC_ERR_ARG, "x/out is NULL");
+    if (L < 1 || n < L) return fail(XC_ERR_ARG, "need 1 <= L <= n (L=%d, n=%lld)", L, (long long)n);
+    XC_TRY(require_device());
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t n_out = n - L + 1;
+    int32_t status = XC_OK;
+    const void* dx = stage_in(SLOT_IN0, x, sizeof(float2) * (size_t)n, where, st, &status);
+    float* dout = (float*)stage_out(SLOT_OUT0, out, sizeof(float) * (size_t)n_out, where, &status);
+    XC_TRY(status);
+    XC_TRY(sliding_sum_device(dx, true, n, 0, L, n_out, dout, 0, st));
+    XC_TRY(fetch_out(out, dout, sizeof(float) * (size_t)n_out, where, st));
+    return finish(where, st);
+}
+
+int32_t xc_moving_average_f32(const float* x, int64_t n, int32_t L, int32_t sum_instead, float* out, int32_t where,
+                              void* stream) {
+    XC_TRY(check_where(where));
+    if (!x || !out) return fail(XC_ERR_ARG, "x/out is NULL");
+    if (L < 1) return fail(XC_ERR_ARG, "avgLength must be >= 1");
+    if (n <= 0) return XC_OK;
+    XC_TRY(require_device());
+    cudaStream_t st = (cudaStream_t)stream;
+    int32_t status = XC_OK;
+    const void* dx = stage_in(SLOT_IN0, x, sizeof(float) * (size_t)n, where, st, &status);
+    float* dout = (float*)stage_out(SLOT_OUT0, out, sizeof(float) * (size_t)n, where, &status);
+    XC_TRY(status);
+    XC_TRY(sliding_sum_device(dx, false, n, (int64_t)L - 1, L, n, dout, sum_instead ? 0 : 1, st));
+    XC_TRY(fetch_out(out, dout, sizeof(float) * (size_t)n, where, st));
+    return finish(where, st);
+}
+
+int32_t xc_complex_magnsq_c64(const void* x, int64_t n, void* out, int32_t out_f64, int32_t where, void* stream) {
+    XC_TRY(check_where(where));
+    if (!x || !out) return fail(XC_ERR_ARG, "x/out is NULL");
+    if (n <= 0) return XC_OK;
+    XC_TRY(require_device());
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t ob = (out_f64 ? 8 : 4) * (size_t)n;
+    int32_t status = XC_OK;
+    const void* dx = stage_in(SLOT_IN0, x, sizeof(float2) * (size_t)n, where, st, &status);
+    void* dout = stage_out(SLOT_OUT0, out, ob, where, &status);
+    XC_TRY(status);
+    XC_TRY(magnsq_device((const float2*)dx, n, dout, out_f64, st));
+    XC_TRY(fetch_out(out, dout, ob, where, st));
+    return finish(where, st);
+}
+
+int32_t xc_fastxcorr_supported(int32_t N) { return fastxcorr_fft_supported(N) ? 1 : 0; }
+
+static int32_t check_shift_args(int32_t N, int64_t rxlen, int64_t shift0, int64_t step, int64_t K,
+                                const int64_t* shifts, int32_t flags) {
+    if (N < 1) return fail(XC_ERR_ARG, "cutout length must be >= 1");
+    if (K < 0) return fail(XC_ERR_ARG, "number of shifts must be >= 0");
+    if (rxlen < 0) return fail(XC_ERR_ARG, "rxlen must be >= 0");
+    if (!shifts && !(flags & XC_FLAG_ZERO_OOB) && K > 0) {
+        const int64_t last = shift0 + (K - 1) * step;
+        const int64_t lo = shift0 < last ? shift0 : last, hi = shift0 < last ? last : shift0;
+        if (lo < 0 || hi + N > rxlen)
+            return fail(XC_ERR_RANGE, "shifts [%lld, %lld] with cutout length %d leave rx of length %lld",
+                        (long long)lo, (long long)hi, N, (long long)rxlen);
+    }
+    return XC_OK;
+}
+
+int32_t xc_fastxcorr_c64(const void* cutout, int32_t N, const void* rx, int64_t rxlen, int64_t shift0, int64_t step,
+                         int64_t K, const int64_t* shifts, int32_t freqsearch, int32_t flags, float* qf2,
+                         uint32_t* fidx, void* cplx, xc_peak* peak, int32_t where, void* stream) {
+    XC_TRY(check_where(where));
+    if (!cutout || !rx) return fail(XC_ERR_ARG, "cutout/rx is NULL");
+    if (!qf2 && !cplx) return fail(XC_ERR_ARG, "qf2 and cplx are both NULL");
+    XC_TRY(check_shift_args(N, rxlen, shift0, step, K, shifts, flags));
+    if (freqsearch && !fastxcorr_fft_supported(N))
+        return fail(XC_ERR_UNSUPPORTED, "fused frequency search supports power-of-two cutout lengths up to 16384, got %d", N);
+    XC_TRY(require_device());
+    if (K == 0) {
+        if (peak) { memset(peak, 0, sizeof(*peak)); peak->index = -1; }
+        return XC_OK;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    int32_t status = XC_OK;
+    const float2* dc = (const float2*)stage_in(SLOT_IN0, cutout, sizeof(float2) * (size_t)N, where, st, &status);
+    const float2* drx = (const float2*)stage_in(SLOT_IN1, rx, sizeof(float2) * (size_t)rxlen, where, st, &status);
+    const int64_t* dsh = (const int64_t*)stage_in(SLOT_IN2, shifts, sizeof(int64_t) * (size_t)K, where, st, &status);
+    // qf2 is always produced on the device when a peak is wanted
+    float* dq = (float*)stage_out(SLOT_OUT0, qf2, sizeof(float) * (size_t)K, where, &status);
+    if (!dq && peak) dq = (float*)workspace(SLOT_OUT0, sizeof(float) * (size_t)K);
+    uint32_t* df = (uint32_t*)stage_out(SLOT_OUT1, fidx, sizeof(uint32_t) * (size_t)K, where, &status);
+    if (!df && peak && freqsearch) df = (uint32_t*)workspace(SLOT_OUT1, sizeof(uint32_t) * (size_t)K);
+    float2* dz = (float2*)stage_out(SLOT_OUT2, cplx, sizeof(float2) * (size_t)K, where, &status);
+    XC_TRY(status);
+    ShiftList sl{shift0, step, K, dsh};
+    if (freqsearch) {
+        XC_TRY(fastxcorr_freq_device(dc, N, drx, rxlen, sl, dq, df, dz, nullptr, 0, st));
+    } else {
+        XC_TRY(fastxcorr_nofreq_device(dc, N, drx, rxlen, sl, dq, dz, st));
+        if (fidx && df) XC_CUDA_TRY(cudaMemsetAsync(df, 0, sizeof(uint32_t) * (size_t)K, st));
+    }
+    XC_TRY(fetch_out(qf2, dq, sizeof(float) * (size_t)K, where, st));
+    XC_TRY(fetch_out(fidx, df, sizeof(uint32_t) * (size_t)K, where, st));
+    XC_TRY(fetch_out(cplx, dz, sizeof(float2) * (size_t)K, where, st));
+    if (peak) XC_TRY(collect_peak(dq, freqsearch ? df : nullptr, nullptr, K, shift0, step, dsh, peak, st));
+    return finish(where, st);
+}
+
+int32_t xc_fastxcorr_caf_c64(const void* cutout, int32_t N, const void* rx, int64_t rxlen, int64_t shift0,
+                             int64_t step, int64_t K, const int64_t* shifts, void* caf, int32_t complex_out,
+                             int32_t where, void* stream) {
+    XC_TRY(check_where(where));
+    if (!cutout || !rx || !caf) return fail(XC_ERR_ARG, "cutout/rx/caf is NULL");
+    XC_TRY(check_shift_args(N, rxlen, shift0, step, K, shifts, 0));
+    if (!fastxcorr_fft_supported(N))
+        return fail(XC_ERR_UNSUPPORTED, "fused frequency search supports power-of-two cutout lengths up to 16384, got %d", N);
+    XC_TRY(require_device());
+    if (K == 0) return XC_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t cb = (complex_out ? sizeof(float2) : sizeof(float)) * (size_t)K * (size_t)N;
+    int32_t status = XC_OK;
+    const float2* dc = (const float2*)stage_in(SLOT_IN0, cutout, sizeof(float2) * (size_t)N, where, st, &status);
+    const float2* drx = (const float2*)stage_in(SLOT_IN1, rx, sizeof(float2) * (size_t)rxlen, where, st, &status);
+    const int64_t* dsh = (const int64_t*)stage_in(SLOT_IN2, shifts, sizeof(int64_t) * (size_t)K, where, st, &status);
+    void* dcaf = stage_out(SLOT_OUT0, caf, cb, where, &status);
+    XC_TRY(status);
+    ShiftList sl{shift0, step, K, dsh};
+    XC_TRY(fastxcorr_freq_device(dc, N, drx, rxlen, sl, nullptr, nullptr, nullptr, dcaf, complex_out, st));
+    XC_TRY(fetch_out(caf, dcaf, cb, where, st));
+    return finish(where, st);
+}
+
+int32_t xc_row_argmax_c64(const void* x, int64_t rows, int64_t cols, int32_t use_normsq, uint32_t* idx, float* val,
+                          int32_t where, void* stream) {
+    XC_TRY(check_where(where));
+    if (!x || !idx) return fail(XC_ERR_ARG, "x/idx is NULL");
+    if (rows < 0 || cols < 1) return fail(XC_ERR_ARG, "need rows >= 0 and cols >= 1");
+    XC_TRY(require_device());
+    if (rows == 0) return XC_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    int32_t status = XC_OK;
+    const float2* dx = (const float2*)stage_in(SLOT_IN0, x, sizeof(float2) * (size_t)rows * (size_t)cols, where, st, &status);
+    uint32_t* di = (uint32_t*)stage_out(SLOT_OUT0, idx, sizeof(uint32_t) * (size_t)rows, where, &status);
+    float* dv = (float*)stage_out(SLOT_OUT1, val, sizeof(float) * (size_t)rows, where, &status);
+    XC_TRY(status);
+    XC_TRY(row_argmax_device(dx, rows, cols, use_normsq, di, dv, st));
+    XC_TRY(fetch_out(idx, di, sizeof(uint32_t) * (size_t)rows, where, st));
+    XC_TRY(fetch_out(val, dv, sizeof(float) * (size_t)rows, where, st));
+    return finish(where, st);
+}
+
+int32_t xc_find_local_maxima_f32(const float* x, int64_t n, float min_height, int32_t* idx, int32_t cap, int32_t* count,
+                                 int32_t sorted, int32_t where, void* stream) {
+    (void)sorted;   // the compaction is ordered, so the result is always ascending
+    XC_TRY(check_where(where));
+    if (!x || !idx || !count) return fail(XC_ERR_ARG, "x/idx/count is NULL");
+    if (cap < 0 || n < 0) return fail(XC_ERR_ARG, "cap and n must be >= 0");
+    XC_TRY(require_device());
+    cudaStream_t st = (cudaStream_t)stream;
+    int32_t status = XC_OK;
+    const float* dx = (const float*)stage_in(SLOT_IN0, x, sizeof(float) * (size_t)n, where, st, &status);
+    int32_t* di = (int32_t*)stage_out(SLOT_OUT0, idx, sizeof(int32_t) * (size_t)(cap > 0 ? cap : 1), where, &status);
+    int32_t* dcnt = (int32_t*)stage_out(SLOT_OUT1, count, sizeof(int32_t), where, &status);
+    XC_TRY(status);
+    XC_TRY(local_maxima_device(dx, n, min_height, di, cap, dcnt, st));
+    XC_TRY(fetch_out(idx, di, sizeof(int32_t) * (size_t)cap, where, st));
+    XC_TRY(fetch_out(count, dcnt, sizeof(int32_t), where, st));
+    return finish(where, st);
+}
+
+}  // extern "C"

@@ -1,0 +1,92 @@
+// common.cuh -- shared helpers of libxcorr_b200: status/error plumbing, complex arithmetic,
+// the cached device workspace used when the caller passes host pointers.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/xcorr_b200.h"
+
+namespace xc {
+
+// ---------------------------------------------------------------------------------------------
+// error plumbing
+// ---------------------------------------------------------------------------------------------
+void set_error(const char* fmt, ...);
+int32_t fail(int32_t code, const char* fmt, ...);
+void count_launch(int n = 1);
+// optional CUDA-event timing of the dominant (fused) kernel, read back by xc_profile_last_ms()
+void profile_begin(cudaStream_t st);
+void profile_end(cudaStream_t st);
+
+#define XC_CUDA_TRY(expr)                                                                        \
+    do {                                                                                         \
+        cudaError_t _e = (expr);                                                                 \
+        if (_e != cudaSuccess) {                                                                 \
+            return xc::fail(_e == cudaErrorMemoryAllocation ? XC_ERR_NOMEM : XC_ERR_CUDA,        \
+                            "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__,    \
+                            __LINE__);                                                           \
+        }                                                                                        \
+    } while (0)
+
+#define XC_TRY(expr)                  \
+    do {                              \
+        int32_t _s = (expr);          \
+        if (_s != XC_OK) return _s;   \
+    } while (0)
+
+#define XC_LAUNCH_CHECK()                                                                        \
+    do {                                                                                         \
+        cudaError_t _e = cudaGetLastError();                                                     \
+        if (_e != cudaSuccess)                                                                   \
+            return xc::fail(XC_ERR_CUDA, "kernel launch failed: %s (%s:%d)",                     \
+                            cudaGetErrorString(_e), __FILE__, __LINE__);                         \
+        xc::count_launch();                                                                      \
+    } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// device workspace: grow-only named slots, per process (one device per process is the model;
+// switching device releases the slots)
+// ---------------------------------------------------------------------------------------------
+enum Slot {
+    SLOT_IN0 = 0,  // staged inputs (host mode)
+    SLOT_IN1,
+    SLOT_IN2,
+    SLOT_OUT0,     // staged outputs (host mode)
+    SLOT_OUT1,
+    SLOT_OUT2,
+    SLOT_TMP0,     // kernel temporaries (energies, partial peaks, ...)
+    SLOT_TMP1,
+    SLOT_TMP2,
+    SLOT_TMP3,
+    SLOT_COUNT
+};
+// returns a device pointer of at least `bytes` bytes (256-byte aligned), NULL + error on failure
+void* workspace(Slot slot, size_t bytes);
+int32_t release_workspace();
+int sm_count();
+int max_smem_optin();
+
+// ---------------------------------------------------------------------------------------------
+// complex helpers (float2 = interleaved complex64)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float2 cmul(float2 a, float2 b) {
+    return make_float2(fmaf(a.x, b.x, -a.y * b.y), fmaf(a.x, b.y, a.y * b.x));
+}
+// a * conj(b)
+__device__ __forceinline__ float2 cmulc(float2 a, float2 b) {
+    return make_float2(fmaf(a.x, b.x, a.y * b.y), fmaf(a.y, b.x, -a.x * b.y));
+}
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+__device__ __forceinline__ float cnorm2(float2 a) { return fmaf(a.x, a.x, a.y * a.y); }
+
+// per-call peak reduction record kept on the device: packs (value, index) so that a single
+// 64-bit atomicMax picks the largest value and, on ties, the LOWEST index.
+__device__ __forceinline__ unsigned long long pack_peak(float v, uint32_t inv_index) {
+    // v >= 0 here (a QF^2), so its bit pattern is monotone in v
+    return ((unsigned long long)__float_as_uint(v) << 32) | (unsigned long long)inv_index;
+}
+
+}  // namespace xc

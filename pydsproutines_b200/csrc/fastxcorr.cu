@@ -1,0 +1,260 @@
+// fastxcorr.cu -- fastXcorr on the B200.
+//   freqsearch: fused product -> block FFT -> |X|^2 -> normalise -> arg max (fused_fft_kernel.cuh),
+//               replacing the copy/multiply/cuFFT/argmax chain of cp_fastXcorr (xcorrRoutines.py:98-151)
+//               and IppXcorrFFT_32fc::xcorr_thread (IppXcorrFFT.cpp:94-178);
+//   no freqsearch: register-tiled sliding dot product (xcorrRoutines.py:483-509).
+#include "fused_fft_kernel.cuh"
+#include "internal.cuh"
+#include "plans.cuh"
+
+namespace xc {
+
+// ---------------------------------------------------------------------------------------------
+// loader of the fused kernel: v[n] = rx[s + n] * conj(cutout[n])
+// ---------------------------------------------------------------------------------------------
+template <class PL, bool CUT_SMEM>
+struct CutoutLoader {
+    const float2* rx;
+    int64_t rxlen;
+    const float2* cutout;
+    int64_t shift0, step;
+    const int64_t* shifts;
+    float2* cc;   // conj(cutout) in shared memory (set by prepare)
+
+    __host__ __device__ static constexpr size_t smem_bytes() { return CUT_SMEM ? sizeof(float2) * PL::N : 0; }
+
+    __device__ __forceinline__ void prepare(int tid, int nthreads, unsigned char* smem) {
+        cc = reinterpret_cast<float2*>(smem);
+        if (CUT_SMEM) {
+            for (int n = tid; n < PL::N; n += nthreads) {
+                const float2 c = cutout[n];
+                cc[n] = make_float2(c.x, -c.y);
+            }
+        }
+    }
+    __device__ __forceinline__ bool load(float2* v, int t, int64_t i) const {
+        const int64_t s = shifts ? shifts[i] : shift0 + i * step;
+        if (s < 0 || s + PL::N > rxlen) return false;
+        const float2* x = rx + s;
+        constexpr int NQ = PL::V / PL::R1;
+#pragma unroll
+        for (int n1 = 0; n1 < PL::R1; ++n1)
+#pragma unroll
+            for (int q = 0; q < NQ; ++q) v[q * PL::R1 + n1] = __ldg(x + input_index<PL>(t, q, n1));
+#pragma unroll
+        for (int n1 = 0; n1 < PL::R1; ++n1)
+#pragma unroll
+            for (int q = 0; q < NQ; ++q) {
+                const int n = input_index<PL>(t, q, n1);
+                if (CUT_SMEM) {
+                    v[q * PL::R1 + n1] = cmul(v[q * PL::R1 + n1], cc[n]);
+                } else {
+                    v[q * PL::R1 + n1] = cmulc(v[q * PL::R1 + n1], __ldg(cutout + n));
+                }
+            }
+        return true;
+    }
+};
+
+bool fastxcorr_fft_supported(int N) { return fft_length_supported(N); }
+
+struct FreqRunner {
+    const float2* cutout;
+    const float2* rx;
+    int64_t rxlen;
+    const ShiftList& sl;
+    const FusedOut& out;
+    cudaStream_t stream;
+    template <int LOG2N>
+    int32_t run() {
+        using PF = PlanFor<LOG2N>;
+        using LD = CutoutLoader<typename PF::PL, PF::CS>;
+        LD ld{rx, rxlen, cutout, sl.shift0, sl.step, sl.shifts, nullptr};
+        return launch_fused<typename PF::PL, PF::B, LD>(ld, out, sl.K, stream);
+    }
+};
+
+int32_t fastxcorr_freq_device(const float2* cutout, int N, const float2* rx, int64_t rxlen, const ShiftList& sl,
+                              float* qf2, uint32_t* fidx, float2* cplx, void* caf, int caf_complex,
+                              cudaStream_t stream) {
+    if (!fastxcorr_fft_supported(N))
+        return fail(XC_ERR_UNSUPPORTED, "fused frequency search supports power-of-two cutout lengths 2..%d, got %d",
+                    1 << MAX_LOG2N, N);
+    if (sl.K <= 0) return XC_OK;
+    // normalisation terms: ||cutout||^2 (device scalar) and the window energies
+    float* d_refn = reinterpret_cast<float*>(workspace(SLOT_TMP0, 256));
+    float* d_energy = reinterpret_cast<float*>(workspace(SLOT_TMP1, sizeof(float) * (size_t)sl.K));
+    if (!d_refn || !d_energy) return XC_ERR_NOMEM;
+    XC_TRY(normsq_device(cutout, N, 1, N, d_refn, stream));
+    if (!sl.shifts && sl.step == 1 && sl.shift0 >= 0 && sl.shift0 + sl.K - 1 + N <= rxlen) {
+        XC_TRY(sliding_sum_device(rx + sl.shift0, true, rxlen - sl.shift0, 0, N, sl.K, d_energy, 0, stream));
+    } else {
+        XC_TRY(window_energy_device(rx, rxlen, N, sl.shift0, sl.step, sl.shifts, sl.K, d_energy, stream));
+    }
+    FusedOut out{qf2, fidx, cplx, reinterpret_cast<float*>(caf), caf_complex, d_energy, d_refn};
+    return dispatch_log2(ilog2(N), FreqRunner{cutout, rx, rxlen, sl, out, stream});
+}
+
+}  // namespace xc
+
+// =============================================================================================
+// no frequency search: acc[s] = sum_n conj(rx[s+n]) * cutout[n]   (np.vdot(rx[s:s+N], cutout))
+// =============================================================================================
+namespace xc {
+
+constexpr int ND_THREADS = 128;   // threads per CTA
+constexpr int ND_R = 8;           // consecutive shifts per thread
+constexpr int ND_TS = ND_THREADS * ND_R;   // shifts per CTA tile
+constexpr int ND_NC = 256;        // cutout samples per shared-memory chunk
+
+// step-1 fast path.  The rx chunk is kept as 16-byte units (two samples) with one pad unit per four,
+// so the stride-4-unit LDS.128 of neighbouring threads land in distinct bank groups.
+__device__ __forceinline__ int nd_phys_unit(int u) { return u + (u >> 2); }
+
+__global__ void __launch_bounds__(ND_THREADS) nofreq_tiled_kernel(const float2* __restrict__ cutout, int N,
+                                                                   const float2* __restrict__ rx, int64_t rxlen,
+                                                                   int64_t shift0, int64_t K,
+                                                                   const float* __restrict__ energy,
+                                                                   const float* __restrict__ refnormsq,
+                                                                   float* __restrict__ qf2, float2* __restrict__ cplx) {
+    constexpr int RX_UNITS = (ND_TS + ND_NC) / 2;
+    __shared__ float4 s_rx[RX_UNITS + RX_UNITS / 4 + 4];
+    __shared__ float4 s_c[ND_NC / 2];
+    const int tid = threadIdx.x;
+    const int64_t i0 = (int64_t)blockIdx.x * ND_TS;          // first shift-list entry of the tile
+    const int64_t base = shift0 + i0;                         // rx index of (shift i0, n = 0)
+    float2 acc[ND_R];
+#pragma unroll
+    for (int j = 0; j < ND_R; ++j) acc[j] = make_float2(0.f, 0.f);
+    float2* s_rx2 = reinterpret_cast<float2*>(s_rx);
+    float2* s_c2 = reinterpret_cast<float2*>(s_c);
+
+    for (int n0 = 0; n0 < N; n0 += ND_NC) {
+        __syncthreads();
+        for (int j = tid; j < ND_TS + ND_NC; j += ND_THREADS) {
+            const int64_t g = base + n0 + j;
+            float2 val = make_float2(0.f, 0.f);
+            if (g >= 0 && g < rxlen) val = __ldg(rx + g);
+            s_rx2[2 * nd_phys_unit(j >> 1) + (j & 1)] = val;
+        }
+        for (int j = tid; j < ND_NC; j += ND_THREADS) s_c2[j] = (n0 + j < N) ? cutout[n0 + j] : make_float2(0.f, 0.f);
+        __syncthreads();
+        // window registers: w[0..15] = rx chunk samples [b + 8m, b + 8m + 16), b = tid*8
+        float2 w[16];
+        {
+            const int u0 = tid * 4;
+#pragma unroll
+            for (int vv = 0; vv < 4; ++vv) {
+                const float4 f = s_rx[nd_phys_unit(u0 + vv)];
+                w[2 * vv] = make_float2(f.x, f.y);
+                w[2 * vv + 1] = make_float2(f.z, f.w);
+            }
+        }
+#pragma unroll 1
+        for (int m = 0; m < ND_NC / 8; ++m) {
+            const int u1 = tid * 4 + 4 * m + 4;
+#pragma unroll
+            for (int vv = 0; vv < 4; ++vv) {
+                const float4 f = s_rx[nd_phys_unit(u1 + vv)];
+                w[8 + 2 * vv] = make_float2(f.x, f.y);
+                w[8 + 2 * vv + 1] = make_float2(f.z, f.w);
+            }
+            float2 c[8];
+#pragma unroll
+            for (int vv = 0; vv < 4; ++vv) {
+                const float4 f = s_c[4 * m + vv];
+                c[2 * vv] = make_float2(f.x, f.y);
+                c[2 * vv + 1] = make_float2(f.z, f.w);
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+#pragma unroll
+                for (int j = 0; j < ND_R; ++j) {
+                    const float2 x = w[u + j];
+                    // conj(x) * c
+                    acc[j].x = fmaf(x.x, c[u].x, fmaf(x.y, c[u].y, acc[j].x));
+                    acc[j].y = fmaf(x.x, c[u].y, fmaf(-x.y, c[u].x, acc[j].y));
+                }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) w[j] = w[8 + j];
+        }
+    }
+    const float refn = *refnormsq;
+#pragma unroll
+    for (int j = 0; j < ND_R; ++j) {
+        const int64_t i = i0 + tid * ND_R + j;
+        if (i < K) {
+            const float e = energy[i];
+            if (qf2) qf2[i] = cnorm2(acc[j]) / refn / e;
+            if (cplx) {
+                const float sc = 1.f / (sqrtf(refn) * sqrtf(e));
+                cplx[i] = make_float2(acc[j].x * sc, acc[j].y * sc);
+            }
+        }
+    }
+}
+
+// general shift lists: one warp per shift
+__global__ void nofreq_warp_kernel(const float2* __restrict__ cutout, int N, const float2* __restrict__ rx,
+                                   int64_t rxlen, int64_t shift0, int64_t step, const int64_t* __restrict__ shifts,
+                                   int64_t K, const float* __restrict__ energy, const float* __restrict__ refnormsq,
+                                   float* __restrict__ qf2, float2* __restrict__ cplx) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const float refn = *refnormsq;
+    for (int64_t i = warp; i < K; i += nwarps) {
+        const int64_t s = shifts ? shifts[i] : shift0 + i * step;
+        const bool ok = s >= 0 && s + N <= rxlen;
+        float ar = 0.f, ai = 0.f;
+        if (ok) {
+            for (int n = lane; n < N; n += 32) {
+                const float2 x = __ldg(rx + s + n);
+                const float2 c = __ldg(cutout + n);
+                ar = fmaf(x.x, c.x, fmaf(x.y, c.y, ar));
+                ai = fmaf(x.x, c.y, fmaf(-x.y, c.x, ai));
+            }
+        }
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) {
+            ar += __shfl_xor_sync(0xffffffffu, ar, o);
+            ai += __shfl_xor_sync(0xffffffffu, ai, o);
+        }
+        if (lane == 0) {
+            const float e = ok ? energy[i] : 1.f;
+            if (qf2) qf2[i] = ok ? fmaf(ar, ar, ai * ai) / refn / e : 0.f;
+            if (cplx) {
+                const float sc = ok ? 1.f / (sqrtf(refn) * sqrtf(e)) : 0.f;
+                cplx[i] = make_float2(ar * sc, ai * sc);
+            }
+        }
+    }
+}
+
+int32_t fastxcorr_nofreq_device(const float2* cutout, int N, const float2* rx, int64_t rxlen, const ShiftList& sl,
+                                float* qf2, float2* cplx, cudaStream_t stream) {
+    if (sl.K <= 0) return XC_OK;
+    float* d_refn = reinterpret_cast<float*>(workspace(SLOT_TMP0, 256));
+    float* d_energy = reinterpret_cast<float*>(workspace(SLOT_TMP1, sizeof(float) * (size_t)sl.K));
+    if (!d_refn || !d_energy) return XC_ERR_NOMEM;
+    XC_TRY(normsq_device(cutout, N, 1, N, d_refn, stream));
+    const bool contiguous = !sl.shifts && sl.step == 1 && sl.shift0 >= 0 && sl.shift0 + sl.K - 1 + N <= rxlen;
+    if (contiguous) {
+        XC_TRY(sliding_sum_device(rx + sl.shift0, true, rxlen - sl.shift0, 0, N, sl.K, d_energy, 0, stream));
+        const int64_t blocks = (sl.K + ND_TS - 1) / ND_TS;
+        nofreq_tiled_kernel<<<(unsigned)blocks, ND_THREADS, 0, stream>>>(cutout, N, rx, rxlen, sl.shift0, sl.K, d_energy,
+                                                                          d_refn, qf2, cplx);
+        XC_LAUNCH_CHECK();
+    } else {
+        XC_TRY(window_energy_device(rx, rxlen, N, sl.shift0, sl.step, sl.shifts, sl.K, d_energy, stream));
+        int64_t blocks = (sl.K * 32 + 255) / 256;
+        const int64_t cap = (int64_t)sm_count() * 8;
+        if (blocks > cap) blocks = cap;
+        nofreq_warp_kernel<<<(unsigned)blocks, 256, 0, stream>>>(cutout, N, rx, rxlen, sl.shift0, sl.step, sl.shifts, sl.K,
+                                                                 d_energy, d_refn, qf2, cplx);
+        XC_LAUNCH_CHECK();
+    }
+    return XC_OK;
+}
+
+}  // namespace xc

@@ -1,0 +1,215 @@
+// fft_engine.cuh -- in-register radix codelets and the shared-memory block FFT used by the fused
+// cross-correlation kernels.  No cuFFT: a forward power-of-two FFT of N = R1*R2*R3 points is done by
+// a group of TG threads holding V = N/TG points each, in at most three register passes joined by
+// two in-place exchanges through one padded shared-memory buffer.
+//
+// Decomposition (decimation in frequency, natural-order input, digit-permuted output):
+//   n = n1*M1 + c         (M1 = N/R1)      pass 1: DFT_R1 over n1, times W_N^(c*k1)
+//   c = n2*M2 + d         (M2 = M1/R2)     pass 2: DFT_R2 over n2, times W_M1^(d*k2)
+//   d in [0, R3)                           pass 3: DFT_R3 over d
+//   bin k = k1 + R1*k2 + R1*R2*k3
+// The buffer index of a point is always  i = k1*M1 + (k2 or n2)*M2 + d  stored at i + (i >> log2(R_last)),
+// so a thread writes back exactly the cells it read (no barrier between read and write of a pass),
+// pass-1 stores and pass-2 loads/stores are lane-contiguous, and the stride-R_last loads of the last
+// pass hit distinct banks thanks to the one-cell skew per R_last cells.
+#pragma once
+#include "common.cuh"
+
+namespace xc {
+
+// ---------------------------------------------------------------------------------------------
+// compile-time helpers
+// ---------------------------------------------------------------------------------------------
+__host__ __device__ constexpr int ilog2(int v) { return v <= 1 ? 0 : 1 + ilog2(v >> 1); }
+__host__ __device__ constexpr int bitrev(int v, int bits) {
+    int r = 0;
+    for (int i = 0; i < bits; ++i) r |= ((v >> i) & 1) << (bits - 1 - i);
+    return r;
+}
+
+// d * exp(-2*pi*i*idx/32), idx in [0, 32); idx is a compile-time constant after unrolling, so the
+// branches fold away and the general case becomes 2 FMUL + 2 FFMA with immediate operands.
+__device__ __forceinline__ float2 mul_w32(float2 d, int idx) {
+    // cos(2*pi*k/32), k = 1..7
+    constexpr float C1 = 0.98078528040323044913f, C2 = 0.92387953251128675613f,
+                    C3 = 0.83146961230254523708f, C4 = 0.70710678118654752440f,
+                    C5 = 0.55557023301960222474f, C6 = 0.38268343236508977173f,
+                    C7 = 0.19509032201612826785f;
+    idx &= 31;
+    if (idx >= 16) {  // W^(idx) = -W^(idx-16)
+        d = make_float2(-d.x, -d.y);
+        idx -= 16;
+    }
+    float c = 0.f, s = 0.f;  // W = c - i*s
+    switch (idx) {
+        case 0: return d;
+        case 8: return make_float2(d.y, -d.x);
+        case 4: return make_float2((d.x + d.y) * C4, (d.y - d.x) * C4);
+        case 12: return make_float2((d.y - d.x) * C4, -(d.x + d.y) * C4);
+        case 1: c = C1; s = C7; break;
+        case 2: c = C2; s = C6; break;
+        case 3: c = C3; s = C5; break;
+        case 5: c = C5; s = C3; break;
+        case 6: c = C6; s = C2; break;
+        case 7: c = C7; s = C1; break;
+        case 9: c = -C7; s = C1; break;
+        case 10: c = -C6; s = C2; break;
+        case 11: c = -C5; s = C3; break;
+        case 13: c = -C3; s = C5; break;
+        case 14: c = -C2; s = C6; break;
+        default: c = -C1; s = C7; break;  // 15
+    }
+    return make_float2(fmaf(d.x, c, d.y * s), fmaf(d.y, c, -d.x * s));
+}
+
+// In-register forward DFT of R points (R = 2,4,8,16,32), decimation in frequency.
+// On return a[j] holds X[bitrev(j, log2 R)].
+template <int R>
+__device__ __forceinline__ void dif_fft(float2* a) {
+#pragma unroll
+    for (int h = R / 2; h >= 1; h >>= 1) {
+#pragma unroll
+        for (int blk = 0; blk < R; blk += 2 * h) {
+#pragma unroll
+            for (int j = 0; j < h; ++j) {
+                const float2 u = a[blk + j], v = a[blk + j + h];
+                a[blk + j] = cadd(u, v);
+                a[blk + j + h] = mul_w32(csub(u, v), j * (16 / h));
+            }
+        }
+    }
+}
+template <>
+__device__ __forceinline__ void dif_fft<1>(float2*) {}
+
+// multiply the bit-reversed outputs of a codelet by successive powers of w: a[bitrev(k)] *= w^k
+template <int R>
+__device__ __forceinline__ void twiddle_powers(float2* a, float2 w) {
+    float2 p = w;
+#pragma unroll
+    for (int k = 1; k < R; ++k) {
+        const int j = bitrev(k, ilog2(R));
+        a[j] = cmul(a[j], p);
+        if (k + 1 < R) p = cmul(p, w);
+    }
+}
+
+__device__ __forceinline__ float2 unit_root(int num, int den) {
+    // exp(-2*pi*i*num/den), evaluated in double once per thread
+    double s, c;
+    sincospi(-2.0 * (double)num / (double)den, &s, &c);
+    return make_float2((float)c, (float)s);
+}
+
+// ---------------------------------------------------------------------------------------------
+// block FFT plan
+// ---------------------------------------------------------------------------------------------
+template <int LOG2N_, int TG_, int R1_, int R2_, int R3_>
+struct FftPlan {
+    static constexpr int LOG2N = LOG2N_;
+    static constexpr int N = 1 << LOG2N_;
+    static constexpr int TG = TG_;          // threads cooperating on one FFT
+    static constexpr int V = N / TG_;       // points per thread
+    static constexpr int R1 = R1_, R2 = R2_, R3 = R3_;
+    static constexpr int P = (R3_ > 1) ? 3 : ((R2_ > 1) ? 2 : 1);
+    static constexpr int RL = (P == 3) ? R3_ : ((P == 2) ? R2_ : R1_);   // radix of the last pass
+    static constexpr int M1 = N / R1_;
+    static constexpr int M2 = M1 / R2_;
+    static constexpr int LOG2RL = ilog2(RL);
+    static constexpr int BUF = (P == 1) ? 0 : N + (N >> LOG2RL);   // float2 cells per FFT buffer
+    static_assert(R1_ * R2_ * R3_ == N, "radices must multiply to N");
+    static_assert(V % R1_ == 0 && V % R2_ == 0 && V % R3_ == 0, "each pass must fill the registers");
+    static_assert(R1_ <= 32 && R2_ <= 32 && R3_ <= 32, "codelets go up to radix 32");
+    __device__ static __forceinline__ int phys(int i) { return i + (i >> LOG2RL); }
+};
+
+// Per-thread constants of a plan: base twiddles of the two exchanges.
+template <class PL>
+struct FftThread {
+    float2 tw1[PL::V / PL::R1];                       // W_N^(t + TG*q)
+    float2 tw2[(PL::P == 3) ? PL::V / PL::R2 : 1];    // W_M1^((t + TG*q) % M2)
+    __device__ __forceinline__ void init(int t) {
+        if (PL::P >= 2) {
+#pragma unroll
+            for (int q = 0; q < PL::V / PL::R1; ++q) tw1[q] = unit_root(t + PL::TG * q, PL::N);
+        }
+        if (PL::P == 3) {
+#pragma unroll
+            for (int q = 0; q < PL::V / PL::R2; ++q)
+                tw2[q] = unit_root((t + PL::TG * q) % PL::M2, PL::M1);
+        }
+    }
+};
+
+// Sample index held in register slot (q*R1 + n1) of thread t before pass 1.
+template <class PL>
+__device__ __forceinline__ int input_index(int t, int q, int n1) {
+    return n1 * PL::M1 + t + PL::TG * q;
+}
+
+// Bin index held in register slot (q*RL + j) of thread t after the last pass.
+template <class PL>
+__device__ __forceinline__ int output_bin(int t, int q, int j) {
+    const int kl = bitrev(j, PL::LOG2RL);
+    const int f = t + PL::TG * q;
+    if (PL::P == 1) return kl;
+    if (PL::P == 2) return f + PL::R1 * kl;
+    return (f / PL::R2) + PL::R1 * (f % PL::R2) + PL::R1 * PL::R2 * kl;
+}
+
+// Runs the forward FFT on the V points the thread loaded according to input_index(); on return the
+// registers hold the bins given by output_bin().  `buf` is the group's padded exchange buffer and
+// BAR() a barrier over the TG threads of the group.  The caller must guarantee (with BAR) that the
+// previous user of `buf` is done before calling.
+template <class PL, class Bar>
+__device__ __forceinline__ void block_fft(float2* v, const FftThread<PL>& th, float2* buf, int t, Bar bar) {
+    // ---- pass 1 ----
+#pragma unroll
+    for (int q = 0; q < PL::V / PL::R1; ++q) dif_fft<PL::R1>(v + q * PL::R1);
+    if (PL::P == 1) return;
+#pragma unroll
+    for (int q = 0; q < PL::V / PL::R1; ++q) {
+        twiddle_powers<PL::R1>(v + q * PL::R1, th.tw1[q]);
+        const int c = t + PL::TG * q;
+#pragma unroll
+        for (int j = 0; j < PL::R1; ++j) {
+            const int k1 = bitrev(j, ilog2(PL::R1));
+            buf[PL::phys(k1 * PL::M1 + c)] = v[q * PL::R1 + j];
+        }
+    }
+    bar();
+    if (PL::P == 3) {
+        // ---- pass 2 (in place) ----
+#pragma unroll
+        for (int q = 0; q < PL::V / PL::R2; ++q) {
+            const int e = t + PL::TG * q;
+            const int base = (e / PL::M2) * PL::M1 + (e % PL::M2);
+#pragma unroll
+            for (int n2 = 0; n2 < PL::R2; ++n2) v[q * PL::R2 + n2] = buf[PL::phys(base + n2 * PL::M2)];
+        }
+#pragma unroll
+        for (int q = 0; q < PL::V / PL::R2; ++q) {
+            dif_fft<PL::R2>(v + q * PL::R2);
+            twiddle_powers<PL::R2>(v + q * PL::R2, th.tw2[q]);
+            const int e = t + PL::TG * q;
+            const int base = (e / PL::M2) * PL::M1 + (e % PL::M2);
+#pragma unroll
+            for (int j = 0; j < PL::R2; ++j) {
+                const int k2 = bitrev(j, ilog2(PL::R2));
+                buf[PL::phys(base + k2 * PL::M2)] = v[q * PL::R2 + j];
+            }
+        }
+        bar();
+    }
+    // ---- last pass ----
+#pragma unroll
+    for (int q = 0; q < PL::V / PL::RL; ++q) {
+        const int f = t + PL::TG * q;
+#pragma unroll
+        for (int d = 0; d < PL::RL; ++d) v[q * PL::RL + d] = buf[PL::phys(f * PL::RL + d)];
+    }
+#pragma unroll
+    for (int q = 0; q < PL::V / PL::RL; ++q) dif_fft<PL::RL>(v + q * PL::RL);
+}
+
+}  // namespace xc

@@ -1,0 +1,292 @@
+// group.cu -- GroupXcorrFFT on the B200 (xcorrRoutines.py:1047-1262, GroupXcorrFFT.cpp:3-199).
+//
+// The reference does G zero-padded F-point FFTs per shift, rotates each by the group's start phase
+// and sums them.  Because the starts are integers,
+//     sum_g exp(-j 2 pi k s_g / F) FFT_F(p_g)[k]  ==  FFT_F(z)[k],   z[m] = sum_{(g,n): (s_g+n) mod F = m} p_g[n]
+// so ONE F-point FFT of the products folded (time-aliased) into F cells gives the same surface.
+// The fold is precomputed at create time as padded per-register-slot contributor lists laid out for
+// the block FFT's thread mapping ("ELL by slot"): slot c of thread t sums
+//     y[(base_c + j)*TG + t] * rx[shift + off[(base_c + j)*TG + t]],  j < len_c
+// -- uniform trip counts inside a group of threads, coalesced loads, no atomics.
+#include <vector>
+
+#include "fused_fft_kernel.cuh"
+#include "internal.cuh"
+#include "plans.cuh"
+
+struct xc_group {
+    int32_t G, L, F;
+    int64_t span;            // max(starts) + L: samples needed after the shift
+    int64_t min_start;
+    int64_t* d_starts;       // [G]
+    float2* d_ell_y;         // [rows * TG]
+    int32_t* d_ell_off;      // [rows * TG]
+    int32_t* d_slot_base;    // [V + 1]
+    float* d_refn;           // ||ygroups||^2
+    int32_t rows;
+};
+
+namespace xc {
+
+template <class PL>
+struct GroupLoader {
+    const float2* rx;
+    int64_t rxlen;
+    int64_t shift0, step;
+    const int64_t* shifts;
+    const float2* ell_y;
+    const int32_t* ell_off;
+    const int32_t* slot_base_g;   // global [V + 1]
+    int64_t lo, hi;               // valid shifts satisfy s + lo >= 0 and s + hi <= rxlen
+    int32_t* slot_base;           // shared copy
+
+    __host__ __device__ static constexpr size_t smem_bytes() { return ((sizeof(int32_t) * (PL::V + 1) + 15) / 16) * 16; }
+
+    __device__ __forceinline__ void prepare(int tid, int nthreads, unsigned char* smem) {
+        slot_base = reinterpret_cast<int32_t*>(smem);
+        for (int i = tid; i <= PL::V; i += nthreads) slot_base[i] = slot_base_g[i];
+    }
+    __device__ __forceinline__ bool load(float2* v, int t, int64_t i) const {
+        const int64_t s = shifts ? shifts[i] : shift0 + i * step;
+        if (s + lo < 0 || s + hi > rxlen) return false;
+        const float2* x = rx + s;
+#pragma unroll
+        for (int c = 0; c < PL::V; ++c) {
+            float2 acc = make_float2(0.f, 0.f);
+            const int j0 = slot_base[c], j1 = slot_base[c + 1];
+            for (int j = j0; j < j1; ++j) {
+                const float2 y = __ldg(ell_y + (size_t)j * PL::TG + t);
+                const int off = __ldg(ell_off + (size_t)j * PL::TG + t);
+                const float2 r = __ldg(x + off);
+                acc.x = fmaf(y.x, r.x, fmaf(-y.y, r.y, acc.x));
+                acc.y = fmaf(y.x, r.y, fmaf(y.y, r.x, acc.y));
+            }
+            v[c] = acc;
+        }
+        return true;
+    }
+};
+
+// sum of the per-group window energies: E[i] = sum_g EL[shift_i + s_g]
+__global__ void group_energy_kernel(const float* __restrict__ el, int64_t el_len, const int64_t* __restrict__ starts,
+                                    int G, int64_t shift0, int64_t step, const int64_t* __restrict__ shifts, int64_t K,
+                                    float* __restrict__ out) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < K; i += stride) {
+        const int64_t s = shifts ? shifts[i] : shift0 + i * step;
+        double acc = 0.0;
+        for (int g = 0; g < G; ++g) {
+            const int64_t p = s + starts[g];
+            if (p >= 0 && p < el_len) acc += (double)__ldg(el + p);
+        }
+        out[i] = (float)acc;
+    }
+}
+
+struct GroupBuilder {
+    const float2* y;         // host, already conjugated if requested
+    const int64_t* starts;   // host
+    xc_group* h;
+    template <int LOG2N>
+    int32_t run() {
+        using PL = typename PlanFor<LOG2N>::PL;
+        const int F = PL::N, TG = PL::TG, V = PL::V, G = h->G, L = h->L;
+        struct Contrib { int32_t off; float2 y; };
+        std::vector<std::vector<Contrib>> rows(F);
+        for (int g = 0; g < G; ++g)
+            for (int n = 0; n < L; ++n) {
+                const int64_t a = starts[g] + n;
+                const int64_t m = ((a % F) + F) % F;
+                rows[(size_t)m].push_back(Contrib{(int32_t)a, y[(size_t)g * L + n]});
+            }
+        std::vector<int32_t> base(V + 1, 0);
+        for (int c = 0; c < V; ++c) {
+            const int q = c / PL::R1, n1 = c % PL::R1;
+            size_t len = 0;
+            for (int t = 0; t < TG; ++t) {
+                const int m = n1 * PL::M1 + t + TG * q;
+                if (rows[m].size() > len) len = rows[m].size();
+            }
+            base[c + 1] = base[c] + (int32_t)len;
+        }
+        const int nrows = base[V];
+        std::vector<float2> ey((size_t)(nrows > 0 ? nrows : 1) * TG, make_float2(0.f, 0.f));
+        // padded entries point at a valid sample (the smallest start) and carry a zero weight
+        std::vector<int32_t> eo((size_t)(nrows > 0 ? nrows : 1) * TG, (int32_t)h->min_start);
+        for (int c = 0; c < V; ++c) {
+            const int q = c / PL::R1, n1 = c % PL::R1;
+            for (int t = 0; t < TG; ++t) {
+                const int m = n1 * PL::M1 + t + TG * q;
+                for (size_t j = 0; j < rows[m].size(); ++j) {
+                    ey[((size_t)base[c] + j) * TG + t] = rows[m][j].y;
+                    eo[((size_t)base[c] + j) * TG + t] = rows[m][j].off;
+                }
+            }
+        }
+        h->rows = nrows;
+        XC_CUDA_TRY(cudaMalloc(&h->d_ell_y, sizeof(float2) * ey.size()));
+        XC_CUDA_TRY(cudaMalloc(&h->d_ell_off, sizeof(int32_t) * eo.size()));
+        XC_CUDA_TRY(cudaMalloc(&h->d_slot_base, sizeof(int32_t) * (V + 1)));
+        XC_CUDA_TRY(cudaMemcpy(h->d_ell_y, ey.data(), sizeof(float2) * ey.size(), cudaMemcpyHostToDevice));
+        XC_CUDA_TRY(cudaMemcpy(h->d_ell_off, eo.data(), sizeof(int32_t) * eo.size(), cudaMemcpyHostToDevice));
+        XC_CUDA_TRY(cudaMemcpy(h->d_slot_base, base.data(), sizeof(int32_t) * (V + 1), cudaMemcpyHostToDevice));
+        return XC_OK;
+    }
+};
+
+struct GroupRunner {
+    xc_group* h;
+    const float2* rx;
+    int64_t rxlen;
+    const ShiftList& sl;
+    const FusedOut& out;
+    cudaStream_t stream;
+    template <int LOG2N>
+    int32_t run() {
+        using PF = PlanFor<LOG2N>;
+        using LD = GroupLoader<typename PF::PL>;
+        LD ld{rx, rxlen, sl.shift0, sl.step, sl.shifts, h->d_ell_y, h->d_ell_off, h->d_slot_base,
+              h->min_start, h->span, nullptr};
+        return launch_fused<typename PF::PL, PF::B, LD>(ld, out, sl.K, stream);
+    }
+};
+
+}  // namespace xc
+
+using namespace xc;
+
+namespace xc {
+int32_t collect_peak(const float* d_qf2, const uint32_t* d_fidx, const int32_t* d_aux, int64_t K, int64_t shift0,
+                     int64_t step, const int64_t* d_shifts, xc_peak* peak, cudaStream_t st);
+}
+
+extern "C" {
+
+int32_t xc_group_create(const void* ygroups, int32_t G, int32_t L, const int64_t* starts, int32_t F, int32_t auto_conj,
+                        xc_group** handle) {
+    if (!ygroups || !starts || !handle) return fail(XC_ERR_ARG, "ygroups/starts/handle is NULL");
+    if (G < 1 || L < 1) return fail(XC_ERR_ARG, "need at least one group of at least one sample");
+    if (F < L) return fail(XC_ERR_ARG, "INVALID_FFTLEN: fftlen %d is shorter than the group length %d", F, L);   // GroupXcorrFFT.cpp:11-14
+    if (!fft_length_supported(F))
+        return fail(XC_ERR_UNSUPPORTED, "GroupXcorrFFT supports power-of-two fftlen 2..%d, got %d", 1 << MAX_LOG2N, F);
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(XC_ERR_CUDA, "no CUDA device available; libxcorr_b200 has no CPU fallback");
+    }
+    int64_t mn = starts[0], mx = starts[0];
+    for (int g = 1; g < G; ++g) {
+        if (starts[g] < mn) mn = starts[g];
+        if (starts[g] > mx) mx = starts[g];
+    }
+    if (mx + L >= (1ll << 31) || mn <= -(1ll << 31)) return fail(XC_ERR_UNSUPPORTED, "group starts must fit in 31 bits");
+    xc_group* h = new xc_group();
+    memset(h, 0, sizeof(*h));
+    h->G = G; h->L = L; h->F = F;
+    h->span = mx + L;
+    h->min_start = mn;
+    const float2* yin = reinterpret_cast<const float2*>(ygroups);
+    std::vector<float2> y((size_t)G * L);
+    double nsq = 0.0;
+    for (size_t i = 0; i < y.size(); ++i) {
+        y[i] = auto_conj ? make_float2(yin[i].x, -yin[i].y) : yin[i];
+        nsq += (double)yin[i].x * yin[i].x + (double)yin[i].y * yin[i].y;
+    }
+    int32_t st = dispatch_log2(ilog2(F), GroupBuilder{y.data(), starts, h});
+    if (st == XC_OK) {
+        const float nf = (float)nsq;
+        cudaError_t e = cudaMalloc(&h->d_refn, 256);
+        if (e == cudaSuccess) e = cudaMemcpy(h->d_refn, &nf, sizeof(float), cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = cudaMalloc(&h->d_starts, sizeof(int64_t) * G);
+        if (e == cudaSuccess) e = cudaMemcpy(h->d_starts, starts, sizeof(int64_t) * G, cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) st = fail(XC_ERR_CUDA, "group handle allocation failed: %s", cudaGetErrorString(e));
+    }
+    if (st != XC_OK) {
+        xc_group_destroy(h);
+        return st;
+    }
+    *handle = h;
+    return XC_OK;
+}
+
+int32_t xc_group_destroy(xc_group* h) {
+    if (!h) return XC_OK;
+    cudaFree(h->d_ell_y);
+    cudaFree(h->d_ell_off);
+    cudaFree(h->d_slot_base);
+    cudaFree(h->d_refn);
+    cudaFree(h->d_starts);
+    delete h;
+    return XC_OK;
+}
+
+int32_t xc_group_xcorr(xc_group* h, const void* rx, int64_t rxlen, int64_t shift0, int64_t step, int64_t K,
+                       const int64_t* shifts, float* qf2, uint32_t* fidx, float* caf, xc_peak* peak, int32_t where,
+                       void* stream) {
+    if (where != XC_HOST && where != XC_DEVICE) return fail(XC_ERR_ARG, "where must be XC_HOST (0) or XC_DEVICE (1)");
+    if (!h || !rx) return fail(XC_ERR_ARG, "handle/rx is NULL");
+    if (!qf2 && !caf) return fail(XC_ERR_ARG, "qf2 and caf are both NULL");
+    if (K < 0 || rxlen < h->L) return fail(XC_ERR_ARG, "need K >= 0 and rx at least one group long");
+    if (K == 0) {
+        if (peak) { memset(peak, 0, sizeof(*peak)); peak->index = -1; }
+        return XC_OK;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t cafb = sizeof(float) * (size_t)K * (size_t)h->F;
+    const float2* drx = reinterpret_cast<const float2*>(rx);
+    const int64_t* dsh = shifts;
+    float *dq = qf2, *dcaf = caf;
+    uint32_t* df = fidx;
+    if (where == XC_HOST) {
+        float2* b = (float2*)workspace(SLOT_IN1, sizeof(float2) * (size_t)rxlen);
+        if (!b) return XC_ERR_NOMEM;
+        XC_CUDA_TRY(cudaMemcpyAsync(b, rx, sizeof(float2) * (size_t)rxlen, cudaMemcpyHostToDevice, st));
+        drx = b;
+        if (shifts) {
+            int64_t* s = (int64_t*)workspace(SLOT_IN2, sizeof(int64_t) * (size_t)K);
+            if (!s) return XC_ERR_NOMEM;
+            XC_CUDA_TRY(cudaMemcpyAsync(s, shifts, sizeof(int64_t) * (size_t)K, cudaMemcpyHostToDevice, st));
+            dsh = s;
+        }
+        if (qf2 || peak) { dq = (float*)workspace(SLOT_OUT0, sizeof(float) * (size_t)K); if (!dq) return XC_ERR_NOMEM; }
+        if (fidx || peak) { df = (uint32_t*)workspace(SLOT_OUT1, sizeof(uint32_t) * (size_t)K); if (!df) return XC_ERR_NOMEM; }
+        if (caf) { dcaf = (float*)workspace(SLOT_OUT2, cafb); if (!dcaf) return XC_ERR_NOMEM; }
+    } else if (peak && (!dq || !df)) {
+        if (!dq) dq = (float*)workspace(SLOT_OUT0, sizeof(float) * (size_t)K);
+        if (!df) df = (uint32_t*)workspace(SLOT_OUT1, sizeof(uint32_t) * (size_t)K);
+        if (!dq || !df) return XC_ERR_NOMEM;
+    }
+    // energies: length-L sliding energy of the whole record, then the sum over the groups per shift
+    const int64_t el_len = rxlen - h->L + 1;
+    float* d_el = (float*)workspace(SLOT_TMP2, sizeof(float) * (size_t)el_len);
+    float* d_energy = (float*)workspace(SLOT_TMP1, sizeof(float) * (size_t)K);
+    if (!d_el || !d_energy) return XC_ERR_NOMEM;
+    XC_TRY(sliding_sum_device(drx, true, rxlen, 0, h->L, el_len, d_el, 0, st));
+    {
+        int64_t blocks = (K + 255) / 256;
+        const int64_t cap = (int64_t)sm_count() * 16;
+        if (blocks > cap) blocks = cap;
+        group_energy_kernel<<<(unsigned)blocks, 256, 0, st>>>(d_el, el_len, h->d_starts, h->G, shift0, step, dsh, K, d_energy);
+        XC_LAUNCH_CHECK();
+    }
+    ShiftList sl{shift0, step, K, dsh};
+    // the fused kernel either reduces to (max, arg max) or writes CAF rows; both wanted = two passes
+    if (dq || df) {
+        FusedOut out{dq, df, nullptr, nullptr, 0, d_energy, h->d_refn};
+        XC_TRY(dispatch_log2(ilog2(h->F), GroupRunner{h, drx, rxlen, sl, out, st}));
+    }
+    if (dcaf) {
+        FusedOut out{nullptr, nullptr, nullptr, dcaf, 0, d_energy, h->d_refn};
+        XC_TRY(dispatch_log2(ilog2(h->F), GroupRunner{h, drx, rxlen, sl, out, st}));
+    }
+    if (where == XC_HOST) {
+        if (qf2) XC_CUDA_TRY(cudaMemcpyAsync(qf2, dq, sizeof(float) * (size_t)K, cudaMemcpyDeviceToHost, st));
+        if (fidx) XC_CUDA_TRY(cudaMemcpyAsync(fidx, df, sizeof(uint32_t) * (size_t)K, cudaMemcpyDeviceToHost, st));
+        if (caf) XC_CUDA_TRY(cudaMemcpyAsync(caf, dcaf, cafb, cudaMemcpyDeviceToHost, st));
+    }
+    if (peak) XC_TRY(collect_peak(dq, df, nullptr, K, shift0, step, dsh, peak, st));
+    if (where == XC_HOST) XC_CUDA_TRY(cudaStreamSynchronize(st));
+    return XC_OK;
+}
+
+}  // extern "C"

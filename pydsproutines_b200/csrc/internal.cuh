@@ -1,0 +1,36 @@
+// internal.cuh -- device-side entry points shared between the translation units of libxcorr_b200
+// (all take DEVICE pointers and enqueue on `stream`; the C-ABI layer in api.cu does the staging).
+#pragma once
+#include "common.cuh"
+
+namespace xc {
+
+// energy.cu
+int32_t sliding_sum_device(const void* x, bool complex_in, int64_t n_in, int64_t front_pad, int L, int64_t n_out,
+                           float* out, int average, cudaStream_t stream);
+int32_t window_energy_device(const float2* x, int64_t xlen, int L, int64_t shift0, int64_t step, const int64_t* shifts,
+                             int64_t K, float* out, cudaStream_t stream);
+int32_t normsq_device(const float2* x, int64_t n, int64_t rows, int64_t row_stride, float* out, cudaStream_t stream);
+int32_t magnsq_device(const float2* x, int64_t n, void* out, int out_f64, cudaStream_t stream);
+
+// fastxcorr.cu
+struct ShiftList {
+    int64_t shift0, step, K;
+    const int64_t* shifts;   // device pointer or NULL
+};
+bool fastxcorr_fft_supported(int N);
+int32_t fastxcorr_freq_device(const float2* cutout, int N, const float2* rx, int64_t rxlen, const ShiftList& sl,
+                              float* qf2, uint32_t* fidx, float2* cplx, void* caf, int caf_complex,
+                              cudaStream_t stream);
+int32_t fastxcorr_nofreq_device(const float2* cutout, int N, const float2* rx, int64_t rxlen, const ShiftList& sl,
+                                float* qf2, float2* cplx, cudaStream_t stream);
+
+// misc.cu
+int32_t peak_reduce_device(const float* qf2, const uint32_t* fidx, const int32_t* aux, int64_t K,
+                           unsigned long long* d_packed, cudaStream_t stream);
+int32_t row_argmax_device(const float2* x, int64_t rows, int64_t cols, int use_normsq, uint32_t* idx, float* val,
+                          cudaStream_t stream);
+int32_t local_maxima_device(const float* x, int64_t n, float min_height, int32_t* idx, int32_t cap, int32_t* count,
+                            cudaStream_t stream);
+
+}  // namespace xc

@@ -1,0 +1,453 @@
+"""Host-side mirror of the reference's cross-correlation API (xcorrRoutines.py of pydsproutines @ e005737)
+on top of libxcorr_b200: same names, argument meaning, return tuples and error behaviour, so a caller
+only swaps the import line.  numpy arrays are host buffers (staged by the library); torch CUDA tensors
+take the place of the reference's cupy arrays and stay on the device.
+
+Nothing here computes on the CPU beyond argument bookkeeping and dtype conversion of the results.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import XC_DEVICE, XC_FLAG_ZERO_OOB, XC_HOST, check, xc_peak
+
+
+# ------------------------------------------------------------------------------------------------
+# helpers
+# ------------------------------------------------------------------------------------------------
+def _require_c64(name, x):
+    """cupyRequireDtype (cupyHelpers.py:50-69): complex64 only, TypeError otherwise."""
+    dt = _lib.np_dtype_of(x)
+    if dt != np.dtype(np.complex64):
+        raise TypeError("%s must be complex64, got %s" % (name, dt))
+    if x.ndim != 1:
+        raise ValueError("%s must be 1-D" % name)
+    return _lib.contiguous(x)
+
+
+def _select_device(ref):
+    if _lib.is_device(ref):
+        check(_lib.load().xc_set_device(ref.device.index or 0))
+
+
+class _Shifts:
+    """A shift list as the kernels take it: arithmetic progression (shift0, step, K) or explicit int64 list."""
+
+    def __init__(self, shifts, rxlen, N, like):
+        self.array = None
+        if shifts is None:
+            self.shift0, self.step, self.K = 0, 1, max(rxlen - N + 1, 0)
+            lo, hi = 0, self.K - 1
+        else:
+            if _lib.is_torch(shifts):
+                shifts = shifts.detach().cpu().numpy()
+            s = np.asarray(shifts).astype(np.int64).reshape(-1)
+            self.K = int(s.size)
+            lo, hi = (int(s.min()), int(s.max())) if s.size else (0, -1)
+            if s.size <= 1:
+                self.shift0, self.step = (int(s[0]) if s.size else 0), 1
+            else:
+                d = np.diff(s)
+                if np.all(d == d[0]):
+                    self.shift0, self.step = int(s[0]), int(d[0])
+                else:
+                    self.shift0, self.step = 0, 0
+                    self.array = np.ascontiguousarray(s)
+                    if _lib.is_device(like):
+                        import torch
+                        self.array = torch.from_numpy(self.array).to(like.device)
+        if self.K and (lo < 0 or hi + N > rxlen):
+            # numpy slicing would silently shorten the window and then fail to broadcast
+            raise ValueError("shifts [%d, %d] with a cutout of %d samples leave rx (%d samples)" % (lo, hi, N, rxlen))
+
+
+def _fastxcorr_call(cutout, rx, sh, freqsearch, want_qf2=True, want_fidx=False, want_cplx=False, want_peak=False,
+                    flags=0):
+    lib = _lib.load()
+    where = _lib.where_of(cutout, rx)
+    _select_device(rx)
+    K = sh.K
+    qf2 = _lib.empty_like_space(rx, K, np.float32) if want_qf2 else None
+    fidx = _lib.empty_like_space(rx, K, np.uint32) if want_fidx else None
+    cplx = _lib.empty_like_space(rx, K, np.complex64) if want_cplx else None
+    peak = xc_peak() if want_peak else None
+    check(lib.xc_fastxcorr_c64(_lib.ptr(cutout), cutout.shape[0], _lib.ptr(rx), rx.shape[0], sh.shift0, sh.step, K,
+                               _lib.ptr(sh.array), 1 if freqsearch else 0, flags, _lib.ptr(qf2), _lib.ptr(fidx),
+                               _lib.ptr(cplx), C.byref(peak) if peak is not None else None, where,
+                               _lib.current_stream(rx)))
+    return qf2, fidx, cplx, peak
+
+
+def _caf_call(cutout, rx, sh, complex_out):
+    lib = _lib.load()
+    where = _lib.where_of(cutout, rx)
+    _select_device(rx)
+    N = cutout.shape[0]
+    caf = _lib.empty_like_space(rx, (sh.K, N), np.complex64 if complex_out else np.float32)
+    check(lib.xc_fastxcorr_caf_c64(_lib.ptr(cutout), N, _lib.ptr(rx), rx.shape[0], sh.shift0, sh.step, sh.K,
+                                   _lib.ptr(sh.array), _lib.ptr(caf), 1 if complex_out else 0, where,
+                                   _lib.current_stream(rx)))
+    return caf
+
+
+def _as(x, np_dtype):
+    """Result dtype conversion (the reference returns float64 / uint32 / complex128 from fastXcorr)."""
+    if x is None:
+        return None
+    if _lib.is_torch(x):
+        import torch
+        target = {np.dtype(np.float64): torch.float64, np.dtype(np.float32): torch.float32,
+                  np.dtype(np.complex128): torch.complex128, np.dtype(np.complex64): torch.complex64}
+        # device indices stay int32 (torch has no first-class uint32)
+        return x.to(target[np.dtype(np_dtype)]) if np.dtype(np_dtype) in target else x
+    return x.astype(np_dtype, copy=False)
+
+
+# ------------------------------------------------------------------------------------------------
+# a1/a2/a3: fastXcorr  (xcorrRoutines.py:460-580)
+# ------------------------------------------------------------------------------------------------
+def fastXcorr(cutout, rx, freqsearch=False, outputCAF=False, shifts=None, absResult=True):
+    """Same signature and return values as the reference's fastXcorr (xcorrRoutines.py:460-580):
+
+    freqsearch=False                    -> QF^2 float64[K]                 (complex128[K] if absResult=False)
+    freqsearch=True                     -> (QF^2 float64[K], freqlist uint32[K])   ((complex128[K], uint32[K]))
+    freqsearch=True, outputCAF=True     -> float64 (K, N)                  (complex128 (K, N))
+    `shifts` defaults to every valid shift (473-474).
+    """
+    cutout = _require_c64("cutout", cutout)
+    rx = _require_c64("rx", rx)
+    sh = _Shifts(shifts, rx.shape[0], cutout.shape[0], rx)
+    if not freqsearch:
+        if absResult:
+            qf2, _, _, _ = _fastxcorr_call(cutout, rx, sh, False)
+            return _as(qf2, np.float64)
+        _, _, z, _ = _fastxcorr_call(cutout, rx, sh, False, want_qf2=False, want_cplx=True)
+        return _as(z, np.complex128)
+    if not outputCAF:
+        if absResult:
+            qf2, fidx, _, _ = _fastxcorr_call(cutout, rx, sh, True, want_fidx=True)
+            return _as(qf2, np.float64), fidx
+        _, fidx, z, _ = _fastxcorr_call(cutout, rx, sh, True, want_qf2=False, want_fidx=True, want_cplx=True)
+        return _as(z, np.complex128), fidx
+    caf = _caf_call(cutout, rx, sh, not absResult)
+    return _as(caf, np.float64 if absResult else np.complex128)
+
+
+def fastXcorrPeak(cutout, rx, freqsearch=True, shifts=None):
+    """(QF^2, frequency index, peak shift) of the whole search in one call -- the tuple ranks exchange in
+    the shift-sharded multi-GPU run (pydsproutines_b200.dist)."""
+    cutout = _require_c64("cutout", cutout)
+    rx = _require_c64("rx", rx)
+    sh = _Shifts(shifts, rx.shape[0], cutout.shape[0], rx)
+    qf2, fidx, _, peak = _fastxcorr_call(cutout, rx, sh, freqsearch, want_fidx=freqsearch, want_peak=True)
+    return qf2, fidx, peak
+
+
+# ------------------------------------------------------------------------------------------------
+# a4: cp_fastXcorr  (xcorrRoutines.py:29-167)
+# ------------------------------------------------------------------------------------------------
+def cp_fastXcorr(cutout, rx, freqsearch=True, outputCAF=False, shifts=None, absResult=True, BATCH=1024,
+                 copyToCpu=True):
+    """GPU fastXcorr of the reference.  Accepts numpy arrays or device tensors; BATCH is accepted and
+    ignored (no (BATCH, N) intermediate exists any more).  Returns (float64[K], uint32[K]) as numpy
+    when copyToCpu, else device tensors.  Like the reference, only the flattened frequency search is
+    implemented (67, 164, 167 print "Not implemented.")."""
+    if _lib.np_dtype_of(cutout) != _lib.np_dtype_of(rx):
+        raise Exception("Cutout and Rx must be same type, please cast one of them manually.")   # :54-57
+    if not freqsearch or outputCAF or not absResult:
+        raise NotImplementedError("cp_fastXcorr implements freqsearch=True, outputCAF=False, absResult=True only "
+                                  "(as the reference); use fastXcorr for the other variants")
+    result, freqlist = fastXcorr(cutout, rx, freqsearch=True, shifts=shifts)
+    if copyToCpu and _lib.is_torch(result):
+        return result.cpu().numpy(), freqlist.cpu().numpy().astype(np.uint32)
+    return result, freqlist
+
+
+# ------------------------------------------------------------------------------------------------
+# a5: cp_fastXcorr_v2  (xcorrRoutines.py:169-274)
+# ------------------------------------------------------------------------------------------------
+def cp_fastXcorr_v2(cutout, rx, startIdx=0, idxlen=None, THREADS_PER_BLOCK=32, numSlidesPerBlk=None, cztObj=None,
+                    flattenCAF=False, BATCH=None):
+    """Step-1 search over rx[startIdx : startIdx+idxlen].  Returns (freqIdx uint32, qf2 float32) -- in THAT
+    order (xcorrRoutines.py:272) -- when flattenCAF, else the float32 (idxlen, N) ambiguity surface.
+    THREADS_PER_BLOCK / numSlidesPerBlk / BATCH are accepted and ignored; cztObj is not supported yet."""
+    if cztObj is not None:
+        raise NotImplementedError("the CZT branch (xcorrRoutines.py:247-249) is not part of this build yet")
+    cutout = _require_c64("cutout", cutout)
+    rx = _require_c64("rx", rx)
+    if idxlen is None:
+        idxlen = rx.shape[0] - cutout.shape[0] - startIdx + 1       # :209-210
+    if startIdx < 0 or idxlen < 0 or startIdx + idxlen - 1 + cutout.shape[0] > rx.shape[0]:
+        raise ValueError("Search range exceeds the input array.")                 # cupyExtensions.py:512-515
+    sh = _Shifts(np.arange(startIdx, startIdx + idxlen), rx.shape[0], cutout.shape[0], rx)
+    if flattenCAF:
+        qf2, fidx, _, _ = _fastxcorr_call(cutout, rx, sh, True, want_fidx=True)
+        return fidx, qf2
+    return _caf_call(cutout, rx, sh, False)
+
+
+# ------------------------------------------------------------------------------------------------
+# a6: CyIppXcorrFFT  (CyIppXcorrFFT.pyx:25-80, IppXcorrFFT.cpp:94-194)
+# ------------------------------------------------------------------------------------------------
+class CyIppXcorrFFT:
+    """Drop-in for cython_ext.CyIppXcorrFFT: float32 peaks, int32 bins, out-of-range shifts give 0 / 0."""
+
+    def __init__(self, cutout, num_threads=1, autoConj=True):
+        cutout = np.ascontiguousarray(cutout)
+        if cutout.dtype != np.complex64 or cutout.ndim != 1:
+            raise ValueError("Buffer dtype mismatch, expected 'complex64_t' 1-D")     # Cython's own check
+        # the kernels conjugate the cutout themselves; autoConj=False means "already conjugated"
+        self._cutout = cutout if autoConj else np.ascontiguousarray(cutout.conj())
+        self._num_threads = num_threads
+        self.m_productpeaks = None
+        self.m_freqlistinds = None
+
+    def xcorr(self, rx, startIdx, endIdx, step):
+        if _lib.np_dtype_of(rx) != np.dtype(np.complex64) or rx.ndim != 1:
+            raise ValueError("Buffer dtype mismatch, expected 'complex64_t' 1-D")
+        rx = _lib.contiguous(rx)
+        K = len(range(startIdx, endIdx, step))
+        sh = _Shifts.__new__(_Shifts)
+        sh.shift0, sh.step, sh.K, sh.array = int(startIdx), int(step), K, None
+        cutout = self._cutout
+        if _lib.is_device(rx):
+            import torch
+            cutout = torch.from_numpy(cutout).to(rx.device)
+        qf2, fidx, _, _ = _fastxcorr_call(cutout, rx, sh, True, want_fidx=True, flags=XC_FLAG_ZERO_OOB)
+        if not _lib.is_torch(fidx):
+            fidx = fidx.view(np.int32)
+        self.m_productpeaks, self.m_freqlistinds = qf2, fidx
+        return qf2, fidx
+
+    def results(self):
+        return self.m_productpeaks, self.m_freqlistinds
+
+
+# ------------------------------------------------------------------------------------------------
+# a7: GroupXcorrFFT  (xcorrRoutines.py:1047-1262)
+# ------------------------------------------------------------------------------------------------
+def makeFreq(length, fs):
+    """signalCreationRoutines.py:380-386."""
+    f = np.arange(length, dtype=np.float64) / length * fs
+    f[f >= fs / 2] -= fs
+    return f
+
+
+class _GroupHandle:
+    """Owns an xc_group* (folded contributor lists + ||ygroups||^2 on the device)."""
+
+    def __init__(self, ygroups, starts, fftlen, autoConj):
+        lib = _lib.load()
+        y = np.ascontiguousarray(ygroups, dtype=np.complex64)
+        st = np.ascontiguousarray(starts, dtype=np.int64)
+        self._h = C.c_void_p()
+        check(lib.xc_group_create(_lib.ptr(y), y.shape[0], y.shape[1], _lib.ptr(st), int(fftlen), 1 if autoConj else 0,
+                                  C.byref(self._h)))
+
+    def run(self, rx, sh, want_flat, want_caf, want_peak=False):
+        lib = _lib.load()
+        where = _lib.where_of(rx)
+        _select_device(rx)
+        K = sh.K
+        qf2 = _lib.empty_like_space(rx, K, np.float32) if want_flat else None
+        fidx = _lib.empty_like_space(rx, K, np.uint32) if want_flat else None
+        caf = _lib.empty_like_space(rx, (K, self.F), np.float32) if want_caf else None
+        peak = xc_peak() if want_peak else None
+        check(lib.xc_group_xcorr(self._h, _lib.ptr(rx), rx.shape[0], sh.shift0, sh.step, K, _lib.ptr(sh.array),
+                                 _lib.ptr(qf2), _lib.ptr(fidx), _lib.ptr(caf),
+                                 C.byref(peak) if peak is not None else None, where, _lib.current_stream(rx)))
+        return qf2, fidx, caf, peak
+
+    def __del__(self):
+        try:
+            if self._h:
+                _lib.load().xc_group_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
+def _group_shifts(shifts, like):
+    sh = _Shifts.__new__(_Shifts)
+    sh.array = None
+    if _lib.is_torch(shifts):
+        shifts = shifts.detach().cpu().numpy()
+    s = np.asarray(shifts).astype(np.int64).reshape(-1)
+    sh.K = int(s.size)
+    if s.size <= 1:
+        sh.shift0, sh.step = (int(s[0]) if s.size else 0), 1
+    else:
+        d = np.diff(s)
+        if np.all(d == d[0]):
+            sh.shift0, sh.step = int(s[0]), int(d[0])
+        else:
+            sh.shift0, sh.step = 0, 0
+            sh.array = np.ascontiguousarray(s)
+            if _lib.is_device(like):
+                import torch
+                sh.array = torch.from_numpy(sh.array).to(like.device)
+    return sh
+
+
+class GroupXcorrFFT:
+    """Drop-in for xcorrRoutines.GroupXcorrFFT (1047-1262): same constructor, attributes and
+    xcorr / xcorrThreads / xcorrGPU methods.  The G zero-padded FFTs + phase rotation + sum of the
+    reference are computed as ONE folded F-point FFT per shift (see csrc/group.cu)."""
+
+    def __init__(self, ygroups, starts, fs, autoConj=True, fftlen=None, autoZeroStarts=True):
+        ygroups = np.asarray(ygroups)
+        starts = np.asarray(starts)
+        assert starts.size == ygroups.shape[0]                                  # :1057
+        self.starts = starts - starts[0] if autoZeroStarts else starts         # :1058-1060
+        self.numGroups = self.starts.size
+        self.fs = fs
+        self.ygroupLen = ygroups.shape[1]
+        self.fftlen = self.ygroupLen if fftlen is None else fftlen             # :1065-1068
+        self.ygroupNormSq = np.linalg.norm(ygroups.flatten()) ** 2             # :1070
+        self.ygroups = ygroups.conj() if autoConj else ygroups                 # :1072-1073
+        self.fftfreq = makeFreq(self.fftlen, self.fs)                          # :1076
+        self._handle = _GroupHandle(self.ygroups, self.starts, self.fftlen, False)
+        self._handle.F = int(self.fftlen)
+
+    @property
+    def groupPhases(self):
+        """The (G, F) complex128 phase table of the reference (1077-1079); not used by the kernels."""
+        return np.exp(-1j * 2 * np.pi * self.fftfreq * self.starts.reshape((-1, 1)) / self.fs)
+
+    def _shifts(self, rx, shifts):
+        if shifts is None:
+            shifts = np.arange(rx.shape[0] - (int(self.starts[-1]) + self.fftlen) + 1)    # :1141
+        else:
+            assert shifts[-1] + self.starts[-1] + self.fftlen < rx.shape[0]               # :1143
+        sh = _group_shifts(shifts, rx)
+        return sh
+
+    def xcorr(self, rx, shifts=None, flattenToTime=True):
+        """(xc float64[K], fi uint32[K]) when flattenToTime, else the CAF float64 (K, F)."""
+        if _lib.np_dtype_of(rx) != np.dtype(np.complex64):
+            raise TypeError("rx must be complex64")
+        rx = _lib.contiguous(rx)
+        sh = self._shifts(rx, shifts)
+        if flattenToTime:
+            qf2, fidx, _, _ = self._handle.run(rx, sh, True, False)
+            return _as(qf2, np.float64), fidx
+        _, _, caf, _ = self._handle.run(rx, sh, False, True)
+        return _as(caf, np.float64)
+
+    def xcorrThreads(self, rx, shifts=None, NUM_THREADS=4):
+        """CAF only, like the reference (1114-1135); NUM_THREADS is accepted and ignored."""
+        return self.xcorr(rx, shifts, flattenToTime=False)
+
+    def xcorrGPU(self, rx, shifts=None, flattenToTime=True):
+        """Device-resident variant (1191-1262): rx is a torch CUDA tensor, results stay on the device."""
+        if not _lib.is_device(rx):
+            raise TypeError("rx must be a CUDA tensor (the reference requires a cupy array here)")
+        return self.xcorr(rx, shifts, flattenToTime)
+
+    def xcorrPeak(self, rx, shifts=None):
+        """(QF^2[K], fi[K], xc_peak) -- the per-call peak tuple used by the sharded multi-GPU run."""
+        rx = _lib.contiguous(rx)
+        sh = self._shifts(rx, shifts)
+        qf2, fidx, _, peak = self._handle.run(rx, sh, True, False, want_peak=True)
+        return qf2, fidx, peak
+
+
+# ------------------------------------------------------------------------------------------------
+# a8: CyGroupXcorrFFT  (CyGroupXcorrFFT.pyx:13-66, GroupXcorrFFT.cpp:3-199)
+# ------------------------------------------------------------------------------------------------
+class CyGroupXcorrFFT:
+    """Drop-in for cython_ext.CyGroupXcorrFFT: offsets used as given, CAF float32 (K, F) only."""
+
+    def __init__(self, ygroups, offsets, fs, fftlen=-1, autoConj=True):
+        ygroups = np.ascontiguousarray(ygroups)
+        offsets = np.ascontiguousarray(offsets)
+        if ygroups.dtype != np.complex64 or ygroups.ndim != 2:
+            raise ValueError("Buffer dtype mismatch, expected 'complex64_t' 2-D")
+        if offsets.dtype != np.int32:
+            raise ValueError("Buffer dtype mismatch, expected 'int32_t'")
+        L = ygroups.shape[1]
+        self.fftlen = L if fftlen < 0 else int(fftlen)
+        if self.fftlen < L:
+            raise RuntimeError("INVALID_FFTLEN")                   # GroupXcorrFFT.cpp:11-14 throws int 1
+        self._handle = _GroupHandle(ygroups, offsets.astype(np.int64), self.fftlen, autoConj)
+        self._handle.F = self.fftlen
+
+    def xcorr(self, rx, shifts, NUM_THREADS=1):
+        if _lib.np_dtype_of(rx) != np.dtype(np.complex64):
+            raise ValueError("Buffer dtype mismatch, expected 'complex64_t'")
+        rx = _lib.contiguous(rx)
+        sh = _group_shifts(shifts, rx)
+        _, _, caf, _ = self._handle.run(rx, sh, False, True)
+        return caf
+
+
+# ------------------------------------------------------------------------------------------------
+# a9: TemplateCrossCorrelator  (xcorrRoutines.py:277-371)
+# ------------------------------------------------------------------------------------------------
+class _MtHandle:
+    def __init__(self, templates, conj, energies=None):
+        lib = _lib.load()
+        if _lib.is_torch(templates):
+            templates = templates.detach().cpu().numpy()
+        t = np.ascontiguousarray(templates, dtype=np.complex64)
+        e = None
+        if energies is not None:
+            if _lib.is_torch(energies):
+                energies = energies.detach().cpu().numpy()
+            e = np.ascontiguousarray(energies, dtype=np.float32)
+        self.T, self.L = t.shape
+        self._h = C.c_void_p()
+        check(lib.xc_mt_create(_lib.ptr(t), self.T, self.L, 1 if conj else 0, _lib.ptr(e), C.byref(self._h)))
+
+    def run(self, x, start, K, want_best, want_full, sqrt_out, want_peak=False):
+        lib = _lib.load()
+        where = _lib.where_of(x)
+        _select_device(x)
+        best = _lib.empty_like_space(x, K, np.float32) if want_best else None
+        tidx = _lib.empty_like_space(x, K, np.int32) if want_best else None
+        full = _lib.empty_like_space(x, (self.T, K), np.complex64) if want_full else None
+        peak = xc_peak() if want_peak else None
+        check(lib.xc_mt_correlate(self._h, _lib.ptr(x), x.shape[0], int(start), int(K), _lib.ptr(best), _lib.ptr(tidx),
+                                  _lib.ptr(full), 1 if sqrt_out else 0, C.byref(peak) if peak is not None else None,
+                                  where, _lib.current_stream(x)))
+        return best, tidx, full, peak
+
+    def __del__(self):
+        try:
+            if self._h:
+                _lib.load().xc_mt_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
+class TemplateCrossCorrelator:
+    """Drop-in for xcorrRoutines.TemplateCrossCorrelator (277-371).  `templates` is (T, L) complex64
+    (numpy or device tensor); correlate(x) returns the complex QF (T, inputSize-L+1), or with
+    returnMax=True the tuple (QF float32[K], templateIdx int64[K])."""
+
+    def __init__(self, templates, inputSize):
+        if templates.ndim != 2:
+            raise ValueError("Templates must be a 2D array; 1 row for 1 template.")     # :295-296
+        if _lib.np_dtype_of(templates) != np.dtype(np.complex64):
+            raise TypeError("templates must be complex64")
+        self._inputSize = int(inputSize)
+        self._templateLength = templates.shape[1]
+        self._handle = _MtHandle(templates, True)
+
+    def correlate(self, x, returnMax=False):
+        if _lib.np_dtype_of(x) != np.dtype(np.complex64):
+            raise TypeError("x must be complex64")
+        if x.ndim != 1 or x.shape[0] != self._inputSize:
+            raise ValueError("x must be 1D with length %d" % self._inputSize)            # :335-336
+        x = _lib.contiguous(x)
+        K = self._inputSize - self._templateLength + 1
+        if not returnMax:
+            _, _, full, _ = self._handle.run(x, 0, K, False, True, False)
+            return full
+        best, tidx, _, _ = self._handle.run(x, 0, K, True, False, True)
+        if _lib.is_torch(tidx):
+            import torch
+            return best, tidx.to(torch.int64)
+        return best, tidx.astype(np.int64)                                               # cp.argmax dtype (:367)

@@ -1,0 +1,354 @@
+"""GPU parity tests (run on the B200 box: `pytest -m gpu`): the CUDA library, called through the
+reference-shaped Python API over the ctypes C-ABI, against (1) the golden vectors generated from the
+REAL reference (tests/golden, oracle/make_golden.py), (2) the numpy oracle on seeded inputs and
+(3) the reference's own known-answer tests.
+
+Tolerances (BASELINE.json north_star): peak time index and frequency bin identical; QF^2 within
+1e-4 relative (plus an absolute floor of 1e-6 of the largest value for near-zero off-peak values).
+Per-shift bins on noise-only shifts must be identical too unless the two candidate bins are a
+float32 near-tie, which is adjudicated with a float64 recomputation."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+from oracle import xcorr_oracle as orc
+from pydsproutines_b200 import signals
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+RTOL = 1e-4
+
+
+def _load(pattern):
+    files = sorted(glob.glob(os.path.join(GOLDEN, pattern)))
+    assert files, "golden vectors missing: %s" % pattern
+    return [(os.path.basename(f)[:-4], np.load(f)) for f in files]
+
+
+def assert_qf2(got, ref, rtol=RTOL):
+    got = np.asarray(got, dtype=np.float64)
+    ref = np.asarray(ref, dtype=np.float64)
+    assert got.shape == ref.shape
+    atol = 1e-6 * float(np.max(np.abs(ref))) if ref.size else 0.0
+    bad = np.abs(got - ref) > rtol * np.abs(ref) + atol
+    assert not bad.any(), "QF^2 mismatch at %s: got %s ref %s" % (np.nonzero(bad)[0][:5], got[bad][:5], ref[bad][:5])
+
+
+def assert_bins(got, ref, spectrum_of, what="bin"):
+    """Bins must be equal; a differing bin is accepted only if a float64 recomputation of the
+    spectrum shows the two candidates within 1e-5 relative (a float32 near-tie)."""
+    got = np.asarray(got).astype(np.int64)
+    ref = np.asarray(ref).astype(np.int64)
+    assert got.shape == ref.shape
+    diff = np.nonzero(got != ref)[0]
+    assert diff.size <= max(1, got.size // 200), "too many %s mismatches: %d of %d" % (what, diff.size, got.size)
+    for i in diff:
+        p = spectrum_of(int(i))
+        assert abs(p[got[i]] - p[ref[i]]) <= 1e-5 * p[ref[i]], "%s mismatch at %d is not a near-tie" % (what, i)
+
+
+def _spec64(cutout, rx, s):
+    w = rx[s:s + len(cutout)].astype(np.complex128) * cutout.astype(np.complex128).conj()
+    return np.abs(np.fft.fft(w)) ** 2
+
+
+@pytest.fixture(scope="module")
+def xr():
+    import torch
+    assert torch.cuda.is_available()
+    from pydsproutines_b200 import _lib
+    assert _lib.load().xc_device_count() > 0
+    import pydsproutines_b200.xcorrRoutines as m
+    return m
+
+
+def _dev(a):
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+# ---------------------------------------------------------------------------------------------
+# fastXcorr vs golden vectors of the real reference
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name,d", _load("fastxcorr_*.npz"), ids=lambda v: v if isinstance(v, str) else "")
+@pytest.mark.parametrize("space", ["host", "device"])
+def test_fastxcorr_golden(xr, name, d, space):
+    cutout, rx = d["cutout"], d["rx"]
+    shifts = d["shifts"] if "shifts" in d.files else None
+    sh = np.arange(len(rx) - len(cutout) + 1) if shifts is None else shifts
+    conv = _dev if space == "device" else (lambda a: a)
+    back = (lambda t: t.cpu().numpy()) if space == "device" else (lambda a: a)
+    c, r = conv(cutout), conv(rx)
+    q = back(xr.fastXcorr(c, r, shifts=shifts))
+    assert q.dtype == np.float64
+    assert_qf2(q, d["qf2_nofreq"])
+    assert sh[np.argmax(q)] == int(d["p0"])
+    pow2 = (len(cutout) & (len(cutout) - 1)) == 0
+    if not pow2:
+        with pytest.raises(NotImplementedError):
+            xr.fastXcorr(c, r, freqsearch=True, shifts=shifts)
+        return
+    q, f = xr.fastXcorr(c, r, freqsearch=True, shifts=shifts)
+    q, f = back(q), back(f)
+    assert_qf2(q, d["qf2_freq"])
+    assert_bins(f, d["fidx_freq"], lambda i: _spec64(cutout, rx, int(sh[i])))
+    k = int(np.argmax(q))
+    assert sh[k] == int(d["p0"]) and int(f[k]) == int(d["k0"])
+    if "caf" in d.files:
+        z = back(xr.fastXcorr(c, r, shifts=shifts, absResult=False))
+        np.testing.assert_allclose(z, d["cplx_nofreq"], rtol=0, atol=2e-5 * np.abs(d["cplx_nofreq"]).max())
+        z, f2 = xr.fastXcorr(c, r, freqsearch=True, shifts=shifts, absResult=False)
+        z, f2 = back(z), back(f2)
+        same = f2.astype(np.int64) == d["cplx_fidx"].astype(np.int64)
+        assert same.mean() > 0.99
+        np.testing.assert_allclose(z[same], d["cplx_freq"][same], rtol=0, atol=2e-5 * np.abs(d["cplx_freq"]).max())
+        caf = back(xr.fastXcorr(c, r, freqsearch=True, outputCAF=True, shifts=shifts))
+        assert caf.shape == d["caf"].shape
+        np.testing.assert_allclose(caf, d["caf"], rtol=RTOL, atol=1e-6 * d["caf"].max())
+        cafc = back(xr.fastXcorr(c, r, freqsearch=True, outputCAF=True, shifts=shifts, absResult=False))
+        np.testing.assert_allclose(cafc, d["caf_cplx"], rtol=0, atol=2e-5 * np.abs(d["caf_cplx"]).max())
+
+
+@pytest.mark.parametrize("log2n", list(range(1, 15)))
+def test_fastxcorr_every_power_of_two_vs_oracle(xr, log2n):
+    """Every block-FFT plan (N = 2 .. 16384) against the numpy oracle on a seeded planted case."""
+    N = 1 << log2n
+    K = 96 if N <= 2048 else 24
+    p0, k0 = K // 3, (3 * N) // 8 + 1 if N > 2 else 1
+    cutout, rx = signals.make_fastxcorr_case(100 + log2n, N, N + K - 1, p0, k0 % N, amp=0.9)
+    qr, fr = orc.fastXcorr(cutout, rx, freqsearch=True)
+    q, f = xr.fastXcorr(cutout, rx, freqsearch=True)
+    assert_qf2(q, qr)
+    assert_bins(f, fr, lambda i: _spec64(cutout, rx, i))
+    if N >= 8:
+        assert int(np.argmax(q)) == p0 and int(f[p0]) == k0 % N
+    assert_qf2(xr.fastXcorr(cutout, rx), orc.fastXcorr(cutout, rx))
+
+
+def test_fastxcorr_shift_lists_and_errors(xr):
+    cutout, rx = signals.make_fastxcorr_case(31, 128, 3000, 777, 5)
+    ragged = np.array([5, 6, 100, 777, 778, 2000, 13, 2872], dtype=np.int64)      # not an arithmetic progression
+    for fs in (False, True):
+        ref = orc.fastXcorr(cutout, rx, freqsearch=fs, shifts=ragged)
+        got = xr.fastXcorr(cutout, rx, freqsearch=fs, shifts=ragged)
+        if fs:
+            assert_qf2(got[0], ref[0])
+            assert np.array_equal(got[1], ref[1])
+        else:
+            assert_qf2(got, ref)
+    step = np.arange(2871, 0, -7)                                                  # negative step progression
+    assert_qf2(xr.fastXcorr(cutout, rx, shifts=step), orc.fastXcorr(cutout, rx, shifts=step))
+    q, f = xr.fastXcorr(cutout, rx, freqsearch=True, shifts=step)
+    qr, fr = orc.fastXcorr(cutout, rx, freqsearch=True, shifts=step)
+    assert_qf2(q, qr)
+    assert np.array_equal(f, fr)
+    with pytest.raises(ValueError):
+        xr.fastXcorr(cutout, rx, shifts=np.array([0, 2873]))
+    with pytest.raises(TypeError):
+        xr.fastXcorr(cutout.astype(np.complex128), rx)
+    e = xr.fastXcorr(cutout, rx[:128], freqsearch=True)                           # a single shift
+    assert e[0].shape == (1,)
+    empty = xr.fastXcorr(cutout, rx, shifts=np.array([], dtype=np.int64))
+    assert empty.shape == (0,)
+
+
+def test_cp_fastxcorr_variants_and_cyipp(xr):
+    cutout, rx = signals.make_fastxcorr_case(32, 256, 256 + 500, 123, 40)
+    qr, fr = orc.fastXcorr(cutout, rx, freqsearch=True)
+    q, f = xr.cp_fastXcorr(cutout, rx)
+    assert q.dtype == np.float64 and f.dtype == np.uint32
+    assert_qf2(q, qr)
+    assert np.array_equal(f, fr)
+    q, f = xr.cp_fastXcorr(_dev(cutout), _dev(rx))                                 # device in, copyToCpu
+    assert isinstance(q, np.ndarray) and np.array_equal(f, fr)
+    fi, q2 = xr.cp_fastXcorr_v2(_dev(cutout), _dev(rx), startIdx=100, idxlen=50, flattenCAF=True)   # (freqIdx, qf2) order
+    assert q2.dtype.is_floating_point and np.array_equal(fi.cpu().numpy(), fr[100:150])
+    assert_qf2(q2.cpu().numpy(), qr[100:150])
+    caf = xr.cp_fastXcorr_v2(_dev(cutout), _dev(rx), startIdx=120, idxlen=8)
+    np.testing.assert_allclose(caf.cpu().numpy(), orc.fastXcorr(cutout, rx, True, True, np.arange(120, 128)),
+                               rtol=RTOL, atol=1e-6)
+    with pytest.raises(ValueError):
+        xr.cp_fastXcorr_v2(_dev(cutout), _dev(rx), startIdx=400, idxlen=200)
+    with pytest.raises(Exception):
+        xr.cp_fastXcorr(cutout, rx.astype(np.complex128))
+    # CyIppXcorrFFT conventions: float32 / int32, out-of-range shifts are zero (IppXcorrFFT.cpp:125-130)
+    pr, br = orc.cyIppXcorrFFT(cutout, rx, -6, 520, 3)
+    p, b = xr.CyIppXcorrFFT(cutout).xcorr(rx, -6, 520, 3)
+    assert p.dtype == np.float32 and b.dtype == np.int32 and p.size == pr.size
+    assert_qf2(p, pr)
+    assert np.array_equal(b, br)
+    assert p[0] == 0 and p[1] == 0 and p[-1] == 0 and b[-1] == 0
+
+
+# ---------------------------------------------------------------------------------------------
+# GroupXcorrFFT vs golden vectors of the real reference
+# ---------------------------------------------------------------------------------------------
+def _group_spec64(d, s):
+    y, starts, F = d["ygroups"].astype(np.complex128), d["starts"] - d["starts"][0], int(d["F"])
+    L = y.shape[1]
+    z = np.zeros(F, np.complex128)
+    for g in range(y.shape[0]):
+        seg = d["rx"][s + starts[g]: s + starts[g] + L].astype(np.complex128)
+        np.add.at(z, (starts[g] + np.arange(L)) % F, y[g].conj() * seg)
+    return np.abs(np.fft.fft(z)) ** 2
+
+
+@pytest.mark.parametrize("name,d", _load("groupxcorr_*.npz"), ids=lambda v: v if isinstance(v, str) else "")
+@pytest.mark.parametrize("space", ["host", "device"])
+def test_groupxcorr_golden(xr, name, d, space):
+    F = int(d["F"])
+    obj = xr.GroupXcorrFFT(d["ygroups"], d["starts"], 1, fftlen=F)
+    rx = _dev(d["rx"]) if space == "device" else d["rx"]
+    back = (lambda t: t.cpu().numpy()) if space == "device" else (lambda a: a)
+    xc, fi = obj.xcorr(rx, d["shifts"])
+    xc, fi = back(xc), back(fi)
+    assert xc.dtype == np.float64
+    assert_qf2(xc, d["xc"])
+    assert_bins(fi, d["fi"], lambda i: _group_spec64(d, int(d["shifts"][i])))
+    k = int(np.argmax(xc))
+    assert d["shifts"][k] == int(d["p0"]) and int(fi[k]) == int(d["k0"])
+    caf = back(obj.xcorr(rx, d["shifts"], flattenToTime=False))
+    assert caf.shape == d["caf"].shape
+    np.testing.assert_allclose(caf, d["caf"], rtol=RTOL, atol=1e-6 * d["caf"].max())
+    if space == "host":
+        np.testing.assert_allclose(obj.xcorrThreads(rx, d["shifts"]), d["caf"], rtol=RTOL, atol=1e-6 * d["caf"].max())
+        # CyGroupXcorrFFT: offsets as given, float32 CAF
+        cy = xr.CyGroupXcorrFFT(d["ygroups"], (d["starts"] - d["starts"][0]).astype(np.int32), 1, fftlen=F)
+        out = cy.xcorr(d["rx"], d["shifts"].astype(np.int32))
+        assert out.dtype == np.float32 and out.shape == d["caf"].shape
+        np.testing.assert_allclose(out, d["caf"], rtol=RTOL, atol=1e-6 * d["caf"].max())
+    else:
+        xc2, fi2 = obj.xcorrGPU(rx, d["shifts"])
+        assert np.array_equal(fi2.cpu().numpy(), fi)
+
+
+def test_groupxcorr_errors(xr):
+    y = signals.qpsk(np.random.default_rng(1), 64).reshape(4, 16)
+    with pytest.raises(ValueError):
+        xr.GroupXcorrFFT(y, np.array([0, 20, 40, 60]), 1, fftlen=8)              # fftlen < group length
+    with pytest.raises(RuntimeError):
+        xr.CyGroupXcorrFFT(y, np.array([0, 20, 40, 60], np.int32), 1, fftlen=8)   # INVALID_FFTLEN
+    with pytest.raises(NotImplementedError):
+        xr.GroupXcorrFFT(y, np.array([0, 20, 40, 60]), 1, fftlen=48)             # not a power of two (yet)
+
+
+# ---------------------------------------------------------------------------------------------
+# template correlators: the reference's known-answer tests (xcorrRoutines.py:2130-2241)
+# ---------------------------------------------------------------------------------------------
+def _qpsk_templates():
+    rng = np.random.default_rng(7)
+    x = signals.qpsk(rng, 100).astype(np.complex64)
+    return x, np.vstack((x[20:40] * 1.234, x[40:60] * 2.345)).astype(np.complex64)
+
+
+@pytest.mark.parametrize("space", ["host", "device"])
+def test_template_correlator_known_answers(xr, space):
+    x, templates = _qpsk_templates()
+    conv = _dev if space == "device" else (lambda a: a)
+    back = (lambda t: t.cpu().numpy()) if space == "device" else (lambda a: a)
+    tc = xr.TemplateCrossCorrelator(conv(templates), x.size)
+    out = back(tc.correlate(conv(x)))
+    assert out.shape == (2, 81) and out.dtype == np.complex64
+    np.testing.assert_almost_equal(np.abs(out[0, 20]), 1.0, 5)
+    np.testing.assert_almost_equal(np.abs(out[1, 40]), 1.0, 5)
+    qf, tidx = tc.correlate(conv(x), returnMax=True)
+    qf, tidx = back(qf), back(tidx)
+    assert tidx.dtype == np.int64 and tidx[20] == 0 and tidx[40] == 1
+    np.testing.assert_allclose(qf, np.abs(out).max(axis=0), rtol=1e-5)
+    for i in range(2):
+        np.testing.assert_almost_equal(np.abs(out[i]), orc.fastXcorr(templates[i], x) ** 0.5, 5)   # :2180-2200
+        np.testing.assert_allclose(np.abs(out[i]), np.abs(orc.fastXcorr(templates[i], x, absResult=False)), atol=2e-6)
+    ref = orc.TemplateCrossCorrelator(templates, x.size).correlate(x)
+    np.testing.assert_allclose(out, ref, atol=3e-6)
+    with pytest.raises(ValueError):
+        xr.TemplateCrossCorrelator(templates[0], 100)
+    with pytest.raises(ValueError):
+        tc.correlate(conv(x[:50]))
+
+
+def test_multitemplate_dot_vs_oracle():
+    from pydsproutines_b200 import cupyExtensions as ce
+    rng = np.random.default_rng(8)
+    for T, L, n in ((5, 24, 300), (3, 1, 40), (17, 100, 5000), (2, 1030, 4000)):
+        templates = signals.qpsk(rng, T * L).reshape(T, L)
+        x = signals.cnoise(rng, n)
+        x[n // 3:n // 3 + L] += templates[T - 1]
+        K = n - L + 1
+        ti_ref, q_ref = orc.multiTemplateSlidingDotProduct(x, templates.conj(), 0, K)
+        ti, q = ce.multiTemplateSlidingDotProduct(x, templates.conj().copy(), 0, K)
+        assert ti.dtype == np.int32 and q.dtype == np.float32
+        assert_qf2(q, q_ref)
+        bad = np.nonzero(ti != ti_ref)[0]
+        assert bad.size <= K // 100
+        assert int(np.argmax(q)) == n // 3 and ti[n // 3] == T - 1
+        ti2, q2 = ce.multiTemplateSlidingDotProduct(_dev(x), _dev(templates.conj()), 7, K - 11)
+        assert np.array_equal(ti2.cpu().numpy(), ti[7:K - 4]) and np.allclose(q2.cpu().numpy(), q[7:K - 4], rtol=1e-6)
+    with pytest.raises(ValueError):
+        ce.multiTemplateSlidingDotProduct(x, templates, -1, 10)
+    with pytest.raises(ValueError):
+        ce.multiTemplateSlidingDotProduct(x, templates, 0, x.size)
+    with pytest.raises(ValueError):
+        ce.multiTemplateSlidingDotProduct(x, templates[0], 0, 10)
+    with pytest.raises(TypeError):
+        ce.multiTemplateSlidingDotProduct(x.astype(np.complex128), templates, 0, 10)
+
+
+# ---------------------------------------------------------------------------------------------
+# primitives: sliding energy / moving average / |x|^2 / row argmax / local maxima
+# ---------------------------------------------------------------------------------------------
+def test_moving_average_known_answers():
+    import scipy.signal as sps
+    from pydsproutines_b200 import filterRoutines as fr
+    x = np.random.default_rng(9).random(100).astype(np.float32)               # filterRoutines.py:1326-1335
+    np.testing.assert_almost_equal(fr.cupyMovingAverage(x, 20, sumInstead=True), sps.lfilter(np.ones(20), 1, x), 5)
+    np.testing.assert_almost_equal(fr.cupyMovingAverage(x, 20), sps.lfilter(np.ones(20) / 20, 1, x), 5)
+    with pytest.raises(ValueError):
+        fr.cupyMovingAverage(x, 20, NUM_PER_THREAD=32)                          # :1308-1313
+    with pytest.raises(TypeError):
+        fr.cupyMovingAverage(x.astype(np.float64), 20)
+    rng = np.random.default_rng(10)
+    for n, L in ((5000, 1), (5000, 33), (70000, 4096), (20000, 20000), (3, 7)):
+        x = rng.random(n).astype(np.float32)
+        got = fr.cupyMovingAverage(_dev(x), L, sumInstead=True).cpu().numpy()
+        np.testing.assert_allclose(got, orc.movingAverage(x, L, sumInstead=True), rtol=2e-6)
+    z = signals.cnoise(rng, 50000)
+    for L in (1, 100, 8192, 50000):
+        np.testing.assert_allclose(fr.slidingEnergy(z, L), orc.slidingEnergy(z, L), rtol=2e-6)
+        ref = np.array([np.linalg.norm(z[s:s + L].astype(np.complex128)) ** 2 for s in (0, (50000 - L) // 2, 50000 - L)])
+        np.testing.assert_allclose(fr.slidingEnergy(z, L)[[0, (50000 - L) // 2, 50000 - L]], ref, rtol=1e-6)
+
+
+def test_magnsq_argmax_local_maxima():
+    from pydsproutines_b200 import cupyExtensions as ce
+    rng = np.random.default_rng(11)
+    z = signals.cnoise(rng, 10001)
+    np.testing.assert_allclose(ce.cupyComplexMagnSq(z), orc.complexMagnSq(z, np.float64), rtol=1e-12)
+    m32 = ce.cupyComplexMagnSq(_dev(z), np.float32).cpu().numpy()
+    assert m32.dtype == np.float32
+    np.testing.assert_allclose(m32, orc.complexMagnSq(z, np.float32), rtol=3e-7)
+    X = signals.cnoise(rng, 37 * 1000).reshape(37, 1000)
+    X[5, 10] = X[5, 900] = 9 + 0j                                                # exact tie -> lowest index
+    for ns in (False, True):
+        idx_ref, val_ref = orc.argmaxAbsRows(X, useNormSqInstead=ns)
+        idx, val = ce.cupyArgmaxAbsRows_complex64(X, returnMaxValues=True, useNormSqInstead=ns)
+        assert idx.dtype == np.uint32 and np.array_equal(idx, idx_ref) and idx[5] == 10
+        np.testing.assert_allclose(val, val_ref, rtol=1e-6)
+    idx = ce.cupyArgmaxAbsRows_complex64(_dev(X))
+    assert np.array_equal(idx.cpu().numpy().astype(np.uint32), idx_ref)
+    with pytest.raises(TypeError):
+        ce.cupyArgmaxAbsRows_complex64(X.astype(np.complex128))
+    x = np.zeros(50, np.float32)                                                  # cupyExtensions.py:697-712
+    x[5], x[8], x[9], x[37], x[41] = 1.0, 0.5, 0.6, 0.9, 0.7
+    pk, cnt = ce.cupyFindLocalMaxima(x, 0.4)
+    assert cnt.dtype == np.int32 and int(cnt[0]) == 4 and list(pk[:4]) == [5, 9, 37, 41]
+    big = rng.random(300000).astype(np.float32)
+    ref = orc.findLocalMaxima(big, 0.9)
+    pk, cnt = ce.cupyFindLocalMaxima(_dev(big), 0.9, maxNumPeaks=ref.size + 10)
+    assert int(cnt[0]) == ref.size and np.array_equal(pk.cpu().numpy()[:ref.size], ref)
+    pk, cnt = ce.cupyFindLocalMaxima(big, 0.9, maxNumPeaks=100)                   # capped output
+    assert int(cnt[0]) == ref.size and np.array_equal(pk, ref[:100])
+    with pytest.raises(TypeError):
+        ce.cupyFindLocalMaxima(big.astype(np.float64), 0.5)
