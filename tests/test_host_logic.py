@@ -1,0 +1,150 @@
+"""CPU-only tests: the C-ABI library loads and exports every symbol include/xcorr_b200.h declares, the
+host-side mirror keeps the reference's argument checks, compute calls fail loudly without a GPU (no
+CPU fallback), and the shift-range sharding + peak exchange works over gloo with world_size 2."""
+import ctypes
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    from pydsproutines_b200 import _lib
+    if not os.path.isfile(_lib.LIB_PATH):
+        import __graft_entry__
+        __graft_entry__.build()
+    return _lib.load()
+
+
+def test_library_exports_every_declared_symbol(lib):
+    from pydsproutines_b200 import _lib
+    hdr = open(os.path.join(ROOT, "include", "xcorr_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(xc_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 20
+    raw = ctypes.CDLL(_lib.LIB_PATH)
+    for name in sorted(declared):
+        assert hasattr(raw, name), "libxcorr_b200.so does not export %s" % name
+    assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
+    assert lib.xc_version() >= 100
+    assert ctypes.sizeof(_lib.xc_peak) == 32
+    assert lib.xc_fastxcorr_supported(8192) == 1 and lib.xc_fastxcorr_supported(100) == 0
+
+
+def test_no_cpu_fallback(lib):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from pydsproutines_b200 import xcorrRoutines as xr
+    from pydsproutines_b200 import _lib
+    c = np.ones(8, np.complex64)
+    rx = np.ones(64, np.complex64)
+    with pytest.raises(_lib.XcorrB200Error, match="no CUDA device"):
+        xr.fastXcorr(c, rx)
+    with pytest.raises(_lib.XcorrB200Error, match="no CUDA device"):
+        xr.fastXcorr(c, rx, freqsearch=True)
+    with pytest.raises(_lib.XcorrB200Error):
+        xr.GroupXcorrFFT(np.ones((2, 4), np.complex64), np.array([0, 8]), 1, fftlen=8)
+    with pytest.raises(_lib.XcorrB200Error):
+        xr.TemplateCrossCorrelator(np.ones((2, 4), np.complex64), 64)
+    # the product never imports the oracle
+    for mod in ("xcorrRoutines", "cupyExtensions", "filterRoutines", "dist", "_lib", "signals"):
+        src = open(os.path.join(ROOT, "pydsproutines_b200", mod + ".py")).read()
+        assert "oracle" not in src.replace("the oracle", "").replace("numpy oracle", ""), mod
+
+
+def test_argument_checks_match_reference(lib):
+    from pydsproutines_b200 import xcorrRoutines as xr
+    from pydsproutines_b200 import cupyExtensions as ce
+    from pydsproutines_b200 import filterRoutines as fr
+    c = np.ones(8, np.complex64)
+    rx = np.ones(64, np.complex64)
+    with pytest.raises(TypeError):
+        xr.fastXcorr(c.astype(np.complex128), rx)
+    with pytest.raises(ValueError):
+        xr.fastXcorr(c, rx, shifts=np.array([60]))                        # window leaves rx
+    with pytest.raises(ValueError):
+        xr.cp_fastXcorr_v2(c, rx, startIdx=50, idxlen=20)
+    with pytest.raises(Exception):
+        xr.cp_fastXcorr(c, rx.astype(np.complex128))
+    with pytest.raises(ValueError):
+        xr.TemplateCrossCorrelator(c, 64)                                   # templates must be 2-D
+    with pytest.raises(ValueError):
+        ce.multiTemplateSlidingDotProduct(rx, c.reshape(1, -1), -1, 4)
+    with pytest.raises(ValueError):
+        ce.multiTemplateSlidingDotProduct(rx, c.reshape(1, -1), 0, 64)
+    with pytest.raises(TypeError):
+        ce.cupyFindLocalMaxima(np.zeros(4, np.float64), 0.1)
+    with pytest.raises(ValueError):
+        fr.cupyMovingAverage(np.zeros(4, np.float32), 2, NUM_PER_THREAD=32)
+    with pytest.raises(TypeError):
+        fr.cupyMovingAverage(np.zeros(4, np.float64), 2)
+    with pytest.raises(RuntimeError):
+        xr.CyGroupXcorrFFT(np.ones((2, 16), np.complex64), np.array([0, 20], np.int32), 1, fftlen=8)
+    sh = xr._Shifts(np.arange(3, 40, 4), 64, 8, rx)
+    assert (sh.shift0, sh.step, sh.K, sh.array) == (3, 4, 10, None)
+    sh = xr._Shifts(np.array([1, 5, 6]), 64, 8, rx)
+    assert sh.array is not None and sh.array.dtype == np.int64 and sh.K == 3
+    sh = xr._Shifts(None, 64, 8, rx)
+    assert (sh.shift0, sh.step, sh.K) == (0, 1, 57)
+
+
+def test_shard_ranges_and_global_peak():
+    from pydsproutines_b200 import dist as xd
+    for K, world in ((10, 3), (1 << 20, 8), (5, 8), (0, 2)):
+        parts = [xd.shard_range(K, r, world) for r in range(world)]
+        assert parts[0][0] == 0 and parts[-1][1] == K
+        assert all(parts[i][1] == parts[i + 1][0] for i in range(world - 1))
+        assert max(b - a for a, b in parts) - min(b - a for a, b in parts) <= 1
+    first, n = xd.shard_samples(100, 16, 1, 4)
+    assert (first, n) == (25, 25 + 15)
+    rows = [xd.peak_to_row(0.5, 7, 900, 0, 0), xd.peak_to_row(0.9, 3, 5000, 0, 1),
+            xd.peak_to_row(0.9, 4, 4000, 0, 2), xd.peak_to_row(0.0, 0, -1, 0, 3)]
+    g = xd.global_peak(np.stack(rows))
+    assert g == dict(qf2=0.9, fidx=4, shift=4000, aux=0, rank=2)             # tie -> lowest shift
+    assert xd.global_peak(np.stack(rows[3:]))["rank"] == -1
+
+
+_GLOO_WORKER = r"""
+import os, sys
+import numpy as np
+sys.path.insert(0, %(root)r)
+import torch.distributed as dist
+from pydsproutines_b200 import dist as xd, signals
+from oracle import xcorr_oracle as orc     # the CPU checker stands in for the GPU search in this host-logic test
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+N, total = 64, 1000
+cutout, rx = signals.make_fastxcorr_case(77, N, total, 700, 9, decoy=(100, 0.5, 20))
+K = total - N + 1
+first, n = xd.shard_samples(K, N, rank, world)
+shard = rx[first:first + n]
+q, f = orc.fastXcorr(cutout, shard, freqsearch=True)
+k = int(np.argmax(q))
+rows = xd.allgather_peak(xd.peak_to_row(q[k], f[k], first + k, 0, rank))
+g = xd.global_peak(rows)
+assert rows.shape == (world, 5)
+assert g["shift"] == 700 and g["fidx"] == 9 and g["rank"] == 1, g
+qa, fa = orc.fastXcorr(cutout, rx, freqsearch=True)
+lo, hi = xd.shard_range(K, rank, world)
+assert np.array_equal(q, qa[lo:hi]) and np.array_equal(f, fa[lo:hi])        # halo makes shards exact
+dist.destroy_process_group()
+sys.stdout.write("rank%d-ok\n" % rank)
+"""
+
+
+def test_sharded_peak_exchange_gloo_world2(tmp_path):
+    script = tmp_path / "worker.py"
+    script.write_text(_GLOO_WORKER % {"root": ROOT})
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29517", str(script)]
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    assert "rank0-ok" in r.stdout and "rank1-ok" in r.stdout
