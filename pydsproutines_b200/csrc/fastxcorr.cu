@@ -19,39 +19,43 @@ struct CutoutLoader {
     const float2* cutout;
     int64_t shift0, step;
     const int64_t* shifts;
-    float2* cc;   // conj(cutout) in shared memory (set by prepare)
 
     __host__ __device__ static constexpr size_t smem_bytes() { return CUT_SMEM ? sizeof(float2) * PL::N : 0; }
 
-    __device__ __forceinline__ void prepare(int tid, int nthreads, unsigned char* smem) {
-        cc = reinterpret_cast<float2*>(smem);
+    // conj(cutout) into shared memory
+    __device__ __forceinline__ void prepare(int tid, int nthreads, unsigned char* smem) const {
         if (CUT_SMEM) {
+            float2* cc = reinterpret_cast<float2*>(smem);
             for (int n = tid; n < PL::N; n += nthreads) {
                 const float2 c = cutout[n];
                 cc[n] = make_float2(c.x, -c.y);
             }
         }
     }
-    __device__ __forceinline__ bool load(float2* v, int t, int64_t i) const {
+    __device__ __forceinline__ bool load(float2* v, int t, int64_t i, const unsigned char* smem) const {
         const int64_t s = shifts ? shifts[i] : shift0 + i * step;
         if (s < 0 || s + PL::N > rxlen) return false;
-        const float2* x = rx + s;
+        const float2* x = rx + s + t;
         constexpr int NQ = PL::V / PL::R1;
 #pragma unroll
         for (int n1 = 0; n1 < PL::R1; ++n1)
 #pragma unroll
-            for (int q = 0; q < NQ; ++q) v[q * PL::R1 + n1] = __ldg(x + input_index<PL>(t, q, n1));
+            for (int q = 0; q < NQ; ++q) v[q * PL::R1 + n1] = __ldg(x + input_index<PL>(0, q, n1));
+        if (CUT_SMEM) {
+            const float2* cc = reinterpret_cast<const float2*>(smem) + t;
 #pragma unroll
-        for (int n1 = 0; n1 < PL::R1; ++n1)
+            for (int n1 = 0; n1 < PL::R1; ++n1)
 #pragma unroll
-            for (int q = 0; q < NQ; ++q) {
-                const int n = input_index<PL>(t, q, n1);
-                if (CUT_SMEM) {
-                    v[q * PL::R1 + n1] = cmul(v[q * PL::R1 + n1], cc[n]);
-                } else {
-                    v[q * PL::R1 + n1] = cmulc(v[q * PL::R1 + n1], __ldg(cutout + n));
-                }
-            }
+                for (int q = 0; q < NQ; ++q)
+                    v[q * PL::R1 + n1] = cmul(v[q * PL::R1 + n1], cc[input_index<PL>(0, q, n1)]);
+        } else {
+            const float2* cg = cutout + t;
+#pragma unroll
+            for (int n1 = 0; n1 < PL::R1; ++n1)
+#pragma unroll
+                for (int q = 0; q < NQ; ++q)
+                    v[q * PL::R1 + n1] = cmulc(v[q * PL::R1 + n1], __ldg(cg + input_index<PL>(0, q, n1)));
+        }
         return true;
     }
 };
@@ -69,7 +73,7 @@ struct FreqRunner {
     int32_t run() {
         using PF = PlanFor<LOG2N>;
         using LD = CutoutLoader<typename PF::PL, PF::CS>;
-        LD ld{rx, rxlen, cutout, sl.shift0, sl.step, sl.shifts, nullptr};
+        LD ld{rx, rxlen, cutout, sl.shift0, sl.step, sl.shifts};
         return launch_fused<typename PF::PL, PF::B, LD>(ld, out, sl.K, stream);
     }
 };

@@ -120,6 +120,8 @@ struct FftPlan {
     static_assert(R1_ * R2_ * R3_ == N, "radices must multiply to N");
     static_assert(V % R1_ == 0 && V % R2_ == 0 && V % R3_ == 0, "each pass must fill the registers");
     static_assert(R1_ <= 32 && R2_ <= 32 && R3_ <= 32, "codelets go up to radix 32");
+    static_assert(R3_ == 1 || (TG_ % R3_ == 0 && TG_ % R2_ == 0), "three-pass plans need TG to be a multiple of R2 and R3");
+    static_assert(R3_ > 1 || R2_ == 1 || TG_ * (N / TG_ / R1_) == R2_, "two-pass plans: the columns of pass 1 are the R2 points");
     __device__ static __forceinline__ int phys(int i) { return i + (i >> LOG2RL); }
 };
 
@@ -127,17 +129,13 @@ struct FftPlan {
 template <class PL>
 struct FftThread {
     float2 tw1[PL::V / PL::R1];                       // W_N^(t + TG*q)
-    float2 tw2[(PL::P == 3) ? PL::V / PL::R2 : 1];    // W_M1^((t + TG*q) % M2)
+    float2 tw2;                                       // W_M1^(t % M2)  (TG is a multiple of M2, so q drops out)
     __device__ __forceinline__ void init(int t) {
         if (PL::P >= 2) {
 #pragma unroll
             for (int q = 0; q < PL::V / PL::R1; ++q) tw1[q] = unit_root(t + PL::TG * q, PL::N);
         }
-        if (PL::P == 3) {
-#pragma unroll
-            for (int q = 0; q < PL::V / PL::R2; ++q)
-                tw2[q] = unit_root((t + PL::TG * q) % PL::M2, PL::M1);
-        }
+        if (PL::P == 3) tw2 = unit_root(t % PL::M2, PL::M1);
     }
 };
 
@@ -147,69 +145,79 @@ __device__ __forceinline__ int input_index(int t, int q, int n1) {
     return n1 * PL::M1 + t + PL::TG * q;
 }
 
-// Bin index held in register slot (q*RL + j) of thread t after the last pass.
+// Bin index held in register slot (q*RL + j) of thread t after the last pass, split into a per-thread
+// base and a compile-time offset so that no per-slot value has to live in a register.
+template <class PL>
+__device__ __forceinline__ int output_bin_base(int t) {
+    if (PL::P == 1) return 0;
+    if (PL::P == 2) return t;
+    return (t / PL::R2) + PL::R1 * (t % PL::R2);      // needs TG % R2 == 0 (asserted in the plan)
+}
+template <class PL>
+__host__ __device__ constexpr int output_bin_off(int q, int j) {
+    return (PL::P == 1)   ? bitrev(j, PL::LOG2RL)
+           : (PL::P == 2) ? PL::TG * q + PL::R1 * bitrev(j, PL::LOG2RL)
+                          : q * (PL::TG / PL::R2) + PL::R1 * PL::R2 * bitrev(j, PL::LOG2RL);
+}
 template <class PL>
 __device__ __forceinline__ int output_bin(int t, int q, int j) {
-    const int kl = bitrev(j, PL::LOG2RL);
-    const int f = t + PL::TG * q;
-    if (PL::P == 1) return kl;
-    if (PL::P == 2) return f + PL::R1 * kl;
-    return (f / PL::R2) + PL::R1 * (f % PL::R2) + PL::R1 * PL::R2 * kl;
+    return output_bin_base<PL>(t) + output_bin_off<PL>(q, j);
 }
 
 // Runs the forward FFT on the V points the thread loaded according to input_index(); on return the
 // registers hold the bins given by output_bin().  `buf` is the group's padded exchange buffer and
 // BAR() a barrier over the TG threads of the group.  The caller must guarantee (with BAR) that the
 // previous user of `buf` is done before calling.
+// All shared-memory addresses are (per-thread base) + (compile-time constant): with ROW = RL + 1 the
+// padded position of cell  a*RL + b  (b < RL)  is  a*ROW + b.
 template <class PL, class Bar>
 __device__ __forceinline__ void block_fft(float2* v, const FftThread<PL>& th, float2* buf, int t, Bar bar) {
+    constexpr int RL = PL::RL, ROW = RL + 1;
     // ---- pass 1 ----
 #pragma unroll
     for (int q = 0; q < PL::V / PL::R1; ++q) dif_fft<PL::R1>(v + q * PL::R1);
     if (PL::P == 1) return;
+    {
+        // cell k1*M1 + c, c = t + TG*q.  P == 2: M1 == RL and c < RL.  P == 3: M1 and TG are multiples of RL.
+        constexpr int K1STEP = (PL::M1 / RL) * ROW;
+        constexpr int QSTEP = (PL::P == 2) ? PL::TG : (PL::TG / RL) * ROW;
+        float2* const b1 = buf + ((PL::P == 2) ? t : (t / RL) * ROW + (t % RL));
 #pragma unroll
-    for (int q = 0; q < PL::V / PL::R1; ++q) {
-        twiddle_powers<PL::R1>(v + q * PL::R1, th.tw1[q]);
-        const int c = t + PL::TG * q;
+        for (int q = 0; q < PL::V / PL::R1; ++q) {
+            twiddle_powers<PL::R1>(v + q * PL::R1, th.tw1[q]);
 #pragma unroll
-        for (int j = 0; j < PL::R1; ++j) {
-            const int k1 = bitrev(j, ilog2(PL::R1));
-            buf[PL::phys(k1 * PL::M1 + c)] = v[q * PL::R1 + j];
+            for (int j = 0; j < PL::R1; ++j) b1[bitrev(j, ilog2(PL::R1)) * K1STEP + q * QSTEP] = v[q * PL::R1 + j];
         }
     }
     bar();
     if (PL::P == 3) {
-        // ---- pass 2 (in place) ----
+        // ---- pass 2 (in place): cell k1*M1 + n2*M2 + d with e = t + TG*q = k1*M2 + d, M2 == RL ----
+        constexpr int K1STEP = (PL::M1 / RL) * ROW;
+        constexpr int QSTEP = (PL::TG / PL::M2) * K1STEP;
+        float2* const b2 = buf + (t / PL::M2) * K1STEP + (t % PL::M2);
 #pragma unroll
-        for (int q = 0; q < PL::V / PL::R2; ++q) {
-            const int e = t + PL::TG * q;
-            const int base = (e / PL::M2) * PL::M1 + (e % PL::M2);
+        for (int q = 0; q < PL::V / PL::R2; ++q)
 #pragma unroll
-            for (int n2 = 0; n2 < PL::R2; ++n2) v[q * PL::R2 + n2] = buf[PL::phys(base + n2 * PL::M2)];
-        }
+            for (int n2 = 0; n2 < PL::R2; ++n2) v[q * PL::R2 + n2] = b2[q * QSTEP + n2 * ROW];
 #pragma unroll
         for (int q = 0; q < PL::V / PL::R2; ++q) {
             dif_fft<PL::R2>(v + q * PL::R2);
-            twiddle_powers<PL::R2>(v + q * PL::R2, th.tw2[q]);
-            const int e = t + PL::TG * q;
-            const int base = (e / PL::M2) * PL::M1 + (e % PL::M2);
+            twiddle_powers<PL::R2>(v + q * PL::R2, th.tw2);
 #pragma unroll
-            for (int j = 0; j < PL::R2; ++j) {
-                const int k2 = bitrev(j, ilog2(PL::R2));
-                buf[PL::phys(base + k2 * PL::M2)] = v[q * PL::R2 + j];
-            }
+            for (int j = 0; j < PL::R2; ++j) b2[q * QSTEP + bitrev(j, ilog2(PL::R2)) * ROW] = v[q * PL::R2 + j];
         }
         bar();
     }
-    // ---- last pass ----
+    // ---- last pass: cell f*RL + d, f = t + TG*q ----
+    {
+        const float2* const b3 = buf + t * ROW;
 #pragma unroll
-    for (int q = 0; q < PL::V / PL::RL; ++q) {
-        const int f = t + PL::TG * q;
+        for (int q = 0; q < PL::V / RL; ++q)
 #pragma unroll
-        for (int d = 0; d < PL::RL; ++d) v[q * PL::RL + d] = buf[PL::phys(f * PL::RL + d)];
+            for (int d = 0; d < RL; ++d) v[q * RL + d] = b3[q * PL::TG * ROW + d];
     }
 #pragma unroll
-    for (int q = 0; q < PL::V / PL::RL; ++q) dif_fft<PL::RL>(v + q * PL::RL);
+    for (int q = 0; q < PL::V / RL; ++q) dif_fft<RL>(v + q * RL);
 }
 
 }  // namespace xc

@@ -5,6 +5,10 @@
 //
 // One CTA hosts B independent groups of TG threads; each group walks a contiguous range of the
 // shift list so that consecutive windows re-use the same L2 lines.  Three group barriers per FFT.
+// Register discipline (the 8192-point plan runs 512 threads x 128 registers): nothing but the 32
+// points, the base twiddles and a few 32-bit counters lives across an iteration; kernel arguments
+// stay in the constant bank, pending results stay in shared memory, and the rarely used outputs
+// (complex QF, CAF rows) are compiled into a separate GENERAL instantiation.
 #pragma once
 #include "fft_engine.cuh"
 
@@ -25,53 +29,51 @@ struct GroupBar {
 struct FusedOut {
     float* qf2;          // [K] or NULL
     uint32_t* fidx;      // [K] or NULL
-    float2* cplx;        // [K] or NULL: X[bin] / sqrt(scale) (complex QF)
-    float* caf;          // [K, N] float (or float2 when caf_complex) or NULL
+    float2* cplx;        // [K] or NULL: X[bin] / sqrt(scale) (complex QF)            (GENERAL only)
+    float* caf;          // [K, N] float (or float2 when caf_complex) or NULL          (GENERAL only)
     int caf_complex;
     const float* energy; // [K] window energies (denominator), indexed like the shift list
     const float* refnormsq;  // device scalar: ||cutout||^2 (or ||ygroups||^2)
 };
 
-// Loader concept:
-//   __device__ void prepare(int tid_in_cta, int nthreads, char* smem)   -- once per CTA (before a __syncthreads)
-//   __device__ bool load(float2* v, int t, int64_t i)                   -- fills v for shift-list entry i,
-//                                                                          returns false when the shift is out of range
-//   static size_t smem_bytes()
-template <class PL, int B, class Loader>
-__global__ void __launch_bounds__(PL::TG* B) fused_fft_kernel(Loader loader, FusedOut out, int64_t K, int64_t chunk) {
+// Loader concept (all const; the kernel argument is never copied into registers):
+//   static constexpr size_t smem_bytes()
+//   __device__ void prepare(int tid_in_cta, int nthreads, unsigned char* smem) const   -- once per CTA
+//   __device__ bool load(float2* v, int t, int64_t i, const unsigned char* smem) const -- fills v for shift-list
+//                                                    entry i, returns false when the shift is out of range
+template <class PL, int B, class Loader, bool GENERAL>
+__global__ void __launch_bounds__(PL::TG* B) fused_fft_kernel(const Loader loader, const FusedOut out, const int64_t K,
+                                                              const int chunk) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int TG = PL::TG, V = PL::V, NW = (TG + 31) / 32;
-    const int tid = threadIdx.x;
-    const int g = tid / TG;       // group within the CTA
-    const int t = tid % TG;       // thread within the group
-    // shared layout: [loader area][B exchange buffers][B * NW warp maxima][B bin minima][B flags]
-    unsigned char* p = smem_raw;
-    loader.prepare(tid, TG * B, p);
-    p += Loader::smem_bytes();
-    float2* buf = reinterpret_cast<float2*>(p) + (size_t)g * PL::BUF;
-    p += sizeof(float2) * (size_t)PL::BUF * B;
-    float* wmax = reinterpret_cast<float*>(p) + g * NW;
-    p += sizeof(float) * NW * B;
-    unsigned int* binmin = reinterpret_cast<unsigned int*>(p) + g;
+    constexpr size_t OFF_BUF = Loader::smem_bytes();
+    constexpr size_t OFF_WMAX = OFF_BUF + sizeof(float2) * (size_t)PL::BUF * B;
+    constexpr size_t OFF_BIN = OFF_WMAX + sizeof(float) * NW * B;
+    constexpr size_t OFF_PEND = OFF_BIN + sizeof(unsigned int) * B;     // B floats: pending QF^2 of the previous FFT
+    const int g = threadIdx.x / TG;       // group within the CTA
+    const int t = threadIdx.x % TG;       // thread within the group
+    loader.prepare(threadIdx.x, TG * B, smem_raw);
+    float2* const buf = reinterpret_cast<float2*>(smem_raw + OFF_BUF) + (size_t)g * PL::BUF;
+    float* const wmax = reinterpret_cast<float*>(smem_raw + OFF_WMAX) + g * NW;
+    unsigned int* const binmin = reinterpret_cast<unsigned int*>(smem_raw + OFF_BIN) + g;
+    float* const pend = reinterpret_cast<float*>(smem_raw + OFF_PEND) + g;
     if (t == 0) *binmin = 0xffffffffu;
     __syncthreads();
 
     FftThread<PL> th;
     th.init(t);
     const GroupBar<TG, B> bar{1 + g};
-    const float refn = *out.refnormsq;
 
-    const int64_t gid = (int64_t)blockIdx.x * B + g;
-    const int64_t i0 = gid * chunk;
+    // first shift-list entry of this group; entries [i0, i0 + chunk) clipped to K
+    const int64_t i0 = ((int64_t)blockIdx.x * B + g) * (int64_t)chunk;
+    int n_act = 0;
+    if (i0 < K) n_act = (K - i0 < (int64_t)chunk) ? (int)(K - i0) : chunk;
     float2 v[V];
-    float pend_max = 0.f;      // result of the previous FFT, written one barrier later (thread 0 only)
-    int64_t pend_i = -1;
 
-    for (int64_t it = 0; it < chunk; ++it) {
-        const int64_t i = i0 + it;
-        const bool active = i < K;
+    for (int it = 0; it < chunk; ++it) {
+        const bool active = it < n_act;
         bool ok = false;
-        if (active) ok = loader.load(v, t, i);
+        if (active) ok = loader.load(v, t, i0 + it, smem_raw);
         if (!ok) {
 #pragma unroll
             for (int j = 0; j < V; ++j) v[j] = make_float2(0.f, 0.f);
@@ -80,19 +82,19 @@ __global__ void __launch_bounds__(PL::TG* B) fused_fft_kernel(Loader loader, Fus
         // iteration's bin-minimum atomics before thread 0 reads them below
         block_fft<PL>(v, th, buf, t, bar);
         if (PL::P == 1) bar();
-        if (t == 0 && pend_i >= 0) {
+        if (t == 0 && it > 0 && it <= n_act) {     // results of the previous FFT
             const unsigned int b = *binmin;
             *binmin = 0xffffffffu;
-            if (out.qf2) out.qf2[pend_i] = pend_max;
-            if (out.fidx) out.fidx[pend_i] = (b == 0xffffffffu) ? 0u : b;
-            pend_i = -1;
+            if (out.qf2) out.qf2[i0 + it - 1] = *pend;
+            if (out.fidx) out.fidx[i0 + it - 1] = (b == 0xffffffffu) ? 0u : b;
         }
-        const float denom_e = (active && ok) ? out.energy[i] : 1.f;
-        if (out.caf) {
+        if (GENERAL && out.caf) {
             // ---- CAF row: write all bins (natural order) ----
             if (active) {
+                const float refn = *out.refnormsq;
+                const float denom_e = ok ? out.energy[i0 + it] : 1.f;
                 if (out.caf_complex) {
-                    float2* row = reinterpret_cast<float2*>(out.caf) + (size_t)i * PL::N;
+                    float2* row = reinterpret_cast<float2*>(out.caf) + (size_t)(i0 + it) * PL::N;
                     const float sc = ok ? 1.f / (sqrtf(refn) * sqrtf(denom_e)) : 0.f;
 #pragma unroll
                     for (int q = 0; q < V / PL::RL; ++q)
@@ -102,7 +104,7 @@ __global__ void __launch_bounds__(PL::TG* B) fused_fft_kernel(Loader loader, Fus
                             row[output_bin<PL>(t, q, j)] = make_float2(x.x * sc, x.y * sc);
                         }
                 } else {
-                    float* row = out.caf + (size_t)i * PL::N;
+                    float* row = out.caf + (size_t)(i0 + it) * PL::N;
 #pragma unroll
                     for (int q = 0; q < V / PL::RL; ++q)
 #pragma unroll
@@ -128,7 +130,7 @@ __global__ void __launch_bounds__(PL::TG* B) fused_fft_kernel(Loader loader, Fus
             for (int w = 1; w < NW; ++w) m = fmaxf(m, wmax[w]);
         }
         unsigned int mybin = 0xffffffffu;
-        if (active && ok && tmax == m) {
+        if (ok && tmax == m) {
 #pragma unroll
             for (int q = 0; q < V / PL::RL; ++q)
 #pragma unroll
@@ -136,48 +138,44 @@ __global__ void __launch_bounds__(PL::TG* B) fused_fft_kernel(Loader loader, Fus
                     if (cnorm2(v[q * PL::RL + j]) == m) mybin = min(mybin, (unsigned int)output_bin<PL>(t, q, j));
             atomicMin(binmin, mybin);
         }
-        if (out.cplx) {   // rare variant: one more barrier to learn the winning bin
+        if (GENERAL && out.cplx) {   // rare variant: one more barrier to learn the winning bin
             bar();
             const unsigned int b = *binmin;
-            if (active && ok && mybin == b) {
-                const float sc = 1.f / (sqrtf(refn) * sqrtf(denom_e));
+            if (ok && mybin == b) {
+                const float sc = 1.f / (sqrtf(*out.refnormsq) * sqrtf(out.energy[i0 + it]));
 #pragma unroll
                 for (int q = 0; q < V / PL::RL; ++q)
 #pragma unroll
                     for (int j = 0; j < PL::RL; ++j)
                         if ((unsigned int)output_bin<PL>(t, q, j) == b) {
                             const float2 x = v[q * PL::RL + j];
-                            out.cplx[i] = make_float2(x.x * sc, x.y * sc);
+                            out.cplx[i0 + it] = make_float2(x.x * sc, x.y * sc);
                         }
             }
-            if (active && !ok && t == 0) out.cplx[i] = make_float2(0.f, 0.f);
+            if (active && !ok && t == 0) out.cplx[i0 + it] = make_float2(0.f, 0.f);
             bar();
         }
-        if (t == 0 && active) {
-            pend_i = i;
-            pend_max = ok ? m / refn / denom_e : 0.f;
-        }
+        if (t == 0 && active) *pend = ok ? m / *out.refnormsq / out.energy[i0 + it] : 0.f;
     }
     bar();
-    if (t == 0 && pend_i >= 0) {
+    if (t == 0 && n_act == chunk && !(GENERAL && out.caf)) {   // the last FFT of a full chunk
         const unsigned int b = *binmin;
-        if (out.qf2) out.qf2[pend_i] = pend_max;
-        if (out.fidx) out.fidx[pend_i] = (b == 0xffffffffu) ? 0u : b;
+        if (out.qf2) out.qf2[i0 + chunk - 1] = *pend;
+        if (out.fidx) out.fidx[i0 + chunk - 1] = (b == 0xffffffffu) ? 0u : b;
     }
 }
 
 template <class PL, int B, class Loader>
-size_t fused_smem_bytes() {
+constexpr size_t fused_smem_bytes() {
     constexpr int NW = (PL::TG + 31) / 32;
-    return Loader::smem_bytes() + sizeof(float2) * (size_t)PL::BUF * B + sizeof(float) * NW * B + sizeof(unsigned int) * B + 16;
+    return Loader::smem_bytes() + sizeof(float2) * (size_t)PL::BUF * B + sizeof(float) * NW * B +
+           sizeof(unsigned int) * B + sizeof(float) * B + 16;
 }
 
-// Launches the fused kernel as a persistent grid: as many CTAs as fit on the device (or fewer when
-// K is small), each group taking `chunk` consecutive shift-list entries.
-template <class PL, int B, class Loader>
-int32_t launch_fused(const Loader& loader, const FusedOut& out, int64_t K, cudaStream_t stream) {
-    auto kern = fused_fft_kernel<PL, B, Loader>;
-    const size_t smem = fused_smem_bytes<PL, B, Loader>();
+template <class PL, int B, class Loader, bool GENERAL>
+int32_t launch_fused_variant(const Loader& loader, const FusedOut& out, int64_t K, cudaStream_t stream) {
+    auto kern = fused_fft_kernel<PL, B, Loader, GENERAL>;
+    constexpr size_t smem = fused_smem_bytes<PL, B, Loader>();
     if ((int)smem > max_smem_optin()) return fail(XC_ERR_UNSUPPORTED, "fused kernel needs %zu B of shared memory", smem);
     static bool configured = false;   // per instantiation
     static int occ = 1;
@@ -187,17 +185,25 @@ int32_t launch_fused(const Loader& loader, const FusedOut& out, int64_t K, cudaS
         if (occ < 1) return fail(XC_ERR_CUDA, "fused kernel does not fit on an SM (smem %zu B)", smem);
         configured = true;
     }
-    const int64_t groups_needed = K;
-    int64_t max_ctas = (int64_t)sm_count() * occ;
-    int64_t ctas = (groups_needed + B - 1) / B;
+    const int64_t max_ctas = (int64_t)sm_count() * occ;
+    int64_t ctas = (K + B - 1) / B;
     if (ctas > max_ctas) ctas = max_ctas;
     if (ctas < 1) ctas = 1;
     const int64_t chunk = (K + ctas * B - 1) / (ctas * B);
+    if (chunk >= (1ll << 31)) return fail(XC_ERR_UNSUPPORTED, "too many shifts per thread group");
     profile_begin(stream);
-    kern<<<(unsigned)ctas, PL::TG * B, smem, stream>>>(loader, out, K, chunk);
+    kern<<<(unsigned)ctas, PL::TG * B, smem, stream>>>(loader, out, K, (int)chunk);
     profile_end(stream);
     XC_LAUNCH_CHECK();
     return XC_OK;
+}
+
+// Launches the fused kernel as a persistent grid: as many CTAs as fit on the device (or fewer when
+// K is small), each group taking `chunk` consecutive shift-list entries.
+template <class PL, int B, class Loader>
+int32_t launch_fused(const Loader& loader, const FusedOut& out, int64_t K, cudaStream_t stream) {
+    if (out.caf || out.cplx) return launch_fused_variant<PL, B, Loader, true>(loader, out, K, stream);
+    return launch_fused_variant<PL, B, Loader, false>(loader, out, K, stream);
 }
 
 }  // namespace xc

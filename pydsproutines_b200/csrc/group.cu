@@ -38,15 +38,15 @@ struct GroupLoader {
     const int32_t* ell_off;
     const int32_t* slot_base_g;   // global [V + 1]
     int64_t lo, hi;               // valid shifts satisfy s + lo >= 0 and s + hi <= rxlen
-    int32_t* slot_base;           // shared copy
 
     __host__ __device__ static constexpr size_t smem_bytes() { return ((sizeof(int32_t) * (PL::V + 1) + 15) / 16) * 16; }
 
-    __device__ __forceinline__ void prepare(int tid, int nthreads, unsigned char* smem) {
-        slot_base = reinterpret_cast<int32_t*>(smem);
+    __device__ __forceinline__ void prepare(int tid, int nthreads, unsigned char* smem) const {
+        int32_t* slot_base = reinterpret_cast<int32_t*>(smem);
         for (int i = tid; i <= PL::V; i += nthreads) slot_base[i] = slot_base_g[i];
     }
-    __device__ __forceinline__ bool load(float2* v, int t, int64_t i) const {
+    __device__ __forceinline__ bool load(float2* v, int t, int64_t i, const unsigned char* smem) const {
+        const int32_t* slot_base = reinterpret_cast<const int32_t*>(smem);
         const int64_t s = shifts ? shifts[i] : shift0 + i * step;
         if (s + lo < 0 || s + hi > rxlen) return false;
         const float2* x = rx + s;
@@ -146,7 +146,7 @@ struct GroupRunner {
         using PF = PlanFor<LOG2N>;
         using LD = GroupLoader<typename PF::PL>;
         LD ld{rx, rxlen, sl.shift0, sl.step, sl.shifts, h->d_ell_y, h->d_ell_off, h->d_slot_base,
-              h->min_start, h->span, nullptr};
+              h->min_start, h->span};
         return launch_fused<typename PF::PL, PF::B, LD>(ld, out, sl.K, stream);
     }
 };

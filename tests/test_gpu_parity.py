@@ -123,7 +123,8 @@ def test_fastxcorr_every_power_of_two_vs_oracle(xr, log2n):
     q, f = xr.fastXcorr(cutout, rx, freqsearch=True)
     assert_qf2(q, qr)
     assert_bins(f, fr, lambda i: _spec64(cutout, rx, i))
-    if N >= 8:
+    assert int(np.argmax(q)) == int(np.argmax(qr))
+    if N >= 64:      # below that a noise window can beat the planted copy
         assert int(np.argmax(q)) == p0 and int(f[p0]) == k0 % N
     assert_qf2(xr.fastXcorr(cutout, rx), orc.fastXcorr(cutout, rx))
 
@@ -281,9 +282,11 @@ def test_multitemplate_dot_vs_oracle():
         ti, q = ce.multiTemplateSlidingDotProduct(x, templates.conj().copy(), 0, K)
         assert ti.dtype == np.int32 and q.dtype == np.float32
         assert_qf2(q, q_ref)
-        bad = np.nonzero(ti != ti_ref)[0]
-        assert bad.size <= K // 100
-        assert int(np.argmax(q)) == n // 3 and ti[n // 3] == T - 1
+        if L > 1:        # with L == 1 every template gives QF^2 == 1: the index is decided by rounding
+            bad = np.nonzero(ti != ti_ref)[0]
+            assert bad.size <= K // 100
+        if L > 1:
+            assert int(np.argmax(q)) == n // 3 and ti[n // 3] == T - 1
         ti2, q2 = ce.multiTemplateSlidingDotProduct(_dev(x), _dev(templates.conj()), 7, K - 11)
         assert np.array_equal(ti2.cpu().numpy(), ti[7:K - 4]) and np.allclose(q2.cpu().numpy(), q[7:K - 4], rtol=1e-6)
     with pytest.raises(ValueError):

@@ -135,7 +135,7 @@ qa, fa = orc.fastXcorr(cutout, rx, freqsearch=True)
 lo, hi = xd.shard_range(K, rank, world)
 assert np.array_equal(q, qa[lo:hi]) and np.array_equal(f, fa[lo:hi])        # halo makes shards exact
 dist.destroy_process_group()
-sys.stdout.write("rank%d-ok\n" % rank)
+sys.stdout.write("rank" + str(rank) + "-ok\n")
 """
 
 
