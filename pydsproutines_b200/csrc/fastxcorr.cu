@@ -32,7 +32,8 @@ struct CutoutLoader {
             }
         }
     }
-    __device__ __forceinline__ bool load(float2* v, int t, int64_t i, const unsigned char* smem) const {
+    // global loads of the window of shift-list entry i (false when it leaves rx)
+    __device__ __forceinline__ bool issue(float2* v, int t, int64_t i, const unsigned char*) const {
         const int64_t s = shifts ? shifts[i] : shift0 + i * step;
         if (s < 0 || s + PL::N > rxlen) return false;
         const float2* x = rx + s + t;
@@ -41,13 +42,21 @@ struct CutoutLoader {
         for (int n1 = 0; n1 < PL::R1; ++n1)
 #pragma unroll
             for (int q = 0; q < NQ; ++q) v[q * PL::R1 + n1] = __ldg(x + input_index<PL>(0, q, n1));
+        return true;
+    }
+    // product with conj(cutout)
+    __device__ __forceinline__ void finish(float2* v, int t, const unsigned char* smem) const {
+        constexpr int NQ = PL::V / PL::R1;
         if (CUT_SMEM) {
             const float2* cc = reinterpret_cast<const float2*>(smem) + t;
 #pragma unroll
-            for (int n1 = 0; n1 < PL::R1; ++n1)
+            for (int n1 = 0; n1 < PL::R1; ++n1) {
 #pragma unroll
                 for (int q = 0; q < NQ; ++q)
                     v[q * PL::R1 + n1] = cmul(v[q * PL::R1 + n1], cc[input_index<PL>(0, q, n1)]);
+                // at most 8 cutout values in flight: the 32 points already fill half the register file
+                if (((n1 + 1) * NQ) % 8 == 0) asm volatile("" ::: "memory");
+            }
         } else {
             const float2* cg = cutout + t;
 #pragma unroll
@@ -56,6 +65,10 @@ struct CutoutLoader {
                 for (int q = 0; q < NQ; ++q)
                     v[q * PL::R1 + n1] = cmulc(v[q * PL::R1 + n1], __ldg(cg + input_index<PL>(0, q, n1)));
         }
+    }
+    __device__ __forceinline__ bool load(float2* v, int t, int64_t i, const unsigned char* smem) const {
+        if (!issue(v, t, i, smem)) return false;
+        finish(v, t, smem);
         return true;
     }
 };

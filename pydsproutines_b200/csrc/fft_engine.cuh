@@ -116,26 +116,47 @@ struct FftPlan {
     static constexpr int M1 = N / R1_;
     static constexpr int M2 = M1 / R2_;
     static constexpr int LOG2RL = ilog2(RL);
-    static constexpr int BUF = (P == 1) ? 0 : N + (N >> LOG2RL);   // float2 cells per FFT buffer
+    // exchange buffer: cell a*RL + b (b < RL) lives at a*ROW + b.  ROW = RL + 2 keeps every row 16-byte
+    // aligned (LDS.128 in the last pass) and its 16-byte pitch odd (conflict-free across lanes).
+    static constexpr int ROW = RL + 2;
+    static constexpr int BUF = (P == 1) ? 0 : (N / RL) * ROW;            // float2 cells per FFT buffer
+    // twiddle tables shared by all groups of a CTA (three-pass plans): W_N^c for the M1 columns of
+    // pass 1 (base of a per-FFT power chain) and the full R2 x M2 table W_M1^(d*k2) of pass 2.
+    static constexpr int T1_CELLS = (P == 3) ? M1 : 0;
+    static constexpr int T2_ROW = R2_ + 2;
+    static constexpr int T2_CELLS = (P == 3) ? M2 * T2_ROW : 0;
+    static constexpr size_t TABLE_BYTES = sizeof(float2) * (size_t)(T1_CELLS + T2_CELLS);
+    // second exchange stays inside one warp when every thread owns one radix-32 column in passes 2 and 3
+    static constexpr bool WARP_LOCAL_X2 = (P == 3) && R2_ == 32 && R3_ == 32 && V == 32;
     static_assert(R1_ * R2_ * R3_ == N, "radices must multiply to N");
     static_assert(V % R1_ == 0 && V % R2_ == 0 && V % R3_ == 0, "each pass must fill the registers");
     static_assert(R1_ <= 32 && R2_ <= 32 && R3_ <= 32, "codelets go up to radix 32");
     static_assert(R3_ == 1 || (TG_ % R3_ == 0 && TG_ % R2_ == 0), "three-pass plans need TG to be a multiple of R2 and R3");
     static_assert(R3_ > 1 || R2_ == 1 || TG_ * (N / TG_ / R1_) == R2_, "two-pass plans: the columns of pass 1 are the R2 points");
-    __device__ static __forceinline__ int phys(int i) { return i + (i >> LOG2RL); }
+    static_assert(P == 1 || RL % 2 == 0, "LDS.128 of the last pass needs an even radix");
 };
 
-// Per-thread constants of a plan: base twiddles of the two exchanges.
+// Fills the CTA-wide twiddle tables (call once per CTA, before a __syncthreads()).
+template <class PL>
+__device__ __forceinline__ void build_fft_tables(float2* tab, int tid, int nthreads) {
+    if (PL::P != 3) return;
+    for (int c = tid; c < PL::T1_CELLS; c += nthreads) tab[c] = unit_root(c, PL::N);
+    for (int i = tid; i < PL::M2 * PL::R2; i += nthreads) {
+        const int d = i / PL::R2, k2 = i % PL::R2;
+        tab[PL::T1_CELLS + d * PL::T2_ROW + k2] = unit_root((d * k2) % PL::M1, PL::M1);
+    }
+}
+
+// Per-thread constants of a plan (two-pass plans keep the base twiddles of their one exchange here;
+// three-pass plans read theirs from the shared tables and keep nothing).
 template <class PL>
 struct FftThread {
-    float2 tw1[PL::V / PL::R1];                       // W_N^(t + TG*q)
-    float2 tw2;                                       // W_M1^(t % M2)  (TG is a multiple of M2, so q drops out)
+    float2 tw1[(PL::P == 2) ? PL::V / PL::R1 : 1];    // W_N^(t + TG*q)
     __device__ __forceinline__ void init(int t) {
-        if (PL::P >= 2) {
+        if (PL::P == 2) {
 #pragma unroll
             for (int q = 0; q < PL::V / PL::R1; ++q) tw1[q] = unit_root(t + PL::TG * q, PL::N);
         }
-        if (PL::P == 3) tw2 = unit_root(t % PL::M2, PL::M1);
     }
 };
 
@@ -165,14 +186,14 @@ __device__ __forceinline__ int output_bin(int t, int q, int j) {
 }
 
 // Runs the forward FFT on the V points the thread loaded according to input_index(); on return the
-// registers hold the bins given by output_bin().  `buf` is the group's padded exchange buffer and
-// BAR() a barrier over the TG threads of the group.  The caller must guarantee (with BAR) that the
-// previous user of `buf` is done before calling.
-// All shared-memory addresses are (per-thread base) + (compile-time constant): with ROW = RL + 1 the
-// padded position of cell  a*RL + b  (b < RL)  is  a*ROW + b.
+// registers hold the bins given by output_bin().  `buf` is the group's exchange buffer, `tab` the CTA's
+// twiddle tables and BAR() a barrier over the TG threads of the group.  The caller must guarantee
+// (with BAR) that the previous user of `buf` is done before calling.
+// All shared-memory addresses are (per-thread base) + (compile-time constant).
 template <class PL, class Bar>
-__device__ __forceinline__ void block_fft(float2* v, const FftThread<PL>& th, float2* buf, int t, Bar bar) {
-    constexpr int RL = PL::RL, ROW = RL + 1;
+__device__ __forceinline__ void block_fft(float2* v, const FftThread<PL>& th, const float2* tab, float2* buf, int t,
+                                          Bar bar) {
+    constexpr int RL = PL::RL, ROW = PL::ROW;
     // ---- pass 1 ----
 #pragma unroll
     for (int q = 0; q < PL::V / PL::R1; ++q) dif_fft<PL::R1>(v + q * PL::R1);
@@ -184,7 +205,8 @@ __device__ __forceinline__ void block_fft(float2* v, const FftThread<PL>& th, fl
         float2* const b1 = buf + ((PL::P == 2) ? t : (t / RL) * ROW + (t % RL));
 #pragma unroll
         for (int q = 0; q < PL::V / PL::R1; ++q) {
-            twiddle_powers<PL::R1>(v + q * PL::R1, th.tw1[q]);
+            const float2 w = (PL::P == 2) ? th.tw1[q] : tab[t + PL::TG * q];
+            twiddle_powers<PL::R1>(v + q * PL::R1, w);
 #pragma unroll
             for (int j = 0; j < PL::R1; ++j) b1[bitrev(j, ilog2(PL::R1)) * K1STEP + q * QSTEP] = v[q * PL::R1 + j];
         }
@@ -195,6 +217,7 @@ __device__ __forceinline__ void block_fft(float2* v, const FftThread<PL>& th, fl
         constexpr int K1STEP = (PL::M1 / RL) * ROW;
         constexpr int QSTEP = (PL::TG / PL::M2) * K1STEP;
         float2* const b2 = buf + (t / PL::M2) * K1STEP + (t % PL::M2);
+        const float4* const t2 = reinterpret_cast<const float4*>(tab + PL::T1_CELLS + (t % PL::M2) * PL::T2_ROW);
 #pragma unroll
         for (int q = 0; q < PL::V / PL::R2; ++q)
 #pragma unroll
@@ -202,19 +225,34 @@ __device__ __forceinline__ void block_fft(float2* v, const FftThread<PL>& th, fl
 #pragma unroll
         for (int q = 0; q < PL::V / PL::R2; ++q) {
             dif_fft<PL::R2>(v + q * PL::R2);
-            twiddle_powers<PL::R2>(v + q * PL::R2, th.tw2);
+            // twiddles W_M1^(d*k2) from the table, two per 16-byte load (k2 = 2m, 2m+1)
+#pragma unroll
+            for (int m = 0; m < PL::R2 / 2; ++m) {
+                const float4 w = t2[m];
+                const int j0 = bitrev(2 * m, ilog2(PL::R2)), j1 = bitrev(2 * m + 1, ilog2(PL::R2));
+                if (m > 0) v[q * PL::R2 + j0] = cmul(v[q * PL::R2 + j0], make_float2(w.x, w.y));
+                v[q * PL::R2 + j1] = cmul(v[q * PL::R2 + j1], make_float2(w.z, w.w));
+            }
 #pragma unroll
             for (int j = 0; j < PL::R2; ++j) b2[q * QSTEP + bitrev(j, ilog2(PL::R2)) * ROW] = v[q * PL::R2 + j];
         }
-        bar();
+        if (PL::WARP_LOCAL_X2) {
+            __syncwarp();   // the 32 rows a warp wrote are exactly the 32 rows it reads next
+        } else {
+            bar();
+        }
     }
-    // ---- last pass: cell f*RL + d, f = t + TG*q ----
+    // ---- last pass: cell f*RL + d, f = t + TG*q; rows are 16-byte aligned ----
     {
-        const float2* const b3 = buf + t * ROW;
+        const float4* const b3 = reinterpret_cast<const float4*>(buf + t * ROW);
 #pragma unroll
         for (int q = 0; q < PL::V / RL; ++q)
 #pragma unroll
-            for (int d = 0; d < RL; ++d) v[q * RL + d] = b3[q * PL::TG * ROW + d];
+            for (int d2 = 0; d2 < RL / 2; ++d2) {
+                const float4 x = b3[(q * PL::TG * ROW) / 2 + d2];
+                v[q * RL + 2 * d2] = make_float2(x.x, x.y);
+                v[q * RL + 2 * d2 + 1] = make_float2(x.z, x.w);
+            }
     }
 #pragma unroll
     for (int q = 0; q < PL::V / RL; ++q) dif_fft<RL>(v + q * RL);

@@ -46,13 +46,16 @@ __global__ void __launch_bounds__(PL::TG* B) fused_fft_kernel(const Loader loade
                                                               const int chunk) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int TG = PL::TG, V = PL::V, NW = (TG + 31) / 32;
-    constexpr size_t OFF_BUF = Loader::smem_bytes();
+    constexpr size_t OFF_TAB = Loader::smem_bytes();
+    constexpr size_t OFF_BUF = OFF_TAB + PL::TABLE_BYTES;
     constexpr size_t OFF_WMAX = OFF_BUF + sizeof(float2) * (size_t)PL::BUF * B;
     constexpr size_t OFF_BIN = OFF_WMAX + sizeof(float) * NW * B;
     constexpr size_t OFF_PEND = OFF_BIN + sizeof(unsigned int) * B;     // B floats: pending QF^2 of the previous FFT
     const int g = threadIdx.x / TG;       // group within the CTA
     const int t = threadIdx.x % TG;       // thread within the group
     loader.prepare(threadIdx.x, TG * B, smem_raw);
+    const float2* const tab = reinterpret_cast<const float2*>(smem_raw + OFF_TAB);
+    build_fft_tables<PL>(reinterpret_cast<float2*>(smem_raw + OFF_TAB), threadIdx.x, TG * B);
     float2* const buf = reinterpret_cast<float2*>(smem_raw + OFF_BUF) + (size_t)g * PL::BUF;
     float* const wmax = reinterpret_cast<float*>(smem_raw + OFF_WMAX) + g * NW;
     unsigned int* const binmin = reinterpret_cast<unsigned int*>(smem_raw + OFF_BIN) + g;
@@ -80,7 +83,7 @@ __global__ void __launch_bounds__(PL::TG* B) fused_fft_kernel(const Loader loade
         }
         // block FFT; the barrier inside (after the pass-1 stores) also orders the previous
         // iteration's bin-minimum atomics before thread 0 reads them below
-        block_fft<PL>(v, th, buf, t, bar);
+        block_fft<PL>(v, th, tab, buf, t, bar);
         if (PL::P == 1) bar();
         if (t == 0 && it > 0 && it <= n_act) {     // results of the previous FFT
             const unsigned int b = *binmin;
@@ -168,7 +171,7 @@ __global__ void __launch_bounds__(PL::TG* B) fused_fft_kernel(const Loader loade
 template <class PL, int B, class Loader>
 constexpr size_t fused_smem_bytes() {
     constexpr int NW = (PL::TG + 31) / 32;
-    return Loader::smem_bytes() + sizeof(float2) * (size_t)PL::BUF * B + sizeof(float) * NW * B +
+    return Loader::smem_bytes() + PL::TABLE_BYTES + sizeof(float2) * (size_t)PL::BUF * B + sizeof(float) * NW * B +
            sizeof(unsigned int) * B + sizeof(float) * B + 16;
 }
 

@@ -45,6 +45,10 @@ struct GroupLoader {
         int32_t* slot_base = reinterpret_cast<int32_t*>(smem);
         for (int i = tid; i <= PL::V; i += nthreads) slot_base[i] = slot_base_g[i];
     }
+    __device__ __forceinline__ bool issue(float2* v, int t, int64_t i, const unsigned char* smem) const {
+        return load(v, t, i, smem);
+    }
+    __device__ __forceinline__ void finish(float2*, int, const unsigned char*) const {}
     __device__ __forceinline__ bool load(float2* v, int t, int64_t i, const unsigned char* smem) const {
         const int32_t* slot_base = reinterpret_cast<const int32_t*>(smem);
         const int64_t s = shifts ? shifts[i] : shift0 + i * step;
