@@ -80,6 +80,53 @@ __device__ __forceinline__ float2 cmulc(float2 a, float2 b) {
 }
 __device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
 __device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+
+// ---------------------------------------------------------------------------------------------
+// packed FP32 (sm_100a FFMA2 / FADD2 / FMUL2): one instruction works on both halves of an aligned
+// register pair, i.e. on one interleaved complex value.  Measured on B200 (tools/ubench/f32x2.cu):
+// 2 warp-instructions/clk/SM = the full 128 FP32 lanes at half the issue slots; the half swap,
+// per-half negation and scalar broadcast of an operand are free operand modifiers in SASS, so
+// ptxas folds the make_float2() shuffles below into the arithmetic instruction.
+// ---------------------------------------------------------------------------------------------
+typedef unsigned long long u64;
+__device__ __forceinline__ u64 f2u(float2 a) {
+    u64 r;
+    asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(a.x), "f"(a.y));
+    return r;
+}
+__device__ __forceinline__ float2 u2f(u64 r) {
+    float2 v;
+    asm("mov.b64 {%0,%1}, %2;" : "=f"(v.x), "=f"(v.y) : "l"(r));
+    return v;
+}
+__device__ __forceinline__ float2 padd(float2 a, float2 b) {
+    u64 d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(f2u(a)), "l"(f2u(b)));
+    return u2f(d);
+}
+__device__ __forceinline__ float2 psub(float2 a, float2 b) {
+    u64 d;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(f2u(a)), "l"(f2u(b)));
+    return u2f(d);
+}
+__device__ __forceinline__ float2 pmul(float2 a, float2 b) {
+    u64 d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(f2u(a)), "l"(f2u(b)));
+    return u2f(d);
+}
+__device__ __forceinline__ float2 pfma(float2 a, float2 b, float2 c) {
+    u64 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(f2u(a)), "l"(f2u(b)), "l"(f2u(c)));
+    return u2f(d);
+}
+// a * b in two packed instructions
+__device__ __forceinline__ float2 pcmul(float2 a, float2 b) {
+    return pfma(make_float2(a.y, a.x), make_float2(-b.y, b.y), pmul(a, make_float2(b.x, b.x)));
+}
+// a * conj(b)
+__device__ __forceinline__ float2 pcmulc(float2 a, float2 b) {
+    return pfma(make_float2(a.y, a.x), make_float2(b.y, -b.y), pmul(a, make_float2(b.x, b.x)));
+}
 __device__ __forceinline__ float cnorm2(float2 a) { return fmaf(a.x, a.x, a.y * a.y); }
 
 // per-call peak reduction record kept on the device: packs (value, index) so that a single

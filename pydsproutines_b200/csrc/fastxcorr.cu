@@ -53,7 +53,7 @@ struct CutoutLoader {
             for (int n1 = 0; n1 < PL::R1; ++n1) {
 #pragma unroll
                 for (int q = 0; q < NQ; ++q)
-                    v[q * PL::R1 + n1] = cmul(v[q * PL::R1 + n1], cc[input_index<PL>(0, q, n1)]);
+                    v[q * PL::R1 + n1] = pcmul(v[q * PL::R1 + n1], cc[input_index<PL>(0, q, n1)]);
                 // at most 8 cutout values in flight: the 32 points already fill half the register file
                 if (((n1 + 1) * NQ) % 8 == 0) asm volatile("" ::: "memory");
             }
@@ -63,7 +63,7 @@ struct CutoutLoader {
             for (int n1 = 0; n1 < PL::R1; ++n1)
 #pragma unroll
                 for (int q = 0; q < NQ; ++q)
-                    v[q * PL::R1 + n1] = cmulc(v[q * PL::R1 + n1], __ldg(cg + input_index<PL>(0, q, n1)));
+                    v[q * PL::R1 + n1] = pcmulc(v[q * PL::R1 + n1], __ldg(cg + input_index<PL>(0, q, n1)));
         }
     }
     __device__ __forceinline__ bool load(float2* v, int t, int64_t i, const unsigned char* smem) const {

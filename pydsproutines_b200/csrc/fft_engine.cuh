@@ -27,60 +27,62 @@ __host__ __device__ constexpr int bitrev(int v, int bits) {
     return r;
 }
 
-// d * exp(-2*pi*i*idx/32), idx in [0, 32); idx is a compile-time constant after unrolling, so the
-// branches fold away and the general case becomes 2 FMUL + 2 FFMA with immediate operands.
-__device__ __forceinline__ float2 mul_w32(float2 d, int idx) {
-    // cos(2*pi*k/32), k = 1..7
-    constexpr float C1 = 0.98078528040323044913f, C2 = 0.92387953251128675613f,
-                    C3 = 0.83146961230254523708f, C4 = 0.70710678118654752440f,
-                    C5 = 0.55557023301960222474f, C6 = 0.38268343236508977173f,
-                    C7 = 0.19509032201612826785f;
-    idx &= 31;
-    if (idx >= 16) {  // W^(idx) = -W^(idx-16)
-        d = make_float2(-d.x, -d.y);
-        idx -= 16;
+// One decimation-in-time butterfly (u, v) <- (u + w v, u - w v), w = exp(-2*pi*i*idx/32), idx in [0, 16),
+// in packed FP32: two instructions for w = 1 and w = -i (the half swap and the sign are operand
+// modifiers), three otherwise: S = u + w v by two FFMA2, then u - w v = 2u - S by one more.
+// idx is a compile-time constant after unrolling.
+__device__ __forceinline__ void dit_butterfly(float2& u, float2& v, int idx) {
+    // cos(2*pi*k/32), k = 0..8
+    constexpr float C[9] = {1.f,
+                            0.98078528040323044913f,
+                            0.92387953251128675613f,
+                            0.83146961230254523708f,
+                            0.70710678118654752440f,
+                            0.55557023301960222474f,
+                            0.38268343236508977173f,
+                            0.19509032201612826785f,
+                            0.f};
+    if (idx == 0) {
+        const float2 s = padd(u, v);
+        v = psub(u, v);
+        u = s;
+        return;
     }
-    float c = 0.f, s = 0.f;  // W = c - i*s
-    switch (idx) {
-        case 0: return d;
-        case 8: return make_float2(d.y, -d.x);
-        case 4: return make_float2((d.x + d.y) * C4, (d.y - d.x) * C4);
-        case 12: return make_float2((d.y - d.x) * C4, -(d.x + d.y) * C4);
-        case 1: c = C1; s = C7; break;
-        case 2: c = C2; s = C6; break;
-        case 3: c = C3; s = C5; break;
-        case 5: c = C5; s = C3; break;
-        case 6: c = C6; s = C2; break;
-        case 7: c = C7; s = C1; break;
-        case 9: c = -C7; s = C1; break;
-        case 10: c = -C6; s = C2; break;
-        case 11: c = -C5; s = C3; break;
-        case 13: c = -C3; s = C5; break;
-        case 14: c = -C2; s = C6; break;
-        default: c = -C1; s = C7; break;  // 15
+    if (idx == 8) {   // w = -i: w v = (v.y, -v.x)
+        const float2 r = make_float2(v.y, -v.x);
+        const float2 s = padd(u, r);
+        v = psub(u, r);
+        u = s;
+        return;
     }
-    return make_float2(fmaf(d.x, c, d.y * s), fmaf(d.y, c, -d.x * s));
+    const float c = (idx <= 8) ? C[idx] : -C[16 - idx];   // w = c - i*s
+    const float s = (idx <= 8) ? C[8 - idx] : C[idx - 8];
+    // w v = (c v.x + s v.y, c v.y - s v.x)
+    float2 S = pfma(v, make_float2(c, c), u);
+    S = pfma(make_float2(v.y, v.x), make_float2(s, -s), S);
+    v = pfma(u, make_float2(2.f, 2.f), make_float2(-S.x, -S.y));
+    u = S;
 }
 
-// In-register forward DFT of R points (R = 2,4,8,16,32), decimation in frequency.
-// On return a[j] holds X[bitrev(j, log2 R)].
+// In-register forward DFT of R points (R = 2,4,8,16,32): natural-order input, a[j] holds X[bitrev(j, log2 R)]
+// on return.  Decimation in time on the virtual array b[i] = a[bitrev(i)] (so its bit-reversed input
+// order is the natural order of a); all index arithmetic folds at compile time.
+// 194 packed instructions for R = 32, 26 for R = 8.
 template <int R>
-__device__ __forceinline__ void dif_fft(float2* a) {
+__device__ __forceinline__ void codelet_fft(float2* a) {
+    constexpr int LG = ilog2(R);
 #pragma unroll
-    for (int h = R / 2; h >= 1; h >>= 1) {
+    for (int h = 1; h < R; h <<= 1) {
 #pragma unroll
         for (int blk = 0; blk < R; blk += 2 * h) {
 #pragma unroll
-            for (int j = 0; j < h; ++j) {
-                const float2 u = a[blk + j], v = a[blk + j + h];
-                a[blk + j] = cadd(u, v);
-                a[blk + j + h] = mul_w32(csub(u, v), j * (16 / h));
-            }
+            for (int j = 0; j < h; ++j)
+                dit_butterfly(a[bitrev(blk + j, LG)], a[bitrev(blk + j + h, LG)], j * (16 / h));
         }
     }
 }
 template <>
-__device__ __forceinline__ void dif_fft<1>(float2*) {}
+__device__ __forceinline__ void codelet_fft<1>(float2*) {}
 
 // multiply the bit-reversed outputs of a codelet by successive powers of w: a[bitrev(k)] *= w^k
 template <int R>
@@ -89,8 +91,8 @@ __device__ __forceinline__ void twiddle_powers(float2* a, float2 w) {
 #pragma unroll
     for (int k = 1; k < R; ++k) {
         const int j = bitrev(k, ilog2(R));
-        a[j] = cmul(a[j], p);
-        if (k + 1 < R) p = cmul(p, w);
+        a[j] = pcmul(a[j], p);
+        if (k + 1 < R) p = pcmul(p, w);
     }
 }
 
@@ -196,7 +198,7 @@ __device__ __forceinline__ void block_fft(float2* v, const FftThread<PL>& th, co
     constexpr int RL = PL::RL, ROW = PL::ROW;
     // ---- pass 1 ----
 #pragma unroll
-    for (int q = 0; q < PL::V / PL::R1; ++q) dif_fft<PL::R1>(v + q * PL::R1);
+    for (int q = 0; q < PL::V / PL::R1; ++q) codelet_fft<PL::R1>(v + q * PL::R1);
     if (PL::P == 1) return;
     {
         // cell k1*M1 + c, c = t + TG*q.  P == 2: M1 == RL and c < RL.  P == 3: M1 and TG are multiples of RL.
@@ -224,14 +226,14 @@ __device__ __forceinline__ void block_fft(float2* v, const FftThread<PL>& th, co
             for (int n2 = 0; n2 < PL::R2; ++n2) v[q * PL::R2 + n2] = b2[q * QSTEP + n2 * ROW];
 #pragma unroll
         for (int q = 0; q < PL::V / PL::R2; ++q) {
-            dif_fft<PL::R2>(v + q * PL::R2);
+            codelet_fft<PL::R2>(v + q * PL::R2);
             // twiddles W_M1^(d*k2) from the table, two per 16-byte load (k2 = 2m, 2m+1)
 #pragma unroll
             for (int m = 0; m < PL::R2 / 2; ++m) {
                 const float4 w = t2[m];
                 const int j0 = bitrev(2 * m, ilog2(PL::R2)), j1 = bitrev(2 * m + 1, ilog2(PL::R2));
-                if (m > 0) v[q * PL::R2 + j0] = cmul(v[q * PL::R2 + j0], make_float2(w.x, w.y));
-                v[q * PL::R2 + j1] = cmul(v[q * PL::R2 + j1], make_float2(w.z, w.w));
+                if (m > 0) v[q * PL::R2 + j0] = pcmul(v[q * PL::R2 + j0], make_float2(w.x, w.y));
+                v[q * PL::R2 + j1] = pcmul(v[q * PL::R2 + j1], make_float2(w.z, w.w));
             }
 #pragma unroll
             for (int j = 0; j < PL::R2; ++j) b2[q * QSTEP + bitrev(j, ilog2(PL::R2)) * ROW] = v[q * PL::R2 + j];
@@ -255,7 +257,7 @@ __device__ __forceinline__ void block_fft(float2* v, const FftThread<PL>& th, co
             }
     }
 #pragma unroll
-    for (int q = 0; q < PL::V / RL; ++q) dif_fft<RL>(v + q * RL);
+    for (int q = 0; q < PL::V / RL; ++q) codelet_fft<RL>(v + q * RL);
 }
 
 }  // namespace xc

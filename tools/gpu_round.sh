@@ -1,0 +1,22 @@
+#!/bin/bash
+# One GPU-box visit: parity tests, bench (both arms), per-config timings, ncu launch list + full capture.
+# usage: tools/gpu_round.sh <tag>     (outputs under gpurun_out/<tag>_*)
+tag=${1:-run}
+mkdir -p gpurun_out
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/${tag}_smi.txt 2>&1
+timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/${tag}_pytest.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/${tag}_pytest.log
+tail -3 gpurun_out/${tag}_pytest.log
+timeout 600 python bench.py --steps 10 --warmup 3 > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench rc=$?"
+cat gpurun_out/${tag}_bench.json
+timeout 600 python tools/bench_configs.py c1 c3 c4 > gpurun_out/${tag}_configs.jsonl 2> gpurun_out/${tag}_configs.err; echo "configs rc=$?"
+cat gpurun_out/${tag}_configs.jsonl
+if [ -z "$SKIP_NCU" ]; then
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${tag}_launches.csv \
+   python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/${tag}_ncu_launch.log 2>&1; echo "ncu launches rc=$?"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:fused_fft_kernel -s 3 -c 1 -f -o gpurun_out/${tag}_fused \
+   python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/${tag}_ncu_full.log 2>&1; echo "ncu full rc=$?"
+fi
+if [ -n "$REF_ARM" ]; then
+timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/${tag}_bench_ref.json 2> gpurun_out/${tag}_bench_ref.err; echo "ref rc=$?"
+cat gpurun_out/${tag}_bench_ref.json
+fi
