@@ -33,4 +33,19 @@ int32_t row_argmax_device(const float2* x, int64_t rows, int64_t cols, int use_n
 int32_t local_maxima_device(const float* x, int64_t n, float min_height, int32_t* idx, int32_t cap, int32_t* count,
                             cudaStream_t stream);
 
+// mt_tc.cu -- tensor-core (tcgen05) multi-template correlator
+struct MtTcPlan {
+    int T = 0, L = 0;
+    int L32 = 0;          // template length padded to a multiple of 32 (one pipeline stage = 32 samples)
+    int NT = 0;           // templates per block = UMMA N (multiple of 16, <= 256)
+    int NB = 0;           // template blocks
+    void* d_pack = nullptr;        // BF16 stage images [NB][L32/32][re, im][canonical K-major core matrices]
+    float* d_inv_energy = nullptr; // [NB * NT] 1 / E_t (0 for padding templates)
+    bool usable = false;  // templates exactly representable in BF16 and the tile fits in shared memory
+};
+int32_t mt_tc_prepare(const float2* d_templates, int T, int L, int L8, const float* d_energies, MtTcPlan* plan);
+void mt_tc_release(MtTcPlan* plan);
+int32_t mt_tc_run(const MtTcPlan& plan, const float2* x, int64_t xlen, int64_t start, int64_t K, const float* xenergy,
+                  float* best, int32_t* tidx, int sqrt_out, cudaStream_t stream);
+
 }  // namespace xc

@@ -1,0 +1,347 @@
+// mt_tc.cu -- multi-template sliding correlator on the 5th-generation tensor cores (tcgen05 / TMEM).
+//     d[s, t] = sum_n x[s + n] * tmpl_t[n],   QF^2[s] = max_t |d[s,t]|^2 / E_t / E_x[s],   arg max over t
+// Replaces multiTemplateSlidingDotProduct (multiplySlices.cu:251-399, cupyExtensions.py:563-642) and the
+// returnMax path of TemplateCrossCorrelator.correlate (xcorrRoutines.py:339-371).  This is the one place of
+// the detection path where the work is a dense complex contraction (8 L flops per (template, shift) cell).
+//
+// Formulation (one CTA = one SM, persistent over tiles of 128 consecutive shifts):
+//   * GEMM roles: M = 128 shifts (TMEM lanes), N = up to 256 templates (TMEM columns), K = template samples.
+//     Two FP32 accumulators in TMEM, C_re and C_im, 256 columns each = all 512 columns.
+//       C_re += Xr Tr^T - Xi Ti^T        C_im += Xi Tr^T + Xr Ti^T       (the minus is the A-negate bit)
+//   * precision: templates must be exact in BF16 (any PSK alphabet is); every x plane is split into
+//     BF16 hi + lo, so the products carry 16 mantissa bits of x and the accumulation is FP32: 8 MMAs
+//     (128 x NT x 16) per 16 template samples.  Other template sets take the FP32 SIMT kernel.
+//   * A operand = the Hankel matrix X[s, n] = x[s0 + s + n], never materialised: shared memory holds the
+//     8x-expanded tile E[u][i][j] = x[s0 + 8u + i + j] (one 128-byte core matrix per u), and the core matrix
+//     of (row group a, K chunk b) is E[a + b], so the UMMA descriptor simply uses LBO = SBO = 128 bytes --
+//     overlapping core matrices.  (128 + L) / 8 core matrices per plane: 18 KB for L = 1024.
+//   * B operand = templates, repacked once per handle into stage images in canonical K-major core-matrix
+//     order, streamed by 1-D bulk copies (TMA engine) through a ring of stages, 32 samples per stage.
+//   * warp roles: warps 0-3 build E and run the epilogue (TMEM -> registers, |.|^2 / E_t, running max and
+//     lowest arg max, no cross-thread reduction because a thread owns a shift), warp 4 lane 0 = bulk-copy
+//     producer, warp 5 lane 0 = MMA issuer; smem full/empty and TMEM-full mbarriers.
+#include <vector>
+
+#include "internal.cuh"
+#include "mt_tc.cuh"
+
+namespace xc {
+
+namespace {
+
+constexpr int TC_M = 128;              // shifts per tile
+constexpr int TC_KC = 32;              // template samples per pipeline stage (two K = 16 steps)
+constexpr int TC_THREADS = 192;        // 4 epilogue/builder warps + producer warp + MMA warp
+constexpr int TC_MAX_STAGES = 4;
+constexpr int TC_TMEM_COLS = 512;
+constexpr int TC_MAX_TEMPLATES = 2048; // 1/E_t table in shared memory
+
+__host__ __device__ inline size_t tc_plane_bytes(int L32) { return (size_t)((TC_M + L32) / 8) * 128; }
+__host__ __device__ inline size_t tc_stage_bytes(int NT) { return (size_t)NT * 128; }   // re + im planes of 32 samples
+
+// ---- one-time repack of the templates into stage images; flags inexact BF16 conversions ----
+__global__ void mt_tc_pack_kernel(const float2* __restrict__ templates, int T, int L, int L8, int L32, int NT, int NB,
+                                  __nv_bfloat16* __restrict__ pack, int* __restrict__ inexact) {
+    const int NKC = L32 / TC_KC;
+    const size_t total = (size_t)NB * NKC * 2 * NT * TC_KC;      // bf16 elements
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+        // e = ((((nb * NKC + kc) * 2 + p) * 4 + c8) * (NT / 8) + tg) * 64 + r * 8 + j
+        size_t q = e;
+        const int j = q % 8; q /= 8;
+        const int r = q % 8; q /= 8;
+        const int tg = q % (NT / 8); q /= (NT / 8);
+        const int c8 = q % 4; q /= 4;
+        const int p = q % 2; q /= 2;
+        const int kc = q % NKC; q /= NKC;
+        const int nb = (int)q;
+        const int t = nb * NT + tg * 8 + r;
+        const int n = kc * TC_KC + c8 * 8 + j;
+        float v = 0.f;
+        if (t < T && n < L) {
+            const float2 s = templates[(size_t)t * L8 + n];
+            v = p ? s.y : s.x;
+        }
+        const __nv_bfloat16 b = __float2bfloat16_rn(v);
+        if (__bfloat162float(b) != v) atomicOr(inexact, 1);
+        pack[e] = b;
+    }
+}
+
+__global__ void mt_tc_inv_energy_kernel(const float* __restrict__ energies, int T, int n, float* __restrict__ inv) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) inv[i] = (i < T && energies[i] > 0.f) ? 1.f / energies[i] : 0.f;
+}
+
+
+// shared-memory carve-up (bytes from the 128-byte aligned base)
+struct TcSmem {
+    uint32_t plane, stage, off_stage, off_inv, off_bar, total;
+    int nstages;
+};
+__host__ __device__ inline TcSmem tc_smem_layout(int L32, int NT, int NB, int nstages) {
+    TcSmem m;
+    m.plane = (uint32_t)tc_plane_bytes(L32);
+    m.stage = (uint32_t)tc_stage_bytes(NT);
+    m.nstages = nstages;
+    m.off_stage = 4 * m.plane;
+    m.off_inv = m.off_stage + (uint32_t)nstages * m.stage;
+    m.off_bar = (m.off_inv + (uint32_t)(NB * NT) * 4 + 15) / 16 * 16;
+    m.total = m.off_bar + (2 * TC_MAX_STAGES + 1) * 8 + 16;
+    return m;
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_energy, const int NT, const int NB,
+             const int L32, const int nstages, const float2* __restrict__ x, const int64_t xlen, const int64_t start,
+             const int64_t K, const float* __restrict__ xenergy, float* __restrict__ best_out,
+             int32_t* __restrict__ tidx_out, const int sqrt_out, const int64_t ntiles, const int64_t tiles_per_cta) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const TcSmem lay = tc_smem_layout(L32, NT, NB, nstages);
+    const int NKC = L32 / TC_KC;
+    uint8_t* const sE = smem;
+    float* const sInv = reinterpret_cast<float*>(smem + lay.off_inv);
+    uint64_t* const bars = reinterpret_cast<uint64_t*>(smem + lay.off_bar);
+    const uint32_t bar_full = tc::smem_u32(bars), bar_empty = tc::smem_u32(bars + TC_MAX_STAGES),
+                   bar_tfull = tc::smem_u32(bars + 2 * TC_MAX_STAGES);
+    uint32_t* const tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * TC_MAX_STAGES + 1);
+    const uint32_t sE_u32 = tc::smem_u32(sE), sStage_u32 = tc::smem_u32(smem + lay.off_stage);
+
+    if (tid == 0) {
+        for (int s = 0; s < TC_MAX_STAGES; ++s) {
+            tc::mbar_init(bar_full + 8 * s, 1);
+            tc::mbar_init(bar_empty + 8 * s, 1);
+        }
+        tc::mbar_init(bar_tfull, 1);
+        tc::mbar_fence_init();
+    }
+    if (warp == 0) tc::tmem_alloc(tc::smem_u32(tmem_slot), TC_TMEM_COLS);
+    for (int i = tid; i < NB * NT; i += TC_THREADS) sInv[i] = inv_energy[i];
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    const int64_t tile0 = (int64_t)blockIdx.x * tiles_per_cta;
+    int64_t tile1 = tile0 + tiles_per_cta;
+    if (tile1 > ntiles) tile1 = ntiles;
+    uint32_t it_pipe = 0;      // stage-ring position (producer and MMA thread each advance their own copy)
+    uint32_t it_acc = 0;       // accumulator generations (parity of the TMEM-full barrier)
+    const uint32_t idesc_pos = tc::instr_desc_bf16(TC_M, NT, 0), idesc_neg = tc::instr_desc_bf16(TC_M, NT, 1);
+    const uint32_t b_lbo = (uint32_t)(NT / 8) * 128;
+
+    for (int64_t tile = tile0; tile < tile1; ++tile) {
+        const int64_t s0 = start + tile * TC_M;     // x index of (row 0, n = 0)
+        // ---- expanded x tile: row (u, i) = BF16 hi / lo of x[s0 + 8u + i + j], j = 0..7, for re and im ----
+        {
+            const int rows = (TC_M + L32);          // = 8 U
+            for (int row = tid; row < rows; row += TC_THREADS) {
+                const int64_t g = s0 + row;
+                uint32_t w[4][4];                   // [plane][pair of bf16]
+#pragma unroll
+                for (int jj = 0; jj < 4; ++jj) {
+                    float2 a = make_float2(0.f, 0.f), b = make_float2(0.f, 0.f);
+                    if (g + 2 * jj < xlen) a = __ldg(x + g + 2 * jj);
+                    if (g + 2 * jj + 1 < xlen) b = __ldg(x + g + 2 * jj + 1);
+                    const __nv_bfloat16 arh = __float2bfloat16_rn(a.x), aih = __float2bfloat16_rn(a.y);
+                    const __nv_bfloat16 brh = __float2bfloat16_rn(b.x), bih = __float2bfloat16_rn(b.y);
+                    const __nv_bfloat16 arl = __float2bfloat16_rn(a.x - __bfloat162float(arh));
+                    const __nv_bfloat16 ail = __float2bfloat16_rn(a.y - __bfloat162float(aih));
+                    const __nv_bfloat16 brl = __float2bfloat16_rn(b.x - __bfloat162float(brh));
+                    const __nv_bfloat16 bil = __float2bfloat16_rn(b.y - __bfloat162float(bih));
+                    auto pk = [](__nv_bfloat16 lo, __nv_bfloat16 hi) {
+                        return (uint32_t)__bfloat16_as_ushort(lo) | ((uint32_t)__bfloat16_as_ushort(hi) << 16);
+                    };
+                    w[0][jj] = pk(arh, brh);
+                    w[1][jj] = pk(arl, brl);
+                    w[2][jj] = pk(aih, bih);
+                    w[3][jj] = pk(ail, bil);
+                }
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    *reinterpret_cast<uint4*>(sE + (size_t)q * lay.plane + (size_t)row * 16) =
+                        make_uint4(w[q][0], w[q][1], w[q][2], w[q][3]);
+            }
+        }
+        tc::fence_proxy_async();
+        __syncthreads();
+
+        float bestv = -1.f;
+        int besti = 0;
+        for (int nb = 0; nb < NB; ++nb) {
+            if (warp == 4) {
+                if (lane == 0) {
+                    // ===== producer: one bulk copy per stage =====
+                    const uint8_t* src = pack + (size_t)nb * NKC * lay.stage;
+                    for (int kc = 0; kc < NKC; ++kc) {
+                        const uint32_t st = it_pipe % (uint32_t)nstages, ph = (it_pipe / (uint32_t)nstages) & 1u;
+                        tc::mbar_wait(bar_empty + 8 * st, ph ^ 1u);
+                        tc::mbar_expect_tx(bar_full + 8 * st, lay.stage);
+                        tc::bulk_g2s(sStage_u32 + st * lay.stage, src + (size_t)kc * lay.stage, lay.stage, bar_full + 8 * st);
+                        ++it_pipe;
+                    }
+                }
+            } else if (warp == 5) {
+                if (lane == 0) {
+                    // ===== MMA issuer =====
+                    tc::tc_fence_after();
+                    const uint32_t c_re = tmem, c_im = tmem + 256;
+                    for (int kc = 0; kc < NKC; ++kc) {
+                        const uint32_t st = it_pipe % (uint32_t)nstages, ph = (it_pipe / (uint32_t)nstages) & 1u;
+                        tc::mbar_wait(bar_full + 8 * st, ph);
+                        tc::tc_fence_after();
+                        const uint32_t sb = sStage_u32 + st * lay.stage;
+#pragma unroll
+                        for (int ks = 0; ks < 2; ++ks) {
+                            const uint32_t kk = (uint32_t)(kc * 2 + ks);
+                            const uint32_t acc = (kc > 0 || ks > 0) ? 1u : 0u;
+                            uint64_t a[4], b[2];
+#pragma unroll
+                            for (int q = 0; q < 4; ++q)
+                                a[q] = tc::smem_desc(sE_u32 + (uint32_t)q * lay.plane + 2 * kk * 128, 128, 128);
+#pragma unroll
+                            for (int p = 0; p < 2; ++p)
+                                b[p] = tc::smem_desc(sb + (uint32_t)p * (uint32_t)NT * 64 + 2 * (uint32_t)ks * b_lbo, b_lbo, 128);
+                            tc::umma_bf16(c_re, a[0], b[0], idesc_pos, acc);
+                            tc::umma_bf16(c_re, a[1], b[0], idesc_pos, 1u);
+                            tc::umma_bf16(c_re, a[2], b[1], idesc_neg, 1u);
+                            tc::umma_bf16(c_re, a[3], b[1], idesc_neg, 1u);
+                            tc::umma_bf16(c_im, a[2], b[0], idesc_pos, acc);
+                            tc::umma_bf16(c_im, a[3], b[0], idesc_pos, 1u);
+                            tc::umma_bf16(c_im, a[0], b[1], idesc_pos, 1u);
+                            tc::umma_bf16(c_im, a[1], b[1], idesc_pos, 1u);
+                        }
+                        tc::umma_commit(bar_empty + 8 * st);      // stage free once these MMAs have read it
+                        ++it_pipe;
+                    }
+                    tc::umma_commit(bar_tfull);                   // accumulators complete
+                }
+            } else {
+                // ===== epilogue: thread = one shift (TMEM lane), columns = templates =====
+                tc::mbar_wait(bar_tfull, it_acc & 1u);
+                tc::tc_fence_after();
+                const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+                const float* inv = sInv + nb * NT;
+                for (int c = 0; c < NT / 16; ++c) {
+                    float re[16], im[16];
+                    tc::tmem_ld16(lane_base + 16 * c, re);
+                    tc::tmem_ld16(lane_base + 256 + 16 * c, im);
+                    tc::tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        const float q = fmaf(re[j], re[j], im[j] * im[j]) * inv[16 * c + j];
+                        if (q > bestv) {       // strict '>' keeps the lowest template on ties
+                            bestv = q;
+                            besti = nb * NT + 16 * c + j;
+                        }
+                    }
+                }
+                tc::tc_fence_before();
+            }
+            ++it_acc;
+            __syncwarp();
+            __syncthreads();   // TMEM drained and (last block) E free before the next generation
+        }
+        if (warp < 4) {
+            const int64_t i = tile * TC_M + warp * 32 + lane;
+            if (i < K) {
+                const float q = bestv / xenergy[i];
+                if (best_out) best_out[i] = sqrt_out ? sqrtf(q) : q;
+                if (tidx_out) tidx_out[i] = besti;
+            }
+        }
+    }
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc(tmem, TC_TMEM_COLS);
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+static int tc_pick_stages(int L32, int NT, int NB) {
+    for (int s = TC_MAX_STAGES; s >= 2; --s)
+        if ((int)tc_smem_layout(L32, NT, NB, s).total + 128 <= max_smem_optin()) return s;
+    return 0;
+}
+
+void mt_tc_release(MtTcPlan* plan) {
+    if (!plan) return;
+    cudaFree(plan->d_pack);
+    cudaFree(plan->d_inv_energy);
+    plan->d_pack = nullptr;
+    plan->d_inv_energy = nullptr;
+    plan->usable = false;
+}
+
+// Builds the BF16 stage images of a template set already on the device ([T, L8] float2, conjugated as the
+// caller asked).  plan->usable stays false (and the caller keeps the FP32 kernel) when a template value is
+// not exact in BF16, when there are too many templates for the shared-memory energy table or when the
+// expanded x tile plus two stages do not fit in shared memory.
+int32_t mt_tc_prepare(const float2* d_templates, int T, int L, int L8, const float* d_energies, MtTcPlan* plan) {
+    plan->usable = false;
+    plan->T = T;
+    plan->L = L;
+    plan->L32 = (L + TC_KC - 1) / TC_KC * TC_KC;
+    plan->NT = (T >= 256) ? 256 : (T + 15) / 16 * 16;
+    plan->NB = (T + plan->NT - 1) / plan->NT;
+    if (const char* e = getenv("XC_MT_FP32")) {
+        if (e[0] == '1') return XC_OK;            // A/B switch: force the FP32 SIMT kernel
+    }
+    if (plan->NB * plan->NT > TC_MAX_TEMPLATES) return XC_OK;
+    if (tc_pick_stages(plan->L32, plan->NT, plan->NB) < 2) return XC_OK;
+    int cc_major = 0;
+    int dev = 0;
+    XC_CUDA_TRY(cudaGetDevice(&dev));
+    XC_CUDA_TRY(cudaDeviceGetAttribute(&cc_major, cudaDevAttrComputeCapabilityMajor, dev));
+    if (cc_major != 10) return XC_OK;
+    const size_t elems = (size_t)plan->NB * (plan->L32 / TC_KC) * 2 * plan->NT * TC_KC;
+    int* d_flag = reinterpret_cast<int*>(workspace(SLOT_TMP3, 256));
+    if (!d_flag) return XC_ERR_NOMEM;
+    XC_CUDA_TRY(cudaMemset(d_flag, 0, sizeof(int)));
+    XC_CUDA_TRY(cudaMalloc(&plan->d_pack, elems * sizeof(__nv_bfloat16)));
+    XC_CUDA_TRY(cudaMalloc(&plan->d_inv_energy, sizeof(float) * (size_t)plan->NB * plan->NT));
+    const int blocks = (int)((elems + 255) / 256 < 4096 ? (elems + 255) / 256 : 4096);
+    mt_tc_pack_kernel<<<blocks, 256>>>(d_templates, T, L, L8, plan->L32, plan->NT, plan->NB,
+                                       reinterpret_cast<__nv_bfloat16*>(plan->d_pack), d_flag);
+    XC_LAUNCH_CHECK();
+    const int n = plan->NB * plan->NT;
+    mt_tc_inv_energy_kernel<<<(n + 255) / 256, 256>>>(d_energies, T, n, plan->d_inv_energy);
+    XC_LAUNCH_CHECK();
+    int inexact = 0;
+    XC_CUDA_TRY(cudaMemcpy(&inexact, d_flag, sizeof(int), cudaMemcpyDeviceToHost));
+    if (inexact) {
+        mt_tc_release(plan);
+        return XC_OK;
+    }
+    plan->usable = true;
+    return XC_OK;
+}
+
+int32_t mt_tc_run(const MtTcPlan& plan, const float2* x, int64_t xlen, int64_t start, int64_t K, const float* xenergy,
+                  float* best, int32_t* tidx, int sqrt_out, cudaStream_t stream) {
+    if (!plan.usable) return fail(XC_ERR_UNSUPPORTED, "tensor-core template plan is not usable");
+    const int nstages = tc_pick_stages(plan.L32, plan.NT, plan.NB);
+    const TcSmem lay = tc_smem_layout(plan.L32, plan.NT, plan.NB, nstages);
+    const size_t smem = lay.total + 128;
+    static size_t configured = 0;
+    if (smem > configured) {
+        XC_CUDA_TRY(cudaFuncSetAttribute(mt_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    const int64_t ntiles = (K + TC_M - 1) / TC_M;
+    int64_t ctas = sm_count();
+    if (ctas > ntiles) ctas = ntiles;
+    const int64_t per = (ntiles + ctas - 1) / ctas;
+    ctas = (ntiles + per - 1) / per;
+    profile_begin(stream);
+    mt_tc_kernel<<<(unsigned)ctas, TC_THREADS, smem, stream>>>(reinterpret_cast<const uint8_t*>(plan.d_pack),
+                                                               plan.d_inv_energy, plan.NT, plan.NB, plan.L32, nstages, x,
+                                                               xlen, start, K, xenergy, best, tidx, sqrt_out, ntiles, per);
+    profile_end(stream);
+    XC_LAUNCH_CHECK();
+    return XC_OK;
+}
+
+}  // namespace xc

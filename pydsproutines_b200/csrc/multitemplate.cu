@@ -15,6 +15,7 @@ struct xc_mt {
     int32_t T, L, L8;
     float2* d_templates;   // [T, L8] zero padded rows, conjugated if requested at create time
     float* d_energies;     // [T]
+    xc::MtTcPlan tc;       // tensor-core plan (usable when the templates are exact in BF16)
 };
 
 namespace xc {
@@ -181,12 +182,20 @@ int32_t xc_mt_create(const void* templates, int32_t T, int32_t L, int32_t conj, 
         xc_mt_destroy(h);
         return fail(e == cudaErrorMemoryAllocation ? XC_ERR_NOMEM : XC_ERR_CUDA, "template upload failed: %s", cudaGetErrorString(e));
     }
+    {
+        const int32_t st = mt_tc_prepare(h->d_templates, T, L, L8, h->d_energies, &h->tc);
+        if (st != XC_OK) {
+            xc_mt_destroy(h);
+            return st;
+        }
+    }
     *handle = h;
     return XC_OK;
 }
 
 int32_t xc_mt_destroy(xc_mt* h) {
     if (!h) return XC_OK;
+    mt_tc_release(&h->tc);
     cudaFree(h->d_templates);
     cudaFree(h->d_energies);
     delete h;
@@ -226,16 +235,21 @@ int32_t xc_mt_correlate(xc_mt* h, const void* x, int64_t xlen, int64_t start, in
     float* d_energy = (float*)workspace(SLOT_TMP1, sizeof(float) * (size_t)K);
     if (!d_energy) return XC_ERR_NOMEM;
     XC_TRY(sliding_sum_device(dx + start, true, xlen - start, 0, h->L, K, d_energy, 0, st));
-    const size_t smem = mt_smem_bytes(h->L8);
-    static size_t configured = 0;
-    if (smem > configured) {
-        XC_CUDA_TRY(cudaFuncSetAttribute(mt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
+    if (h->tc.usable && !dfull) {
+        // dense complex contraction on the tensor cores (tcgen05), templates exact in BF16
+        XC_TRY(mt_tc_run(h->tc, dx, xlen, start, K, d_energy, db, dt, sqrt_out, st));
+    } else {
+        const size_t smem = mt_smem_bytes(h->L8);
+        static size_t configured = 0;
+        if (smem > configured) {
+            XC_CUDA_TRY(cudaFuncSetAttribute(mt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            configured = smem;
+        }
+        const int64_t blocks = (K + MT_TS - 1) / MT_TS;
+        mt_kernel<<<(unsigned)blocks, MT_THREADS, smem, st>>>(h->d_templates, h->T, h->L8, h->d_energies, dx, xlen, start,
+                                                              K, d_energy, db, dt, dfull, sqrt_out);
+        XC_LAUNCH_CHECK();
     }
-    const int64_t blocks = (K + MT_TS - 1) / MT_TS;
-    mt_kernel<<<(unsigned)blocks, MT_THREADS, smem, st>>>(h->d_templates, h->T, h->L8, h->d_energies, dx, xlen, start, K,
-                                                          d_energy, db, dt, dfull, sqrt_out);
-    XC_LAUNCH_CHECK();
     if (where == XC_HOST) {
         if (best) XC_CUDA_TRY(cudaMemcpyAsync(best, db, sizeof(float) * (size_t)K, cudaMemcpyDeviceToHost, st));
         if (tidx) XC_CUDA_TRY(cudaMemcpyAsync(tidx, dt, sizeof(int32_t) * (size_t)K, cudaMemcpyDeviceToHost, st));
