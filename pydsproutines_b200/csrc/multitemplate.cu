@@ -202,6 +202,8 @@ int32_t xc_mt_destroy(xc_mt* h) {
     return XC_OK;
 }
 
+int32_t xc_mt_uses_tensor_cores(const xc_mt* h) { return (h && h->tc.usable) ? 1 : 0; }
+
 int32_t xc_mt_correlate(xc_mt* h, const void* x, int64_t xlen, int64_t start, int64_t K, float* best, int32_t* tidx,
                         void* full, int32_t sqrt_out, xc_peak* peak, int32_t where, void* stream) {
     if (where != XC_HOST && where != XC_DEVICE) return fail(XC_ERR_ARG, "where must be XC_HOST (0) or XC_DEVICE (1)");

@@ -400,6 +400,11 @@ class _MtHandle:
         self._h = C.c_void_p()
         check(lib.xc_mt_create(_lib.ptr(t), self.T, self.L, 1 if conj else 0, _lib.ptr(e), C.byref(self._h)))
 
+    @property
+    def uses_tensor_cores(self):
+        """True when the returnMax / multiTemplateSlidingDotProduct path of this template set runs on tcgen05."""
+        return bool(_lib.load().xc_mt_uses_tensor_cores(self._h))
+
     def run(self, x, start, K, want_best, want_full, sqrt_out, want_peak=False):
         lib = _lib.load()
         where = _lib.where_of(x)

@@ -355,3 +355,47 @@ def test_magnsq_argmax_local_maxima():
     assert int(cnt[0]) == ref.size and np.array_equal(pk, ref[:100])
     with pytest.raises(TypeError):
         ce.cupyFindLocalMaxima(big.astype(np.float64), 0.5)
+
+
+# ---------------------------------------------------------------------------------------------
+# tensor-core (tcgen05) multi-template kernel: tile edges, template blocks, padding, dispatch
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("T,L,n,start", [
+    (1, 32, 700, 0),        # one template: N padded to 16
+    (16, 33, 1000, 3),      # L not a multiple of the 32-sample stage, unaligned start
+    (40, 250, 4000, 129),   # N = 48, several tiles, start past one tile
+    (256, 64, 3000, 0),     # full-width block
+    (300, 48, 1500, 5),     # two template blocks (256 + 44 padded)
+    (8, 1500, 6000, 0),     # long templates: fewer pipeline stages
+])
+def test_mt_tensor_core_vs_oracle(xr, T, L, n, start):
+    rng = np.random.default_rng(100 + T + L)
+    alphabet = np.array([1, 1j, -1, -1j, 0.5 + 0.5j, -2.0, 0.25j], dtype=np.complex64)   # all exact in BF16
+    templates = alphabet[rng.integers(0, alphabet.size, (T, L))]
+    x = signals.cnoise(rng, n)
+    K = n - L + 1 - start
+    p = start + K // 2
+    x[p:p + L] += 3.0 * templates[T - 1].conj()
+    h = xr._MtHandle(templates, False)
+    assert h.uses_tensor_cores
+    best, tidx, _, _ = h.run(_dev(x), start, K, True, False, False)
+    best, tidx = best.cpu().numpy(), tidx.cpu().numpy()
+    ti_ref, q_ref = orc.multiTemplateSlidingDotProduct(x, templates, start, K)
+    assert_qf2(best, q_ref)
+    assert int(np.argmax(best)) == K // 2 and tidx[K // 2] == T - 1
+    assert (tidx != ti_ref).sum() <= max(1, K // 100)
+    # host-buffer call and the sqrt output agree with the device-buffer call
+    best_h, tidx_h, _, _ = h.run(x, start, K, True, False, True)
+    np.testing.assert_allclose(best_h, np.sqrt(best), rtol=1e-6)
+    assert np.array_equal(tidx_h, tidx)
+
+
+def test_mt_dispatch_inexact_templates_take_fp32(xr):
+    rng = np.random.default_rng(5)
+    templates = (signals.qpsk(rng, 4 * 64).reshape(4, 64) * np.float32(1.234)).astype(np.complex64)
+    h = xr._MtHandle(templates, False)
+    assert not h.uses_tensor_cores
+    x = signals.cnoise(rng, 1000)
+    best, tidx, _, _ = h.run(_dev(x), 0, 937, True, False, False)
+    ti_ref, q_ref = orc.multiTemplateSlidingDotProduct(x, templates, 0, 937)
+    assert_qf2(best.cpu().numpy(), q_ref)
