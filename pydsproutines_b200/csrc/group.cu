@@ -28,6 +28,8 @@ struct xc_group {
 
 namespace xc {
 
+constexpr int ELL_UNROLL = 8;
+
 template <class PL>
 struct GroupLoader {
     const float2* rx;
@@ -58,12 +60,21 @@ struct GroupLoader {
         for (int c = 0; c < PL::V; ++c) {
             float2 acc = make_float2(0.f, 0.f);
             const int j0 = slot_base[c], j1 = slot_base[c + 1];
-            for (int j = j0; j < j1; ++j) {
-                const float2 y = __ldg(ell_y + (size_t)j * PL::TG + t);
-                const int off = __ldg(ell_off + (size_t)j * PL::TG + t);
-                const float2 r = __ldg(x + off);
-                acc.x = fmaf(y.x, r.x, fmaf(-y.y, r.y, acc.x));
-                acc.y = fmaf(y.x, r.y, fmaf(y.y, r.x, acc.y));
+            // lists are padded to a multiple of ELL_UNROLL (zero weights): all index / weight / sample loads
+            // of a batch are issued before the first dependent one is used
+#pragma unroll 1
+            for (int j = j0; j < j1; j += ELL_UNROLL) {
+                int off[ELL_UNROLL];
+                float2 y[ELL_UNROLL], r[ELL_UNROLL];
+#pragma unroll
+                for (int u = 0; u < ELL_UNROLL; ++u) off[u] = __ldg(ell_off + (size_t)(j + u) * PL::TG + t);
+#pragma unroll
+                for (int u = 0; u < ELL_UNROLL; ++u) y[u] = __ldg(ell_y + (size_t)(j + u) * PL::TG + t);
+#pragma unroll
+                for (int u = 0; u < ELL_UNROLL; ++u) r[u] = __ldg(x + off[u]);
+#pragma unroll
+                for (int u = 0; u < ELL_UNROLL; ++u) acc = pfma(make_float2(r[u].y, r[u].x), make_float2(-y[u].y, y[u].y),
+                                                              pfma(r[u], make_float2(y[u].x, y[u].x), acc));
             }
             v[c] = acc;
         }
@@ -111,6 +122,7 @@ struct GroupBuilder {
                 const int m = n1 * PL::M1 + t + TG * q;
                 if (rows[m].size() > len) len = rows[m].size();
             }
+            len = (len + ELL_UNROLL - 1) / ELL_UNROLL * ELL_UNROLL;
             base[c + 1] = base[c] + (int32_t)len;
         }
         const int nrows = base[V];
