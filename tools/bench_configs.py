@@ -62,7 +62,19 @@ def main():
             name = "C4 multi-template: 256 templates x 1024 vs 2^24 samples"
         else:
             continue
-        print(json.dumps({"workload": name, "ms": ms, "cells_per_s": cells / (ms * 1e-3),
+        extra = {}
+        if w == "c4":
+            # tensor roofline: executed BF16 flops = 2 precision passes (hi/lo split of x) x algorithmic flops
+            peaks = {}
+            pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
+            if os.path.isfile(pk):
+                peaks = json.load(open(pk))
+            peak = float(peaks.get("bf16_tflops", 1590.0))
+            ach = 2.0 * flops / (ms * 1e-3) / 1e12
+            extra = {"tensor_cores": bool(h.uses_tensor_cores),
+                     "roofline": {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                                  "peak_source": "measured" if peaks else "fallback", "precision_passes": 2}}
+        print(json.dumps({"workload": name, "ms": ms, "cells_per_s": cells / (ms * 1e-3), **extra,
                           "algorithmic_tflops": flops / (ms * 1e-3) / 1e12, "fp32_peak_tflops_measured": tf.value,
                           "frac_of_fp32_peak": flops / (ms * 1e-3) / 1e12 / tf.value if tf.value else None}), flush=True)
 
