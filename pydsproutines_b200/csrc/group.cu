@@ -41,23 +41,38 @@ struct GroupLoader {
     const int32_t* slot_base_g;   // global [V + 1]
     int64_t lo, hi;               // valid shifts satisfy s + lo >= 0 and s + hi <= rxlen
 
-    __host__ __device__ static constexpr size_t smem_bytes() { return ((sizeof(int32_t) * (PL::V + 1) + 15) / 16) * 16; }
+    // shared-memory tables: slot_base[V + 1], then the list of non-empty slots ne[V] and their count
+    __host__ __device__ static constexpr size_t smem_bytes() { return ((sizeof(int32_t) * (2 * PL::V + 2) + 15) / 16) * 16; }
 
     __device__ __forceinline__ void prepare(int tid, int nthreads, unsigned char* smem) const {
         int32_t* slot_base = reinterpret_cast<int32_t*>(smem);
         for (int i = tid; i <= PL::V; i += nthreads) slot_base[i] = slot_base_g[i];
+        if (tid == 0) {
+            int32_t* ne = slot_base + PL::V + 1;
+            int n = 0;
+            for (int c = 0; c < PL::V; ++c)
+                if (slot_base_g[c + 1] > slot_base_g[c]) ne[n++] = c;
+            ne[PL::V] = n;
+        }
     }
     __device__ __forceinline__ bool issue(float2* v, int t, int64_t i, const unsigned char* smem) const {
         return load(v, t, i, smem);
     }
     __device__ __forceinline__ void finish(float2*, int, const unsigned char*) const {}
+    // The gather is ONE rolled loop over the non-empty register slots (the code of a fully unrolled slot loop
+    // does not fit the instruction cache); the finished sum is steered into its register by a uniform switch.
     __device__ __forceinline__ bool load(float2* v, int t, int64_t i, const unsigned char* smem) const {
         const int32_t* slot_base = reinterpret_cast<const int32_t*>(smem);
+        const int32_t* ne = slot_base + PL::V + 1;
         const int64_t s = shifts ? shifts[i] : shift0 + i * step;
         if (s + lo < 0 || s + hi > rxlen) return false;
         const float2* x = rx + s;
 #pragma unroll
-        for (int c = 0; c < PL::V; ++c) {
+        for (int c = 0; c < PL::V; ++c) v[c] = make_float2(0.f, 0.f);
+        const int n_ne = ne[PL::V];
+#pragma unroll 1
+        for (int k = 0; k < n_ne; ++k) {
+            const int c = ne[k];
             float2 acc = make_float2(0.f, 0.f);
             const int j0 = slot_base[c], j1 = slot_base[c + 1];
             // lists are padded to a multiple of ELL_UNROLL (zero weights): all index / weight / sample loads
@@ -76,7 +91,15 @@ struct GroupLoader {
                 for (int u = 0; u < ELL_UNROLL; ++u) acc = pfma(make_float2(r[u].y, r[u].x), make_float2(-y[u].y, y[u].y),
                                                               pfma(r[u], make_float2(y[u].x, y[u].x), acc));
             }
-            v[c] = acc;
+#define XC_SLOT(n) case n: if (n < PL::V) v[(n < PL::V) ? n : 0] = acc; break;
+            switch (c) {
+                XC_SLOT(0) XC_SLOT(1) XC_SLOT(2) XC_SLOT(3) XC_SLOT(4) XC_SLOT(5) XC_SLOT(6) XC_SLOT(7)
+                XC_SLOT(8) XC_SLOT(9) XC_SLOT(10) XC_SLOT(11) XC_SLOT(12) XC_SLOT(13) XC_SLOT(14) XC_SLOT(15)
+                XC_SLOT(16) XC_SLOT(17) XC_SLOT(18) XC_SLOT(19) XC_SLOT(20) XC_SLOT(21) XC_SLOT(22) XC_SLOT(23)
+                XC_SLOT(24) XC_SLOT(25) XC_SLOT(26) XC_SLOT(27) XC_SLOT(28) XC_SLOT(29) XC_SLOT(30) XC_SLOT(31)
+                default: break;
+            }
+#undef XC_SLOT
         }
         return true;
     }
