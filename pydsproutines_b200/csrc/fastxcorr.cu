@@ -3,6 +3,12 @@
 //               replacing the copy/multiply/cuFFT/argmax chain of cp_fastXcorr (xcorrRoutines.py:98-151)
 //               and IppXcorrFFT_32fc::xcorr_thread (IppXcorrFFT.cpp:94-178);
 //   no freqsearch: register-tiled sliding dot product (xcorrRoutines.py:483-509).
+#include <math.h>
+
+#include <map>
+#include <vector>
+
+#include "bluestein.cuh"
 #include "fused_fft_kernel.cuh"
 #include "internal.cuh"
 #include "plans.cuh"
@@ -73,7 +79,71 @@ struct CutoutLoader {
     }
 };
 
-bool fastxcorr_fft_supported(int N) { return fft_length_supported(N); }
+// loader of the Bluestein path: like CutoutLoader over the padded length M = PL::N, but only the first `nvalid`
+// points exist in rx (the rest of the chirped product is zero) and `cutout` is cutout[n] * b[n], zero padded.
+template <class PL, bool CUT_SMEM>
+struct ChirpLoader {
+    const float2* rx;
+    int64_t rxlen;
+    const float2* cutout;
+    int64_t shift0, step;
+    const int64_t* shifts;
+    int nvalid;
+
+    __host__ __device__ static constexpr size_t smem_bytes() { return CUT_SMEM ? sizeof(float2) * PL::N : 0; }
+    __device__ __forceinline__ void prepare(int tid, int nthreads, unsigned char* smem) const {
+        if (CUT_SMEM) {
+            float2* cc = reinterpret_cast<float2*>(smem);
+            for (int n = tid; n < PL::N; n += nthreads) {
+                const float2 c = cutout[n];
+                cc[n] = make_float2(c.x, -c.y);
+            }
+        }
+    }
+    __device__ __forceinline__ bool load(float2* v, int t, int64_t i, const unsigned char* smem) const {
+        const int64_t s = shifts ? shifts[i] : shift0 + i * step;
+        if (s < 0 || s + nvalid > rxlen) return false;
+        const float2* x = rx + s + t;
+        constexpr int NQ = PL::V / PL::R1;
+#pragma unroll
+        for (int n1 = 0; n1 < PL::R1; ++n1)
+#pragma unroll
+            for (int q = 0; q < NQ; ++q) {
+                const int n = input_index<PL>(0, q, n1);
+                v[q * PL::R1 + n1] = (n + t < nvalid) ? __ldg(x + n) : make_float2(0.f, 0.f);
+            }
+        if (CUT_SMEM) {
+            const float2* cc = reinterpret_cast<const float2*>(smem) + t;
+#pragma unroll
+            for (int n1 = 0; n1 < PL::R1; ++n1)
+#pragma unroll
+                for (int q = 0; q < NQ; ++q)
+                    v[q * PL::R1 + n1] = pcmul(v[q * PL::R1 + n1], cc[input_index<PL>(0, q, n1)]);
+        } else {
+            const float2* cg = cutout + t;
+#pragma unroll
+            for (int n1 = 0; n1 < PL::R1; ++n1)
+#pragma unroll
+                for (int q = 0; q < NQ; ++q)
+                    v[q * PL::R1 + n1] = pcmulc(v[q * PL::R1 + n1], __ldg(cg + input_index<PL>(0, q, n1)));
+        }
+        return true;
+    }
+};
+
+constexpr int BLUE_MIN_LOG2M = 6;     // smallest plan with an exchange buffer
+
+static int bluestein_log2m(int N) {
+    int lg = BLUE_MIN_LOG2M;
+    while ((1 << lg) < 2 * N - 1) ++lg;
+    return lg;
+}
+
+// power-of-two lengths run the plain fused kernel; every other length 2 <= N <= 2^(MAX_LOG2N - 1) the Bluestein one
+bool fastxcorr_fft_supported(int N) {
+    if (fft_length_supported(N)) return true;
+    return N >= 3 && bluestein_log2m(N) <= MAX_LOG2N;
+}
 
 struct FreqRunner {
     const float2* cutout;
@@ -91,12 +161,147 @@ struct FreqRunner {
     }
 };
 
+// ---------------------------------------------------------------------------------------------
+// Bluestein plan (per cutout length, cached for the life of the process): the chirp b[n] and FFT_M(b) laid
+// out for the block FFT's output registers
+// ---------------------------------------------------------------------------------------------
+struct BluePlan {
+    int N = 0, log2m = 0;
+    float2* d_b = nullptr;          // [M]: b[n] = exp(+i pi n^2 / N) for n < N, 0 beyond
+    float2* d_bhat_perm = nullptr;  // [M]: FFT_M(b extended)[output_bin(t, slot)] at slot * TG + t
+};
+static std::map<int, BluePlan> g_blue;
+
+struct cd {
+    double re, im;
+};
+static void fft_host_radix2(std::vector<cd>& a) {     // forward DFT, in place, length a power of two
+    const size_t n = a.size();
+    for (size_t i = 1, j = 0; i < n; ++i) {
+        size_t bit = n >> 1;
+        for (; j & bit; bit >>= 1) j ^= bit;
+        j ^= bit;
+        if (i < j) std::swap(a[i], a[j]);
+    }
+    for (size_t len = 2; len <= n; len <<= 1) {
+        for (size_t i = 0; i < n; i += len)
+            for (size_t k = 0; k < len / 2; ++k) {
+                const double ang = -2.0 * M_PI * (double)k / (double)len;
+                const cd w{cos(ang), sin(ang)};
+                const cd u = a[i + k], x = a[i + k + len / 2];
+                const cd vv{x.re * w.re - x.im * w.im, x.re * w.im + x.im * w.re};
+                a[i + k] = cd{u.re + vv.re, u.im + vv.im};
+                a[i + k + len / 2] = cd{u.re - vv.re, u.im - vv.im};
+            }
+    }
+}
+
+struct BluePermute {
+    const std::vector<cd>& bhat;
+    std::vector<float2>& perm;
+    template <int LOG2N>
+    int32_t run() {
+        using PL = typename PlanFor<LOG2N>::PL;
+        for (int t = 0; t < PL::TG; ++t)
+            for (int q = 0; q < PL::V / PL::RL; ++q)
+                for (int j = 0; j < PL::RL; ++j) {
+                    const int bin = output_bin_base<PL>(t) + output_bin_off<PL>(q, j);
+                    perm[(size_t)(q * PL::RL + j) * PL::TG + t] = make_float2((float)bhat[bin].re, (float)bhat[bin].im);
+                }
+        return XC_OK;
+    }
+};
+
+static int32_t blue_plan_for(int N, const BluePlan** out) {
+    auto it = g_blue.find(N);
+    if (it != g_blue.end()) {
+        *out = &it->second;
+        return XC_OK;
+    }
+    BluePlan p;
+    p.N = N;
+    p.log2m = bluestein_log2m(N);
+    const int M = 1 << p.log2m;
+    std::vector<cd> b(N), ext(M, cd{0.0, 0.0});
+    std::vector<float2> hb(M, make_float2(0.f, 0.f)), perm(M);
+    for (int n = 0; n < N; ++n) {
+        const long long r = ((long long)n * n) % (2LL * N);      // exact phase reduction
+        const double ang = M_PI * (double)r / (double)N;
+        b[n] = cd{cos(ang), sin(ang)};
+        hb[n] = make_float2((float)b[n].re, (float)b[n].im);
+        ext[n] = b[n];
+        if (n > 0) ext[M - n] = b[n];
+    }
+    fft_host_radix2(ext);
+    XC_TRY(dispatch_log2(p.log2m, BluePermute{ext, perm}));
+    XC_CUDA_TRY(cudaMalloc(&p.d_b, sizeof(float2) * M));
+    XC_CUDA_TRY(cudaMalloc(&p.d_bhat_perm, sizeof(float2) * M));
+    XC_CUDA_TRY(cudaMemcpy(p.d_b, hb.data(), sizeof(float2) * M, cudaMemcpyHostToDevice));
+    XC_CUDA_TRY(cudaMemcpy(p.d_bhat_perm, perm.data(), sizeof(float2) * M, cudaMemcpyHostToDevice));
+    *out = &(g_blue[N] = p);
+    return XC_OK;
+}
+
+// cutB[n] = cutout[n] * b[n] for n < N, 0 for N <= n < M
+__global__ void chirp_cutout_kernel(const float2* __restrict__ cutout, const float2* __restrict__ b, int N, int M,
+                                    float2* __restrict__ out) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n < M) out[n] = (n < N) ? cmul(cutout[n], b[n]) : make_float2(0.f, 0.f);
+}
+
+struct BlueRunner {
+    const float2* cutb;
+    int N;
+    const BluePlan* plan;
+    const float2* rx;
+    int64_t rxlen;
+    const ShiftList& sl;
+    const FusedOut& out;
+    cudaStream_t stream;
+    template <int LOG2N>
+    int32_t run() {
+        using PF = PlanFor<LOG2N>;
+        using PL = typename PF::PL;
+        if constexpr (PL::P >= 2) {
+            using LD = ChirpLoader<PL, PF::CS>;
+            constexpr int B = PF::B;
+            LD ld{rx, rxlen, cutb, sl.shift0, sl.step, sl.shifts, N};
+            auto kern = fused_bluestein_kernel<PL, B, LD>;
+            constexpr size_t smem = fused_smem_bytes<PL, B, LD>();
+            if ((int)smem > max_smem_optin()) return fail(XC_ERR_UNSUPPORTED, "Bluestein kernel needs %zu B of shared memory", smem);
+            static bool configured = false;
+            static int occ = 1;
+            if (!configured) {
+                XC_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                XC_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, PL::TG * B, smem));
+                if (occ < 1) return fail(XC_ERR_CUDA, "Bluestein kernel does not fit on an SM (smem %zu B)", smem);
+                configured = true;
+            }
+            const int64_t max_ctas = (int64_t)sm_count() * occ;
+            int64_t ctas = (sl.K + B - 1) / B;
+            if (ctas > max_ctas) ctas = max_ctas;
+            if (ctas < 1) ctas = 1;
+            const int64_t chunk = (sl.K + ctas * B - 1) / (ctas * B);
+            if (chunk >= (1ll << 31)) return fail(XC_ERR_UNSUPPORTED, "too many shifts per thread group");
+            const double m = (double)PL::N;
+            profile_begin(stream);
+            kern<<<(unsigned)ctas, PL::TG * B, smem, stream>>>(ld, out, sl.K, (int)chunk, plan->d_bhat_perm, N,
+                                                               (float)(1.0 / (m * m)));
+            profile_end(stream);
+            XC_LAUNCH_CHECK();
+            return XC_OK;
+        } else {
+            return fail(XC_ERR_UNSUPPORTED, "no Bluestein plan for 2^%d points", LOG2N);
+        }
+    }
+};
+
 int32_t fastxcorr_freq_device(const float2* cutout, int N, const float2* rx, int64_t rxlen, const ShiftList& sl,
                               float* qf2, uint32_t* fidx, float2* cplx, void* caf, int caf_complex,
                               cudaStream_t stream) {
     if (!fastxcorr_fft_supported(N))
-        return fail(XC_ERR_UNSUPPORTED, "fused frequency search supports power-of-two cutout lengths 2..%d, got %d",
-                    1 << MAX_LOG2N, N);
+        return fail(XC_ERR_UNSUPPORTED, "fused frequency search supports cutout lengths 2..%d (powers of two up to %d), got %d",
+                    1 << (MAX_LOG2N - 1), 1 << MAX_LOG2N, N);
     if (sl.K <= 0) return XC_OK;
     // normalisation terms: ||cutout||^2 (device scalar) and the window energies
     float* d_refn = reinterpret_cast<float*>(workspace(SLOT_TMP0, 256));
@@ -109,6 +314,19 @@ int32_t fastxcorr_freq_device(const float2* cutout, int N, const float2* rx, int
         XC_TRY(window_energy_device(rx, rxlen, N, sl.shift0, sl.step, sl.shifts, sl.K, d_energy, stream));
     }
     FusedOut out{qf2, fidx, cplx, reinterpret_cast<float*>(caf), caf_complex, d_energy, d_refn};
+    if (!fft_length_supported(N)) {
+        // not a power of two: Bluestein inside the fused kernel (flattened outputs only)
+        if (cplx || caf)
+            return fail(XC_ERR_UNSUPPORTED, "CAF / complex outputs need a power-of-two cutout length, got %d", N);
+        const BluePlan* plan = nullptr;
+        XC_TRY(blue_plan_for(N, &plan));
+        const int M = 1 << plan->log2m;
+        float2* d_cutb = reinterpret_cast<float2*>(workspace(SLOT_TMP2, sizeof(float2) * (size_t)M));
+        if (!d_cutb) return XC_ERR_NOMEM;
+        chirp_cutout_kernel<<<(M + 255) / 256, 256, 0, stream>>>(cutout, plan->d_b, N, M, d_cutb);
+        XC_LAUNCH_CHECK();
+        return dispatch_log2(plan->log2m, BlueRunner{d_cutb, N, plan, rx, rxlen, sl, out, stream});
+    }
     return dispatch_log2(ilog2(N), FreqRunner{cutout, rx, rxlen, sl, out, stream});
 }
 

@@ -171,7 +171,7 @@ __device__ __forceinline__ int input_index(int t, int q, int n1) {
 // Bin index held in register slot (q*RL + j) of thread t after the last pass, split into a per-thread
 // base and a compile-time offset so that no per-slot value has to live in a register.
 template <class PL>
-__device__ __forceinline__ int output_bin_base(int t) {
+__host__ __device__ __forceinline__ int output_bin_base(int t) {
     if (PL::P == 1) return 0;
     if (PL::P == 2) return t;
     return (t / PL::R2) + PL::R1 * (t % PL::R2);      // needs TG % R2 == 0 (asserted in the plan)

@@ -87,16 +87,16 @@ def test_fastxcorr_golden(xr, name, d, space):
     assert_qf2(q, d["qf2_nofreq"])
     assert np.argmax(q) == np.argmax(d["qf2_nofreq"])
     pow2 = (len(cutout) & (len(cutout) - 1)) == 0
-    if not pow2:
-        with pytest.raises(NotImplementedError):
-            xr.fastXcorr(c, r, freqsearch=True, shifts=shifts)
-        return
-    q, f = xr.fastXcorr(c, r, freqsearch=True, shifts=shifts)
+    q, f = xr.fastXcorr(c, r, freqsearch=True, shifts=shifts)        # any length: Bluestein when not a power of two
     q, f = back(q), back(f)
     assert_qf2(q, d["qf2_freq"])
     assert_bins(f, d["fidx_freq"], lambda i: _spec64(cutout, rx, int(sh[i])))
     k = int(np.argmax(q))
     assert sh[k] == int(d["p0"]) and int(f[k]) == int(d["k0"])
+    if not pow2:
+        with pytest.raises(NotImplementedError):       # CAF / complex outputs of the Bluestein path: not yet
+            xr.fastXcorr(c, r, freqsearch=True, outputCAF=True, shifts=shifts)
+        return
     if "caf" in d.files:
         z = back(xr.fastXcorr(c, r, shifts=shifts, absResult=False))
         np.testing.assert_allclose(z, d["cplx_nofreq"], rtol=0, atol=2e-5 * np.abs(d["cplx_nofreq"]).max())
@@ -110,6 +110,27 @@ def test_fastxcorr_golden(xr, name, d, space):
         np.testing.assert_allclose(caf, d["caf"], rtol=RTOL, atol=1e-6 * d["caf"].max())
         cafc = back(xr.fastXcorr(c, r, freqsearch=True, outputCAF=True, shifts=shifts, absResult=False))
         np.testing.assert_allclose(cafc, d["caf_cplx"], rtol=0, atol=2e-5 * np.abs(d["caf_cplx"]).max())
+
+
+@pytest.mark.parametrize("N", [3, 5, 17, 31, 33, 100, 257, 480, 1000, 1023, 2049, 3000, 5000, 8191])
+def test_fastxcorr_any_length_bluestein_vs_oracle(xr, N):
+    """Cutout lengths that are not a power of two (the reference takes any length, xcorrRoutines.py:511-531):
+    chirp-z inside the fused kernel, every padded plan from 64 to 16384 points."""
+    K = 64 if N <= 1100 else 16
+    p0, k0 = K // 3, (3 * N) // 8 + 1
+    cutout, rx = signals.make_fastxcorr_case(300 + N, N, N + K - 1, p0, k0 % N, amp=0.9)
+    qr, fr = orc.fastXcorr(cutout, rx, freqsearch=True)
+    q, f = xr.fastXcorr(cutout, rx, freqsearch=True)
+    assert_qf2(q, qr)
+    assert_bins(f, fr, lambda i: _spec64(cutout, rx, i))
+    if N >= 100:      # shorter cutouts do not stand out of the noise
+        assert int(np.argmax(q)) == p0 and int(f[p0]) == k0 % N
+    # device buffers and a strided shift list
+    shifts = np.arange(1, K, 3)
+    q2, f2 = xr.fastXcorr(_dev(cutout), _dev(rx), freqsearch=True, shifts=shifts)
+    q2, f2 = q2.cpu().numpy(), f2.cpu().numpy()
+    np.testing.assert_allclose(q2, q[shifts], rtol=1e-6)
+    assert np.array_equal(f2, f[shifts])
 
 
 @pytest.mark.parametrize("log2n", list(range(1, 15)))
