@@ -125,4 +125,33 @@ fused_bluestein_kernel(const Loader loader, const FusedOut out, const int64_t K,
     }
 }
 
+// Persistent launch, as launch_fused_variant(): `nbins` = the true transform length N, PL::N = the padded length M.
+template <class PL, int B, class Loader>
+int32_t launch_bluestein(const Loader& ld, const FusedOut& out, int64_t K, const float2* bhat_perm, int nbins,
+                         cudaStream_t stream) {
+    auto kern = fused_bluestein_kernel<PL, B, Loader>;
+    constexpr size_t smem = fused_smem_bytes<PL, B, Loader>();
+    if ((int)smem > max_smem_optin()) return fail(XC_ERR_UNSUPPORTED, "Bluestein kernel needs %zu B of shared memory", smem);
+    static bool configured = false;   // per instantiation
+    static int occ = 1;
+    if (!configured) {
+        XC_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        XC_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, PL::TG * B, smem));
+        if (occ < 1) return fail(XC_ERR_CUDA, "Bluestein kernel does not fit on an SM (smem %zu B)", smem);
+        configured = true;
+    }
+    const int64_t max_ctas = (int64_t)sm_count() * occ;
+    int64_t ctas = (K + B - 1) / B;
+    if (ctas > max_ctas) ctas = max_ctas;
+    if (ctas < 1) ctas = 1;
+    const int64_t chunk = (K + ctas * B - 1) / (ctas * B);
+    if (chunk >= (1ll << 31)) return fail(XC_ERR_UNSUPPORTED, "too many shifts per thread group");
+    const double m = (double)PL::N;
+    profile_begin(stream);
+    kern<<<(unsigned)ctas, PL::TG * B, smem, stream>>>(ld, out, K, (int)chunk, bhat_perm, nbins, (float)(1.0 / (m * m)));
+    profile_end(stream);
+    XC_LAUNCH_CHECK();
+    return XC_OK;
+}
+
 }  // namespace xc

@@ -242,6 +242,16 @@ static int32_t blue_plan_for(int N, const BluePlan** out) {
     return XC_OK;
 }
 
+int32_t bluestein_tables(int N, int* log2m, const float2** d_bhat_perm) {
+    if (N < 3 || bluestein_log2m(N) > MAX_LOG2N)
+        return fail(XC_ERR_UNSUPPORTED, "no Bluestein plan for length %d (limit %d)", N, 1 << (MAX_LOG2N - 1));
+    const BluePlan* plan = nullptr;
+    XC_TRY(blue_plan_for(N, &plan));
+    *log2m = plan->log2m;
+    *d_bhat_perm = plan->d_bhat_perm;
+    return XC_OK;
+}
+
 // cutB[n] = cutout[n] * b[n] for n < N, 0 for N <= n < M
 __global__ void chirp_cutout_kernel(const float2* __restrict__ cutout, const float2* __restrict__ b, int N, int M,
                                     float2* __restrict__ out) {
@@ -264,32 +274,8 @@ struct BlueRunner {
         using PL = typename PF::PL;
         if constexpr (PL::P >= 2) {
             using LD = ChirpLoader<PL, PF::CS>;
-            constexpr int B = PF::B;
             LD ld{rx, rxlen, cutb, sl.shift0, sl.step, sl.shifts, N};
-            auto kern = fused_bluestein_kernel<PL, B, LD>;
-            constexpr size_t smem = fused_smem_bytes<PL, B, LD>();
-            if ((int)smem > max_smem_optin()) return fail(XC_ERR_UNSUPPORTED, "Bluestein kernel needs %zu B of shared memory", smem);
-            static bool configured = false;
-            static int occ = 1;
-            if (!configured) {
-                XC_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-                XC_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, PL::TG * B, smem));
-                if (occ < 1) return fail(XC_ERR_CUDA, "Bluestein kernel does not fit on an SM (smem %zu B)", smem);
-                configured = true;
-            }
-            const int64_t max_ctas = (int64_t)sm_count() * occ;
-            int64_t ctas = (sl.K + B - 1) / B;
-            if (ctas > max_ctas) ctas = max_ctas;
-            if (ctas < 1) ctas = 1;
-            const int64_t chunk = (sl.K + ctas * B - 1) / (ctas * B);
-            if (chunk >= (1ll << 31)) return fail(XC_ERR_UNSUPPORTED, "too many shifts per thread group");
-            const double m = (double)PL::N;
-            profile_begin(stream);
-            kern<<<(unsigned)ctas, PL::TG * B, smem, stream>>>(ld, out, sl.K, (int)chunk, plan->d_bhat_perm, N,
-                                                               (float)(1.0 / (m * m)));
-            profile_end(stream);
-            XC_LAUNCH_CHECK();
-            return XC_OK;
+            return launch_bluestein<PL, PF::B, LD>(ld, out, sl.K, plan->d_bhat_perm, N, stream);
         } else {
             return fail(XC_ERR_UNSUPPORTED, "no Bluestein plan for 2^%d points", LOG2N);
         }

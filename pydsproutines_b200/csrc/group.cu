@@ -10,6 +10,9 @@
 // -- uniform trip counts inside a group of threads, coalesced loads, no atomics.
 #include <vector>
 
+#include <math.h>
+
+#include "bluestein.cuh"
 #include "fused_fft_kernel.cuh"
 #include "internal.cuh"
 #include "plans.cuh"
@@ -24,6 +27,9 @@ struct xc_group {
     int32_t* d_slot_base;    // [V + 1]
     float* d_refn;           // ||ygroups||^2
     int32_t rows;
+    int32_t log2m;           // block-FFT plan: log2(F) when F is a power of two, else the padded Bluestein length
+    int32_t blue;            // F is not a power of two: chirped weights, two FFTs per shift (bluestein.cuh)
+    const float2* d_bhat_perm;   // Bluestein: FFT_M(chirp) in register order (owned by the per-length cache)
 };
 
 namespace xc {
@@ -128,14 +134,21 @@ struct GroupBuilder {
     template <int LOG2N>
     int32_t run() {
         using PL = typename PlanFor<LOG2N>::PL;
-        const int F = PL::N, TG = PL::TG, V = PL::V, G = h->G, L = h->L;
+        // cells of the padded plan (PL::N >= F); the fold is modulo the TRANSFORM length F
+        const int F = h->F, TG = PL::TG, V = PL::V, G = h->G, L = h->L;
         struct Contrib { int32_t off; float2 y; };
-        std::vector<std::vector<Contrib>> rows(F);
+        std::vector<std::vector<Contrib>> rows(PL::N);
         for (int g = 0; g < G; ++g)
             for (int n = 0; n < L; ++n) {
                 const int64_t a = starts[g] + n;
                 const int64_t m = ((a % F) + F) % F;
-                rows[(size_t)m].push_back(Contrib{(int32_t)a, y[(size_t)g * L + n]});
+                float2 w = y[(size_t)g * L + n];
+                if (h->blue) {      // times conj(b[m]), b[m] = exp(+i pi m^2 / F)
+                    const long long r = ((long long)m * m) % (2LL * F);
+                    const double ang = -M_PI * (double)r / (double)F, c = cos(ang), sn = sin(ang);
+                    w = make_float2((float)(w.x * c - w.y * sn), (float)(w.x * sn + w.y * c));
+                }
+                rows[(size_t)m].push_back(Contrib{(int32_t)a, w});
             }
         std::vector<int32_t> base(V + 1, 0);
         for (int c = 0; c < V; ++c) {
@@ -186,6 +199,13 @@ struct GroupRunner {
         using LD = GroupLoader<typename PF::PL>;
         LD ld{rx, rxlen, sl.shift0, sl.step, sl.shifts, h->d_ell_y, h->d_ell_off, h->d_slot_base,
               h->min_start, h->span};
+        if (h->blue) {
+            if constexpr (PF::PL::P >= 2) {
+                return launch_bluestein<typename PF::PL, PF::B, LD>(ld, out, sl.K, h->d_bhat_perm, h->F, stream);
+            } else {
+                return fail(XC_ERR_UNSUPPORTED, "no Bluestein plan for 2^%d points", LOG2N);
+            }
+        }
         return launch_fused<typename PF::PL, PF::B, LD>(ld, out, sl.K, stream);
     }
 };
@@ -206,8 +226,16 @@ int32_t xc_group_create(const void* ygroups, int32_t G, int32_t L, const int64_t
     if (!ygroups || !starts || !handle) return fail(XC_ERR_ARG, "ygroups/starts/handle is NULL");
     if (G < 1 || L < 1) return fail(XC_ERR_ARG, "need at least one group of at least one sample");
     if (F < L) return fail(XC_ERR_ARG, "INVALID_FFTLEN: fftlen %d is shorter than the group length %d", F, L);   // GroupXcorrFFT.cpp:11-14
-    if (!fft_length_supported(F))
-        return fail(XC_ERR_UNSUPPORTED, "GroupXcorrFFT supports power-of-two fftlen 2..%d, got %d", 1 << MAX_LOG2N, F);
+    int log2m = 0;
+    const float2* d_bhat_perm = nullptr;
+    const bool blue = !fft_length_supported(F);
+    if (blue) {
+        if (F < 3 || F > (1 << (MAX_LOG2N - 1)))
+            return fail(XC_ERR_UNSUPPORTED, "GroupXcorrFFT supports fftlen 2..%d (powers of two up to %d), got %d",
+                        1 << (MAX_LOG2N - 1), 1 << MAX_LOG2N, F);
+    } else {
+        log2m = ilog2(F);
+    }
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
         cudaGetLastError();
@@ -222,6 +250,16 @@ int32_t xc_group_create(const void* ygroups, int32_t G, int32_t L, const int64_t
     xc_group* h = new xc_group();
     memset(h, 0, sizeof(*h));
     h->G = G; h->L = L; h->F = F;
+    if (blue) {
+        const int32_t bs = bluestein_tables(F, &log2m, &d_bhat_perm);
+        if (bs != XC_OK) {
+            delete h;
+            return bs;
+        }
+    }
+    h->log2m = log2m;
+    h->blue = blue ? 1 : 0;
+    h->d_bhat_perm = d_bhat_perm;
     h->span = mx + L;
     h->min_start = mn;
     const float2* yin = reinterpret_cast<const float2*>(ygroups);
@@ -231,7 +269,7 @@ int32_t xc_group_create(const void* ygroups, int32_t G, int32_t L, const int64_t
         y[i] = auto_conj ? make_float2(yin[i].x, -yin[i].y) : yin[i];
         nsq += (double)yin[i].x * yin[i].x + (double)yin[i].y * yin[i].y;
     }
-    int32_t st = dispatch_log2(ilog2(F), GroupBuilder{y.data(), starts, h});
+    int32_t st = dispatch_log2(h->log2m, GroupBuilder{y.data(), starts, h});
     if (st == XC_OK) {
         const float nf = (float)nsq;
         cudaError_t e = cudaMalloc(&h->d_refn, 256);
@@ -265,6 +303,8 @@ int32_t xc_group_xcorr(xc_group* h, const void* rx, int64_t rxlen, int64_t shift
     if (where != XC_HOST && where != XC_DEVICE) return fail(XC_ERR_ARG, "where must be XC_HOST (0) or XC_DEVICE (1)");
     if (!h || !rx) return fail(XC_ERR_ARG, "handle/rx is NULL");
     if (!qf2 && !caf) return fail(XC_ERR_ARG, "qf2 and caf are both NULL");
+    if (caf && h->blue)
+        return fail(XC_ERR_UNSUPPORTED, "CAF rows need a power-of-two fftlen, got %d (the flattened outputs take any)", h->F);
     if (K < 0 || rxlen < h->L) return fail(XC_ERR_ARG, "need K >= 0 and rx at least one group long");
     if (K == 0) {
         if (peak) { memset(peak, 0, sizeof(*peak)); peak->index = -1; }
@@ -312,11 +352,11 @@ int32_t xc_group_xcorr(xc_group* h, const void* rx, int64_t rxlen, int64_t shift
     // the fused kernel either reduces to (max, arg max) or writes CAF rows; both wanted = two passes
     if (dq || df) {
         FusedOut out{dq, df, nullptr, nullptr, 0, d_energy, h->d_refn};
-        XC_TRY(dispatch_log2(ilog2(h->F), GroupRunner{h, drx, rxlen, sl, out, st}));
+        XC_TRY(dispatch_log2(h->log2m, GroupRunner{h, drx, rxlen, sl, out, st}));
     }
     if (dcaf) {
         FusedOut out{nullptr, nullptr, nullptr, dcaf, 0, d_energy, h->d_refn};
-        XC_TRY(dispatch_log2(ilog2(h->F), GroupRunner{h, drx, rxlen, sl, out, st}));
+        XC_TRY(dispatch_log2(h->log2m, GroupRunner{h, drx, rxlen, sl, out, st}));
     }
     if (where == XC_HOST) {
         if (qf2) XC_CUDA_TRY(cudaMemcpyAsync(qf2, dq, sizeof(float) * (size_t)K, cudaMemcpyDeviceToHost, st));

@@ -253,8 +253,38 @@ def test_groupxcorr_errors(xr):
         xr.GroupXcorrFFT(y, np.array([0, 20, 40, 60]), 1, fftlen=8)              # fftlen < group length
     with pytest.raises(RuntimeError):
         xr.CyGroupXcorrFFT(y, np.array([0, 20, 40, 60], np.int32), 1, fftlen=8)   # INVALID_FFTLEN
+    obj = xr.GroupXcorrFFT(y, np.array([0, 20, 40, 60]), 1, fftlen=48)           # not a power of two: flattened only
     with pytest.raises(NotImplementedError):
-        xr.GroupXcorrFFT(y, np.array([0, 20, 40, 60]), 1, fftlen=48)             # not a power of two (yet)
+        obj.xcorr(signals.cnoise(np.random.default_rng(2), 400), np.arange(10), flattenToTime=False)
+
+
+@pytest.mark.parametrize("G,L,F,ragged", [(4, 16, 48, False), (5, 20, 20, True), (8, 100, 100, False),
+                                          (6, 33, 1000, True), (3, 1200, 3000, False)])
+def test_groupxcorr_any_fftlen_bluestein_vs_oracle(xr, G, L, F, ragged):
+    """fftlen that is not a power of two (the default fftlen is the group length, xcorrRoutines.py:1065-1068):
+    folded gather with chirped weights + the two-FFT Bluestein kernel."""
+    rng = np.random.default_rng(1000 + F)
+    y = signals.qpsk(rng, G * L).reshape(G, L)
+    gap = L + (7 if ragged else 0)
+    starts = np.arange(G) * gap + (rng.integers(0, 5, G) if ragged else 0)
+    starts = (starts - starts[0]).astype(np.int64)
+    K = 40
+    span = int(starts[-1]) + F
+    rx = signals.cnoise(rng, K + span + 8)
+    p0, k0 = 17, (F // 3) + 1
+    for g in range(G):
+        n = np.arange(L)
+        rx[p0 + starts[g]:p0 + starts[g] + L] += 2.0 * y[g] * np.exp(2j * np.pi * k0 * (starts[g] + n) / F).astype(np.complex64)
+    shifts = np.arange(K)
+    ref = orc.GroupXcorrFFT(y, starts, 1, fftlen=F)
+    xc_ref, fi_ref = ref.xcorr(rx, shifts)
+    obj = xr.GroupXcorrFFT(y, starts, 1, fftlen=F)
+    xc, fi = obj.xcorr(rx, shifts)
+    assert_qf2(xc, xc_ref)
+    assert (np.asarray(fi) != np.asarray(fi_ref)).sum() <= 1
+    assert int(np.argmax(xc)) == p0 and int(fi[p0]) == k0
+    xc2, fi2 = obj.xcorrGPU(_dev(rx), shifts)
+    np.testing.assert_allclose(xc2.cpu().numpy(), xc, rtol=1e-6)
 
 
 # ---------------------------------------------------------------------------------------------
