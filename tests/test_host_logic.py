@@ -34,7 +34,8 @@ def test_library_exports_every_declared_symbol(lib):
     assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
     assert lib.xc_version() >= 100
     assert ctypes.sizeof(_lib.xc_peak) == 32
-    assert lib.xc_fastxcorr_supported(8192) == 1 and lib.xc_fastxcorr_supported(100) == 0
+    assert lib.xc_fastxcorr_supported(8192) == 1 and lib.xc_fastxcorr_supported(100) == 1      # any length (Bluestein)
+    assert lib.xc_fastxcorr_supported(16384) == 1 and lib.xc_fastxcorr_supported(8193) == 0 and lib.xc_fastxcorr_supported(1) == 0
 
 
 def test_no_cpu_fallback(lib):
