@@ -145,6 +145,26 @@ int32_t xc_mt_destroy(xc_mt* handle);
  * counterpart; the result tuples are the same either way. */
 int32_t xc_mt_uses_tensor_cores(const xc_mt* handle);
 
+/* ---- a14: gather / copy helpers of the reference's GPU path -----------------------------------
+ * Not on the hot path any more (the fused kernels never materialise windows or products in HBM); kept as thin,
+ * bandwidth-bound compatibility functions.
+ * cupyCopyGroups32fc (cupyExtensions.py:41-83): y[y_starts[g] + i] = x[x_starts[g] + i], i < lengths[g];
+ * no bounds or overlap checks, as in the reference. xlen / ylen are only used to stage HOST buffers. */
+int32_t xc_copy_groups_c64(const void* x, int64_t xlen, void* y, int64_t ylen, const int32_t* x_starts,
+                           const int32_t* y_starts, const int32_t* lengths, int32_t G, int32_t where,
+                           void* stream);
+/* cupyCopyIncrementalEqualSlicesToMatrix_32fc (cupyExtensions.py:161-215 -> copying.cu:83-137):
+ * out[r, c] = x[start + r * increment + c], complex64 (num_rows, row_length); 0 where the index leaves x */
+int32_t xc_copy_slices_to_matrix_c64(const void* x, int64_t xlen, int64_t start, int64_t increment,
+                                     int64_t row_length, int64_t num_rows, void* out, int32_t where,
+                                     void* stream);
+/* multiplySlidesNormalised (cupyExtensions.py:491-560 -> multiplySlices.cu:112-216):
+ * out[r, t] = x[t] * y[start + r + t] / (float)(sqrt(sum_t |y[start + r + t]|^2) * coefficient), complex64
+ * (idxlen, xlen); x is used as given (not conjugated); coefficient <= 0 means the norm of x (the default). */
+int32_t xc_multiply_slides_normalised_c64(const void* x, int32_t xlen, const void* y, int64_t ylen,
+                                          int64_t start, int64_t idxlen, double coefficient, void* out,
+                                          int32_t where, void* stream);
+
 /* ---- a12: row argmax (cupyExtensions.py:268-319 -> argmax.cu:93-152) ------------------------ */
 /* per row of the complex64 (rows, cols) matrix: index of the largest abs(x) (use_normsq == 0) or
  * abs(x)^2 (use_normsq != 0), lowest index on ties; val (optional) receives that value */

@@ -299,3 +299,36 @@ def findLocalMaxima(x, minHeight):
     mid = p[1:-1]
     ok = (mid > np.float32(minHeight)) & (mid > p[:-2]) & (mid > p[2:])
     return np.nonzero(ok)[0].astype(np.int32)
+
+
+# ---------------------------------------------------------------------------------------------
+# a14: gather / copy helpers (restated from the kernels; the reference has no CPU version)
+# ---------------------------------------------------------------------------------------------
+def cupyCopyGroups32fc(x, y, xStarts, yStarts, lengths):
+    """copying.cu copy_groups_kernel32fc via cupyExtensions.py:41-83 (in place on y)."""
+    for xs, ys, n in zip(xStarts, yStarts, lengths):
+        y[ys:ys + n] = x[xs:xs + n]
+
+
+def cupyCopyIncrementalEqualSlicesToMatrix_32fc(x, startIdx, increment, rowLength, numRows):
+    """copying.cu:83-137: rows are slices start + r*increment, zero past the end of x."""
+    out = np.zeros((numRows, rowLength), np.complex64)
+    for r in range(numRows):
+        a = startIdx + r * increment
+        seg = x[a:a + rowLength]
+        out[r, :seg.size] = seg
+    return out
+
+
+def multiplySlidesNormalised(x, y, startIdx, idxlen, coefficient=None):
+    """multiplySlices.cu:112-216: x[t] * y[s + t] / float32(sqrt(window energy in double) * coefficient)."""
+    x = np.asarray(x, np.complex64)
+    coef = float(np.linalg.norm(x.astype(np.complex128))) if coefficient is None else float(np.asarray(coefficient).reshape(-1)[0])
+    out = np.zeros((idxlen, x.size), np.complex64)
+    for r in range(idxlen):
+        seg = np.zeros(x.size, np.complex64)
+        w = y[startIdx + r:startIdx + r + x.size]
+        seg[:w.size] = w
+        e = float(np.sum(np.abs(seg.astype(np.complex128)) ** 2))
+        out[r] = (x * seg) / np.float32(np.sqrt(e) * coef)
+    return out

@@ -100,3 +100,58 @@ def cupyFindLocalMaxima(x, minHeight, numOutputPerBlk=32, THREADS_PER_BLK=32, ma
                                                int(maxNumPeaks), _lib.ptr(numPeaksFound), 1, _lib.where_of(x),
                                                _lib.current_stream(x)))
     return peakIndex, numPeaksFound
+
+
+# ------------------------------------------------------------------------------------------------
+# gather / copy helpers: compatibility functions, not used by the fused paths
+# ------------------------------------------------------------------------------------------------
+def cupyCopyGroups32fc(x, y, xStarts, yStarts, lengths, threads_per_blk=256):
+    """cupyExtensions.py:41-83: y[yStarts[g] : yStarts[g] + lengths[g]] = x[xStarts[g] : ...] for every group,
+    in place; like the reference, no dtype, bounds or overlap checks beyond the equal-length assert."""
+    assert len(xStarts) == len(yStarts) and len(xStarts) == len(lengths)
+    where = _lib.where_of(x, y, xStarts, yStarts, lengths)
+    _select_device(x)
+    if where == _lib.XC_HOST:
+        xStarts, yStarts, lengths = (np.ascontiguousarray(a, dtype=np.int32) for a in (xStarts, yStarts, lengths))
+    check(_lib.load().xc_copy_groups_c64(_lib.ptr(x), int(np.prod(x.shape)), _lib.ptr(y), int(np.prod(y.shape)),
+                                         _lib.ptr(xStarts), _lib.ptr(yStarts), _lib.ptr(lengths), len(xStarts), where,
+                                         _lib.current_stream(x)))
+
+
+def cupyCopyIncrementalEqualSlicesToMatrix_32fc(d_x, startIdx, increment, rowLength, numRows, d_out=None):
+    """cupyExtensions.py:161-215: d_out[r, :] = d_x[startIdx + r * increment : ... + rowLength] (0 past the end)."""
+    cupyRequireDtype(np.complex64, d_x)
+    d_x = _lib.contiguous(d_x)
+    if d_out is None:
+        d_out = _lib.empty_like_space(d_x, (numRows, rowLength), np.complex64)
+    else:
+        cupyRequireDtype(np.complex64, d_out)
+        if tuple(d_out.shape) != (numRows, rowLength):
+            raise ValueError("d_out must have the shape %d, %d" % (numRows, rowLength))
+    _select_device(d_x)
+    check(_lib.load().xc_copy_slices_to_matrix_c64(_lib.ptr(d_x), int(d_x.shape[0]), int(startIdx), int(increment),
+                                                   int(rowLength), int(numRows), _lib.ptr(d_out),
+                                                   _lib.where_of(d_x, d_out), _lib.current_stream(d_x)))
+    return d_out
+
+
+def multiplySlidesNormalised(d_x, d_y, startIdx, idxlen, THREADS_PER_BLOCK=128, numSlidesPerBlk=None, coefficient=None):
+    """cupyExtensions.py:491-560: (idxlen, len(d_x)) complex64 matrix of d_x[t] * d_y[startIdx + r + t] divided by
+    the norm of the d_y window times `coefficient` (a one-element float64 array; default the norm of d_x)."""
+    cupyRequireDtype(np.complex64, d_x)
+    cupyRequireDtype(np.complex64, d_y)
+    if startIdx < 0 or startIdx + idxlen > d_y.shape[0]:
+        raise ValueError("startIdx and idxlen should be within the bounds of d_y.")
+    coef = 0.0
+    if coefficient is not None:
+        cupyRequireDtype(np.float64, coefficient)
+        if int(np.prod(coefficient.shape)) != 1:
+            raise ValueError("coefficient should be a single element 1D array.")
+        coef = float(coefficient.reshape(-1)[0])
+    d_x, d_y = _lib.contiguous(d_x), _lib.contiguous(d_y)
+    _select_device(d_y)
+    out = _lib.empty_like_space(d_y, (int(idxlen), int(d_x.shape[0])), np.complex64)
+    check(_lib.load().xc_multiply_slides_normalised_c64(_lib.ptr(d_x), int(d_x.shape[0]), _lib.ptr(d_y), int(d_y.shape[0]),
+                                                        int(startIdx), int(idxlen), coef, _lib.ptr(out),
+                                                        _lib.where_of(d_x, d_y), _lib.current_stream(d_y)))
+    return out

@@ -450,3 +450,43 @@ def test_mt_dispatch_inexact_templates_take_fp32(xr):
     best, tidx, _, _ = h.run(_dev(x), 0, 937, True, False, False)
     ti_ref, q_ref = orc.multiTemplateSlidingDotProduct(x, templates, 0, 937)
     assert_qf2(best.cpu().numpy(), q_ref)
+
+
+# ---------------------------------------------------------------------------------------------
+# a14: gather / copy helpers
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("space", ["host", "device"])
+def test_copy_helpers_vs_oracle(xr, space):
+    from pydsproutines_b200 import cupyExtensions as ce
+    rng = np.random.default_rng(14)
+    conv = _dev if space == "device" else (lambda a: a.copy())
+    back = (lambda t: t.cpu().numpy()) if space == "device" else (lambda a: a)
+    x = signals.cnoise(rng, 5000)
+    xs = np.array([0, 700, 4100, 33], np.int32)
+    ys = np.array([10, 1000, 2500, 3500], np.int32)
+    ln = np.array([300, 1, 900, 257], np.int32)
+    y0 = signals.cnoise(rng, 4000)
+    y_ref = y0.copy()
+    orc.cupyCopyGroups32fc(x, y_ref, xs, ys, ln)
+    y = conv(y0)
+    ce.cupyCopyGroups32fc(conv(x), y, conv(xs), conv(ys), conv(ln))
+    assert np.array_equal(back(y), y_ref)
+    for start, inc, rowlen, rows in ((0, 1, 64, 10), (17, 300, 1000, 16), (4000, 7, 500, 40)):    # the last one runs off the end
+        m = back(ce.cupyCopyIncrementalEqualSlicesToMatrix_32fc(conv(x), start, inc, rowlen, rows))
+        assert np.array_equal(m, orc.cupyCopyIncrementalEqualSlicesToMatrix_32fc(x, start, inc, rowlen, rows))
+    with pytest.raises(ValueError):
+        ce.cupyCopyIncrementalEqualSlicesToMatrix_32fc(conv(x), 0, 1, 8, 4, conv(np.zeros((4, 9), np.complex64)))
+    t = signals.qpsk(rng, 100)
+    z = back(ce.multiplySlidesNormalised(conv(t), conv(x), 11, 300))
+    np.testing.assert_allclose(z, orc.multiplySlidesNormalised(t, x, 11, 300), rtol=2e-6, atol=1e-7)
+    coef = np.array([2.5], np.float64)
+    z = back(ce.multiplySlidesNormalised(conv(t), conv(x), 4950, 50, coefficient=conv(coef)))             # windows past the end
+    np.testing.assert_allclose(z, orc.multiplySlidesNormalised(t, x, 4950, 50, coef), rtol=2e-6, atol=1e-7)
+    # a row of products summed = the complex QF of fastXcorr at that shift (how cp_fastXcorr_v2 used the matrix)
+    qf = xr.fastXcorr(t, x, absResult=False, shifts=np.arange(11, 311))
+    zz = back(ce.multiplySlidesNormalised(conv(t.conj().copy()), conv(x), 11, 300))
+    np.testing.assert_allclose(np.abs(zz.sum(axis=1)), np.abs(qf), rtol=0, atol=3e-5)
+    with pytest.raises(ValueError):
+        ce.multiplySlidesNormalised(conv(t), conv(x), 4990, 20)
+    with pytest.raises(TypeError):
+        ce.multiplySlidesNormalised(conv(t.astype(np.complex128)) if space == "host" else conv(t).to(dtype=__import__("torch").complex128), conv(x), 0, 5)
