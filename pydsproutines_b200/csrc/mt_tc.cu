@@ -16,10 +16,11 @@
 //     of (row group a, K chunk b) is E[a + b], so the UMMA descriptor simply uses LBO = SBO = 128 bytes --
 //     overlapping core matrices.  (128 + L) / 8 core matrices per plane: 18 KB for L = 1024.
 //   * B operand = templates, repacked once per handle into stage images in canonical K-major core-matrix
-//     order, streamed by 1-D bulk copies (TMA engine) through a ring of stages, 32 samples per stage.
-//   * warp roles: warps 0-3 build E and run the epilogue (TMEM -> registers, |.|^2 / E_t, running max and
-//     lowest arg max, no cross-thread reduction because a thread owns a shift), warp 4 lane 0 = bulk-copy
-//     producer, warp 5 lane 0 = MMA issuer; smem full/empty and TMEM-full mbarriers.
+//     order, streamed by 1-D bulk copies (TMA engine) through a ring of stages, 16 samples per stage.
+//   * warp roles: warps 0-3 build E of the NEXT tile (double buffered) while the MMAs of the current one run,
+//     then run the epilogue (TMEM -> registers, |.|^2 / E_t, running max and lowest arg max, no cross-thread
+//     reduction because a thread owns a shift); warp 4 lane 0 = bulk-copy producer, warp 5 lane 0 = MMA
+//     issuer.  No CTA-wide barrier in the loop: stage full/empty, E full/empty and TMEM full/empty mbarriers.
 #include <vector>
 
 #include "internal.cuh"
@@ -74,37 +75,41 @@ __global__ void mt_tc_inv_energy_kernel(const float* __restrict__ energies, int 
 
 
 // shared-memory carve-up (bytes from the 128-byte aligned base)
+constexpr int TC_SUB = 16;             // template samples per pipeline stage = one K step (half a stage image)
+constexpr int TC_NBAR = 2 * TC_MAX_STAGES + 2 + 2 + 2;   // stage full/empty, E full/empty (x2), TMEM full/empty
 struct TcSmem {
     uint32_t plane, stage, off_stage, off_inv, off_bar, total;
-    int nstages;
+    int nstages, ne;
 };
-__host__ __device__ inline TcSmem tc_smem_layout(int L32, int NT, int NB, int nstages) {
+__host__ __device__ inline TcSmem tc_smem_layout(int L32, int NT, int NB, int nstages, int ne) {
     TcSmem m;
     m.plane = (uint32_t)tc_plane_bytes(L32);
-    m.stage = (uint32_t)tc_stage_bytes(NT);
+    m.stage = (uint32_t)NT * 64;                       // re + im, 16 samples
     m.nstages = nstages;
-    m.off_stage = 4 * m.plane;
+    m.ne = ne;
+    m.off_stage = (uint32_t)ne * 4 * m.plane;
     m.off_inv = m.off_stage + (uint32_t)nstages * m.stage;
     m.off_bar = (m.off_inv + (uint32_t)(NB * NT) * 4 + 15) / 16 * 16;
-    m.total = m.off_bar + (2 * TC_MAX_STAGES + 1) * 8 + 16;
+    m.total = m.off_bar + TC_NBAR * 8 + 16;
     return m;
 }
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
 mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_energy, const int NT, const int NB,
-             const int L32, const int nstages, const float2* __restrict__ x, const int64_t xlen, const int64_t start,
-             const int64_t K, const float* __restrict__ xenergy, float* __restrict__ best_out,
+             const int L32, const int nstages, const int ne, const float2* __restrict__ x, const int64_t xlen,
+             const int64_t start, const int64_t K, const float* __restrict__ xenergy, float* __restrict__ best_out,
              int32_t* __restrict__ tidx_out, const int sqrt_out, const int64_t ntiles, const int64_t tiles_per_cta) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const TcSmem lay = tc_smem_layout(L32, NT, NB, nstages);
-    const int NKC = L32 / TC_KC;
+    const TcSmem lay = tc_smem_layout(L32, NT, NB, nstages, ne);
+    const int NKS = L32 / TC_SUB;          // K steps (= pipeline stages consumed) per template block
     uint8_t* const sE = smem;
     float* const sInv = reinterpret_cast<float*>(smem + lay.off_inv);
     uint64_t* const bars = reinterpret_cast<uint64_t*>(smem + lay.off_bar);
     const uint32_t bar_full = tc::smem_u32(bars), bar_empty = tc::smem_u32(bars + TC_MAX_STAGES),
-                   bar_tfull = tc::smem_u32(bars + 2 * TC_MAX_STAGES);
-    uint32_t* const tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * TC_MAX_STAGES + 1);
+                   bar_efull = tc::smem_u32(bars + 2 * TC_MAX_STAGES), bar_eempty = tc::smem_u32(bars + 2 * TC_MAX_STAGES + 2),
+                   bar_tfull = tc::smem_u32(bars + 2 * TC_MAX_STAGES + 4), bar_tempty = tc::smem_u32(bars + 2 * TC_MAX_STAGES + 5);
+    uint32_t* const tmem_slot = reinterpret_cast<uint32_t*>(bars + TC_NBAR);
     const uint32_t sE_u32 = tc::smem_u32(sE), sStage_u32 = tc::smem_u32(smem + lay.off_stage);
 
     if (tid == 0) {
@@ -112,7 +117,12 @@ mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_ene
             tc::mbar_init(bar_full + 8 * s, 1);
             tc::mbar_init(bar_empty + 8 * s, 1);
         }
-        tc::mbar_init(bar_tfull, 1);
+        for (int b = 0; b < 2; ++b) {
+            tc::mbar_init(bar_efull + 8 * b, 128);     // every builder thread arrives
+            tc::mbar_init(bar_eempty + 8 * b, 1);      // tcgen05.commit of the last MMA that reads the buffer
+        }
+        tc::mbar_init(bar_tfull, 1);                   // tcgen05.commit of the last MMA of an accumulator generation
+        tc::mbar_init(bar_tempty, 128);                // every epilogue thread arrives
         tc::mbar_fence_init();
     }
     if (warp == 0) tc::tmem_alloc(tc::smem_u32(tmem_slot), TC_TMEM_COLS);
@@ -125,100 +135,59 @@ mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_ene
     const int64_t tile0 = (int64_t)blockIdx.x * tiles_per_cta;
     int64_t tile1 = tile0 + tiles_per_cta;
     if (tile1 > ntiles) tile1 = ntiles;
-    uint32_t it_pipe = 0;      // stage-ring position (producer and MMA thread each advance their own copy)
-    uint32_t it_acc = 0;       // accumulator generations (parity of the TMEM-full barrier)
+    const int ntl = (tile1 > tile0) ? (int)(tile1 - tile0) : 0;     // tiles of this CTA
     const uint32_t idesc_pos = tc::instr_desc_bf16(TC_M, NT, 0), idesc_neg = tc::instr_desc_bf16(TC_M, NT, 1);
     const uint32_t b_lbo = (uint32_t)(NT / 8) * 128;
 
-    for (int64_t tile = tile0; tile < tile1; ++tile) {
-        const int64_t s0 = start + tile * TC_M;     // x index of (row 0, n = 0)
-        // ---- expanded x tile: row (u, i) = BF16 hi / lo of x[s0 + 8u + i + j], j = 0..7, for re and im ----
-        {
-            const int rows = (TC_M + L32);          // = 8 U
-            for (int row = tid; row < rows; row += TC_THREADS) {
+    if (warp < 4) {
+        // ===== warps 0-3: build the expanded x tile of the NEXT tile while the MMAs of this one run, then the
+        // epilogue of this tile.  thread = one shift (TMEM lane), columns = templates =====
+        auto build = [&](int i) {
+            const int b = i % ne;
+            const uint32_t use = (uint32_t)(i / ne);
+            tc::mbar_wait(bar_eempty + 8 * b, (use & 1u) ^ 1u);      // the MMAs that read this buffer are done
+            const int64_t s0 = start + (tile0 + i) * TC_M;           // x index of (row 0, n = 0)
+            uint8_t* const E = sE + (size_t)b * 4 * lay.plane;
+            // row (u, i) = BF16 hi / lo of x[s0 + 8u + i + j], j = 0..7, for re and im
+            const int rows = TC_M + L32;                              // = 8 U
+            for (int row = tid; row < rows; row += 128) {
                 const int64_t g = s0 + row;
-                uint32_t w[4][4];                   // [plane][pair of bf16]
+                uint32_t w[4][4];                                     // [plane][pair of bf16]
 #pragma unroll
                 for (int jj = 0; jj < 4; ++jj) {
-                    float2 a = make_float2(0.f, 0.f), b = make_float2(0.f, 0.f);
+                    float2 a = make_float2(0.f, 0.f), c = make_float2(0.f, 0.f);
                     if (g + 2 * jj < xlen) a = __ldg(x + g + 2 * jj);
-                    if (g + 2 * jj + 1 < xlen) b = __ldg(x + g + 2 * jj + 1);
+                    if (g + 2 * jj + 1 < xlen) c = __ldg(x + g + 2 * jj + 1);
                     const __nv_bfloat16 arh = __float2bfloat16_rn(a.x), aih = __float2bfloat16_rn(a.y);
-                    const __nv_bfloat16 brh = __float2bfloat16_rn(b.x), bih = __float2bfloat16_rn(b.y);
+                    const __nv_bfloat16 crh = __float2bfloat16_rn(c.x), cih = __float2bfloat16_rn(c.y);
                     const __nv_bfloat16 arl = __float2bfloat16_rn(a.x - __bfloat162float(arh));
                     const __nv_bfloat16 ail = __float2bfloat16_rn(a.y - __bfloat162float(aih));
-                    const __nv_bfloat16 brl = __float2bfloat16_rn(b.x - __bfloat162float(brh));
-                    const __nv_bfloat16 bil = __float2bfloat16_rn(b.y - __bfloat162float(bih));
+                    const __nv_bfloat16 crl = __float2bfloat16_rn(c.x - __bfloat162float(crh));
+                    const __nv_bfloat16 cil = __float2bfloat16_rn(c.y - __bfloat162float(cih));
                     auto pk = [](__nv_bfloat16 lo, __nv_bfloat16 hi) {
                         return (uint32_t)__bfloat16_as_ushort(lo) | ((uint32_t)__bfloat16_as_ushort(hi) << 16);
                     };
-                    w[0][jj] = pk(arh, brh);
-                    w[1][jj] = pk(arl, brl);
-                    w[2][jj] = pk(aih, bih);
-                    w[3][jj] = pk(ail, bil);
+                    w[0][jj] = pk(arh, crh);
+                    w[1][jj] = pk(arl, crl);
+                    w[2][jj] = pk(aih, cih);
+                    w[3][jj] = pk(ail, cil);
                 }
 #pragma unroll
                 for (int q = 0; q < 4; ++q)
-                    *reinterpret_cast<uint4*>(sE + (size_t)q * lay.plane + (size_t)row * 16) =
+                    *reinterpret_cast<uint4*>(E + (size_t)q * lay.plane + (size_t)row * 16) =
                         make_uint4(w[q][0], w[q][1], w[q][2], w[q][3]);
             }
-        }
-        tc::fence_proxy_async();
-        __syncthreads();
-
-        float bestv = -1.f;
-        int besti = 0;
-        for (int nb = 0; nb < NB; ++nb) {
-            if (warp == 4) {
-                if (lane == 0) {
-                    // ===== producer: one bulk copy per stage =====
-                    const uint8_t* src = pack + (size_t)nb * NKC * lay.stage;
-                    for (int kc = 0; kc < NKC; ++kc) {
-                        const uint32_t st = it_pipe % (uint32_t)nstages, ph = (it_pipe / (uint32_t)nstages) & 1u;
-                        tc::mbar_wait(bar_empty + 8 * st, ph ^ 1u);
-                        tc::mbar_expect_tx(bar_full + 8 * st, lay.stage);
-                        tc::bulk_g2s(sStage_u32 + st * lay.stage, src + (size_t)kc * lay.stage, lay.stage, bar_full + 8 * st);
-                        ++it_pipe;
-                    }
-                }
-            } else if (warp == 5) {
-                if (lane == 0) {
-                    // ===== MMA issuer =====
-                    tc::tc_fence_after();
-                    const uint32_t c_re = tmem, c_im = tmem + 256;
-                    for (int kc = 0; kc < NKC; ++kc) {
-                        const uint32_t st = it_pipe % (uint32_t)nstages, ph = (it_pipe / (uint32_t)nstages) & 1u;
-                        tc::mbar_wait(bar_full + 8 * st, ph);
-                        tc::tc_fence_after();
-                        const uint32_t sb = sStage_u32 + st * lay.stage;
-#pragma unroll
-                        for (int ks = 0; ks < 2; ++ks) {
-                            const uint32_t kk = (uint32_t)(kc * 2 + ks);
-                            const uint32_t acc = (kc > 0 || ks > 0) ? 1u : 0u;
-                            uint64_t a[4], b[2];
-#pragma unroll
-                            for (int q = 0; q < 4; ++q)
-                                a[q] = tc::smem_desc(sE_u32 + (uint32_t)q * lay.plane + 2 * kk * 128, 128, 128);
-#pragma unroll
-                            for (int p = 0; p < 2; ++p)
-                                b[p] = tc::smem_desc(sb + (uint32_t)p * (uint32_t)NT * 64 + 2 * (uint32_t)ks * b_lbo, b_lbo, 128);
-                            tc::umma_bf16(c_re, a[0], b[0], idesc_pos, acc);
-                            tc::umma_bf16(c_re, a[1], b[0], idesc_pos, 1u);
-                            tc::umma_bf16(c_re, a[2], b[1], idesc_neg, 1u);
-                            tc::umma_bf16(c_re, a[3], b[1], idesc_neg, 1u);
-                            tc::umma_bf16(c_im, a[2], b[0], idesc_pos, acc);
-                            tc::umma_bf16(c_im, a[3], b[0], idesc_pos, 1u);
-                            tc::umma_bf16(c_im, a[0], b[1], idesc_pos, 1u);
-                            tc::umma_bf16(c_im, a[1], b[1], idesc_pos, 1u);
-                        }
-                        tc::umma_commit(bar_empty + 8 * st);      // stage free once these MMAs have read it
-                        ++it_pipe;
-                    }
-                    tc::umma_commit(bar_tfull);                   // accumulators complete
-                }
-            } else {
-                // ===== epilogue: thread = one shift (TMEM lane), columns = templates =====
-                tc::mbar_wait(bar_tfull, it_acc & 1u);
+            tc::fence_proxy_async();                                  // generic-proxy stores -> tensor-core reads
+            tc::mbar_arrive(bar_efull + 8 * b);
+        };
+        if (ntl > 0) build(0);
+        uint32_t gen = 0;                                             // accumulator generations
+        for (int i = 0; i < ntl; ++i) {
+            if (i + 1 < ntl) build(i + 1);
+            float bestv = -1.f;
+            int besti = 0;
+            for (int nb = 0; nb < NB; ++nb) {
+                tc::mbar_wait(bar_tfull, gen & 1u);
                 tc::tc_fence_after();
                 const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
                 const float* inv = sInv + nb * NT;
@@ -237,20 +206,83 @@ mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_ene
                     }
                 }
                 tc::tc_fence_before();
+                tc::mbar_arrive(bar_tempty);                          // TMEM may be overwritten
+                ++gen;
             }
-            ++it_acc;
-            __syncwarp();
-            __syncthreads();   // TMEM drained and (last block) E free before the next generation
+            const int64_t o = (tile0 + i) * TC_M + warp * 32 + lane;
+            if (o < K) {
+                const float q = bestv / xenergy[o];
+                if (best_out) best_out[o] = sqrt_out ? sqrtf(q) : q;
+                if (tidx_out) tidx_out[o] = besti;
+            }
         }
-        if (warp < 4) {
-            const int64_t i = tile * TC_M + warp * 32 + lane;
-            if (i < K) {
-                const float q = bestv / xenergy[i];
-                if (best_out) best_out[i] = sqrt_out ? sqrtf(q) : q;
-                if (tidx_out) tidx_out[i] = besti;
+    } else if (warp == 4) {
+        if (lane == 0) {
+            // ===== producer: half a stage image (16 samples: re part + im part) per stage =====
+            uint32_t it = 0;
+            const uint32_t part = (uint32_t)NT * 32;
+            for (int i = 0; i < ntl; ++i)
+                for (int nb = 0; nb < NB; ++nb) {
+                    const uint8_t* src = pack + (size_t)nb * (NKS / 2) * ((size_t)NT * 128);
+                    for (int ks = 0; ks < NKS; ++ks) {
+                        const uint32_t st = it % (uint32_t)nstages, ph = (it / (uint32_t)nstages) & 1u;
+                        tc::mbar_wait(bar_empty + 8 * st, ph ^ 1u);
+                        tc::mbar_expect_tx(bar_full + 8 * st, 2 * part);
+                        const uint8_t* img = src + (size_t)(ks >> 1) * ((size_t)NT * 128) + (size_t)(ks & 1) * part;
+                        const uint32_t dst = sStage_u32 + st * lay.stage;
+                        tc::bulk_g2s(dst, img, part, bar_full + 8 * st);
+                        tc::bulk_g2s(dst + part, img + (size_t)NT * 64, part, bar_full + 8 * st);
+                        ++it;
+                    }
+                }
+        }
+    } else {
+        if (lane == 0) {
+            // ===== MMA issuer =====
+            uint32_t it = 0, gen = 0;
+            const uint32_t c_re = tmem, c_im = tmem + 256;
+            for (int i = 0; i < ntl; ++i) {
+                const int b = i % ne;
+                const uint32_t use = (uint32_t)(i / ne);
+                tc::mbar_wait(bar_efull + 8 * b, use & 1u);
+                const uint32_t eb = sE_u32 + (uint32_t)b * 4 * lay.plane;
+                for (int nb = 0; nb < NB; ++nb) {
+                    tc::mbar_wait(bar_tempty, (gen & 1u) ^ 1u);       // the epilogue has drained the accumulators
+                    tc::tc_fence_after();
+                    for (int ks = 0; ks < NKS; ++ks) {
+                        const uint32_t st = it % (uint32_t)nstages, ph = (it / (uint32_t)nstages) & 1u;
+                        tc::mbar_wait(bar_full + 8 * st, ph);
+                        tc::tc_fence_after();
+                        const uint32_t sb = sStage_u32 + st * lay.stage;
+                        const uint32_t acc = (ks > 0) ? 1u : 0u;
+                        uint64_t a[4], bd[2];
+#pragma unroll
+                        for (int q = 0; q < 4; ++q)
+                            a[q] = tc::smem_desc(eb + (uint32_t)q * lay.plane + 2 * (uint32_t)ks * 128, 128, 128);
+#pragma unroll
+                        for (int p2 = 0; p2 < 2; ++p2) bd[p2] = tc::smem_desc(sb + (uint32_t)p2 * (uint32_t)NT * 32, b_lbo, 128);
+                        tc::umma_bf16(c_re, a[0], bd[0], idesc_pos, acc);
+                        tc::umma_bf16(c_re, a[1], bd[0], idesc_pos, 1u);
+                        tc::umma_bf16(c_re, a[2], bd[1], idesc_neg, 1u);
+                        tc::umma_bf16(c_re, a[3], bd[1], idesc_neg, 1u);
+                        tc::umma_bf16(c_im, a[2], bd[0], idesc_pos, acc);
+                        tc::umma_bf16(c_im, a[3], bd[0], idesc_pos, 1u);
+                        tc::umma_bf16(c_im, a[0], bd[1], idesc_pos, 1u);
+                        tc::umma_bf16(c_im, a[1], bd[1], idesc_pos, 1u);
+                        tc::umma_commit(bar_empty + 8 * st);          // stage free once these MMAs have read it
+                        ++it;
+                    }
+                    tc::umma_commit(bar_tfull);                       // accumulators complete
+                    ++gen;
+                }
+                tc::umma_commit(bar_eempty + 8 * b);                  // x tile buffer free
             }
+            if (ntl > 0)      // every commit has landed before the CTA tears down
+                tc::mbar_wait(bar_eempty + 8 * ((ntl - 1) % ne), (uint32_t)((ntl - 1) / ne) & 1u);
         }
     }
+    tc::tc_fence_before();
+    __syncwarp();
     __syncthreads();
     if (warp == 0) tc::tmem_dealloc(tmem, TC_TMEM_COLS);
 }
@@ -260,9 +292,15 @@ mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_ene
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
-static int tc_pick_stages(int L32, int NT, int NB) {
-    for (int s = TC_MAX_STAGES; s >= 2; --s)
-        if ((int)tc_smem_layout(L32, NT, NB, s).total + 128 <= max_smem_optin()) return s;
+// number of x-tile buffers (2 = the build of the next tile overlaps the MMAs) and of pipeline stages that fit
+static int tc_pick_stages(int L32, int NT, int NB, int* ne_out) {
+    for (int ne = 2; ne >= 1; --ne)
+        for (int s = TC_MAX_STAGES; s >= (ne == 2 ? 3 : 2); --s)
+            if ((int)tc_smem_layout(L32, NT, NB, s, ne).total + 128 <= max_smem_optin()) {
+                *ne_out = ne;
+                return s;
+            }
+    *ne_out = 0;
     return 0;
 }
 
@@ -290,7 +328,8 @@ int32_t mt_tc_prepare(const float2* d_templates, int T, int L, int L8, const flo
         if (e[0] == '1') return XC_OK;            // A/B switch: force the FP32 SIMT kernel
     }
     if (plan->NB * plan->NT > TC_MAX_TEMPLATES) return XC_OK;
-    if (tc_pick_stages(plan->L32, plan->NT, plan->NB) < 2) return XC_OK;
+    int ne_probe = 0;
+    if (tc_pick_stages(plan->L32, plan->NT, plan->NB, &ne_probe) < 2) return XC_OK;
     int cc_major = 0;
     int dev = 0;
     XC_CUDA_TRY(cudaGetDevice(&dev));
@@ -322,8 +361,9 @@ int32_t mt_tc_prepare(const float2* d_templates, int T, int L, int L8, const flo
 int32_t mt_tc_run(const MtTcPlan& plan, const float2* x, int64_t xlen, int64_t start, int64_t K, const float* xenergy,
                   float* best, int32_t* tidx, int sqrt_out, cudaStream_t stream) {
     if (!plan.usable) return fail(XC_ERR_UNSUPPORTED, "tensor-core template plan is not usable");
-    const int nstages = tc_pick_stages(plan.L32, plan.NT, plan.NB);
-    const TcSmem lay = tc_smem_layout(plan.L32, plan.NT, plan.NB, nstages);
+    int ne = 0;
+    const int nstages = tc_pick_stages(plan.L32, plan.NT, plan.NB, &ne);
+    const TcSmem lay = tc_smem_layout(plan.L32, plan.NT, plan.NB, nstages, ne);
     const size_t smem = lay.total + 128;
     static size_t configured = 0;
     if (smem > configured) {
@@ -337,8 +377,8 @@ int32_t mt_tc_run(const MtTcPlan& plan, const float2* x, int64_t xlen, int64_t s
     ctas = (ntiles + per - 1) / per;
     profile_begin(stream);
     mt_tc_kernel<<<(unsigned)ctas, TC_THREADS, smem, stream>>>(reinterpret_cast<const uint8_t*>(plan.d_pack),
-                                                               plan.d_inv_energy, plan.NT, plan.NB, plan.L32, nstages, x,
-                                                               xlen, start, K, xenergy, best, tidx, sqrt_out, ntiles, per);
+                                                               plan.d_inv_energy, plan.NT, plan.NB, plan.L32, nstages, ne,
+                                                               x, xlen, start, K, xenergy, best, tidx, sqrt_out, ntiles, per);
     profile_end(stream);
     XC_LAUNCH_CHECK();
     return XC_OK;
