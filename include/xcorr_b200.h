@@ -140,9 +140,10 @@ int32_t xc_mt_correlate(xc_mt* handle, const void* x, int64_t xlen, int64_t star
                         float* best, int32_t* tidx, void* full, int32_t sqrt_out, xc_peak* peak,
                         int32_t where, void* stream);
 int32_t xc_mt_destroy(xc_mt* handle);
-/* which kernel xc_mt_correlate runs for this handle when `full` is NULL: 1 = tensor cores (tcgen05; the
- * templates are exactly representable in BF16, e.g. any PSK alphabet), 0 = FP32 SIMT.  No reference
- * counterpart; the result tuples are the same either way. */
+/* which kernel xc_mt_correlate runs for this handle when `full` is NULL: 1 = tensor cores (tcgen05: x split
+ * into BF16 hi + lo, templates too unless they are exact in BF16, FP32 accumulation), 0 = FP32 SIMT (the
+ * tile does not fit in shared memory, or more than 2048 templates).  No reference counterpart; the result
+ * tuples are the same either way. */
 int32_t xc_mt_uses_tensor_cores(const xc_mt* handle);
 
 /* ---- a14: gather / copy helpers of the reference's GPU path -----------------------------------

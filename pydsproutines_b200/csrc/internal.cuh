@@ -43,9 +43,10 @@ struct MtTcPlan {
     int L32 = 0;          // template length padded to a multiple of 32 (one pipeline stage = 32 samples)
     int NT = 0;           // templates per block = UMMA N (multiple of 16, <= 256)
     int NB = 0;           // template blocks
-    void* d_pack = nullptr;        // BF16 stage images [NB][L32/32][re, im][canonical K-major core matrices]
+    void* d_pack = nullptr;        // BF16 stage images [NB][L32/32][planes][canonical K-major core matrices]
     float* d_inv_energy = nullptr; // [NB * NT] 1 / E_t (0 for padding templates)
-    bool usable = false;  // templates exactly representable in BF16 and the tile fits in shared memory
+    int planes = 2;       // 2: templates exact in BF16 (re, im); 4: BF16 hi + lo split (re, im, re_lo, im_lo)
+    bool usable = false;  // the tile fits in shared memory (otherwise the FP32 kernel is used)
 };
 int32_t mt_tc_prepare(const float2* d_templates, int T, int L, int L8, const float* d_energies, MtTcPlan* plan);
 void mt_tc_release(MtTcPlan* plan);

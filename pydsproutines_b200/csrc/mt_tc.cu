@@ -8,9 +8,10 @@
 //   * GEMM roles: M = 128 shifts (TMEM lanes), N = up to 256 templates (TMEM columns), K = template samples.
 //     Two FP32 accumulators in TMEM, C_re and C_im, 256 columns each = all 512 columns.
 //       C_re += Xr Tr^T - Xi Ti^T        C_im += Xi Tr^T + Xr Ti^T       (the minus is the A-negate bit)
-//   * precision: templates must be exact in BF16 (any PSK alphabet is); every x plane is split into
-//     BF16 hi + lo, so the products carry 16 mantissa bits of x and the accumulation is FP32: 8 MMAs
-//     (128 x NT x 16) per 16 template samples.  Other template sets take the FP32 SIMT kernel.
+//   * precision: every x plane is split into BF16 hi + lo (16 mantissa bits) and the accumulation is FP32.
+//     Templates that are exact in BF16 (any PSK alphabet) need 8 MMAs (128 x NT x 16) per 16 samples:
+//     (x_hi + x_lo) t.  Other template sets are split too, t = t_hi + t_lo, and take 12: the t_lo part against
+//     x_hi only (the x_lo t_lo term is below 2^-17 of the product).
 //   * A operand = the Hankel matrix X[s, n] = x[s0 + s + n], never materialised: shared memory holds the
 //     8x-expanded tile E[u][i][j] = x[s0 + 8u + i + j] (one 128-byte core matrix per u), and the core matrix
 //     of (row group a, K chunk b) is E[a + b], so the UMMA descriptor simply uses LBO = SBO = 128 bytes --
@@ -42,17 +43,18 @@ __host__ __device__ inline size_t tc_stage_bytes(int NT) { return (size_t)NT * 1
 
 // ---- one-time repack of the templates into stage images; flags inexact BF16 conversions ----
 __global__ void mt_tc_pack_kernel(const float2* __restrict__ templates, int T, int L, int L8, int L32, int NT, int NB,
-                                  __nv_bfloat16* __restrict__ pack, int* __restrict__ inexact) {
+                                  int NP, __nv_bfloat16* __restrict__ pack, int* __restrict__ inexact) {
     const int NKC = L32 / TC_KC;
-    const size_t total = (size_t)NB * NKC * 2 * NT * TC_KC;      // bf16 elements
+    const size_t total = (size_t)NB * NKC * NP * NT * TC_KC;      // bf16 elements
     for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
-        // e = ((((nb * NKC + kc) * 2 + p) * 4 + c8) * (NT / 8) + tg) * 64 + r * 8 + j
+        // e = ((((nb * NKC + kc) * NP + p) * 4 + c8) * (NT / 8) + tg) * 64 + r * 8 + j
+        // plane p: bit 0 = re / im, bit 1 = BF16 hi / lo part (NP = 4 only)
         size_t q = e;
         const int j = q % 8; q /= 8;
         const int r = q % 8; q /= 8;
         const int tg = q % (NT / 8); q /= (NT / 8);
         const int c8 = q % 4; q /= 4;
-        const int p = q % 2; q /= 2;
+        const int p = q % NP; q /= NP;
         const int kc = q % NKC; q /= NKC;
         const int nb = (int)q;
         const int t = nb * NT + tg * 8 + r;
@@ -60,11 +62,11 @@ __global__ void mt_tc_pack_kernel(const float2* __restrict__ templates, int T, i
         float v = 0.f;
         if (t < T && n < L) {
             const float2 s = templates[(size_t)t * L8 + n];
-            v = p ? s.y : s.x;
+            v = (p & 1) ? s.y : s.x;
         }
-        const __nv_bfloat16 b = __float2bfloat16_rn(v);
-        if (__bfloat162float(b) != v) atomicOr(inexact, 1);
-        pack[e] = b;
+        const __nv_bfloat16 hi = __float2bfloat16_rn(v);
+        if (__bfloat162float(hi) != v) atomicOr(inexact, 1);
+        pack[e] = (p & 2) ? __float2bfloat16_rn(v - __bfloat162float(hi)) : hi;
     }
 }
 
@@ -81,10 +83,10 @@ struct TcSmem {
     uint32_t plane, stage, off_stage, off_inv, off_bar, total;
     int nstages, ne;
 };
-__host__ __device__ inline TcSmem tc_smem_layout(int L32, int NT, int NB, int nstages, int ne) {
+__host__ __device__ inline TcSmem tc_smem_layout(int L32, int NT, int NB, int nstages, int ne, int np) {
     TcSmem m;
     m.plane = (uint32_t)tc_plane_bytes(L32);
-    m.stage = (uint32_t)NT * 64;                       // re + im, 16 samples
+    m.stage = (uint32_t)NT * 32 * (uint32_t)np;        // np planes (re, im[, re_lo, im_lo]) of 16 samples
     m.nstages = nstages;
     m.ne = ne;
     m.off_stage = (uint32_t)ne * 4 * m.plane;
@@ -96,12 +98,12 @@ __host__ __device__ inline TcSmem tc_smem_layout(int L32, int NT, int NB, int ns
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
 mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_energy, const int NT, const int NB,
-             const int L32, const int nstages, const int ne, const float2* __restrict__ x, const int64_t xlen,
+             const int L32, const int nstages, const int ne, const int np, const float2* __restrict__ x, const int64_t xlen,
              const int64_t start, const int64_t K, const float* __restrict__ xenergy, float* __restrict__ best_out,
              int32_t* __restrict__ tidx_out, const int sqrt_out, const int64_t ntiles, const int64_t tiles_per_cta) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const TcSmem lay = tc_smem_layout(L32, NT, NB, nstages, ne);
+    const TcSmem lay = tc_smem_layout(L32, NT, NB, nstages, ne, np);
     const int NKS = L32 / TC_SUB;          // K steps (= pipeline stages consumed) per template block
     uint8_t* const sE = smem;
     float* const sInv = reinterpret_cast<float*>(smem + lay.off_inv);
@@ -218,20 +220,21 @@ mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_ene
         }
     } else if (warp == 4) {
         if (lane == 0) {
-            // ===== producer: half a stage image (16 samples: re part + im part) per stage =====
+            // ===== producer: half a stage image (16 samples of every plane) per stage =====
             uint32_t it = 0;
             const uint32_t part = (uint32_t)NT * 32;
+            const size_t image = (size_t)NT * 64 * (size_t)np;       // 32 samples, all planes
             for (int i = 0; i < ntl; ++i)
                 for (int nb = 0; nb < NB; ++nb) {
-                    const uint8_t* src = pack + (size_t)nb * (NKS / 2) * ((size_t)NT * 128);
+                    const uint8_t* src = pack + (size_t)nb * (NKS / 2) * image;
                     for (int ks = 0; ks < NKS; ++ks) {
                         const uint32_t st = it % (uint32_t)nstages, ph = (it / (uint32_t)nstages) & 1u;
                         tc::mbar_wait(bar_empty + 8 * st, ph ^ 1u);
-                        tc::mbar_expect_tx(bar_full + 8 * st, 2 * part);
-                        const uint8_t* img = src + (size_t)(ks >> 1) * ((size_t)NT * 128) + (size_t)(ks & 1) * part;
+                        tc::mbar_expect_tx(bar_full + 8 * st, (uint32_t)np * part);
+                        const uint8_t* img = src + (size_t)(ks >> 1) * image + (size_t)(ks & 1) * part;
                         const uint32_t dst = sStage_u32 + st * lay.stage;
-                        tc::bulk_g2s(dst, img, part, bar_full + 8 * st);
-                        tc::bulk_g2s(dst + part, img + (size_t)NT * 64, part, bar_full + 8 * st);
+                        for (int p2 = 0; p2 < np; ++p2)
+                            tc::bulk_g2s(dst + (uint32_t)p2 * part, img + (size_t)p2 * NT * 64, part, bar_full + 8 * st);
                         ++it;
                     }
                 }
@@ -255,12 +258,12 @@ mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_ene
                         tc::tc_fence_after();
                         const uint32_t sb = sStage_u32 + st * lay.stage;
                         const uint32_t acc = (ks > 0) ? 1u : 0u;
-                        uint64_t a[4], bd[2];
+                        uint64_t a[4], bd[4];
 #pragma unroll
                         for (int q = 0; q < 4; ++q)
                             a[q] = tc::smem_desc(eb + (uint32_t)q * lay.plane + 2 * (uint32_t)ks * 128, 128, 128);
 #pragma unroll
-                        for (int p2 = 0; p2 < 2; ++p2) bd[p2] = tc::smem_desc(sb + (uint32_t)p2 * (uint32_t)NT * 32, b_lbo, 128);
+                        for (int p2 = 0; p2 < 4; ++p2) bd[p2] = tc::smem_desc(sb + (uint32_t)p2 * (uint32_t)NT * 32, b_lbo, 128);
                         tc::umma_bf16(c_re, a[0], bd[0], idesc_pos, acc);
                         tc::umma_bf16(c_re, a[1], bd[0], idesc_pos, 1u);
                         tc::umma_bf16(c_re, a[2], bd[1], idesc_neg, 1u);
@@ -269,6 +272,12 @@ mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_ene
                         tc::umma_bf16(c_im, a[3], bd[0], idesc_pos, 1u);
                         tc::umma_bf16(c_im, a[0], bd[1], idesc_pos, 1u);
                         tc::umma_bf16(c_im, a[1], bd[1], idesc_pos, 1u);
+                        if (np == 4) {      // templates split into BF16 hi + lo: the lo part against x_hi
+                            tc::umma_bf16(c_re, a[0], bd[2], idesc_pos, 1u);
+                            tc::umma_bf16(c_re, a[2], bd[3], idesc_neg, 1u);
+                            tc::umma_bf16(c_im, a[2], bd[2], idesc_pos, 1u);
+                            tc::umma_bf16(c_im, a[0], bd[3], idesc_pos, 1u);
+                        }
                         tc::umma_commit(bar_empty + 8 * st);          // stage free once these MMAs have read it
                         ++it;
                     }
@@ -293,10 +302,10 @@ mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_ene
 // host side
 // ---------------------------------------------------------------------------------------------
 // number of x-tile buffers (2 = the build of the next tile overlaps the MMAs) and of pipeline stages that fit
-static int tc_pick_stages(int L32, int NT, int NB, int* ne_out) {
+static int tc_pick_stages(int L32, int NT, int NB, int np, int* ne_out) {
     for (int ne = 2; ne >= 1; --ne)
         for (int s = TC_MAX_STAGES; s >= (ne == 2 ? 3 : 2); --s)
-            if ((int)tc_smem_layout(L32, NT, NB, s, ne).total + 128 <= max_smem_optin()) {
+            if ((int)tc_smem_layout(L32, NT, NB, s, ne, np).total + 128 <= max_smem_optin()) {
                 *ne_out = ne;
                 return s;
             }
@@ -314,9 +323,9 @@ void mt_tc_release(MtTcPlan* plan) {
 }
 
 // Builds the BF16 stage images of a template set already on the device ([T, L8] float2, conjugated as the
-// caller asked).  plan->usable stays false (and the caller keeps the FP32 kernel) when a template value is
-// not exact in BF16, when there are too many templates for the shared-memory energy table or when the
-// expanded x tile plus two stages do not fit in shared memory.
+// caller asked).  plan->usable stays false (and the caller keeps the FP32 kernel) when there are too many
+// templates for the shared-memory energy table or when the expanded x tile plus two stages do not fit in
+// shared memory.  plan->planes = 2 when every template value is exact in BF16, 4 (hi + lo split) otherwise.
 int32_t mt_tc_prepare(const float2* d_templates, int T, int L, int L8, const float* d_energies, MtTcPlan* plan) {
     plan->usable = false;
     plan->T = T;
@@ -329,30 +338,34 @@ int32_t mt_tc_prepare(const float2* d_templates, int T, int L, int L8, const flo
     }
     if (plan->NB * plan->NT > TC_MAX_TEMPLATES) return XC_OK;
     int ne_probe = 0;
-    if (tc_pick_stages(plan->L32, plan->NT, plan->NB, &ne_probe) < 2) return XC_OK;
+    if (tc_pick_stages(plan->L32, plan->NT, plan->NB, 4, &ne_probe) < 2) return XC_OK;
     int cc_major = 0;
     int dev = 0;
     XC_CUDA_TRY(cudaGetDevice(&dev));
     XC_CUDA_TRY(cudaDeviceGetAttribute(&cc_major, cudaDevAttrComputeCapabilityMajor, dev));
     if (cc_major != 10) return XC_OK;
-    const size_t elems = (size_t)plan->NB * (plan->L32 / TC_KC) * 2 * plan->NT * TC_KC;
     int* d_flag = reinterpret_cast<int*>(workspace(SLOT_TMP3, 256));
     if (!d_flag) return XC_ERR_NOMEM;
-    XC_CUDA_TRY(cudaMemset(d_flag, 0, sizeof(int)));
-    XC_CUDA_TRY(cudaMalloc(&plan->d_pack, elems * sizeof(__nv_bfloat16)));
     XC_CUDA_TRY(cudaMalloc(&plan->d_inv_energy, sizeof(float) * (size_t)plan->NB * plan->NT));
-    const int blocks = (int)((elems + 255) / 256 < 4096 ? (elems + 255) / 256 : 4096);
-    mt_tc_pack_kernel<<<blocks, 256>>>(d_templates, T, L, L8, plan->L32, plan->NT, plan->NB,
-                                       reinterpret_cast<__nv_bfloat16*>(plan->d_pack), d_flag);
-    XC_LAUNCH_CHECK();
     const int n = plan->NB * plan->NT;
     mt_tc_inv_energy_kernel<<<(n + 255) / 256, 256>>>(d_energies, T, n, plan->d_inv_energy);
     XC_LAUNCH_CHECK();
-    int inexact = 0;
-    XC_CUDA_TRY(cudaMemcpy(&inexact, d_flag, sizeof(int), cudaMemcpyDeviceToHost));
-    if (inexact) {
-        mt_tc_release(plan);
-        return XC_OK;
+    // first try the two-plane images (templates exact in BF16); when a value does not survive the conversion,
+    // repack with the BF16 hi + lo split of the templates (four planes, a third precision pass)
+    for (int np = 2; np <= 4; np += 2) {
+        const size_t elems = (size_t)plan->NB * (plan->L32 / TC_KC) * np * plan->NT * TC_KC;
+        XC_CUDA_TRY(cudaMemset(d_flag, 0, sizeof(int)));
+        XC_CUDA_TRY(cudaMalloc(&plan->d_pack, elems * sizeof(__nv_bfloat16)));
+        const int blocks = (int)((elems + 255) / 256 < 4096 ? (elems + 255) / 256 : 4096);
+        mt_tc_pack_kernel<<<blocks, 256>>>(d_templates, T, L, L8, plan->L32, plan->NT, plan->NB, np,
+                                           reinterpret_cast<__nv_bfloat16*>(plan->d_pack), d_flag);
+        XC_LAUNCH_CHECK();
+        int inexact = 0;
+        XC_CUDA_TRY(cudaMemcpy(&inexact, d_flag, sizeof(int), cudaMemcpyDeviceToHost));
+        plan->planes = np;
+        if (!inexact || np == 4) break;
+        cudaFree(plan->d_pack);
+        plan->d_pack = nullptr;
     }
     plan->usable = true;
     return XC_OK;
@@ -362,8 +375,8 @@ int32_t mt_tc_run(const MtTcPlan& plan, const float2* x, int64_t xlen, int64_t s
                   float* best, int32_t* tidx, int sqrt_out, cudaStream_t stream) {
     if (!plan.usable) return fail(XC_ERR_UNSUPPORTED, "tensor-core template plan is not usable");
     int ne = 0;
-    const int nstages = tc_pick_stages(plan.L32, plan.NT, plan.NB, &ne);
-    const TcSmem lay = tc_smem_layout(plan.L32, plan.NT, plan.NB, nstages, ne);
+    const int nstages = tc_pick_stages(plan.L32, plan.NT, plan.NB, plan.planes, &ne);
+    const TcSmem lay = tc_smem_layout(plan.L32, plan.NT, plan.NB, nstages, ne, plan.planes);
     const size_t smem = lay.total + 128;
     static size_t configured = 0;
     if (smem > configured) {
@@ -377,7 +390,7 @@ int32_t mt_tc_run(const MtTcPlan& plan, const float2* x, int64_t xlen, int64_t s
     ctas = (ntiles + per - 1) / per;
     profile_begin(stream);
     mt_tc_kernel<<<(unsigned)ctas, TC_THREADS, smem, stream>>>(reinterpret_cast<const uint8_t*>(plan.d_pack),
-                                                               plan.d_inv_energy, plan.NT, plan.NB, plan.L32, nstages, ne,
+                                                               plan.d_inv_energy, plan.NT, plan.NB, plan.L32, nstages, ne, plan.planes,
                                                                x, xlen, start, K, xenergy, best, tidx, sqrt_out, ntiles, per);
     profile_end(stream);
     XC_LAUNCH_CHECK();

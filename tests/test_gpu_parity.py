@@ -441,15 +441,34 @@ def test_mt_tensor_core_vs_oracle(xr, T, L, n, start):
     assert np.array_equal(tidx_h, tidx)
 
 
-def test_mt_dispatch_inexact_templates_take_fp32(xr):
+def test_mt_inexact_templates_split_hi_lo(xr):
+    """Templates that are not exact in BF16 (frequency-shifted copies, scaled symbols): hi + lo split, 12 MMAs per
+    K step; the FP32 kernel (XC_MT_FP32=1 at create time, or the full (T, K) output) must agree."""
+    import os
     rng = np.random.default_rng(5)
-    templates = (signals.qpsk(rng, 4 * 64).reshape(4, 64) * np.float32(1.234)).astype(np.complex64)
+    base = signals.qpsk(rng, 4 * 200).reshape(4, 200)
+    tones = np.exp(2j * np.pi * np.outer(np.array([0.0, 0.013, -0.02, 0.11]), np.arange(200))).astype(np.complex64)
+    templates = (base * tones * np.float32(1.234)).astype(np.complex64)
+    x = signals.cnoise(rng, 3000)
+    x[700:900] += 2.0 * templates[2].conj()
+    K = 3000 - 200 + 1
     h = xr._MtHandle(templates, False)
-    assert not h.uses_tensor_cores
-    x = signals.cnoise(rng, 1000)
-    best, tidx, _, _ = h.run(_dev(x), 0, 937, True, False, False)
-    ti_ref, q_ref = orc.multiTemplateSlidingDotProduct(x, templates, 0, 937)
-    assert_qf2(best.cpu().numpy(), q_ref)
+    assert h.uses_tensor_cores
+    best, tidx, _, _ = h.run(_dev(x), 0, K, True, False, False)
+    best, tidx = best.cpu().numpy(), tidx.cpu().numpy()
+    ti_ref, q_ref = orc.multiTemplateSlidingDotProduct(x, templates, 0, K)
+    assert_qf2(best, q_ref)
+    assert int(np.argmax(best)) == 700 and tidx[700] == 2
+    assert (tidx != ti_ref).sum() <= K // 100
+    os.environ["XC_MT_FP32"] = "1"
+    try:
+        h32 = xr._MtHandle(templates, False)
+    finally:
+        del os.environ["XC_MT_FP32"]
+    assert not h32.uses_tensor_cores
+    b32, t32, _, _ = h32.run(_dev(x), 0, K, True, False, False)
+    np.testing.assert_allclose(best, b32.cpu().numpy(), rtol=1e-4, atol=1e-9)
+    assert (tidx != t32.cpu().numpy()).sum() <= K // 100
 
 
 # ---------------------------------------------------------------------------------------------
