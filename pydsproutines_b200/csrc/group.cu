@@ -25,6 +25,7 @@ struct xc_group {
     float2* d_ell_y;         // [rows * TG]
     int32_t* d_ell_off;      // [rows * TG]
     int32_t* d_slot_base;    // [V + 1]
+    int32_t* d_row_base;     // [rows] when every contributor row is a run off = row_base + t, else NULL
     float* d_refn;           // ||ygroups||^2
     int32_t rows;
     int32_t log2m;           // block-FFT plan: log2(F) when F is a power of two, else the padded Bluestein length
@@ -46,6 +47,7 @@ struct GroupLoader {
     const int32_t* ell_off;
     const int32_t* slot_base_g;   // global [V + 1]
     int64_t lo, hi;               // valid shifts satisfy s + lo >= 0 and s + hi <= rxlen
+    const int32_t* row_base;      // [rows] or NULL: offsets are row_base[j] + t (clamped into [lo, hi)), no per-thread table
 
     // shared-memory tables: slot_base[V + 1], then the list of non-empty slots ne[V] and their count
     __host__ __device__ static constexpr size_t smem_bytes() { return ((sizeof(int32_t) * (2 * PL::V + 2) + 15) / 16) * 16; }
@@ -83,19 +85,39 @@ struct GroupLoader {
             const int j0 = slot_base[c], j1 = slot_base[c + 1];
             // lists are padded to a multiple of ELL_UNROLL (zero weights): all index / weight / sample loads
             // of a batch are issued before the first dependent one is used
+            if (row_base) {
+                // run-structured lists (every group contributes consecutive samples to consecutive cells): the
+                // sample address does not depend on a loaded offset, so weights and samples go out together
+                const int omin = (int)lo, omax = (int)hi - 1;
 #pragma unroll 1
-            for (int j = j0; j < j1; j += ELL_UNROLL) {
-                int off[ELL_UNROLL];
-                float2 y[ELL_UNROLL], r[ELL_UNROLL];
+                for (int j = j0; j < j1; j += ELL_UNROLL) {
+                    float2 y[ELL_UNROLL], r[ELL_UNROLL];
 #pragma unroll
-                for (int u = 0; u < ELL_UNROLL; ++u) off[u] = __ldg(ell_off + (size_t)(j + u) * PL::TG + t);
+                    for (int u = 0; u < ELL_UNROLL; ++u) {
+                        const int o = min(max(__ldg(row_base + j + u) + t, omin), omax);
+                        r[u] = __ldg(x + o);
+                    }
 #pragma unroll
-                for (int u = 0; u < ELL_UNROLL; ++u) y[u] = __ldg(ell_y + (size_t)(j + u) * PL::TG + t);
+                    for (int u = 0; u < ELL_UNROLL; ++u) y[u] = __ldg(ell_y + (size_t)(j + u) * PL::TG + t);
 #pragma unroll
-                for (int u = 0; u < ELL_UNROLL; ++u) r[u] = __ldg(x + off[u]);
+                    for (int u = 0; u < ELL_UNROLL; ++u) acc = pfma(make_float2(r[u].y, r[u].x), make_float2(-y[u].y, y[u].y),
+                                                                  pfma(r[u], make_float2(y[u].x, y[u].x), acc));
+                }
+            } else {
+#pragma unroll 1
+                for (int j = j0; j < j1; j += ELL_UNROLL) {
+                    int off[ELL_UNROLL];
+                    float2 y[ELL_UNROLL], r[ELL_UNROLL];
 #pragma unroll
-                for (int u = 0; u < ELL_UNROLL; ++u) acc = pfma(make_float2(r[u].y, r[u].x), make_float2(-y[u].y, y[u].y),
-                                                              pfma(r[u], make_float2(y[u].x, y[u].x), acc));
+                    for (int u = 0; u < ELL_UNROLL; ++u) off[u] = __ldg(ell_off + (size_t)(j + u) * PL::TG + t);
+#pragma unroll
+                    for (int u = 0; u < ELL_UNROLL; ++u) y[u] = __ldg(ell_y + (size_t)(j + u) * PL::TG + t);
+#pragma unroll
+                    for (int u = 0; u < ELL_UNROLL; ++u) r[u] = __ldg(x + off[u]);
+#pragma unroll
+                    for (int u = 0; u < ELL_UNROLL; ++u) acc = pfma(make_float2(r[u].y, r[u].x), make_float2(-y[u].y, y[u].y),
+                                                                  pfma(r[u], make_float2(y[u].x, y[u].x), acc));
+                }
             }
 #define XC_SLOT(n) case n: if (n < PL::V) v[(n < PL::V) ? n : 0] = acc; break;
             switch (c) {
@@ -176,6 +198,34 @@ struct GroupBuilder {
             }
         }
         h->rows = nrows;
+        // run structure: in every row the real contributors sit at off = base + t
+        {
+            std::vector<int32_t> rb((size_t)(nrows > 0 ? nrows : 1), (int32_t)h->min_start);
+            std::vector<char> has((size_t)(nrows > 0 ? nrows : 1), 0);
+            bool runs = true;
+            for (int c = 0; c < V && runs; ++c) {
+                const int q = c / PL::R1, n1 = c % PL::R1;
+                for (int t = 0; t < TG && runs; ++t) {
+                    const int m = n1 * PL::M1 + t + TG * q;
+                    for (size_t j = 0; j < rows[m].size(); ++j) {
+                        const size_t r = (size_t)base[c] + j;
+                        const int32_t b0 = rows[m][j].off - t;
+                        if (!has[r]) {
+                            has[r] = 1;
+                            rb[r] = b0;
+                        } else if (rb[r] != b0) {
+                            runs = false;
+                            break;
+                        }
+                    }
+                }
+            }
+            h->d_row_base = nullptr;
+            if (runs && nrows > 0) {
+                XC_CUDA_TRY(cudaMalloc(&h->d_row_base, sizeof(int32_t) * rb.size()));
+                XC_CUDA_TRY(cudaMemcpy(h->d_row_base, rb.data(), sizeof(int32_t) * rb.size(), cudaMemcpyHostToDevice));
+            }
+        }
         XC_CUDA_TRY(cudaMalloc(&h->d_ell_y, sizeof(float2) * ey.size()));
         XC_CUDA_TRY(cudaMalloc(&h->d_ell_off, sizeof(int32_t) * eo.size()));
         XC_CUDA_TRY(cudaMalloc(&h->d_slot_base, sizeof(int32_t) * (V + 1)));
@@ -198,7 +248,7 @@ struct GroupRunner {
         using PF = PlanFor<LOG2N>;
         using LD = GroupLoader<typename PF::PL>;
         LD ld{rx, rxlen, sl.shift0, sl.step, sl.shifts, h->d_ell_y, h->d_ell_off, h->d_slot_base,
-              h->min_start, h->span};
+              h->min_start, h->span, h->d_row_base};
         if (h->blue) {
             if constexpr (PF::PL::P >= 2) {
                 return launch_bluestein<typename PF::PL, PF::B, LD>(ld, out, sl.K, h->d_bhat_perm, h->F, stream);
@@ -291,6 +341,7 @@ int32_t xc_group_destroy(xc_group* h) {
     cudaFree(h->d_ell_y);
     cudaFree(h->d_ell_off);
     cudaFree(h->d_slot_base);
+    cudaFree(h->d_row_base);
     cudaFree(h->d_refn);
     cudaFree(h->d_starts);
     delete h;
