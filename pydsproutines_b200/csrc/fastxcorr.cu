@@ -27,6 +27,7 @@ struct CutoutLoader {
     const int64_t* shifts;
 
     __host__ __device__ static constexpr size_t smem_bytes() { return CUT_SMEM ? sizeof(float2) * PL::N : 0; }
+    size_t dyn_smem() const { return 0; }
 
     // conj(cutout) into shared memory
     __device__ __forceinline__ void prepare(int tid, int nthreads, unsigned char* smem) const {
@@ -91,6 +92,7 @@ struct ChirpLoader {
     int nvalid;
 
     __host__ __device__ static constexpr size_t smem_bytes() { return CUT_SMEM ? sizeof(float2) * PL::N : 0; }
+    size_t dyn_smem() const { return 0; }
     __device__ __forceinline__ void prepare(int tid, int nthreads, unsigned char* smem) const {
         if (CUT_SMEM) {
             float2* cc = reinterpret_cast<float2*>(smem);

@@ -35,7 +35,7 @@ struct xc_group {
 
 namespace xc {
 
-constexpr int ELL_UNROLL = 8;
+constexpr int ELL_UNROLL = 16;
 
 template <class PL>
 struct GroupLoader {
@@ -48,6 +48,10 @@ struct GroupLoader {
     const int32_t* slot_base_g;   // global [V + 1]
     int64_t lo, hi;               // valid shifts satisfy s + lo >= 0 and s + hi <= rxlen
     const int32_t* row_base;      // [rows] or NULL: offsets are row_base[j] + t (clamped into [lo, hi)), no per-thread table
+    int32_t rows;                 // contributor rows (each TG weights)
+    int32_t y_smem_off;           // byte offset of the shared-memory copy of ell_y behind the static carve-up, -1 = none
+
+    size_t dyn_smem() const { return y_smem_off >= 0 ? sizeof(float2) * (size_t)rows * PL::TG + 16 : 0; }   // + alignment slack
 
     // shared-memory tables: slot_base[V + 1], then the list of non-empty slots ne[V] and their count
     __host__ __device__ static constexpr size_t smem_bytes() { return ((sizeof(int32_t) * (2 * PL::V + 2) + 15) / 16) * 16; }
@@ -62,6 +66,10 @@ struct GroupLoader {
                 if (slot_base_g[c + 1] > slot_base_g[c]) ne[n++] = c;
             ne[PL::V] = n;
         }
+        if (y_smem_off >= 0) {      // the weights never change: keep them next to the FFT buffers
+            float2* ys = reinterpret_cast<float2*>(smem + y_smem_off);
+            for (int i = tid; i < rows * PL::TG; i += nthreads) ys[i] = ell_y[i];
+        }
     }
     __device__ __forceinline__ bool issue(float2* v, int t, int64_t i, const unsigned char* smem) const {
         return load(v, t, i, smem);
@@ -75,6 +83,8 @@ struct GroupLoader {
         const int64_t s = shifts ? shifts[i] : shift0 + i * step;
         if (s + lo < 0 || s + hi > rxlen) return false;
         const float2* x = rx + s;
+        // weights: shared-memory copy when it fits (generic pointer either way)
+        const float2* const yp = (y_smem_off >= 0) ? reinterpret_cast<const float2*>(smem + y_smem_off) : ell_y;
 #pragma unroll
         for (int c = 0; c < PL::V; ++c) v[c] = make_float2(0.f, 0.f);
         const int n_ne = ne[PL::V];
@@ -98,7 +108,7 @@ struct GroupLoader {
                         r[u] = __ldg(x + o);
                     }
 #pragma unroll
-                    for (int u = 0; u < ELL_UNROLL; ++u) y[u] = __ldg(ell_y + (size_t)(j + u) * PL::TG + t);
+                    for (int u = 0; u < ELL_UNROLL; ++u) y[u] = yp[(size_t)(j + u) * PL::TG + t];
 #pragma unroll
                     for (int u = 0; u < ELL_UNROLL; ++u) acc = pfma(make_float2(r[u].y, r[u].x), make_float2(-y[u].y, y[u].y),
                                                                   pfma(r[u], make_float2(y[u].x, y[u].x), acc));
@@ -111,7 +121,7 @@ struct GroupLoader {
 #pragma unroll
                     for (int u = 0; u < ELL_UNROLL; ++u) off[u] = __ldg(ell_off + (size_t)(j + u) * PL::TG + t);
 #pragma unroll
-                    for (int u = 0; u < ELL_UNROLL; ++u) y[u] = __ldg(ell_y + (size_t)(j + u) * PL::TG + t);
+                    for (int u = 0; u < ELL_UNROLL; ++u) y[u] = yp[(size_t)(j + u) * PL::TG + t];
 #pragma unroll
                     for (int u = 0; u < ELL_UNROLL; ++u) r[u] = __ldg(x + off[u]);
 #pragma unroll
@@ -247,8 +257,12 @@ struct GroupRunner {
     int32_t run() {
         using PF = PlanFor<LOG2N>;
         using LD = GroupLoader<typename PF::PL>;
+        // the weights move into shared memory when they fit behind the static carve-up
+        const size_t stat = (fused_smem_bytes<typename PF::PL, PF::B, LD>() + 15) / 16 * 16;
+        const size_t ybytes = sizeof(float2) * (size_t)h->rows * PF::PL::TG;
+        const int32_t yoff = (h->rows > 0 && stat + ybytes + 16 <= (size_t)max_smem_optin()) ? (int32_t)stat : -1;
         LD ld{rx, rxlen, sl.shift0, sl.step, sl.shifts, h->d_ell_y, h->d_ell_off, h->d_slot_base,
-              h->min_start, h->span, h->d_row_base};
+              h->min_start, h->span, h->d_row_base, h->rows, yoff};
         if (h->blue) {
             if constexpr (PF::PL::P >= 2) {
                 return launch_bluestein<typename PF::PL, PF::B, LD>(ld, out, sl.K, h->d_bhat_perm, h->F, stream);
