@@ -172,7 +172,7 @@ struct BluePlan {
     float2* d_b = nullptr;          // [M]: b[n] = exp(+i pi n^2 / N) for n < N, 0 beyond
     float2* d_bhat_perm = nullptr;  // [M]: FFT_M(b extended)[output_bin(t, slot)] at slot * TG + t
 };
-static std::map<int, BluePlan> g_blue;
+static std::map<std::pair<int, int>, BluePlan> g_blue;    // keyed by (device, length)
 
 struct cd {
     double re, im;
@@ -215,7 +215,10 @@ struct BluePermute {
 };
 
 static int32_t blue_plan_for(int N, const BluePlan** out) {
-    auto it = g_blue.find(N);
+    int dev = 0;
+    XC_CUDA_TRY(cudaGetDevice(&dev));
+    const std::pair<int, int> key(dev, N);
+    auto it = g_blue.find(key);
     if (it != g_blue.end()) {
         *out = &it->second;
         return XC_OK;
@@ -240,7 +243,7 @@ static int32_t blue_plan_for(int N, const BluePlan** out) {
     XC_CUDA_TRY(cudaMalloc(&p.d_bhat_perm, sizeof(float2) * M));
     XC_CUDA_TRY(cudaMemcpy(p.d_b, hb.data(), sizeof(float2) * M, cudaMemcpyHostToDevice));
     XC_CUDA_TRY(cudaMemcpy(p.d_bhat_perm, perm.data(), sizeof(float2) * M, cudaMemcpyHostToDevice));
-    *out = &(g_blue[N] = p);
+    *out = &(g_blue[key] = p);
     return XC_OK;
 }
 
