@@ -105,7 +105,7 @@ int32_t xc_fastxcorr_caf_c64(const void* cutout, int32_t N, const void* rx, int6
                              int64_t shift0, int64_t step, int64_t K, const int64_t* shifts,
                              void* caf, int32_t complex_out, int32_t where, void* stream);
 /* 1 when the fused frequency-search kernel takes this cutout length: powers of two 2..16384 (one block FFT per
- * shift) and every other length 3..8192 (Bluestein: two block FFTs per shift; flattened outputs only) */
+ * shift) and every other length 3..8192 (Bluestein: two block FFTs per shift) */
 int32_t xc_fastxcorr_supported(int32_t N);
 
 /* ---- a7, a8: GroupXcorrFFT ----------------------------------------------------------------

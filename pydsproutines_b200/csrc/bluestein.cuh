@@ -19,7 +19,8 @@ __device__ __forceinline__ int blue_cell(int i) { return i + ((i >> 5) << 1); }
 template <class PL, int B, class Loader>
 __global__ void __launch_bounds__(PL::TG* B)
 fused_bluestein_kernel(const Loader loader, const FusedOut out, const int64_t K, const int chunk,
-                       const float2* __restrict__ bhat_perm, const int nbins, const float inv_m2) {
+                       const float2* __restrict__ bhat_perm, const float2* __restrict__ chirp, const int nbins,
+                       const float inv_m2) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int TG = PL::TG, V = PL::V, NW = (TG + 31) / 32;
     static_assert(PL::P >= 2, "the Bluestein path needs an exchange buffer");
@@ -85,8 +86,36 @@ fused_bluestein_kernel(const Loader loader, const FusedOut out, const int64_t K,
         bar();    // all reads done before the pass-1 stores of FFT #2
         // ---- FFT #2 ----
         block_fft<PL>(v, th, tab, buf, t, bar);
-        // ---- |X[k]|^2 for k < N, group max, lowest arg max ----
         const unsigned int bbase = (unsigned int)output_bin_base<PL>(t);
+        if (out.caf) {
+            // ---- CAF row (natural order, nbins columns): |X[k]|^2 scaled, or X[k] = conj(b[k]) conj(v) / M ----
+            if (active) {
+                const float refn = *out.refnormsq;
+                const float denom_e = ok ? out.energy[i0 + it] : 1.f;
+                const float sc2 = ok ? inv_m2 / refn / denom_e : 0.f;
+                const float sc1 = ok ? sqrtf(inv_m2) / (sqrtf(refn) * sqrtf(denom_e)) : 0.f;
+#pragma unroll
+                for (int q = 0; q < V / PL::RL; ++q)
+#pragma unroll
+                    for (int j = 0; j < PL::RL; ++j) {
+                        const unsigned int bin = bbase + (unsigned int)output_bin_off<PL>(q, j);
+                        if (bin < (unsigned int)nbins) {
+                            const float2 x = v[q * PL::RL + j];
+                            if (out.caf_complex) {
+                                const float2 b = __ldg(chirp + bin);
+                                // conj(b) * conj(x) = conj(b x)
+                                const float2 p = cmul(b, x);
+                                reinterpret_cast<float2*>(out.caf)[(size_t)(i0 + it) * nbins + bin] = make_float2(p.x * sc1, -p.y * sc1);
+                            } else {
+                                out.caf[(size_t)(i0 + it) * nbins + bin] = cnorm2(x) * sc2;
+                            }
+                        }
+                    }
+            }
+            bar();   // buffer free for the next iteration
+            continue;
+        }
+        // ---- |X[k]|^2 for k < N, group max, lowest arg max ----
         float tmax = -1.f;
 #pragma unroll
         for (int q = 0; q < V / PL::RL; ++q)
@@ -115,10 +144,27 @@ fused_bluestein_kernel(const Loader loader, const FusedOut out, const int64_t K,
                 }
             atomicMin(binmin, mybin);
         }
+        if (out.cplx) {   // complex QF at the winning bin: one more barrier to learn it
+            bar();
+            const unsigned int b = *binmin;
+            if (ok && tmax == m) {
+                const float sc = sqrtf(inv_m2) / (sqrtf(*out.refnormsq) * sqrtf(out.energy[i0 + it]));
+#pragma unroll
+                for (int q = 0; q < V / PL::RL; ++q)
+#pragma unroll
+                    for (int j = 0; j < PL::RL; ++j)
+                        if (bbase + (unsigned int)output_bin_off<PL>(q, j) == b) {
+                            const float2 p = cmul(__ldg(chirp + b), v[q * PL::RL + j]);
+                            out.cplx[i0 + it] = make_float2(p.x * sc, -p.y * sc);
+                        }
+            }
+            if (active && !ok && t == 0) out.cplx[i0 + it] = make_float2(0.f, 0.f);
+            bar();
+        }
         if (t == 0 && active) *pend = ok ? m * inv_m2 / *out.refnormsq / out.energy[i0 + it] : 0.f;
     }
     bar();
-    if (t == 0 && n_act == chunk) {
+    if (t == 0 && n_act == chunk && !out.caf) {
         const unsigned int b = *binmin;
         if (out.qf2) out.qf2[i0 + chunk - 1] = *pend;
         if (out.fidx) out.fidx[i0 + chunk - 1] = (b == 0xffffffffu) ? 0u : b;
@@ -127,8 +173,8 @@ fused_bluestein_kernel(const Loader loader, const FusedOut out, const int64_t K,
 
 // Persistent launch, as launch_fused_variant(): `nbins` = the true transform length N, PL::N = the padded length M.
 template <class PL, int B, class Loader>
-int32_t launch_bluestein(const Loader& ld, const FusedOut& out, int64_t K, const float2* bhat_perm, int nbins,
-                         cudaStream_t stream) {
+int32_t launch_bluestein(const Loader& ld, const FusedOut& out, int64_t K, const float2* bhat_perm, const float2* chirp,
+                         int nbins, cudaStream_t stream) {
     auto kern = fused_bluestein_kernel<PL, B, Loader>;
     const size_t dyn = ld.dyn_smem();
     const size_t smem = fused_smem_bytes<PL, B, Loader>() + dyn;
@@ -155,7 +201,7 @@ int32_t launch_bluestein(const Loader& ld, const FusedOut& out, int64_t K, const
     if (chunk >= (1ll << 31)) return fail(XC_ERR_UNSUPPORTED, "too many shifts per thread group");
     const double m = (double)PL::N;
     profile_begin(stream);
-    kern<<<(unsigned)ctas, PL::TG * B, smem, stream>>>(ld, out, K, (int)chunk, bhat_perm, nbins, (float)(1.0 / (m * m)));
+    kern<<<(unsigned)ctas, PL::TG * B, smem, stream>>>(ld, out, K, (int)chunk, bhat_perm, chirp, nbins, (float)(1.0 / (m * m)));
     profile_end(stream);
     XC_LAUNCH_CHECK();
     return XC_OK;

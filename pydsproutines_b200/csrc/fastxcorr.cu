@@ -247,13 +247,14 @@ static int32_t blue_plan_for(int N, const BluePlan** out) {
     return XC_OK;
 }
 
-int32_t bluestein_tables(int N, int* log2m, const float2** d_bhat_perm) {
+int32_t bluestein_tables(int N, int* log2m, const float2** d_bhat_perm, const float2** d_chirp) {
     if (N < 3 || bluestein_log2m(N) > MAX_LOG2N)
         return fail(XC_ERR_UNSUPPORTED, "no Bluestein plan for length %d (limit %d)", N, 1 << (MAX_LOG2N - 1));
     const BluePlan* plan = nullptr;
     XC_TRY(blue_plan_for(N, &plan));
     *log2m = plan->log2m;
     *d_bhat_perm = plan->d_bhat_perm;
+    *d_chirp = plan->d_b;
     return XC_OK;
 }
 
@@ -280,7 +281,7 @@ struct BlueRunner {
         if constexpr (PL::P >= 2) {
             using LD = ChirpLoader<PL, PF::CS>;
             LD ld{rx, rxlen, cutb, sl.shift0, sl.step, sl.shifts, N};
-            return launch_bluestein<PL, PF::B, LD>(ld, out, sl.K, plan->d_bhat_perm, N, stream);
+            return launch_bluestein<PL, PF::B, LD>(ld, out, sl.K, plan->d_bhat_perm, plan->d_b, N, stream);
         } else {
             return fail(XC_ERR_UNSUPPORTED, "no Bluestein plan for 2^%d points", LOG2N);
         }
@@ -306,9 +307,7 @@ int32_t fastxcorr_freq_device(const float2* cutout, int N, const float2* rx, int
     }
     FusedOut out{qf2, fidx, cplx, reinterpret_cast<float*>(caf), caf_complex, d_energy, d_refn};
     if (!fft_length_supported(N)) {
-        // not a power of two: Bluestein inside the fused kernel (flattened outputs only)
-        if (cplx || caf)
-            return fail(XC_ERR_UNSUPPORTED, "CAF / complex outputs need a power-of-two cutout length, got %d", N);
+        // not a power of two: Bluestein inside the fused kernel
         const BluePlan* plan = nullptr;
         XC_TRY(blue_plan_for(N, &plan));
         const int M = 1 << plan->log2m;

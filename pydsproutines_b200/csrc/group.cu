@@ -31,6 +31,7 @@ struct xc_group {
     int32_t log2m;           // block-FFT plan: log2(F) when F is a power of two, else the padded Bluestein length
     int32_t blue;            // F is not a power of two: chirped weights, two FFTs per shift (bluestein.cuh)
     const float2* d_bhat_perm;   // Bluestein: FFT_M(chirp) in register order (owned by the per-length cache)
+    const float2* d_chirp;       // Bluestein: b[k] = exp(+i pi k^2 / F), k < F
 };
 
 namespace xc {
@@ -265,7 +266,7 @@ struct GroupRunner {
               h->min_start, h->span, h->d_row_base, h->rows, yoff};
         if (h->blue) {
             if constexpr (PF::PL::P >= 2) {
-                return launch_bluestein<typename PF::PL, PF::B, LD>(ld, out, sl.K, h->d_bhat_perm, h->F, stream);
+                return launch_bluestein<typename PF::PL, PF::B, LD>(ld, out, sl.K, h->d_bhat_perm, h->d_chirp, h->F, stream);
             } else {
                 return fail(XC_ERR_UNSUPPORTED, "no Bluestein plan for 2^%d points", LOG2N);
             }
@@ -292,6 +293,7 @@ int32_t xc_group_create(const void* ygroups, int32_t G, int32_t L, const int64_t
     if (F < L) return fail(XC_ERR_ARG, "INVALID_FFTLEN: fftlen %d is shorter than the group length %d", F, L);   // GroupXcorrFFT.cpp:11-14
     int log2m = 0;
     const float2* d_bhat_perm = nullptr;
+    const float2* d_chirp = nullptr;
     const bool blue = !fft_length_supported(F);
     if (blue) {
         if (F < 3 || F > (1 << (MAX_LOG2N - 1)))
@@ -315,7 +317,7 @@ int32_t xc_group_create(const void* ygroups, int32_t G, int32_t L, const int64_t
     memset(h, 0, sizeof(*h));
     h->G = G; h->L = L; h->F = F;
     if (blue) {
-        const int32_t bs = bluestein_tables(F, &log2m, &d_bhat_perm);
+        const int32_t bs = bluestein_tables(F, &log2m, &d_bhat_perm, &d_chirp);
         if (bs != XC_OK) {
             delete h;
             return bs;
@@ -324,6 +326,7 @@ int32_t xc_group_create(const void* ygroups, int32_t G, int32_t L, const int64_t
     h->log2m = log2m;
     h->blue = blue ? 1 : 0;
     h->d_bhat_perm = d_bhat_perm;
+    h->d_chirp = d_chirp;
     h->span = mx + L;
     h->min_start = mn;
     const float2* yin = reinterpret_cast<const float2*>(ygroups);
@@ -368,8 +371,6 @@ int32_t xc_group_xcorr(xc_group* h, const void* rx, int64_t rxlen, int64_t shift
     if (where != XC_HOST && where != XC_DEVICE) return fail(XC_ERR_ARG, "where must be XC_HOST (0) or XC_DEVICE (1)");
     if (!h || !rx) return fail(XC_ERR_ARG, "handle/rx is NULL");
     if (!qf2 && !caf) return fail(XC_ERR_ARG, "qf2 and caf are both NULL");
-    if (caf && h->blue)
-        return fail(XC_ERR_UNSUPPORTED, "CAF rows need a power-of-two fftlen, got %d (the flattened outputs take any)", h->F);
     if (K < 0 || rxlen < h->L) return fail(XC_ERR_ARG, "need K >= 0 and rx at least one group long");
     if (K == 0) {
         if (peak) { memset(peak, 0, sizeof(*peak)); peak->index = -1; }

@@ -27,7 +27,7 @@ int32_t fastxcorr_nofreq_device(const float2* cutout, int N, const float2* rx, i
 
 // Bluestein tables of a transform length that is not a power of two (cached per length): padded plan length and
 // FFT_M(chirp) laid out for the block FFT's output registers
-int32_t bluestein_tables(int N, int* log2m, const float2** d_bhat_perm);
+int32_t bluestein_tables(int N, int* log2m, const float2** d_bhat_perm, const float2** d_chirp);
 
 // misc.cu
 int32_t peak_reduce_device(const float* qf2, const uint32_t* fidx, const int32_t* aux, int64_t K,

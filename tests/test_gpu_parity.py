@@ -86,17 +86,12 @@ def test_fastxcorr_golden(xr, name, d, space):
     assert q.dtype == np.float64
     assert_qf2(q, d["qf2_nofreq"])
     assert np.argmax(q) == np.argmax(d["qf2_nofreq"])
-    pow2 = (len(cutout) & (len(cutout) - 1)) == 0
     q, f = xr.fastXcorr(c, r, freqsearch=True, shifts=shifts)        # any length: Bluestein when not a power of two
     q, f = back(q), back(f)
     assert_qf2(q, d["qf2_freq"])
     assert_bins(f, d["fidx_freq"], lambda i: _spec64(cutout, rx, int(sh[i])))
     k = int(np.argmax(q))
     assert sh[k] == int(d["p0"]) and int(f[k]) == int(d["k0"])
-    if not pow2:
-        with pytest.raises(NotImplementedError):       # CAF / complex outputs of the Bluestein path: not yet
-            xr.fastXcorr(c, r, freqsearch=True, outputCAF=True, shifts=shifts)
-        return
     if "caf" in d.files:
         z = back(xr.fastXcorr(c, r, shifts=shifts, absResult=False))
         np.testing.assert_allclose(z, d["cplx_nofreq"], rtol=0, atol=2e-5 * np.abs(d["cplx_nofreq"]).max())
@@ -125,6 +120,20 @@ def test_fastxcorr_any_length_bluestein_vs_oracle(xr, N):
     assert_bins(f, fr, lambda i: _spec64(cutout, rx, i))
     if N >= 100:      # shorter cutouts do not stand out of the noise
         assert int(np.argmax(q)) == p0 and int(f[p0]) == k0 % N
+    # CAF rows and complex QF through the same Bluestein kernel
+    sub = np.arange(0, min(K, 12))
+    caf_ref = orc.fastXcorr(cutout, rx, freqsearch=True, outputCAF=True, shifts=sub)
+    caf = xr.fastXcorr(cutout, rx, freqsearch=True, outputCAF=True, shifts=sub)
+    assert caf.shape == caf_ref.shape
+    np.testing.assert_allclose(caf, caf_ref, rtol=RTOL, atol=2e-6 * caf_ref.max())
+    z_ref, f_ref = orc.fastXcorr(cutout, rx, freqsearch=True, shifts=sub, absResult=False)
+    z, fz = xr.fastXcorr(cutout, rx, freqsearch=True, shifts=sub, absResult=False)
+    same = np.asarray(fz).astype(np.int64) == np.asarray(f_ref).astype(np.int64)
+    assert same.mean() > 0.9
+    np.testing.assert_allclose(np.asarray(z)[same], np.asarray(z_ref)[same], rtol=0, atol=3e-5 * np.abs(z_ref).max())
+    cafc_ref = orc.fastXcorr(cutout, rx, freqsearch=True, outputCAF=True, shifts=sub, absResult=False)
+    cafc = xr.fastXcorr(cutout, rx, freqsearch=True, outputCAF=True, shifts=sub, absResult=False)
+    np.testing.assert_allclose(cafc, cafc_ref, rtol=0, atol=3e-5 * np.abs(cafc_ref).max())
     # device buffers and a strided shift list
     shifts = np.arange(1, K, 3)
     q2, f2 = xr.fastXcorr(_dev(cutout), _dev(rx), freqsearch=True, shifts=shifts)
@@ -253,9 +262,8 @@ def test_groupxcorr_errors(xr):
         xr.GroupXcorrFFT(y, np.array([0, 20, 40, 60]), 1, fftlen=8)              # fftlen < group length
     with pytest.raises(RuntimeError):
         xr.CyGroupXcorrFFT(y, np.array([0, 20, 40, 60], np.int32), 1, fftlen=8)   # INVALID_FFTLEN
-    obj = xr.GroupXcorrFFT(y, np.array([0, 20, 40, 60]), 1, fftlen=48)           # not a power of two: flattened only
     with pytest.raises(NotImplementedError):
-        obj.xcorr(signals.cnoise(np.random.default_rng(2), 400), np.arange(10), flattenToTime=False)
+        xr.GroupXcorrFFT(y, np.array([0, 20, 40, 60]), 1, fftlen=9000)           # beyond the Bluestein plans
 
 
 @pytest.mark.parametrize("G,L,F,ragged", [(4, 16, 48, False), (5, 20, 20, True), (8, 100, 100, False),
@@ -285,6 +293,13 @@ def test_groupxcorr_any_fftlen_bluestein_vs_oracle(xr, G, L, F, ragged):
     assert int(np.argmax(xc)) == p0 and int(fi[p0]) == k0
     xc2, fi2 = obj.xcorrGPU(_dev(rx), shifts)
     np.testing.assert_allclose(xc2.cpu().numpy(), xc, rtol=1e-6)
+    # CAF rows (flattenToTime=False) and the CAF-only CyGroupXcorrFFT
+    caf_ref = ref.xcorr(rx, shifts[:12], flattenToTime=False)
+    caf = obj.xcorr(rx, shifts[:12], flattenToTime=False)
+    assert caf.shape == caf_ref.shape
+    np.testing.assert_allclose(caf, caf_ref, rtol=RTOL, atol=2e-6 * caf_ref.max())
+    cy = xr.CyGroupXcorrFFT(y, starts.astype(np.int32), 1, fftlen=F)
+    np.testing.assert_allclose(cy.xcorr(rx, shifts[:12].astype(np.int32)), caf_ref, rtol=RTOL, atol=2e-6 * caf_ref.max())
 
 
 # ---------------------------------------------------------------------------------------------
