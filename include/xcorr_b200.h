@@ -104,6 +104,17 @@ int32_t xc_fastxcorr_c64(const void* cutout, int32_t N, const void* rx, int64_t 
 int32_t xc_fastxcorr_caf_c64(const void* cutout, int32_t N, const void* rx, int64_t rxlen,
                              int64_t shift0, int64_t step, int64_t K, const int64_t* shifts,
                              void* caf, int32_t complex_out, int32_t where, void* stream);
+/* ---- 8f-1: chirp-z frequency zoom --------------------------------------------------------------
+ * xcorrRoutines.cztXcorr (xcorrRoutines.py:413-457) with spectralRoutines.CZTCached (spectralRoutines.py:239-309):
+ * per shift the product rx[s:s+N] * conj(cutout) is evaluated on the frequency grid
+ *     f_k = (f0_cycles + k * df_cycles) cycles per sample,  k < nbins      (f / fs in the reference's units)
+ * by the same fused kernel (Bluestein with a general chirp; N + nbins - 1 <= 16384).  qf2[i] = max_k |X[k]|^2 /
+ * ||cutout||^2 / ||rx slice||^2, fidx[i] = arg max, cplx[i] = X[arg max] / ||cutout|| / ||rx slice||,
+ * caf (optional float32 (K, nbins)) = all bins.  Any of the outputs may be NULL. */
+int32_t xc_cztxcorr_c64(const void* cutout, int32_t N, const void* rx, int64_t rxlen, int64_t shift0,
+                        int64_t step, int64_t K, const int64_t* shifts, double f0_cycles, double df_cycles,
+                        int32_t nbins, float* qf2, uint32_t* fidx, void* cplx, float* caf, int32_t where,
+                        void* stream);
 /* 1 when the fused frequency-search kernel takes this cutout length: powers of two 2..16384 (one block FFT per
  * shift) and every other length 3..8192 (Bluestein: two block FFTs per shift) */
 int32_t xc_fastxcorr_supported(int32_t N);

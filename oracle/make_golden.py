@@ -80,10 +80,32 @@ def group_cases(ref):
     return cases
 
 
+def czt_cases(ref):
+    """cztXcorr (xcorrRoutines.py:413-457): a planted cutout with a fractional-bin frequency offset."""
+    cases = {}
+    # name, seed, N, rxlen, p0, f_off (cycles/sample * fs), fs, f1, f2, step
+    specs = [
+        ("n100_fine", 31, 100, 260, 60, 0.0123, 1.0, -0.02, 0.02, 0.0005),
+        ("n1000_hz", 32, 1000, 1200, 90, 37.5, 10000.0, -100.0, 100.0, 2.5),
+        ("n4096_narrow", 33, 4096, 4096 + 40, 17, -3.2, 1000.0, -5.0, 5.0, 0.1),
+    ]
+    for name, seed, N, rxlen, p0, foff, fs, f1, f2, step in specs:
+        rng = np.random.default_rng(seed)
+        cutout = signals.qpsk(rng, N)
+        rx = signals.cnoise(rng, rxlen)
+        rx[p0:p0 + N] += np.complex64(0.8) * cutout * np.exp(2j * np.pi * foff * np.arange(N) / fs).astype(np.complex64)
+        shifts = np.arange(max(p0 - 12, 0), min(p0 + 12, rxlen - N + 1))
+        res, freqs = ref.cztXcorr(cutout, rx, f1, f2, fs, cztStep=step, shifts=shifts)
+        caf, fsearch = ref.cztXcorr(cutout, rx, f1, f2, fs, cztStep=step, outputCAF=True, shifts=shifts)
+        cases[name] = dict(cutout=cutout, rx=rx, shifts=shifts, f1=f1, f2=f2, fs=fs, step=step, p0=p0, foff=foff,
+                           res=res, freqs=freqs, caf=caf.astype(np.float32), fsearch=fsearch)
+    return cases
+
+
 def main():
     ref = ref_import.load()
     os.makedirs(OUT, exist_ok=True)
-    for fam, cases in (("fastxcorr", fastxcorr_cases(ref)), ("groupxcorr", group_cases(ref))):
+    for fam, cases in (("fastxcorr", fastxcorr_cases(ref)), ("groupxcorr", group_cases(ref)), ("cztxcorr", czt_cases(ref))):
         for name, d in cases.items():
             path = os.path.join(OUT, "%s_%s.npz" % (fam, name))
             np.savez_compressed(path, **d)

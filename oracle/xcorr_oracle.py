@@ -332,3 +332,39 @@ def multiplySlidesNormalised(x, y, startIdx, idxlen, coefficient=None):
         e = float(np.sum(np.abs(seg.astype(np.complex128)) ** 2))
         out[r] = (x * seg) / np.float32(np.sqrt(e) * coef)
     return out
+
+
+# ---------------------------------------------------------------------------------------------
+# 8f-1: chirp-z frequency zoom
+# ---------------------------------------------------------------------------------------------
+def cztXcorr(cutout, rx, f_searchMin, f_searchMax, fs, cztStep=0.1, outputCAF=False, shifts=None):
+    """xcorrRoutines.py:413-457 on the grid of CZTCached (spectralRoutines.py:239-309), evaluated directly:
+    X[k] = sum_n pdt[n] exp(-2j pi (f1 + k d) n / fs), d = (f2 - f1 + step) / k  (what the chirp-z transform computes)."""
+    cutout = np.asarray(cutout, np.complex64)
+    rx = np.asarray(rx, np.complex64)
+    N = cutout.size
+    k = int((f_searchMax - f_searchMin) / cztStep + 1)
+    f_search = np.arange(k) * cztStep + f_searchMin
+    d = (f_searchMax - f_searchMin + cztStep) / k
+    if shifts is None:
+        shifts = np.arange(len(rx) - N + 1)
+    n = np.arange(N)
+    E = np.exp(-2j * np.pi * np.outer(f_searchMin + np.arange(k) * d, n) / fs)            # (k, N) complex128
+    cn = np.linalg.norm(cutout)
+    cc = cutout.conj()
+    if outputCAF:
+        out = np.zeros((len(shifts), k))
+        for i, s in enumerate(shifts):
+            sl = rx[s:s + N]
+            X = E @ (sl * cc).astype(np.complex128)
+            out[i] = np.abs(X) ** 2 / np.linalg.norm(sl) ** 2 / cn ** 2
+        return out, f_search
+    res = np.zeros(len(shifts), rx.dtype)
+    freqs = np.zeros(len(shifts))
+    for i, s in enumerate(shifts):
+        sl = rx[s:s + N]
+        X = E @ (sl * cc).astype(np.complex128)
+        mi = int(np.argmax(np.abs(X)))
+        res[i] = X[mi] / np.linalg.norm(sl) / cn
+        freqs[i] = f_search[mi]
+    return res, freqs

@@ -46,6 +46,8 @@ SIGNATURES = {
                                 C.POINTER(xc_peak), _i32, _vp]),
     "xc_fastxcorr_caf_c64": (_i32, [_vp, _i32, _vp, _i64, _i64, _i64, _i64, _vp, _vp, _i32, _i32, _vp]),
     "xc_fastxcorr_supported": (_i32, [_i32]),
+    "xc_cztxcorr_c64": (_i32, [_vp, _i32, _vp, _i64, _i64, _i64, _i64, _vp, C.c_double, C.c_double, _i32, _vp, _vp, _vp, _vp,
+                               _i32, _vp]),
     "xc_group_create": (_i32, [_vp, _i32, _i32, _vp, _i32, _i32, C.POINTER(_vp)]),
     "xc_group_xcorr": (_i32, [_vp, _vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp, _vp, C.POINTER(xc_peak), _i32, _vp]),
     "xc_group_destroy": (_i32, [_vp]),

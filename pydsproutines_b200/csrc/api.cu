@@ -353,6 +353,38 @@ int32_t xc_fastxcorr_caf_c64(const void* cutout, int32_t N, const void* rx, int6
     return finish(where, st);
 }
 
+int32_t xc_cztxcorr_c64(const void* cutout, int32_t N, const void* rx, int64_t rxlen, int64_t shift0, int64_t step,
+                        int64_t K, const int64_t* shifts, double f0_cycles, double df_cycles, int32_t nbins, float* qf2,
+                        uint32_t* fidx, void* cplx, float* caf, int32_t where, void* stream) {
+    XC_TRY(check_where(where));
+    if (!cutout || !rx) return fail(XC_ERR_ARG, "cutout/rx is NULL");
+    if (!qf2 && !cplx && !caf) return fail(XC_ERR_ARG, "qf2, cplx and caf are all NULL");
+    if (nbins < 1) return fail(XC_ERR_ARG, "need at least one frequency bin");
+    XC_TRY(check_shift_args(N, rxlen, shift0, step, K, shifts, 0));
+    XC_TRY(require_device());
+    if (K == 0) return XC_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t cb = sizeof(float) * (size_t)K * (size_t)nbins;
+    int32_t status = XC_OK;
+    const float2* dc = (const float2*)stage_in(SLOT_IN0, cutout, sizeof(float2) * (size_t)N, where, st, &status);
+    const float2* drx = (const float2*)stage_in(SLOT_IN1, rx, sizeof(float2) * (size_t)rxlen, where, st, &status);
+    const int64_t* dsh = (const int64_t*)stage_in(SLOT_IN2, shifts, sizeof(int64_t) * (size_t)K, where, st, &status);
+    float* dq = (float*)stage_out(SLOT_OUT0, qf2, sizeof(float) * (size_t)K, where, &status);
+    uint32_t* df = (uint32_t*)stage_out(SLOT_OUT1, fidx, sizeof(uint32_t) * (size_t)K, where, &status);
+    float2* dz = (float2*)stage_out(SLOT_OUT2, cplx, sizeof(float2) * (size_t)K, where, &status);
+    float* dcaf = (float*)stage_out(SLOT_TMP3, caf, cb, where, &status);
+    XC_TRY(status);
+    ShiftList sl{shift0, step, K, dsh};
+    const CztSpec spec{nbins, f0_cycles, df_cycles};
+    if (dq || df || dz) XC_TRY(fastxcorr_freq_device(dc, N, drx, rxlen, sl, dq, df, dz, nullptr, 0, st, &spec));
+    if (dcaf) XC_TRY(fastxcorr_freq_device(dc, N, drx, rxlen, sl, nullptr, nullptr, nullptr, dcaf, 0, st, &spec));
+    XC_TRY(fetch_out(qf2, dq, sizeof(float) * (size_t)K, where, st));
+    XC_TRY(fetch_out(fidx, df, sizeof(uint32_t) * (size_t)K, where, st));
+    XC_TRY(fetch_out(cplx, dz, sizeof(float2) * (size_t)K, where, st));
+    XC_TRY(fetch_out(caf, dcaf, cb, where, st));
+    return finish(where, st);
+}
+
 int32_t xc_row_argmax_c64(const void* x, int64_t rows, int64_t cols, int32_t use_normsq, uint32_t* idx, float* val,
                           int32_t where, void* stream) {
     XC_TRY(check_where(where));

@@ -6,6 +6,7 @@
 #include <math.h>
 
 #include <map>
+#include <tuple>
 #include <vector>
 
 #include "bluestein.cuh"
@@ -167,16 +168,33 @@ struct FreqRunner {
 // Bluestein plan (per cutout length, cached for the life of the process): the chirp b[n] and FFT_M(b) laid
 // out for the block FFT's output registers
 // ---------------------------------------------------------------------------------------------
-struct BluePlan {
-    int N = 0, log2m = 0;
-    float2* d_b = nullptr;          // [M]: b[n] = exp(+i pi n^2 / N) for n < N, 0 beyond
-    float2* d_bhat_perm = nullptr;  // [M]: FFT_M(b extended)[output_bin(t, slot)] at slot * TG + t
-};
-static std::map<std::pair<int, int>, BluePlan> g_blue;    // keyed by (device, length)
-
 struct cd {
     double re, im;
 };
+
+struct BluePlan {
+    int N = 0, nbins = 0, log2m = 0;
+    float2* d_b = nullptr;          // [M]: pre-chirp conj(aa[n]) = exp(+i 2 pi (a n + w n^2 / 2)) for n < N, 0 beyond
+    float2* d_bhat_perm = nullptr;  // [M]: FFT_M(W^(-d^2/2) wrapped)[output_bin(t, slot)] at slot * TG + t
+    float2* d_post = nullptr;       // [nbins]: exp(+i 2 pi w k^2 / 2); X[k] = conj(d_post[k] v) / M
+};
+// keyed by (device, length, bins, start frequency a, frequency step w) -- a, w in cycles per sample
+static std::map<std::tuple<int, int, int, double, double>, BluePlan> g_blue;
+
+// exp(+i 2 pi (lin + w d^2 / 2)); the DFT case (w = 1/N) reduces d^2 modulo 2N exactly
+static cd chirp_phase(double lin_cycles, double w, long long d, int exact_n) {
+    double frac;
+    if (exact_n > 0) {
+        const long long r = (d * d) % (2LL * exact_n);
+        frac = (double)r / (2.0 * (double)exact_n);
+    } else {
+        const long double q = (long double)w * (long double)d * (long double)d / 2.0L;
+        frac = (double)(q - floorl(q));
+    }
+    const double ang = 2.0 * M_PI * (frac + (lin_cycles - floor(lin_cycles)));
+    return cd{cos(ang), sin(ang)};
+}
+
 static void fft_host_radix2(std::vector<cd>& a) {     // forward DFT, in place, length a power of two
     const size_t n = a.size();
     for (size_t i = 1, j = 0; i < n; ++i) {
@@ -214,10 +232,20 @@ struct BluePermute {
     }
 };
 
-static int32_t blue_plan_for(int N, const BluePlan** out) {
+// plan for X[k] = sum_n p[n] exp(-i 2 pi (a + w k) n), k < nbins (chirp-z).  The DFT of a length that is not a
+// power of two is nbins = N, a = 0, w = 1/N.
+static int czt_log2m(int N, int nbins) {
+    int lg = BLUE_MIN_LOG2M;
+    while ((1 << lg) < N + nbins - 1) ++lg;
+    return lg;
+}
+static int32_t blue_plan_for(int N, const CztSpec* spec, const BluePlan** out) {
     int dev = 0;
     XC_CUDA_TRY(cudaGetDevice(&dev));
-    const std::pair<int, int> key(dev, N);
+    const int nbins = spec ? spec->nbins : N;
+    const double a = spec ? spec->a_cycles : 0.0, w = spec ? spec->w_cycles : 1.0 / (double)N;
+    const int exact_n = spec ? 0 : N;
+    const auto key = std::make_tuple(dev, N, nbins, a, w);
     auto it = g_blue.find(key);
     if (it != g_blue.end()) {
         *out = &it->second;
@@ -225,24 +253,30 @@ static int32_t blue_plan_for(int N, const BluePlan** out) {
     }
     BluePlan p;
     p.N = N;
-    p.log2m = bluestein_log2m(N);
+    p.nbins = nbins;
+    p.log2m = czt_log2m(N, nbins);
+    if (p.log2m > MAX_LOG2N)
+        return fail(XC_ERR_UNSUPPORTED, "chirp-z of %d samples onto %d bins needs more than %d points", N, nbins, 1 << MAX_LOG2N);
     const int M = 1 << p.log2m;
-    std::vector<cd> b(N), ext(M, cd{0.0, 0.0});
-    std::vector<float2> hb(M, make_float2(0.f, 0.f)), perm(M);
+    std::vector<cd> ext(M, cd{0.0, 0.0});
+    std::vector<float2> hb(M, make_float2(0.f, 0.f)), perm(M), post(nbins);
     for (int n = 0; n < N; ++n) {
-        const long long r = ((long long)n * n) % (2LL * N);      // exact phase reduction
-        const double ang = M_PI * (double)r / (double)N;
-        b[n] = cd{cos(ang), sin(ang)};
-        hb[n] = make_float2((float)b[n].re, (float)b[n].im);
-        ext[n] = b[n];
-        if (n > 0) ext[M - n] = b[n];
+        const cd pre = chirp_phase(a * (double)n, w, n, exact_n);
+        hb[n] = make_float2((float)pre.re, (float)pre.im);
+    }
+    for (int d = -(N - 1); d <= nbins - 1; ++d) ext[(d + M) % M] = chirp_phase(0.0, w, d, exact_n);
+    for (int k = 0; k < nbins; ++k) {
+        const cd q = chirp_phase(0.0, w, k, exact_n);
+        post[k] = make_float2((float)q.re, (float)q.im);
     }
     fft_host_radix2(ext);
     XC_TRY(dispatch_log2(p.log2m, BluePermute{ext, perm}));
     XC_CUDA_TRY(cudaMalloc(&p.d_b, sizeof(float2) * M));
     XC_CUDA_TRY(cudaMalloc(&p.d_bhat_perm, sizeof(float2) * M));
+    XC_CUDA_TRY(cudaMalloc(&p.d_post, sizeof(float2) * nbins));
     XC_CUDA_TRY(cudaMemcpy(p.d_b, hb.data(), sizeof(float2) * M, cudaMemcpyHostToDevice));
     XC_CUDA_TRY(cudaMemcpy(p.d_bhat_perm, perm.data(), sizeof(float2) * M, cudaMemcpyHostToDevice));
+    XC_CUDA_TRY(cudaMemcpy(p.d_post, post.data(), sizeof(float2) * nbins, cudaMemcpyHostToDevice));
     *out = &(g_blue[key] = p);
     return XC_OK;
 }
@@ -251,10 +285,10 @@ int32_t bluestein_tables(int N, int* log2m, const float2** d_bhat_perm, const fl
     if (N < 3 || bluestein_log2m(N) > MAX_LOG2N)
         return fail(XC_ERR_UNSUPPORTED, "no Bluestein plan for length %d (limit %d)", N, 1 << (MAX_LOG2N - 1));
     const BluePlan* plan = nullptr;
-    XC_TRY(blue_plan_for(N, &plan));
+    XC_TRY(blue_plan_for(N, nullptr, &plan));
     *log2m = plan->log2m;
     *d_bhat_perm = plan->d_bhat_perm;
-    *d_chirp = plan->d_b;
+    *d_chirp = plan->d_post;
     return XC_OK;
 }
 
@@ -281,7 +315,7 @@ struct BlueRunner {
         if constexpr (PL::P >= 2) {
             using LD = ChirpLoader<PL, PF::CS>;
             LD ld{rx, rxlen, cutb, sl.shift0, sl.step, sl.shifts, N};
-            return launch_bluestein<PL, PF::B, LD>(ld, out, sl.K, plan->d_bhat_perm, plan->d_b, N, stream);
+            return launch_bluestein<PL, PF::B, LD>(ld, out, sl.K, plan->d_bhat_perm, plan->d_post, plan->nbins, stream);
         } else {
             return fail(XC_ERR_UNSUPPORTED, "no Bluestein plan for 2^%d points", LOG2N);
         }
@@ -290,8 +324,12 @@ struct BlueRunner {
 
 int32_t fastxcorr_freq_device(const float2* cutout, int N, const float2* rx, int64_t rxlen, const ShiftList& sl,
                               float* qf2, uint32_t* fidx, float2* cplx, void* caf, int caf_complex,
-                              cudaStream_t stream) {
-    if (!fastxcorr_fft_supported(N))
+                              cudaStream_t stream, const CztSpec* czt) {
+    if (czt) {
+        if (N < 1 || czt->nbins < 1 || czt_log2m(N, czt->nbins) > MAX_LOG2N)
+            return fail(XC_ERR_UNSUPPORTED, "chirp-z search: cutout length + frequency bins - 1 must be <= %d, got %d + %d",
+                        1 << MAX_LOG2N, N, czt->nbins);
+    } else if (!fastxcorr_fft_supported(N))
         return fail(XC_ERR_UNSUPPORTED, "fused frequency search supports cutout lengths 2..%d (powers of two up to %d), got %d",
                     1 << (MAX_LOG2N - 1), 1 << MAX_LOG2N, N);
     if (sl.K <= 0) return XC_OK;
@@ -306,10 +344,10 @@ int32_t fastxcorr_freq_device(const float2* cutout, int N, const float2* rx, int
         XC_TRY(window_energy_device(rx, rxlen, N, sl.shift0, sl.step, sl.shifts, sl.K, d_energy, stream));
     }
     FusedOut out{qf2, fidx, cplx, reinterpret_cast<float*>(caf), caf_complex, d_energy, d_refn};
-    if (!fft_length_supported(N)) {
-        // not a power of two: Bluestein inside the fused kernel
+    if (czt || !fft_length_supported(N)) {
+        // not a power of two, or a chirp-z frequency grid: Bluestein inside the fused kernel
         const BluePlan* plan = nullptr;
-        XC_TRY(blue_plan_for(N, &plan));
+        XC_TRY(blue_plan_for(N, czt, &plan));
         const int M = 1 << plan->log2m;
         float2* d_cutb = reinterpret_cast<float2*>(workspace(SLOT_TMP2, sizeof(float2) * (size_t)M));
         if (!d_cutb) return XC_ERR_NOMEM;

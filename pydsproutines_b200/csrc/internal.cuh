@@ -19,9 +19,15 @@ struct ShiftList {
     const int64_t* shifts;   // device pointer or NULL
 };
 bool fastxcorr_fft_supported(int N);
+// chirp-z frequency grid: bins k < nbins at (a_cycles + k * w_cycles) cycles per sample
+struct CztSpec {
+    int nbins;
+    double a_cycles, w_cycles;
+};
+// czt == NULL: the N-point DFT grid (bin k at k / N cycles per sample)
 int32_t fastxcorr_freq_device(const float2* cutout, int N, const float2* rx, int64_t rxlen, const ShiftList& sl,
                               float* qf2, uint32_t* fidx, float2* cplx, void* caf, int caf_complex,
-                              cudaStream_t stream);
+                              cudaStream_t stream, const CztSpec* czt = nullptr);
 int32_t fastxcorr_nofreq_device(const float2* cutout, int N, const float2* rx, int64_t rxlen, const ShiftList& sl,
                                 float* qf2, float2* cplx, cudaStream_t stream);
 

@@ -134,6 +134,45 @@ def fastXcorr(cutout, rx, freqsearch=False, outputCAF=False, shifts=None, absRes
     return _as(caf, np.float64 if absResult else np.complex128)
 
 
+def cztXcorr(cutout, rx, f_searchMin, f_searchMax, fs, cztStep=0.1, outputCAF=False, shifts=None):
+    """Same signature and return values as the reference's cztXcorr (xcorrRoutines.py:413-457): the frequency search of
+    fastXcorr on the chirp-z grid of CZTCached (spectralRoutines.py:239-309), k = int((f2 - f1) / step + 1) bins of
+    width (f2 - f1 + step) / k starting at f1, labelled np.arange(k) * step + f1.
+
+    outputCAF=False -> (complex QF at the best bin, complex64[K]; its frequency label, float64[K])
+    outputCAF=True  -> (QF^2 float64 (K, k), frequency labels float64[k])
+    """
+    cutout = _require_c64("cutout", cutout)
+    rx = _require_c64("rx", rx)
+    k = int((f_searchMax - f_searchMin) / cztStep + 1)
+    if k < 1:
+        raise ValueError("empty frequency range")
+    f_search = np.arange(k) * cztStep + f_searchMin                                   # CZTCached.getFreq
+    df = (f_searchMax - f_searchMin + cztStep) / k                                    # spectralRoutines.py:258
+    sh = _Shifts(shifts, rx.shape[0], cutout.shape[0], rx)
+    lib = _lib.load()
+    _select_device(rx)
+    where = _lib.where_of(cutout, rx)
+    K = sh.K
+    z = fidx = caf = None
+    if outputCAF:
+        caf = _lib.empty_like_space(rx, (K, k), np.float32)
+    else:
+        z = _lib.empty_like_space(rx, K, np.complex64)
+        fidx = _lib.empty_like_space(rx, K, np.uint32)
+    check(lib.xc_cztxcorr_c64(_lib.ptr(cutout), cutout.shape[0], _lib.ptr(rx), rx.shape[0], sh.shift0, sh.step, K,
+                              _lib.ptr(sh.array), float(f_searchMin) / float(fs), float(df) / float(fs), k, None,
+                              _lib.ptr(fidx), _lib.ptr(z), _lib.ptr(caf), where, _lib.current_stream(rx)))
+    if outputCAF:
+        return _as(caf, np.float64), f_search
+    if _lib.is_torch(fidx):
+        import torch
+        freqs = torch.from_numpy(f_search).to(fidx.device)[fidx.to(torch.int64)]
+    else:
+        freqs = f_search[fidx.astype(np.int64)]
+    return z, freqs
+
+
 def fastXcorrPeak(cutout, rx, freqsearch=True, shifts=None):
     """(QF^2, frequency index, peak shift) of the whole search in one call -- the tuple ranks exchange in
     the shift-sharded multi-GPU run (pydsproutines_b200.dist)."""

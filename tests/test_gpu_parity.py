@@ -524,3 +524,35 @@ def test_copy_helpers_vs_oracle(xr, space):
         ce.multiplySlidesNormalised(conv(t), conv(x), 4990, 20)
     with pytest.raises(TypeError):
         ce.multiplySlidesNormalised(conv(t.astype(np.complex128)) if space == "host" else conv(t).to(dtype=__import__("torch").complex128), conv(x), 0, 5)
+
+
+# ---------------------------------------------------------------------------------------------
+# chirp-z frequency zoom (cztXcorr) vs golden vectors of the real reference
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name,d", _load("cztxcorr_*.npz"), ids=lambda v: v if isinstance(v, str) else "")
+@pytest.mark.parametrize("space", ["host", "device"])
+def test_cztxcorr_golden(xr, name, d, space):
+    conv = _dev if space == "device" else (lambda a: a)
+    back = (lambda t: t.cpu().numpy()) if space == "device" else (lambda a: a)
+    args = (conv(d["cutout"]), conv(d["rx"]), float(d["f1"]), float(d["f2"]), float(d["fs"]), float(d["step"]))
+    res, freqs = xr.cztXcorr(*args, shifts=d["shifts"])
+    res, freqs = back(res), back(freqs)
+    assert res.dtype == np.complex64 and freqs.dtype == np.float64
+    same = freqs == d["freqs"]
+    assert same.mean() > 0.9                       # a noise-only shift may have a near-tie between bins
+    np.testing.assert_allclose(res[same], d["res"][same], rtol=0, atol=3e-5 * np.abs(d["res"]).max())
+    i = int(np.argmax(np.abs(res)))
+    assert d["shifts"][i] == int(d["p0"]) and freqs[i] == d["freqs"][i]
+    caf, fsearch = xr.cztXcorr(*args, outputCAF=True, shifts=d["shifts"])
+    caf = back(caf)
+    assert caf.dtype == np.float64 and caf.shape == d["caf"].shape and np.array_equal(fsearch, d["fsearch"])
+    np.testing.assert_allclose(caf, d["caf"], rtol=RTOL, atol=2e-6 * d["caf"].max())
+
+
+def test_cztxcorr_limits(xr):
+    rng = np.random.default_rng(3)
+    c, rx = signals.qpsk(rng, 9000), signals.cnoise(rng, 9100)
+    with pytest.raises(NotImplementedError):       # N + bins - 1 > 16384
+        xr.cztXcorr(c, rx, -1.0, 1.0, 100.0, cztStep=0.0002)
+    with pytest.raises(TypeError):
+        xr.cztXcorr(c.astype(np.complex128), rx, -1.0, 1.0, 100.0)

@@ -107,3 +107,20 @@ def test_find_local_maxima_known_answer():
     assert list(orc.findLocalMaxima(x, 0.4)) == [5, 9, 37, 41]
     idx, val = orc.argmaxAbsRows(np.array([[1, 3j, -3, 0], [0, 0, 0, 0]], np.complex64))
     assert list(idx) == [1, 0] and list(val) == [3.0, 0.0]
+
+
+@pytest.mark.parametrize("name,d", _load("cztxcorr_*.npz"), ids=lambda v: v if isinstance(v, str) else "")
+def test_cztxcorr_restatement_matches_reference(name, d):
+    """The direct-evaluation restatement of cztXcorr against the reference's chirp-z implementation (the reference
+    runs the transform in complex128, so the two agree to float32 rounding of the result, not bit for bit)."""
+    args = (d["cutout"], d["rx"], float(d["f1"]), float(d["f2"]), float(d["fs"]), float(d["step"]))
+    res, freqs = orc.cztXcorr(*args, shifts=d["shifts"])
+    assert res.dtype == np.complex64 and freqs.dtype == np.float64
+    np.testing.assert_allclose(res, d["res"], rtol=0, atol=1e-6)
+    assert np.array_equal(freqs, d["freqs"])
+    caf, fsearch = orc.cztXcorr(*args, outputCAF=True, shifts=d["shifts"])
+    np.testing.assert_allclose(caf, d["caf"], rtol=1e-5, atol=1e-7 * d["caf"].max())
+    assert np.array_equal(fsearch, d["fsearch"])
+    # the planted offset is found at the planted shift, to within one frequency step
+    i = int(np.argmax(np.abs(res)))
+    assert d["shifts"][i] == int(d["p0"]) and abs(freqs[i] - float(d["foff"])) <= float(d["step"])
