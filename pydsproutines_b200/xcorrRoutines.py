@@ -134,6 +134,22 @@ def fastXcorr(cutout, rx, freqsearch=False, outputCAF=False, shifts=None, absRes
     return _as(caf, np.float64 if absResult else np.complex128)
 
 
+def _czt_call(cutout, rx, sh, cztobj, want_qf2=False, want_fidx=False, want_cplx=False, want_caf=False):
+    """xc_cztxcorr_c64 on the grid of a CZTCached object; returns (qf2, fidx, cplx, caf) in the memory space of rx."""
+    lib = _lib.load()
+    _select_device(rx)
+    where = _lib.where_of(cutout, rx)
+    K = sh.K
+    qf2 = _lib.empty_like_space(rx, K, np.float32) if want_qf2 else None
+    fidx = _lib.empty_like_space(rx, K, np.uint32) if want_fidx else None
+    z = _lib.empty_like_space(rx, K, np.complex64) if want_cplx else None
+    caf = _lib.empty_like_space(rx, (K, cztobj.k), np.float32) if want_caf else None
+    check(lib.xc_cztxcorr_c64(_lib.ptr(cutout), cutout.shape[0], _lib.ptr(rx), rx.shape[0], sh.shift0, sh.step, K,
+                              _lib.ptr(sh.array), cztobj.f0_cycles, cztobj.df_cycles, cztobj.k, _lib.ptr(qf2),
+                              _lib.ptr(fidx), _lib.ptr(z), _lib.ptr(caf), where, _lib.current_stream(rx)))
+    return qf2, fidx, z, caf
+
+
 def cztXcorr(cutout, rx, f_searchMin, f_searchMax, fs, cztStep=0.1, outputCAF=False, shifts=None):
     """Same signature and return values as the reference's cztXcorr (xcorrRoutines.py:413-457): the frequency search of
     fastXcorr on the chirp-z grid of CZTCached (spectralRoutines.py:239-309), k = int((f2 - f1) / step + 1) bins of
@@ -144,25 +160,11 @@ def cztXcorr(cutout, rx, f_searchMin, f_searchMax, fs, cztStep=0.1, outputCAF=Fa
     """
     cutout = _require_c64("cutout", cutout)
     rx = _require_c64("rx", rx)
-    k = int((f_searchMax - f_searchMin) / cztStep + 1)
-    if k < 1:
-        raise ValueError("empty frequency range")
-    f_search = np.arange(k) * cztStep + f_searchMin                                   # CZTCached.getFreq
-    df = (f_searchMax - f_searchMin + cztStep) / k                                    # spectralRoutines.py:258
+    from .spectralRoutines import CZTCached
+    cztobj = CZTCached(cutout.shape[0], f_searchMin, f_searchMax, cztStep, fs)
+    f_search = cztobj.getFreq()
     sh = _Shifts(shifts, rx.shape[0], cutout.shape[0], rx)
-    lib = _lib.load()
-    _select_device(rx)
-    where = _lib.where_of(cutout, rx)
-    K = sh.K
-    z = fidx = caf = None
-    if outputCAF:
-        caf = _lib.empty_like_space(rx, (K, k), np.float32)
-    else:
-        z = _lib.empty_like_space(rx, K, np.complex64)
-        fidx = _lib.empty_like_space(rx, K, np.uint32)
-    check(lib.xc_cztxcorr_c64(_lib.ptr(cutout), cutout.shape[0], _lib.ptr(rx), rx.shape[0], sh.shift0, sh.step, K,
-                              _lib.ptr(sh.array), float(f_searchMin) / float(fs), float(df) / float(fs), k, None,
-                              _lib.ptr(fidx), _lib.ptr(z), _lib.ptr(caf), where, _lib.current_stream(rx)))
+    _, fidx, z, caf = _czt_call(cutout, rx, sh, cztobj, want_cplx=not outputCAF, want_fidx=not outputCAF, want_caf=outputCAF)
     if outputCAF:
         return _as(caf, np.float64), f_search
     if _lib.is_torch(fidx):
@@ -210,16 +212,23 @@ def cp_fastXcorr_v2(cutout, rx, startIdx=0, idxlen=None, THREADS_PER_BLOCK=32, n
                     flattenCAF=False, BATCH=None):
     """Step-1 search over rx[startIdx : startIdx+idxlen].  Returns (freqIdx uint32, qf2 float32) -- in THAT
     order (xcorrRoutines.py:272) -- when flattenCAF, else the float32 (idxlen, N) ambiguity surface.
-    THREADS_PER_BLOCK / numSlidesPerBlk / BATCH are accepted and ignored; cztObj is not supported yet."""
-    if cztObj is not None:
-        raise NotImplementedError("the CZT branch (xcorrRoutines.py:247-249) is not part of this build yet")
+    THREADS_PER_BLOCK / numSlidesPerBlk / BATCH are accepted and ignored.  With cztObj (a spectralRoutines.CZTCached /
+    CZTCachedGPU) the frequency axis is its chirp-z grid (xcorrRoutines.py:247-249): indices into cztObj.getFreq(),
+    surface of shape (idxlen, cztObj.k)."""
     cutout = _require_c64("cutout", cutout)
     rx = _require_c64("rx", rx)
+    if cztObj is not None and cztObj.m != cutout.shape[0]:
+        raise ValueError("CZT object input length doesn't match the cutout array size")   # :212-215
     if idxlen is None:
         idxlen = rx.shape[0] - cutout.shape[0] - startIdx + 1       # :209-210
     if startIdx < 0 or idxlen < 0 or startIdx + idxlen - 1 + cutout.shape[0] > rx.shape[0]:
         raise ValueError("Search range exceeds the input array.")                 # cupyExtensions.py:512-515
     sh = _Shifts(np.arange(startIdx, startIdx + idxlen), rx.shape[0], cutout.shape[0], rx)
+    if cztObj is not None:
+        if flattenCAF:
+            qf2, fidx, _, _ = _czt_call(cutout, rx, sh, cztObj, want_qf2=True, want_fidx=True)
+            return fidx, qf2
+        return _czt_call(cutout, rx, sh, cztObj, want_caf=True)[3]
     if flattenCAF:
         qf2, fidx, _, _ = _fastxcorr_call(cutout, rx, sh, True, want_fidx=True)
         return fidx, qf2

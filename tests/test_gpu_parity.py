@@ -556,3 +556,23 @@ def test_cztxcorr_limits(xr):
         xr.cztXcorr(c, rx, -1.0, 1.0, 100.0, cztStep=0.0002)
     with pytest.raises(TypeError):
         xr.cztXcorr(c.astype(np.complex128), rx, -1.0, 1.0, 100.0)
+
+
+def test_cp_fastxcorr_v2_czt_branch(xr):
+    """cp_fastXcorr_v2(cztObj=...) (xcorrRoutines.py:247-249): indices into the chirp-z grid, (freqIdx, qf2) order."""
+    from pydsproutines_b200.spectralRoutines import CZTCachedGPU
+    d = dict(np.load(os.path.join(GOLDEN, "cztxcorr_n1000_hz.npz")))
+    cutout, rx = d["cutout"], d["rx"]
+    obj = CZTCachedGPU(cutout.size, float(d["f1"]), float(d["f2"]), float(d["step"]), float(d["fs"]))
+    assert obj.k == d["caf"].shape[1] and np.array_equal(obj.getFreq(), d["fsearch"])
+    s0, n = int(d["shifts"][0]), int(d["shifts"].size)
+    fi, q = xr.cp_fastXcorr_v2(_dev(cutout), _dev(rx), s0, n, cztObj=obj, flattenCAF=True)
+    fi, q = fi.cpu().numpy(), q.cpu().numpy()
+    assert q.dtype == np.float32
+    assert_qf2(q, d["caf"].max(axis=1))
+    assert (fi == d["caf"].argmax(axis=1)).mean() > 0.9
+    surf = xr.cp_fastXcorr_v2(_dev(cutout), _dev(rx), s0, n, cztObj=obj).cpu().numpy()
+    assert surf.dtype == np.float32 and surf.shape == d["caf"].shape
+    np.testing.assert_allclose(surf, d["caf"], rtol=RTOL, atol=2e-6 * d["caf"].max())
+    with pytest.raises(ValueError):
+        xr.cp_fastXcorr_v2(_dev(cutout[:500].copy()), _dev(rx), 0, 10, cztObj=obj)
