@@ -26,6 +26,7 @@ struct xc_group {
     int32_t* d_ell_off;      // [rows * TG]
     int32_t* d_slot_base;    // [V + 1]
     int32_t* d_row_base;     // [rows] when every contributor row is a run off = row_base + t, else NULL
+    int32_t runs_inside;     // every row_base + t (t < TG) is a valid sample offset: no clamping needed
     float* d_refn;           // ||ygroups||^2
     int32_t rows;
     int32_t log2m;           // block-FFT plan: log2(F) when F is a power of two, else the padded Bluestein length
@@ -37,6 +38,23 @@ struct xc_group {
 namespace xc {
 
 constexpr int ELL_UNROLL = 16;
+
+// v[c] = acc for a warp-uniform runtime c: a tree of uniform branches (log2 V of them) instead of V predicated
+// selects; the empty asm keeps the leaves from being if-converted back into selects
+template <int LO, int HI>
+__device__ __forceinline__ void slot_store(float2* v, int c, float2 acc) {
+    if constexpr (HI - LO == 1) {
+        v[LO] = acc;
+        asm volatile("" ::: "memory");
+    } else {
+        constexpr int MID = (LO + HI) / 2;
+        if (c < MID) {
+            slot_store<LO, MID>(v, c, acc);
+        } else {
+            slot_store<MID, HI>(v, c, acc);
+        }
+    }
+}
 
 template <class PL>
 struct GroupLoader {
@@ -51,8 +69,9 @@ struct GroupLoader {
     const int32_t* row_base;      // [rows] or NULL: offsets are row_base[j] + t (clamped into [lo, hi)), no per-thread table
     int32_t rows;                 // contributor rows (each TG weights)
     int32_t y_smem_off;           // byte offset of the shared-memory copy of ell_y behind the static carve-up, -1 = none
+    int32_t runs_inside;          // row_base + t never leaves [lo, hi): skip the clamp
 
-    size_t dyn_smem() const { return y_smem_off >= 0 ? sizeof(float2) * (size_t)rows * PL::TG + 16 : 0; }   // + alignment slack
+    size_t dyn_smem() const { return y_smem_off >= 0 ? sizeof(float2) * (size_t)rows * PL::TG + sizeof(int32_t) * (size_t)rows + 16 : 0; }   // weights, row bases, alignment slack
 
     // shared-memory tables: slot_base[V + 1], then the list of non-empty slots ne[V] and their count
     __host__ __device__ static constexpr size_t smem_bytes() { return ((sizeof(int32_t) * (2 * PL::V + 2) + 15) / 16) * 16; }
@@ -70,6 +89,10 @@ struct GroupLoader {
         if (y_smem_off >= 0) {      // the weights never change: keep them next to the FFT buffers
             float2* ys = reinterpret_cast<float2*>(smem + y_smem_off);
             for (int i = tid; i < rows * PL::TG; i += nthreads) ys[i] = ell_y[i];
+            if (row_base) {
+                int32_t* rb = reinterpret_cast<int32_t*>(ys + (size_t)rows * PL::TG);
+                for (int i = tid; i < rows; i += nthreads) rb[i] = row_base[i];
+            }
         }
     }
     __device__ __forceinline__ bool issue(float2* v, int t, int64_t i, const unsigned char* smem) const {
@@ -99,20 +122,44 @@ struct GroupLoader {
             if (row_base) {
                 // run-structured lists (every group contributes consecutive samples to consecutive cells): the
                 // sample address does not depend on a loaded offset, so weights and samples go out together
-                const int omin = (int)lo, omax = (int)hi - 1;
+                const int32_t* const rb = (y_smem_off >= 0) ? reinterpret_cast<const int32_t*>(yp + (size_t)rows * PL::TG) : row_base;
+                if (runs_inside && y_smem_off >= 0) {
+                    // fast path: weights and row bases in shared memory (explicit ld.shared), unclamped offsets
+                    const float2* const xt = x + t;
+                    const uint32_t ys_s = (uint32_t)__cvta_generic_to_shared(smem + y_smem_off) + (uint32_t)t * 8u;
+                    const uint32_t rb_s = (uint32_t)__cvta_generic_to_shared(smem + y_smem_off) + (uint32_t)rows * PL::TG * 8u;
 #pragma unroll 1
-                for (int j = j0; j < j1; j += ELL_UNROLL) {
-                    float2 y[ELL_UNROLL], r[ELL_UNROLL];
+                    for (int j = j0; j < j1; j += ELL_UNROLL) {
+                        float2 r[ELL_UNROLL];
 #pragma unroll
-                    for (int u = 0; u < ELL_UNROLL; ++u) {
-                        const int o = min(max(__ldg(row_base + j + u) + t, omin), omax);
-                        r[u] = __ldg(x + o);
+                        for (int u = 0; u < ELL_UNROLL; ++u) {
+                            int o;
+                            asm volatile("ld.shared.s32 %0, [%1];" : "=r"(o) : "r"(rb_s + 4u * (uint32_t)(j + u)));
+                            r[u] = __ldg(xt + o);
+                        }
+#pragma unroll
+                        for (int u = 0; u < ELL_UNROLL; ++u) {
+                            float2 y;
+                            asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(y.x), "=f"(y.y) : "r"(ys_s + (uint32_t)(j + u) * (PL::TG * 8u)));
+                            acc = pfma(make_float2(r[u].y, r[u].x), make_float2(-y.y, y.y), pfma(r[u], make_float2(y.x, y.x), acc));
+                        }
                     }
+                } else {
+                    const int omin = (int)lo, omax = (int)hi - 1;
+#pragma unroll 1
+                    for (int j = j0; j < j1; j += ELL_UNROLL) {
+                        float2 y[ELL_UNROLL], r[ELL_UNROLL];
 #pragma unroll
-                    for (int u = 0; u < ELL_UNROLL; ++u) y[u] = yp[(size_t)(j + u) * PL::TG + t];
+                        for (int u = 0; u < ELL_UNROLL; ++u) {
+                            const int o = min(max(rb[j + u] + t, omin), omax);
+                            r[u] = __ldg(x + o);
+                        }
 #pragma unroll
-                    for (int u = 0; u < ELL_UNROLL; ++u) acc = pfma(make_float2(r[u].y, r[u].x), make_float2(-y[u].y, y[u].y),
-                                                                  pfma(r[u], make_float2(y[u].x, y[u].x), acc));
+                        for (int u = 0; u < ELL_UNROLL; ++u) y[u] = yp[(size_t)(j + u) * PL::TG + t];
+#pragma unroll
+                        for (int u = 0; u < ELL_UNROLL; ++u) acc = pfma(make_float2(r[u].y, r[u].x), make_float2(-y[u].y, y[u].y),
+                                                                      pfma(r[u], make_float2(y[u].x, y[u].x), acc));
+                    }
                 }
             } else {
 #pragma unroll 1
@@ -130,15 +177,7 @@ struct GroupLoader {
                                                                   pfma(r[u], make_float2(y[u].x, y[u].x), acc));
                 }
             }
-#define XC_SLOT(n) case n: if (n < PL::V) v[(n < PL::V) ? n : 0] = acc; break;
-            switch (c) {
-                XC_SLOT(0) XC_SLOT(1) XC_SLOT(2) XC_SLOT(3) XC_SLOT(4) XC_SLOT(5) XC_SLOT(6) XC_SLOT(7)
-                XC_SLOT(8) XC_SLOT(9) XC_SLOT(10) XC_SLOT(11) XC_SLOT(12) XC_SLOT(13) XC_SLOT(14) XC_SLOT(15)
-                XC_SLOT(16) XC_SLOT(17) XC_SLOT(18) XC_SLOT(19) XC_SLOT(20) XC_SLOT(21) XC_SLOT(22) XC_SLOT(23)
-                XC_SLOT(24) XC_SLOT(25) XC_SLOT(26) XC_SLOT(27) XC_SLOT(28) XC_SLOT(29) XC_SLOT(30) XC_SLOT(31)
-                default: break;
-            }
-#undef XC_SLOT
+            slot_store<0, PL::V>(v, c, acc);
         }
         return true;
     }
@@ -232,7 +271,12 @@ struct GroupBuilder {
                 }
             }
             h->d_row_base = nullptr;
+            h->runs_inside = 0;
             if (runs && nrows > 0) {
+                bool inside = true;
+                for (int r = 0; r < nrows; ++r)
+                    if (rb[r] < h->min_start || (int64_t)rb[r] + TG > h->span) inside = false;
+                h->runs_inside = inside ? 1 : 0;
                 XC_CUDA_TRY(cudaMalloc(&h->d_row_base, sizeof(int32_t) * rb.size()));
                 XC_CUDA_TRY(cudaMemcpy(h->d_row_base, rb.data(), sizeof(int32_t) * rb.size(), cudaMemcpyHostToDevice));
             }
@@ -261,9 +305,9 @@ struct GroupRunner {
         // the weights move into shared memory when they fit behind the static carve-up
         const size_t stat = (fused_smem_bytes<typename PF::PL, PF::B, LD>() + 15) / 16 * 16;
         const size_t ybytes = sizeof(float2) * (size_t)h->rows * PF::PL::TG;
-        const int32_t yoff = (h->rows > 0 && stat + ybytes + 16 <= (size_t)max_smem_optin()) ? (int32_t)stat : -1;
+        const int32_t yoff = (h->rows > 0 && stat + ybytes + sizeof(int32_t) * (size_t)h->rows + 16 <= (size_t)max_smem_optin()) ? (int32_t)stat : -1;
         LD ld{rx, rxlen, sl.shift0, sl.step, sl.shifts, h->d_ell_y, h->d_ell_off, h->d_slot_base,
-              h->min_start, h->span, h->d_row_base, h->rows, yoff};
+              h->min_start, h->span, h->d_row_base, h->rows, yoff, h->runs_inside};
         if (h->blue) {
             if constexpr (PF::PL::P >= 2) {
                 return launch_bluestein<typename PF::PL, PF::B, LD>(ld, out, sl.K, h->d_bhat_perm, h->d_chirp, h->F, stream);
