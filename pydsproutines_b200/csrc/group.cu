@@ -91,7 +91,8 @@ struct GroupLoader {
             for (int i = tid; i < rows * PL::TG; i += nthreads) ys[i] = ell_y[i];
             if (row_base) {
                 int32_t* rb = reinterpret_cast<int32_t*>(ys + (size_t)rows * PL::TG);
-                for (int i = tid; i < rows; i += nthreads) rb[i] = row_base[i];
+                // fast path (runs_inside): unsigned BYTE offsets from sample `lo`, so the address is one 64 + 32 bit add
+                for (int i = tid; i < rows; i += nthreads) rb[i] = runs_inside ? (row_base[i] - (int32_t)lo) * 8 : row_base[i];
             }
         }
     }
@@ -125,17 +126,19 @@ struct GroupLoader {
                 const int32_t* const rb = (y_smem_off >= 0) ? reinterpret_cast<const int32_t*>(yp + (size_t)rows * PL::TG) : row_base;
                 if (runs_inside && y_smem_off >= 0) {
                     // fast path: weights and row bases in shared memory (explicit ld.shared), unclamped offsets
-                    const float2* const xt = x + t;
+                    const char* const xt = reinterpret_cast<const char*>(x + lo + t);
                     const uint32_t ys_s = (uint32_t)__cvta_generic_to_shared(smem + y_smem_off) + (uint32_t)t * 8u;
                     const uint32_t rb_s = (uint32_t)__cvta_generic_to_shared(smem + y_smem_off) + (uint32_t)rows * PL::TG * 8u;
 #pragma unroll 1
                     for (int j = j0; j < j1; j += ELL_UNROLL) {
                         float2 r[ELL_UNROLL];
 #pragma unroll
-                        for (int u = 0; u < ELL_UNROLL; ++u) {
-                            int o;
-                            asm volatile("ld.shared.s32 %0, [%1];" : "=r"(o) : "r"(rb_s + 4u * (uint32_t)(j + u)));
-                            r[u] = __ldg(xt + o);
+                        for (int u = 0; u < ELL_UNROLL; u += 4) {
+                            uint32_t o[4];
+                            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(o[0]), "=r"(o[1]), "=r"(o[2]), "=r"(o[3])
+                                         : "r"(rb_s + 4u * (uint32_t)(j + u)));
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) r[u + q] = __ldg(reinterpret_cast<const float2*>(xt + o[q]));
                         }
 #pragma unroll
                         for (int u = 0; u < ELL_UNROLL; ++u) {
@@ -273,7 +276,7 @@ struct GroupBuilder {
             h->d_row_base = nullptr;
             h->runs_inside = 0;
             if (runs && nrows > 0) {
-                bool inside = true;
+                bool inside = (h->span - h->min_start) < (int64_t(1) << 27);     // byte offsets fit 32 bits
                 for (int r = 0; r < nrows; ++r)
                     if (rb[r] < h->min_start || (int64_t)rb[r] + TG > h->span) inside = false;
                 h->runs_inside = inside ? 1 : 0;
