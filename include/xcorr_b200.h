@@ -134,6 +134,26 @@ int32_t xc_group_xcorr(xc_group* handle, const void* rx, int64_t rxlen, int64_t 
                        xc_peak* peak, int32_t where, void* stream);
 int32_t xc_group_destroy(xc_group* handle);
 
+/* ---- 8(f) rank 1 / 4: grouped correlator over an arbitrary frequency list ------------------
+ * xcorrRoutines.GroupXcorr (xcorrRoutines.py:852-954: freqMat @ (rxconcat * yconcat), max over the list),
+ * xcorrRoutines.GroupXcorrCZT (xcorrRoutines.py:957-1039: CAF over the grid f1 : binWidth : f2) and the
+ * experimental GroupXcorrGPU RawKernels (xcorrRoutines.py:1693-2051).
+ *   d[s, k]    = sum_g sum_t y_g[t] rx[s + starts[g] + t] exp(-j 2 pi freq_cycles[k] (starts[g] + t))
+ *   QF2[s, k]  = |d[s, k]|^2 / sum_g ||rx[s + starts[g] : + lengths[g]]||^2 / ||y||^2
+ * ycat = the group samples back to back (sum of lengths; conjugated on upload when conj != 0), freq_cycles =
+ * f / fs.  start_freq_cycles (NULL = freq_cycles) is the frequency used for the starts[g] part of the phase:
+ * GroupXcorrCZT rotates the groups with the nominal grid f1 + k binWidth while its CZT bins sit at
+ * f1 + k (f2 - f1 + binWidth) / nbins (spectralRoutines.py:239-262).  Shifts are the contiguous range shift0 .. shift0 + K - 1.  qf2/fidx = max / arg max over the list per
+ * shift, caf = the full [K, NF] float surface; any of them may be NULL.  Runs on the tensor cores (tcgen05);
+ * XC_ERR_UNSUPPORTED on anything else. */
+typedef struct xc_groupfreq xc_groupfreq;
+int32_t xc_groupfreq_create(const void* ycat, const int64_t* starts, const int32_t* lengths, int32_t G,
+                            const double* freq_cycles, const double* start_freq_cycles, int32_t NF, int32_t conj,
+                            xc_groupfreq** handle);
+int32_t xc_groupfreq_xcorr(xc_groupfreq* handle, const void* rx, int64_t rxlen, int64_t shift0, int64_t K,
+                           float* qf2, uint32_t* fidx, float* caf, xc_peak* peak, int32_t where, void* stream);
+int32_t xc_groupfreq_destroy(xc_groupfreq* handle);
+
 /* ---- a9, a10: (multi-)template correlator -------------------------------------------------
  * xcorrRoutines.TemplateCrossCorrelator (xcorrRoutines.py:277-371) and
  * cupyExtensions.multiTemplateSlidingDotProduct (cupyExtensions.py:563-642 -> multiplySlices.cu:251-399).

@@ -102,10 +102,43 @@ def czt_cases(ref):
     return cases
 
 
+def groupfreq_cases(ref):
+    """GroupXcorr (xcorrRoutines.py:852-954) and GroupXcorrCZT (957-1039): ragged groups cut from a long template,
+    planted in noise with a frequency offset that sits on / between the searched frequencies."""
+    cases = {}
+    # name, seed, ylen, starts, lengths, fs, freqs (GroupXcorr) , (f1, f2, bw) (GroupXcorrCZT), foff, p0, K
+    specs = [
+        ("g3_ragged", 41, 400, np.array([5, 120, 300]), np.array([40, 33, 64]), 1000.0,
+         np.arange(-20.0, 20.0, 1.25), (-10.0, 10.0, 0.5), 6.25, 21, 50),
+        ("g8_l128", 42, 9000, np.arange(8) * 1100 + 16, np.full(8, 128), 1.0,
+         np.linspace(-0.002, 0.002, 41), (-0.001, 0.001, 0.00005), 0.0007, 9, 24),
+        ("g2_long", 43, 1500, np.array([0, 800]), np.array([600, 530]), 100.0,
+         np.array([-3.0, -1.0, 0.0, 0.4, 1.7, 2.0, 5.5]), (-1.0, 1.0, 0.125), 0.4, 3, 12),
+    ]
+    for name, seed, ylen, starts, lengths, fs, freqs, (f1, f2, bw), foff, p0, K in specs:
+        rng = np.random.default_rng(seed)
+        y = signals.qpsk(rng, ylen)
+        z = starts - starts[0]
+        rx = signals.cnoise(rng, K + int(z[-1]) + int(lengths[-1]) + 8)
+        for g in range(starts.size):
+            n = np.arange(lengths[g]) + z[g]
+            seg = y[starts[g]:starts[g] + lengths[g]] * np.exp(2j * np.pi * foff * n / fs)
+            rx[p0 + z[g]:p0 + z[g] + lengths[g]] += (0.8 * seg).astype(np.complex64)
+        shifts = np.arange(K)
+        a = ref.GroupXcorr(y, starts, lengths, freqs, fs)
+        xc, fp = a.xcorr(rx, shifts)
+        b = ref.GroupXcorrCZT(y, starts, lengths, f1, f2, bw, fs)
+        caf, cf = b.xcorr(rx, shifts)
+        cases[name] = dict(y=y, starts=starts, lengths=lengths, fs=fs, freqs=freqs, f1=f1, f2=f2, bw=bw, rx=rx,
+                           shifts=shifts, xc=xc, freqpeaks=fp, caf=caf, cztFreq=cf, p0=p0, foff=foff)
+    return cases
+
+
 def main():
     ref = ref_import.load()
     os.makedirs(OUT, exist_ok=True)
-    for fam, cases in (("fastxcorr", fastxcorr_cases(ref)), ("groupxcorr", group_cases(ref)), ("cztxcorr", czt_cases(ref))):
+    for fam, cases in (("fastxcorr", fastxcorr_cases(ref)), ("groupxcorr", group_cases(ref)), ("cztxcorr", czt_cases(ref)),
+                       ("groupfreq", groupfreq_cases(ref))):
         for name, d in cases.items():
             path = os.path.join(OUT, "%s_%s.npz" % (fam, name))
             np.savez_compressed(path, **d)

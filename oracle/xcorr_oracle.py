@@ -368,3 +368,74 @@ def cztXcorr(cutout, rx, f_searchMin, f_searchMax, fs, cztStep=0.1, outputCAF=Fa
         res[i] = X[mi] / np.linalg.norm(sl) / cn
         freqs[i] = f_search[mi]
     return res, freqs
+
+
+class GroupXcorr:
+    """xcorrRoutines.py:852-954: coherent sum over groups of y against an arbitrary frequency list, evaluated as the
+    reference does (freqMat @ (rxconcat * yconcat) per shift), complex128."""
+
+    def __init__(self, y, starts, lengths, freqs, fs, autoConj=True, autoZeroStarts=True):
+        y = np.asarray(y)
+        starts = np.asarray(starts)
+        lengths = np.asarray(lengths)
+        self.starts = starts - starts[0] if autoZeroStarts else starts                      # :885-887
+        self.lengths = lengths
+        self.freqs = np.asarray(freqs, np.float64)
+        self.fs = fs
+        yy = y.conj() if autoConj else y
+        G = starts.size
+        self.yconcat = np.hstack([yy[starts[i]:starts[i] + lengths[i]] for i in range(G)])  # :894-905
+        self.yconcatNormSq = np.linalg.norm(self.yconcat) ** 2
+        idx = np.hstack([np.arange(starts[i], starts[i] + lengths[i]) for i in range(G)])
+        self.freqMat = np.exp(-2j * np.pi * self.freqs.reshape(-1, 1) * idx / fs)          # :909-918
+
+    def xcorr(self, rx, shifts=None):
+        rx = np.asarray(rx)
+        if shifts is None:
+            shifts = np.arange(len(rx) - (self.starts[-1] + self.lengths[-1]) + 1)
+        xc = np.zeros(len(shifts))
+        fp = np.zeros(len(shifts))
+        for i, s in enumerate(shifts):
+            rc = np.hstack([rx[s + self.starts[g]:s + self.starts[g] + self.lengths[g]] for g in range(self.starts.size)])
+            pf = np.abs(self.freqMat @ (rc * self.yconcat))
+            m = int(np.argmax(pf))
+            xc[i] = pf[m] ** 2 / np.linalg.norm(rc) ** 2 / self.yconcatNormSq                # :949
+            fp[i] = self.freqs[m]
+        return xc, fp
+
+
+class GroupXcorrCZT:
+    """xcorrRoutines.py:957-1039 with the CZT of every group evaluated directly on the bins CZTCached produces
+    (f1 + k (f2 - f1 + binWidth) / nbins, spectralRoutines.py:239-262) and the group phases on the nominal grid
+    np.arange(f1, f2 + binWidth / 2, binWidth) (:1007-1010)."""
+
+    def __init__(self, y, starts, lengths, f1, f2, binWidth, fs, autoConj=True, autoZeroStarts=True):
+        y = np.asarray(y)
+        starts = np.asarray(starts)
+        lengths = np.asarray(lengths)
+        self.starts = starts - starts[0] if autoZeroStarts else starts
+        self.lengths = lengths
+        self.fs = fs
+        self.groups = [(y[starts[i]:starts[i] + lengths[i]].conj() if autoConj else y[starts[i]:starts[i] + lengths[i]])
+                       for i in range(starts.size)]
+        self.ystackNormSq = sum(np.linalg.norm(g) ** 2 for g in self.groups)
+        self.k = int((f2 - f1) / binWidth + 1)
+        self.bins = f1 + np.arange(self.k) * (f2 - f1 + binWidth) / self.k
+        self.cztFreq = np.arange(f1, f2 + binWidth / 2, binWidth)
+
+    def xcorr(self, rx, shifts=None):
+        rx = np.asarray(rx)
+        if shifts is None:
+            shifts = np.arange(len(rx) - (self.starts[-1] + self.lengths[-1]) + 1)
+        phases = np.exp(-2j * np.pi * self.cztFreq * self.starts.reshape(-1, 1) / self.fs)
+        E = [np.exp(-2j * np.pi * np.outer(self.bins, np.arange(len(g))) / self.fs) for g in self.groups]
+        xc = np.zeros((len(shifts), self.k))
+        for i, s in enumerate(shifts):
+            tot = np.zeros(self.k, np.complex128)
+            en = 0.0
+            for g, yg in enumerate(self.groups):
+                sl = rx[s + self.starts[g]:s + self.starts[g] + len(yg)]
+                en += np.linalg.norm(sl) ** 2
+                tot += (E[g] @ (yg * sl).astype(np.complex128)) * phases[g]
+            xc[i] = np.abs(tot) ** 2 / en / self.ystackNormSq
+        return xc, self.cztFreq

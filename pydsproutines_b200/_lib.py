@@ -51,6 +51,9 @@ SIGNATURES = {
     "xc_group_create": (_i32, [_vp, _i32, _i32, _vp, _i32, _i32, C.POINTER(_vp)]),
     "xc_group_xcorr": (_i32, [_vp, _vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp, _vp, C.POINTER(xc_peak), _i32, _vp]),
     "xc_group_destroy": (_i32, [_vp]),
+    "xc_groupfreq_create": (_i32, [_vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32, C.POINTER(_vp)]),
+    "xc_groupfreq_xcorr": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp, C.POINTER(xc_peak), _i32, _vp]),
+    "xc_groupfreq_destroy": (_i32, [_vp]),
     "xc_mt_create": (_i32, [_vp, _i32, _i32, _i32, _vp, C.POINTER(_vp)]),
     "xc_mt_correlate": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp, _i32, C.POINTER(xc_peak), _i32, _vp]),
     "xc_mt_destroy": (_i32, [_vp]),

@@ -47,6 +47,9 @@ int32_t local_maxima_device(const float* x, int64_t n, float min_height, int32_t
 struct MtTcPlan {
     int T = 0, L = 0;
     int L32 = 0;          // template length padded to a multiple of 32 (one pipeline stage = 32 samples)
+    int Lp = 0;           // samples an x tile must cover: L32 (dense) or the longest group (segmented), multiple of 32
+    int nseg = 1;         // 1 = dense; > 1 = the templates are non-zero only inside nseg groups
+    int32_t* d_segs = nullptr;     // [nseg][2] {x offset of the group, K steps of 16 samples}
     int NT = 0;           // templates per block = UMMA N (multiple of 16, <= 256)
     int NB = 0;           // template blocks
     void* d_pack = nullptr;        // BF16 stage images [NB][L32/32][planes][canonical K-major core matrices]
@@ -54,9 +57,10 @@ struct MtTcPlan {
     int planes = 2;       // 2: templates exact in BF16 (re, im); 4: BF16 hi + lo split (re, im, re_lo, im_lo)
     bool usable = false;  // the tile fits in shared memory (otherwise the FP32 kernel is used)
 };
-int32_t mt_tc_prepare(const float2* d_templates, int T, int L, int L8, const float* d_energies, MtTcPlan* plan);
+int32_t mt_tc_prepare(const float2* d_templates, int T, int L, int L8, const float* d_energies, MtTcPlan* plan,
+                      const int32_t* segs = nullptr, int nseg = 0);
 void mt_tc_release(MtTcPlan* plan);
 int32_t mt_tc_run(const MtTcPlan& plan, const float2* x, int64_t xlen, int64_t start, int64_t K, const float* xenergy,
-                  float* best, int32_t* tidx, int sqrt_out, cudaStream_t stream);
+                  float* best, int32_t* tidx, int sqrt_out, cudaStream_t stream, float* caf = nullptr);
 
 }  // namespace xc

@@ -83,9 +83,11 @@ struct TcSmem {
     uint32_t plane, stage, off_stage, off_inv, off_bar, total;
     int nstages, ne;
 };
-__host__ __device__ inline TcSmem tc_smem_layout(int L32, int NT, int NB, int nstages, int ne, int np) {
+// Lp = longest contiguous run of template samples one x tile must cover (the whole template for a dense set,
+// the longest group of a segmented one)
+__host__ __device__ inline TcSmem tc_smem_layout(int Lp, int NT, int NB, int nstages, int ne, int np) {
     TcSmem m;
-    m.plane = (uint32_t)tc_plane_bytes(L32);
+    m.plane = (uint32_t)tc_plane_bytes(Lp);
     m.stage = (uint32_t)NT * 32 * (uint32_t)np;        // np planes (re, im[, re_lo, im_lo]) of 16 samples
     m.nstages = nstages;
     m.ne = ne;
@@ -98,12 +100,14 @@ __host__ __device__ inline TcSmem tc_smem_layout(int L32, int NT, int NB, int ns
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
 mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_energy, const int NT, const int NB,
-             const int L32, const int nstages, const int ne, const int np, const float2* __restrict__ x, const int64_t xlen,
-             const int64_t start, const int64_t K, const float* __restrict__ xenergy, float* __restrict__ best_out,
-             int32_t* __restrict__ tidx_out, const int sqrt_out, const int64_t ntiles, const int64_t tiles_per_cta) {
+             const int L32, const int Lp, const int nseg, const int32_t* __restrict__ segs, const int nstages, const int ne,
+             const int np, const float2* __restrict__ x, const int64_t xlen, const int64_t start, const int64_t K,
+             const float* __restrict__ xenergy, float* __restrict__ best_out, int32_t* __restrict__ tidx_out,
+             float* __restrict__ caf_out, const int caf_cols, const int sqrt_out, const int64_t ntiles,
+             const int64_t tiles_per_cta) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const TcSmem lay = tc_smem_layout(L32, NT, NB, nstages, ne, np);
+    const TcSmem lay = tc_smem_layout(Lp, NT, NB, nstages, ne, np);
     const int NKS = L32 / TC_SUB;          // K steps (= pipeline stages consumed) per template block
     uint8_t* const sE = smem;
     float* const sInv = reinterpret_cast<float*>(smem + lay.off_inv);
@@ -144,14 +148,25 @@ mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_ene
     if (warp < 4) {
         // ===== warps 0-3: build the expanded x tile of the NEXT tile while the MMAs of this one run, then the
         // epilogue of this tile.  thread = one shift (TMEM lane), columns = templates =====
-        auto build = [&](int i) {
-            const int b = i % ne;
-            const uint32_t use = (uint32_t)(i / ne);
+        // x tile jobs: a dense template set has ONE per tile of shifts (shared by all template blocks); a segmented
+        // set (templates that are non-zero only inside G groups, segs = {x offset, K steps} per group) has one per
+        // (tile, template block, group), consumed in that order
+        const int njobs = (nseg > 1) ? ntl * NB * nseg : ntl;
+        auto build = [&](int job) {
+            const int b = job % ne;
+            const uint32_t use = (uint32_t)(job / ne);
+            int til = job, xoff = 0, nks = NKS;
+            if (nseg > 1) {
+                const int sg = job % nseg;
+                til = (job / nseg) / NB;
+                xoff = __ldg(segs + 2 * sg);
+                nks = __ldg(segs + 2 * sg + 1);
+            }
             tc::mbar_wait(bar_eempty + 8 * b, (use & 1u) ^ 1u);      // the MMAs that read this buffer are done
-            const int64_t s0 = start + (tile0 + i) * TC_M;           // x index of (row 0, n = 0)
+            const int64_t s0 = start + (tile0 + til) * TC_M + xoff;  // x index of (row 0, n = 0)
             uint8_t* const E = sE + (size_t)b * 4 * lay.plane;
             // row (u, i) = BF16 hi / lo of x[s0 + 8u + i + j], j = 0..7, for re and im
-            const int rows = TC_M + L32;                              // = 8 U
+            const int rows = TC_M + TC_SUB * nks;                     // = 8 U
             for (int row = tid; row < rows; row += 128) {
                 const int64_t g = s0 + row;
                 uint32_t w[4][4];                                     // [plane][pair of bf16]
@@ -182,13 +197,25 @@ mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_ene
             tc::fence_proxy_async();                                  // generic-proxy stores -> tensor-core reads
             tc::mbar_arrive(bar_efull + 8 * b);
         };
-        if (ntl > 0) build(0);
+        int built = 0;
+        auto ensure = [&](int upto) {
+            if (upto > njobs) upto = njobs;
+            while (built < upto) build(built++);
+        };
+        ensure(1);
         uint32_t gen = 0;                                             // accumulator generations
         for (int i = 0; i < ntl; ++i) {
-            if (i + 1 < ntl) build(i + 1);
             float bestv = -1.f;
             int besti = 0;
+            const int64_t o = (tile0 + i) * TC_M + warp * 32 + lane;
+            const float inv_ex = (o < K) ? 1.f / xenergy[o] : 0.f;
             for (int nb = 0; nb < NB; ++nb) {
+                // keep the tile builder one job ahead of the MMAs
+                if (nseg > 1) {
+                    for (int sg = 0; sg < nseg; ++sg) ensure((i * NB + nb) * nseg + sg + 2);
+                } else if (nb == 0) {
+                    ensure(i + 2);
+                }
                 tc::mbar_wait(bar_tfull, gen & 1u);
                 tc::tc_fence_after();
                 const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
@@ -205,15 +232,22 @@ mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_ene
                             bestv = q;
                             besti = nb * NT + 16 * c + j;
                         }
+                        re[j] = q * inv_ex;
+                    }
+                    if (caf_out && o < K) {    // full surface: row = shift, column = template
+                        const int col0 = nb * NT + 16 * c;
+                        float* dst = caf_out + (size_t)o * (size_t)caf_cols + col0;
+#pragma unroll
+                        for (int j = 0; j < 16; ++j)
+                            if (col0 + j < caf_cols) dst[j] = re[j];
                     }
                 }
                 tc::tc_fence_before();
                 tc::mbar_arrive(bar_tempty);                          // TMEM may be overwritten
                 ++gen;
             }
-            const int64_t o = (tile0 + i) * TC_M + warp * 32 + lane;
             if (o < K) {
-                const float q = bestv / xenergy[o];
+                const float q = bestv * inv_ex;
                 if (best_out) best_out[o] = sqrt_out ? sqrtf(q) : q;
                 if (tidx_out) tidx_out[o] = besti;
             }
@@ -244,50 +278,60 @@ mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_ene
             // ===== MMA issuer =====
             uint32_t it = 0, gen = 0;
             const uint32_t c_re = tmem, c_im = tmem + 256;
+            int job = 0;
             for (int i = 0; i < ntl; ++i) {
-                const int b = i % ne;
-                const uint32_t use = (uint32_t)(i / ne);
-                tc::mbar_wait(bar_efull + 8 * b, use & 1u);
-                const uint32_t eb = sE_u32 + (uint32_t)b * 4 * lay.plane;
                 for (int nb = 0; nb < NB; ++nb) {
                     tc::mbar_wait(bar_tempty, (gen & 1u) ^ 1u);       // the epilogue has drained the accumulators
                     tc::tc_fence_after();
-                    for (int ks = 0; ks < NKS; ++ks) {
-                        const uint32_t st = it % (uint32_t)nstages, ph = (it / (uint32_t)nstages) & 1u;
-                        tc::mbar_wait(bar_full + 8 * st, ph);
+                    bool first = true;
+                    for (int sg = 0; sg < nseg; ++sg) {
+                        const int b = job % ne;
+                        const uint32_t use = (uint32_t)(job / ne);
+                        if (nseg > 1 || nb == 0) tc::mbar_wait(bar_efull + 8 * b, use & 1u);
                         tc::tc_fence_after();
-                        const uint32_t sb = sStage_u32 + st * lay.stage;
-                        const uint32_t acc = (ks > 0) ? 1u : 0u;
-                        uint64_t a[4], bd[4];
+                        const uint32_t eb = sE_u32 + (uint32_t)b * 4 * lay.plane;
+                        const int nks = (nseg > 1) ? __ldg(segs + 2 * sg + 1) : NKS;
+                        for (int ks = 0; ks < nks; ++ks) {
+                            const uint32_t st = it % (uint32_t)nstages, ph = (it / (uint32_t)nstages) & 1u;
+                            tc::mbar_wait(bar_full + 8 * st, ph);
+                            tc::tc_fence_after();
+                            const uint32_t sb = sStage_u32 + st * lay.stage;
+                            const uint32_t acc = first ? 0u : 1u;
+                            first = false;
+                            uint64_t a[4], bd[4];
 #pragma unroll
-                        for (int q = 0; q < 4; ++q)
-                            a[q] = tc::smem_desc(eb + (uint32_t)q * lay.plane + 2 * (uint32_t)ks * 128, 128, 128);
+                            for (int q = 0; q < 4; ++q)
+                                a[q] = tc::smem_desc(eb + (uint32_t)q * lay.plane + 2 * (uint32_t)ks * 128, 128, 128);
 #pragma unroll
-                        for (int p2 = 0; p2 < 4; ++p2) bd[p2] = tc::smem_desc(sb + (uint32_t)p2 * (uint32_t)NT * 32, b_lbo, 128);
-                        tc::umma_bf16(c_re, a[0], bd[0], idesc_pos, acc);
-                        tc::umma_bf16(c_re, a[1], bd[0], idesc_pos, 1u);
-                        tc::umma_bf16(c_re, a[2], bd[1], idesc_neg, 1u);
-                        tc::umma_bf16(c_re, a[3], bd[1], idesc_neg, 1u);
-                        tc::umma_bf16(c_im, a[2], bd[0], idesc_pos, acc);
-                        tc::umma_bf16(c_im, a[3], bd[0], idesc_pos, 1u);
-                        tc::umma_bf16(c_im, a[0], bd[1], idesc_pos, 1u);
-                        tc::umma_bf16(c_im, a[1], bd[1], idesc_pos, 1u);
-                        if (np == 4) {      // templates split into BF16 hi + lo: the lo part against x_hi
-                            tc::umma_bf16(c_re, a[0], bd[2], idesc_pos, 1u);
-                            tc::umma_bf16(c_re, a[2], bd[3], idesc_neg, 1u);
-                            tc::umma_bf16(c_im, a[2], bd[2], idesc_pos, 1u);
-                            tc::umma_bf16(c_im, a[0], bd[3], idesc_pos, 1u);
+                            for (int p2 = 0; p2 < 4; ++p2) bd[p2] = tc::smem_desc(sb + (uint32_t)p2 * (uint32_t)NT * 32, b_lbo, 128);
+                            tc::umma_bf16(c_re, a[0], bd[0], idesc_pos, acc);
+                            tc::umma_bf16(c_re, a[1], bd[0], idesc_pos, 1u);
+                            tc::umma_bf16(c_re, a[2], bd[1], idesc_neg, 1u);
+                            tc::umma_bf16(c_re, a[3], bd[1], idesc_neg, 1u);
+                            tc::umma_bf16(c_im, a[2], bd[0], idesc_pos, acc);
+                            tc::umma_bf16(c_im, a[3], bd[0], idesc_pos, 1u);
+                            tc::umma_bf16(c_im, a[0], bd[1], idesc_pos, 1u);
+                            tc::umma_bf16(c_im, a[1], bd[1], idesc_pos, 1u);
+                            if (np == 4) {      // templates split into BF16 hi + lo: the lo part against x_hi
+                                tc::umma_bf16(c_re, a[0], bd[2], idesc_pos, 1u);
+                                tc::umma_bf16(c_re, a[2], bd[3], idesc_neg, 1u);
+                                tc::umma_bf16(c_im, a[2], bd[2], idesc_pos, 1u);
+                                tc::umma_bf16(c_im, a[0], bd[3], idesc_pos, 1u);
+                            }
+                            tc::umma_commit(bar_empty + 8 * st);      // stage free once these MMAs have read it
+                            ++it;
                         }
-                        tc::umma_commit(bar_empty + 8 * st);          // stage free once these MMAs have read it
-                        ++it;
+                        if (nseg > 1 || nb == NB - 1) {
+                            tc::umma_commit(bar_eempty + 8 * b);      // x tile buffer free
+                            ++job;
+                        }
                     }
                     tc::umma_commit(bar_tfull);                       // accumulators complete
                     ++gen;
                 }
-                tc::umma_commit(bar_eempty + 8 * b);                  // x tile buffer free
             }
-            if (ntl > 0)      // every commit has landed before the CTA tears down
-                tc::mbar_wait(bar_eempty + 8 * ((ntl - 1) % ne), (uint32_t)((ntl - 1) / ne) & 1u);
+            if (job > 0)      // every commit has landed before the CTA tears down
+                tc::mbar_wait(bar_eempty + 8 * ((job - 1) % ne), (uint32_t)((job - 1) / ne) & 1u);
         }
     }
     tc::tc_fence_before();
@@ -302,10 +346,10 @@ mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_ene
 // host side
 // ---------------------------------------------------------------------------------------------
 // number of x-tile buffers (2 = the build of the next tile overlaps the MMAs) and of pipeline stages that fit
-static int tc_pick_stages(int L32, int NT, int NB, int np, int* ne_out) {
+static int tc_pick_stages(int Lp, int NT, int NB, int np, int* ne_out) {
     for (int ne = 2; ne >= 1; --ne)
         for (int s = TC_MAX_STAGES; s >= (ne == 2 ? 3 : 2); --s)
-            if ((int)tc_smem_layout(L32, NT, NB, s, ne, np).total + 128 <= max_smem_optin()) {
+            if ((int)tc_smem_layout(Lp, NT, NB, s, ne, np).total + 128 <= max_smem_optin()) {
                 *ne_out = ne;
                 return s;
             }
@@ -317,6 +361,8 @@ void mt_tc_release(MtTcPlan* plan) {
     if (!plan) return;
     cudaFree(plan->d_pack);
     cudaFree(plan->d_inv_energy);
+    cudaFree(plan->d_segs);
+    plan->d_segs = nullptr;
     plan->d_pack = nullptr;
     plan->d_inv_energy = nullptr;
     plan->usable = false;
@@ -326,11 +372,27 @@ void mt_tc_release(MtTcPlan* plan) {
 // caller asked).  plan->usable stays false (and the caller keeps the FP32 kernel) when there are too many
 // templates for the shared-memory energy table or when the expanded x tile plus two stages do not fit in
 // shared memory.  plan->planes = 2 when every template value is exact in BF16, 4 (hi + lo split) otherwise.
-int32_t mt_tc_prepare(const float2* d_templates, int T, int L, int L8, const float* d_energies, MtTcPlan* plan) {
+// Segmented sets (segs != NULL, nseg pairs {x offset, K steps of 16 samples}): the template rows hold the
+// concatenated group samples, every group padded to a multiple of 16, and L8 >= 16 * sum(K steps) rounded up to 32.
+int32_t mt_tc_prepare(const float2* d_templates, int T, int L, int L8, const float* d_energies, MtTcPlan* plan,
+                      const int32_t* segs, int nseg) {
     plan->usable = false;
     plan->T = T;
     plan->L = L;
     plan->L32 = (L + TC_KC - 1) / TC_KC * TC_KC;
+    plan->Lp = plan->L32;
+    plan->nseg = 1;
+    plan->d_segs = nullptr;
+    if (segs && nseg > 1) {
+        int lp = 0, total = 0;
+        for (int g = 0; g < nseg; ++g) {
+            if (segs[2 * g + 1] * TC_SUB > lp) lp = segs[2 * g + 1] * TC_SUB;
+            total += segs[2 * g + 1];
+        }
+        if (total * TC_SUB != plan->L32) return fail(XC_ERR_ARG, "segment K steps do not add up to the padded template length");
+        plan->Lp = (lp + TC_KC - 1) / TC_KC * TC_KC;
+        plan->nseg = nseg;
+    }
     plan->NT = (T >= 256) ? 256 : (T + 15) / 16 * 16;
     plan->NB = (T + plan->NT - 1) / plan->NT;
     if (const char* e = getenv("XC_MT_FP32")) {
@@ -338,7 +400,7 @@ int32_t mt_tc_prepare(const float2* d_templates, int T, int L, int L8, const flo
     }
     if (plan->NB * plan->NT > TC_MAX_TEMPLATES) return XC_OK;
     int ne_probe = 0;
-    if (tc_pick_stages(plan->L32, plan->NT, plan->NB, 4, &ne_probe) < 2) return XC_OK;
+    if (tc_pick_stages(plan->Lp, plan->NT, plan->NB, 4, &ne_probe) < 2) return XC_OK;
     int cc_major = 0;
     int dev = 0;
     XC_CUDA_TRY(cudaGetDevice(&dev));
@@ -367,16 +429,20 @@ int32_t mt_tc_prepare(const float2* d_templates, int T, int L, int L8, const flo
         cudaFree(plan->d_pack);
         plan->d_pack = nullptr;
     }
+    if (plan->nseg > 1) {
+        XC_CUDA_TRY(cudaMalloc(&plan->d_segs, sizeof(int32_t) * 2 * (size_t)nseg));
+        XC_CUDA_TRY(cudaMemcpy(plan->d_segs, segs, sizeof(int32_t) * 2 * (size_t)nseg, cudaMemcpyHostToDevice));
+    }
     plan->usable = true;
     return XC_OK;
 }
 
 int32_t mt_tc_run(const MtTcPlan& plan, const float2* x, int64_t xlen, int64_t start, int64_t K, const float* xenergy,
-                  float* best, int32_t* tidx, int sqrt_out, cudaStream_t stream) {
+                  float* best, int32_t* tidx, int sqrt_out, cudaStream_t stream, float* caf) {
     if (!plan.usable) return fail(XC_ERR_UNSUPPORTED, "tensor-core template plan is not usable");
     int ne = 0;
-    const int nstages = tc_pick_stages(plan.L32, plan.NT, plan.NB, plan.planes, &ne);
-    const TcSmem lay = tc_smem_layout(plan.L32, plan.NT, plan.NB, nstages, ne, plan.planes);
+    const int nstages = tc_pick_stages(plan.Lp, plan.NT, plan.NB, plan.planes, &ne);
+    const TcSmem lay = tc_smem_layout(plan.Lp, plan.NT, plan.NB, nstages, ne, plan.planes);
     const size_t smem = lay.total + 128;
     static size_t configured = 0;
     if (smem > configured) {
@@ -390,8 +456,9 @@ int32_t mt_tc_run(const MtTcPlan& plan, const float2* x, int64_t xlen, int64_t s
     ctas = (ntiles + per - 1) / per;
     profile_begin(stream);
     mt_tc_kernel<<<(unsigned)ctas, TC_THREADS, smem, stream>>>(reinterpret_cast<const uint8_t*>(plan.d_pack),
-                                                               plan.d_inv_energy, plan.NT, plan.NB, plan.L32, nstages, ne, plan.planes,
-                                                               x, xlen, start, K, xenergy, best, tidx, sqrt_out, ntiles, per);
+                                                               plan.d_inv_energy, plan.NT, plan.NB, plan.L32, plan.Lp, plan.nseg,
+                                                               plan.d_segs, nstages, ne, plan.planes, x, xlen, start, K, xenergy,
+                                                               best, tidx, caf, plan.T, sqrt_out, ntiles, per);
     profile_end(stream);
     XC_LAUNCH_CHECK();
     return XC_OK;

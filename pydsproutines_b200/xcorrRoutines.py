@@ -402,6 +402,177 @@ class GroupXcorrFFT:
 
 
 # ------------------------------------------------------------------------------------------------
+# 8(f): GroupXcorr / GroupXcorrGPU / GroupXcorrCZT  (xcorrRoutines.py:852-1039, 1896-2051)
+# ------------------------------------------------------------------------------------------------
+class _GroupFreqHandle:
+    """Owns an xc_groupfreq*: the group samples with the frequency list folded in, packed for the tensor cores."""
+
+    def __init__(self, ycat, starts, lengths, freq_cycles, start_freq_cycles=None):
+        lib = _lib.load()
+        y = np.ascontiguousarray(ycat, dtype=np.complex64)
+        st = np.ascontiguousarray(starts, dtype=np.int64)
+        ln = np.ascontiguousarray(lengths, dtype=np.int32)
+        fc = np.ascontiguousarray(freq_cycles, dtype=np.float64)
+        sfc = None if start_freq_cycles is None else np.ascontiguousarray(start_freq_cycles, dtype=np.float64)
+        assert y.size == int(ln.sum()) and (sfc is None or sfc.size == fc.size)
+        self.NF = int(fc.size)
+        self._h = C.c_void_p()
+        check(lib.xc_groupfreq_create(_lib.ptr(y), _lib.ptr(st), _lib.ptr(ln), int(st.size), _lib.ptr(fc), _lib.ptr(sfc),
+                                      self.NF, 0, C.byref(self._h)))
+
+    def run(self, rx, shift0, K, want_flat, want_caf):
+        lib = _lib.load()
+        where = _lib.where_of(rx)
+        _select_device(rx)
+        qf2 = _lib.empty_like_space(rx, K, np.float32) if want_flat else None
+        fidx = _lib.empty_like_space(rx, K, np.uint32) if want_flat else None
+        caf = _lib.empty_like_space(rx, (K, self.NF), np.float32) if want_caf else None
+        check(lib.xc_groupfreq_xcorr(self._h, _lib.ptr(rx), rx.shape[0], int(shift0), int(K), _lib.ptr(qf2),
+                                     _lib.ptr(fidx), _lib.ptr(caf), None, where, _lib.current_stream(rx)))
+        return qf2, fidx, caf
+
+    def run_shifts(self, rx, shifts, want_flat, want_caf):
+        """Any shift list: the kernel works on the covering contiguous range (a tile is 128 consecutive shifts) and
+        the requested rows are picked from it."""
+        if _lib.is_torch(shifts):
+            shifts = shifts.detach().cpu().numpy()
+        s = np.asarray(shifts).astype(np.int64).reshape(-1)
+        if s.size == 0:
+            return self.run(rx, 0, 0, want_flat, want_caf)
+        lo, hi = int(s.min()), int(s.max())
+        out = self.run(rx, lo, hi - lo + 1, want_flat, want_caf)
+        if s.size == hi - lo + 1 and np.all(np.diff(s) == 1):
+            return out
+        pick = s - lo
+        if _lib.is_device(rx):
+            import torch
+            pick = torch.from_numpy(pick).to(rx.device)
+        return tuple(None if o is None else o[pick] for o in out)
+
+    def __del__(self):
+        try:
+            if self._h:
+                _lib.load().xc_groupfreq_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
+class GroupXcorr:
+    """Drop-in for xcorrRoutines.GroupXcorr (852-954): groups y[starts[i] : starts[i] + lengths[i]] correlated
+    coherently over an arbitrary frequency list; xcorr returns (xc float64[K], freqpeaks float64[K]).  The reference's
+    freqMat @ (rxconcat * yconcat) per shift runs as one segmented tensor-core contraction (csrc/groupfreq.cu)."""
+
+    def __init__(self, y, starts, lengths, freqs, fs, autoConj=True, autoZeroStarts=True):
+        y = np.asarray(y)
+        starts = np.asarray(starts)
+        lengths = np.asarray(lengths)
+        assert starts.size == lengths.size                                           # :883
+        self.starts = starts - starts[0] if autoZeroStarts else starts              # :885-887
+        self.lengths = lengths
+        self.numGroups = self.starts.size
+        self.freqs = np.asarray(freqs, dtype=np.float64)
+        self.fs = fs
+        yy = y.conj() if autoConj else y                                             # :894-905
+        self.yconcat = np.hstack([yy[starts[i]:starts[i] + lengths[i]] for i in range(self.numGroups)])
+        self.yconcatNormSq = np.linalg.norm(self.yconcat) ** 2                       # :906
+        # |freqMat @ p| does not depend on a common start offset, so the (zeroed) starts serve as phase origin
+        self._handle = _GroupFreqHandle(self.yconcat, self.starts - self.starts.min(), self.lengths,
+                                        self.freqs / float(fs))
+
+    def _shifts(self, rx, shifts):
+        if shifts is None:
+            return np.arange(rx.shape[0] - (int(self.starts[-1]) + int(self.lengths[-1])) + 1)    # :921
+        assert shifts[-1] + self.starts[-1] + self.lengths[-1] < rx.shape[0]                      # :923-925
+        return shifts
+
+    def _rx(self, rx):
+        if _lib.np_dtype_of(rx) != np.dtype(np.complex64):
+            raise TypeError("rx must be complex64")
+        return _lib.contiguous(rx)
+
+    def _offset(self):
+        return int(self.starts.min())
+
+    def xcorr(self, rx, shifts=None):
+        rx = self._rx(rx)
+        shifts = self._shifts(rx, shifts)
+        qf2, fidx, _ = self._handle.run_shifts(rx, np.asarray(shifts) + self._offset(), True, False)
+        if _lib.is_torch(fidx):
+            import torch
+            freqpeaks = torch.from_numpy(self.freqs).to(fidx.device)[fidx.long()]
+        else:
+            freqpeaks = self.freqs[fidx]
+        return _as(qf2, np.float64), freqpeaks
+
+    def xcorrIndices(self, rx, shifts=None):
+        """(xc float32[K], freqinds int32[K]) -- what GroupXcorrGPU.xcorrKernel returns (2000-2037)."""
+        rx = self._rx(rx)
+        shifts = self._shifts(rx, shifts)
+        qf2, fidx, _ = self._handle.run_shifts(rx, np.asarray(shifts) + self._offset(), True, False)
+        return qf2, (fidx.astype(np.int32) if not _lib.is_torch(fidx) else fidx)
+
+
+class GroupXcorrGPU(GroupXcorr):
+    """Drop-in for xcorrRoutines.GroupXcorrGPU (1896-2051); autoConj / autoZeroStarts at their defaults like the
+    reference's constructor (1905)."""
+
+    def __init__(self, y, starts, lengths, freqs, fs):
+        super().__init__(y, starts, lengths, freqs, fs)
+
+    def xcorrKernel(self, rx, shifts, numShiftsPerBlk=2, verbTiming=False):
+        assert np.asarray(shifts).size % numShiftsPerBlk == 0                        # :1970
+        return self.xcorrIndices(rx, shifts)
+
+
+class GroupXcorrCZT:
+    """Drop-in for xcorrRoutines.GroupXcorrCZT (957-1039): xcorr returns (CAF float64 (K, nbins), cztFreq).  The
+    per-group cached CZT + group phase + coherent sum of the reference is the same segmented contraction with the
+    bins of CZTCached (f1 + k (f2 - f1 + binWidth) / nbins) inside a group and the nominal grid for the group phase."""
+
+    def __init__(self, y, starts, lengths, f1, f2, binWidth, fs, autoConj=True, autoZeroStarts=True):
+        y = np.asarray(y)
+        starts = np.asarray(starts)
+        lengths = np.asarray(lengths)
+        assert starts.size == lengths.size                                           # :971
+        self.starts = starts - starts[0] if autoZeroStarts else starts              # :972-974
+        self.lengths = lengths
+        self.numGroups = self.starts.size
+        self.fs = fs
+        self.f1, self.f2, self.binWidth = f1, f2, binWidth
+        self.maxLength = int(np.max(self.lengths))
+        self.ystack = np.zeros((self.numGroups, self.maxLength), y.dtype)           # :985-990
+        for i in range(self.numGroups):
+            self.ystack[i, :lengths[i]] = y[starts[i]:starts[i] + lengths[i]]
+        if autoConj:
+            self.ystack = self.ystack.conj()
+        self.ystackNormSq = np.linalg.norm(self.ystack.flatten()) ** 2              # :992
+        from .spectralRoutines import CZTCached
+        self.cztc = CZTCached(self.maxLength, f1, f2, binWidth, fs)                 # :995
+        self.cztFreq = np.arange(self.f1, self.f2 + self.binWidth / 2, self.binWidth)   # :1007
+        nb = self.cztc.k
+        if self.cztFreq.size != nb:
+            raise ValueError("operands could not be broadcast together: %d CZT bins against %d group phases"
+                             % (nb, self.cztFreq.size))      # the reference fails the same way at :1033
+        ycat = np.hstack([self.ystack[i, :lengths[i]] for i in range(self.numGroups)])
+        bins = self.cztc.f0_cycles + np.arange(nb) * self.cztc.df_cycles
+        self._off = int(self.starts.min())
+        self._handle = _GroupFreqHandle(ycat, self.starts - self._off, self.lengths, bins,
+                                        self.cztFreq / float(fs))
+
+    def xcorr(self, rx, shifts=None):
+        if _lib.np_dtype_of(rx) != np.dtype(np.complex64):
+            raise TypeError("rx must be complex64")
+        rx = _lib.contiguous(rx)
+        if shifts is None:
+            shifts = np.arange(rx.shape[0] - (int(self.starts[-1]) + int(self.lengths[-1])) + 1)   # :1000
+        else:
+            assert shifts[-1] + self.starts[-1] + self.lengths[-1] < rx.shape[0]                   # :1002-1004
+        _, _, caf = self._handle.run_shifts(rx, np.asarray(shifts) + self._off, False, True)
+        return _as(caf, np.float64), self.cztFreq
+
+
+# ------------------------------------------------------------------------------------------------
 # a8: CyGroupXcorrFFT  (CyGroupXcorrFFT.pyx:13-66, GroupXcorrFFT.cpp:3-199)
 # ------------------------------------------------------------------------------------------------
 class CyGroupXcorrFFT:

@@ -576,3 +576,77 @@ def test_cp_fastxcorr_v2_czt_branch(xr):
     np.testing.assert_allclose(surf, d["caf"], rtol=RTOL, atol=2e-6 * d["caf"].max())
     with pytest.raises(ValueError):
         xr.cp_fastXcorr_v2(_dev(cutout[:500].copy()), _dev(rx), 0, 10, cztObj=obj)
+
+
+# ---------------------------------------------------------------------------------------------
+# grouped correlators over a frequency list (GroupXcorr / GroupXcorrGPU / GroupXcorrCZT): tensor-core segmented
+# contraction vs golden vectors of the real reference and vs the oracle
+# ---------------------------------------------------------------------------------------------
+def _groupfreq_bins_ok(got_f, ref_f, surface_row, freqs):
+    """frequency picks must be equal; a differing pick is accepted only as a near-tie of the float64 surface"""
+    diff = np.nonzero(got_f != ref_f)[0]
+    assert diff.size <= max(1, got_f.size // 50), "too many frequency mismatches: %d of %d" % (diff.size, got_f.size)
+    for i in diff:
+        row = surface_row(int(i))
+        a = row[int(np.nonzero(freqs == got_f[i])[0][0])]
+        b = row[int(np.nonzero(freqs == ref_f[i])[0][0])]
+        assert abs(a - b) <= 1e-4 * b, "frequency mismatch at %d is not a near-tie" % i
+
+
+@pytest.mark.parametrize("name,d", _load("groupfreq_*.npz"), ids=lambda v: v if isinstance(v, str) else "")
+@pytest.mark.parametrize("space", ["host", "device"])
+def test_groupfreq_golden(xr, name, d, space):
+    conv = _dev if space == "device" else (lambda a: a)
+    back = (lambda t: t.cpu().numpy()) if space == "device" else (lambda a: a)
+    rx = conv(d["rx"])
+    fs = float(d["fs"])
+    a = xr.GroupXcorr(d["y"], d["starts"], d["lengths"], d["freqs"], fs)
+    xc, fp = a.xcorr(rx, d["shifts"])
+    xc, fp = back(xc), back(fp)
+    assert xc.dtype == np.float64 and fp.dtype == np.float64
+    assert_qf2(xc, d["xc"])
+    assert int(np.argmax(xc)) == int(d["p0"]) and fp[int(d["p0"])] == d["freqpeaks"][int(d["p0"])]
+    o = orc.GroupXcorr(d["y"], d["starts"], d["lengths"], d["freqs"], fs)
+
+    def row(i):
+        s = int(d["shifts"][i])
+        rc = np.hstack([d["rx"][s + o.starts[g]:s + o.starts[g] + o.lengths[g]] for g in range(o.starts.size)])
+        return np.abs(o.freqMat @ (rc * o.yconcat).astype(np.complex128)) ** 2
+    _groupfreq_bins_ok(fp, d["freqpeaks"], row, np.asarray(d["freqs"], np.float64))
+    b = xr.GroupXcorrCZT(d["y"], d["starts"], d["lengths"], float(d["f1"]), float(d["f2"]), float(d["bw"]), fs)
+    caf, cf = b.xcorr(rx, d["shifts"])
+    caf = back(caf)
+    assert caf.dtype == np.float64 and caf.shape == d["caf"].shape and np.array_equal(cf, d["cztFreq"])
+    np.testing.assert_allclose(caf, d["caf"], rtol=RTOL, atol=2e-6 * d["caf"].max())
+
+
+def test_groupfreq_vs_oracle_many_tiles(xr):
+    """more shifts than one 128-shift tile and more frequencies than one 256-column block, strided and explicit
+    shift lists, GroupXcorrGPU.xcorrKernel return types"""
+    rng = np.random.default_rng(77)
+    ylen, fs = 3000, 1.0
+    starts = np.array([7, 500, 1333, 2100, 2600])
+    lengths = np.array([100, 48, 129, 16, 250])
+    y = signals.qpsk(rng, ylen)
+    freqs = np.linspace(-0.01, 0.01, 300)
+    K = 700
+    z = starts - starts[0]
+    rx = signals.cnoise(rng, K + int(z[-1]) + int(lengths[-1]) + 8)
+    p0, foff = 411, freqs[123]
+    for g in range(starts.size):
+        n = np.arange(lengths[g]) + z[g]
+        rx[p0 + z[g]:p0 + z[g] + lengths[g]] += (0.9 * y[starts[g]:starts[g] + lengths[g]] * np.exp(2j * np.pi * foff * n / fs)).astype(np.complex64)
+    a = xr.GroupXcorrGPU(y, starts, lengths, freqs, fs)
+    o = orc.GroupXcorr(y, starts, lengths, freqs, fs)
+    for shifts in (np.arange(K), np.arange(3, K, 5), np.array([411, 2, 640, 128, 127])):
+        xc, fp = a.xcorr(rx, shifts)
+        rxc, rfp = o.xcorr(rx, shifts)
+        assert_qf2(xc, rxc)
+        assert (fp == rfp).mean() > 0.97
+        if 411 in shifts:
+            i = int(np.argmax(xc))
+            assert shifts[i] == 411 and fp[i] == freqs[123]
+    q, fi = a.xcorrKernel(rx, np.arange(K), numShiftsPerBlk=2)
+    assert q.dtype == np.float32 and fi.dtype == np.int32 and int(fi[411]) == 123
+    with pytest.raises(AssertionError):
+        a.xcorr(rx, np.arange(K + 20))                       # reads past the end of rx (xcorrRoutines.py:923-925)
