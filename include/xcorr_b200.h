@@ -154,6 +154,23 @@ int32_t xc_groupfreq_xcorr(xc_groupfreq* handle, const void* rx, int64_t rxlen, 
                            float* qf2, uint32_t* fidx, float* caf, xc_peak* peak, int32_t where, void* stream);
 int32_t xc_groupfreq_destroy(xc_groupfreq* handle);
 
+/* ---- 8(f) rank 2: refinement around a found peak -------------------------------------------
+ * xcorrRoutines.fineFreqTimeSearch (xcorrRoutines.py:583-667), makeTimeScanSteervec (669-675) and
+ * GenXcorr.xcorr (679-719).  complex128 (interleaved double) like the reference; x / y / steeringvec / pp / cost /
+ * best follow `where`, the short lists freq_cycles / td / freq_bounds are always HOST arrays.
+ *   xc_fine_freq_c128: pp[j] = sum_n y[n] conj(x[n]) exp(-j 2 pi freq_cycles[j] n)  (= np.vdot(y.conj() * x, shift_j),
+ *                      :620-629), *best = np.argmax(np.abs(pp)).
+ *   xc_time_scan_c128: x' = x exp(-j 2 pi shift_cycles n) (:632), X = fft(x'), Y = fft(y) for ANY length N,
+ *                      r = X conj(Y), zeroed where makeFreq(N, fs) is outside [freq_bounds[0], freq_bounds[1]) (:645-654),
+ *                      cost[k] = sum_m r[m] conj(S[k, m]) / ||X|| / ||Y|| (:656-660) with S = steeringvec [NT, N] or, when
+ *                      steeringvec is NULL, exp(+j 2 pi makeFreq(N, fs)[m] td[k]) generated on the fly;
+ *                      *best = np.argmax(np.abs(cost)). */
+int32_t xc_fine_freq_c128(const void* x, const void* y, int64_t N, const double* freq_cycles, int64_t NF, void* pp,
+                          int64_t* best, int32_t where, void* stream);
+int32_t xc_time_scan_c128(const void* x, const void* y, int64_t N, double shift_cycles, const double* td, int64_t NT,
+                          double fs, const double* freq_bounds, const void* steeringvec, void* cost, int64_t* best,
+                          int32_t where, void* stream);
+
 /* ---- a9, a10: (multi-)template correlator -------------------------------------------------
  * xcorrRoutines.TemplateCrossCorrelator (xcorrRoutines.py:277-371) and
  * cupyExtensions.multiTemplateSlidingDotProduct (cupyExtensions.py:563-642 -> multiplySlices.cu:251-399).

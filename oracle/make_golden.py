@@ -134,11 +134,49 @@ def groupfreq_cases(ref):
     return cases
 
 
+def fine_cases(ref):
+    """fineFreqTimeSearch (xcorrRoutines.py:583-667) and GenXcorr (679-719): y = x delayed by a fraction of a sample
+    and shifted by a fraction of a coarse frequency bin, both in noise."""
+    cases = {}
+    # name, seed, N, fs, frac delay (samples), freq offset, coarse freq found, freqRes, fineRes, td range, bounds
+    specs = [
+        ("n1000", 51, 1000, 1000.0, 0.37, 0.31, 0.0, 1.0, [0.1, 0.01], np.arange(-0.002, 0.002, 0.00005), None),
+        ("n777_bounds", 52, 777, 48000.0, -0.21, -13.0, -61.776, 61.776, [5.0, 0.5, 0.05],
+         np.arange(-2, 2, 0.05) / 48000.0, (-12000.0, 12000.0)),
+        ("n4096_nofreq", 53, 4096, 1.0, 0.45, 0.0, 0.0, 0.0, [], np.arange(-1.0, 1.0, 0.01), None),
+    ]
+    for name, seed, N, fs, delay, foff, f0, fres, fineRes, td, bounds in specs:
+        rng = np.random.default_rng(seed)
+        base = (rng.standard_normal(N) + 1j * rng.standard_normal(N))
+        # band-limit to half the band so that a fractional delay is well defined
+        B = np.fft.fft(base)
+        fvec = np.fft.fftfreq(N)
+        B[np.abs(fvec) > 0.25] = 0
+        x = np.fft.ifft(B)
+        yd = np.fft.ifft(B * np.exp(-2j * np.pi * fvec * delay))
+        # fineFreqTimeSearch removes +f from x to match y: y carries -foff relative to x
+        yv = yd * np.exp(-2j * np.pi * foff * np.arange(N) / fs)
+        xn = (x + 0.05 * (rng.standard_normal(N) + 1j * rng.standard_normal(N))).astype(np.complex64)
+        yn = (yv + 0.05 * (rng.standard_normal(N) + 1j * rng.standard_normal(N))).astype(np.complex64)
+        ff, tdiff, cost = ref.fineFreqTimeSearch(xn, yn, fineRes, f0, fres, fs, td, td_scan_freqBounds=bounds)
+        g = ref.GenXcorr(td, fs, N)
+        if bounds is not None:
+            g.setTDscan_freqBounds(np.array(bounds))
+        gtd, gcost = g.xcorr(xn, yn)
+        d = dict(x=xn, y=yn, fs=fs, fineRes=np.array(fineRes, np.float64), f0=f0, freqRes=fres, td=td,
+                 finefreq=np.nan if ff is None else ff, timediff=tdiff, cost=cost, gen_td=gtd, gen_cost=gcost,
+                 delay=delay, foff=foff, qf2=ref.calcQF2(xn, yn))
+        if bounds is not None:
+            d["bounds"] = np.array(bounds)
+        cases[name] = d
+    return cases
+
+
 def main():
     ref = ref_import.load()
     os.makedirs(OUT, exist_ok=True)
     for fam, cases in (("fastxcorr", fastxcorr_cases(ref)), ("groupxcorr", group_cases(ref)), ("cztxcorr", czt_cases(ref)),
-                       ("groupfreq", groupfreq_cases(ref))):
+                       ("groupfreq", groupfreq_cases(ref)), ("fine", fine_cases(ref))):
         for name, d in cases.items():
             path = os.path.join(OUT, "%s_%s.npz" % (fam, name))
             np.savez_compressed(path, **d)

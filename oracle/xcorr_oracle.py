@@ -439,3 +439,45 @@ class GroupXcorrCZT:
                 tot += (E[g] @ (yg * sl).astype(np.complex128)) * phases[g]
             xc[i] = np.abs(tot) ** 2 / en / self.ystackNormSq
         return xc, self.cztFreq
+
+
+def timeScan(x, y, td_scan_range, fs, freqBounds=None, steeringvec=None):
+    """The time-alignment half of fineFreqTimeSearch (xcorrRoutines.py:637-664) = GenXcorr.xcorr (697-719):
+    cost[k] = sum_m X[m] conj(Y[m]) conj(S[k, m]) / ||X|| / ||Y||, S = exp(+2j pi makeFreq(N, fs) td_k)."""
+    X = np.fft.fft(np.asarray(x, np.complex128))
+    Y = np.fft.fft(np.asarray(y, np.complex128))
+    r = X * Y.conj()
+    f = makeFreq(X.size, fs)
+    if freqBounds is not None:
+        r[(f < freqBounds[0]) | (f >= freqBounds[1])] = 0
+    if steeringvec is None:
+        steeringvec = np.exp(2j * np.pi * f * np.asarray(td_scan_range).reshape(-1, 1))
+    cost = (steeringvec.conj() @ r) / np.linalg.norm(X) / np.linalg.norm(Y)
+    return np.asarray(td_scan_range)[int(np.argmax(np.abs(cost)))], cost
+
+
+def fineFreqTimeSearch(x_aligned, y_aligned, fineRes, freqfound, freqRes, fs, td_scan_range, steeringvec=None,
+                       td_scan_freqBounds=None):
+    """xcorrRoutines.py:583-667: successive fine frequency scans pp[j] = vdot(conj(y) x, exp(-2j pi f_j n / fs)),
+    then the time scan on the frequency-corrected x."""
+    x = np.asarray(x_aligned, np.complex128)
+    y = np.asarray(y_aligned, np.complex128)
+    n = np.arange(x.size)
+    finefreq = None
+    for res in fineRes:
+        grid = np.arange(freqfound - freqRes, freqfound + freqRes, res)
+        pp = np.exp(-2j * np.pi * np.outer(grid, n) / fs) @ (y * x.conj())
+        freqfound = grid[int(np.argmax(np.abs(pp)))]
+        finefreq = freqfound
+    if finefreq is not None:
+        x = x * np.exp(-2j * np.pi * finefreq * n / fs)
+    td, cost = timeScan(x, y, td_scan_range, fs, td_scan_freqBounds, steeringvec)
+    return finefreq, td, cost
+
+
+def calcQF2(x, y):
+    """xcorrRoutines.py:833-848 (1-D and row-wise 2-D)."""
+    x = np.atleast_2d(np.asarray(x, np.complex128))
+    y = np.atleast_2d(np.asarray(y, np.complex128))
+    q = np.abs(np.sum(x.conj() * y, axis=1)) ** 2 / np.sum(np.abs(x) ** 2, axis=1) / np.sum(np.abs(y) ** 2, axis=1)
+    return q if q.size > 1 else q[0]

@@ -54,6 +54,8 @@ SIGNATURES = {
     "xc_groupfreq_create": (_i32, [_vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32, C.POINTER(_vp)]),
     "xc_groupfreq_xcorr": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp, C.POINTER(xc_peak), _i32, _vp]),
     "xc_groupfreq_destroy": (_i32, [_vp]),
+    "xc_fine_freq_c128": (_i32, [_vp, _vp, _i64, _vp, _i64, _vp, _vp, _i32, _vp]),
+    "xc_time_scan_c128": (_i32, [_vp, _vp, _i64, C.c_double, _vp, _i64, C.c_double, _vp, _vp, _vp, _vp, _i32, _vp]),
     "xc_mt_create": (_i32, [_vp, _i32, _i32, _i32, _vp, C.POINTER(_vp)]),
     "xc_mt_correlate": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp, _i32, C.POINTER(xc_peak), _i32, _vp]),
     "xc_mt_destroy": (_i32, [_vp]),
@@ -122,7 +124,8 @@ def torch_dtype(np_dtype):
     import torch
     if not _TORCH_DTYPES:
         _TORCH_DTYPES.update({np.dtype(np.float32): torch.float32, np.dtype(np.float64): torch.float64,
-                              np.dtype(np.complex64): torch.complex64, np.dtype(np.int32): torch.int32,
+                              np.dtype(np.complex64): torch.complex64, np.dtype(np.complex128): torch.complex128,
+                              np.dtype(np.int32): torch.int32,
                               np.dtype(np.int64): torch.int64, np.dtype(np.uint32): torch.int32})
     return _TORCH_DTYPES[np.dtype(np_dtype)]
 

@@ -402,6 +402,153 @@ class GroupXcorrFFT:
 
 
 # ------------------------------------------------------------------------------------------------
+# 8(f) rank 2: refinement around the found peak  (xcorrRoutines.py:583-772)
+# ------------------------------------------------------------------------------------------------
+def _c128(a):
+    """complex128 view of an aligned pair of arrays (the reference's arithmetic promotes to complex128)."""
+    if _lib.is_torch(a):
+        import torch
+        return a.to(torch.complex128).contiguous()
+    return np.ascontiguousarray(a, dtype=np.complex128)
+
+
+def _fine_freq(x, y, freq_cycles):
+    lib = _lib.load()
+    where = _lib.where_of(x, y)
+    _select_device(x)
+    fc = np.ascontiguousarray(freq_cycles, dtype=np.float64)
+    pp = _lib.empty_like_space(x, fc.size, np.complex128)
+    best = C.c_int64(-1)
+    bdev = _lib.empty_like_space(x, 1, np.int64) if where == XC_DEVICE else None
+    check(lib.xc_fine_freq_c128(_lib.ptr(x), _lib.ptr(y), x.shape[0], _lib.ptr(fc), fc.size, _lib.ptr(pp),
+                                _lib.ptr(bdev) if bdev is not None else C.cast(C.byref(best), C.c_void_p), where,
+                                _lib.current_stream(x)))
+    return pp, (int(bdev.item()) if bdev is not None else int(best.value))
+
+
+def _time_scan(x, y, shift_cycles, td_scan_range, fs, freqBounds, steeringvec):
+    lib = _lib.load()
+    where = _lib.where_of(x, y, steeringvec)
+    _select_device(x)
+    N = x.shape[0]
+    td = None if td_scan_range is None else np.ascontiguousarray(td_scan_range, dtype=np.float64)
+    if steeringvec is not None:
+        steeringvec = _c128(steeringvec)
+        assert steeringvec.ndim == 2 and steeringvec.shape[1] == N
+        NT = steeringvec.shape[0]
+    else:
+        NT = td.size
+    fb = None if freqBounds is None else np.ascontiguousarray(freqBounds, dtype=np.float64)
+    cost = _lib.empty_like_space(x, NT, np.complex128)
+    best = C.c_int64(-1)
+    bdev = _lib.empty_like_space(x, 1, np.int64) if where == XC_DEVICE else None
+    check(lib.xc_time_scan_c128(_lib.ptr(x), _lib.ptr(y), N, float(shift_cycles), _lib.ptr(td), NT, float(fs),
+                                _lib.ptr(fb), _lib.ptr(steeringvec), _lib.ptr(cost),
+                                _lib.ptr(bdev) if bdev is not None else C.cast(C.byref(best), C.c_void_p), where,
+                                _lib.current_stream(x)))
+    return cost, (int(bdev.item()) if bdev is not None else int(best.value))
+
+
+def makeTimeScanSteervec(td_scan_range, fs, siglen):
+    """xcorrRoutines.py:669-675 (only needed by callers that want the matrix itself; the scans generate it on the fly)."""
+    return np.exp(1j * 2 * np.pi * makeFreq(siglen, fs) * np.asarray(td_scan_range).reshape((-1, 1)))
+
+
+def fineFreqTimeSearch(x_aligned, y_aligned, fineRes, freqfound, freqRes, fs, td_scan_range, steeringvec=None,
+                       td_scan_freqBounds=None):
+    """Drop-in for xcorrRoutines.fineFreqTimeSearch (583-667): returns (finefreqfound, timediff, cost_vec complex128).
+    Each frequency pass and the time scan are FP64 kernels (csrc/fine.cu); the spectra are exact dense DFTs, so any
+    length works."""
+    x = _c128(x_aligned)
+    y = _c128(y_aligned)
+    assert x.ndim == 1 and x.shape == y.shape
+    shift_cycles = 0.0
+    if len(fineRes) > 0:
+        for i in range(len(fineRes)):
+            fineFreq = np.arange(freqfound - freqRes, freqfound + freqRes, fineRes[i])           # :618
+            _, ind = _fine_freq(x, y, fineFreq / float(fs))
+            freqfound = fineFreq[ind]                                                             # :628-629
+        finefreqfound = freqfound
+        shift_cycles = float(freqfound) / float(fs)                                              # :632-633
+    else:
+        finefreqfound = None
+    td = np.asarray(td_scan_range)
+    cost, idx_td = _time_scan(x, y, shift_cycles, td, fs, td_scan_freqBounds, steeringvec)
+    return finefreqfound, td[idx_td], cost
+
+
+class GenXcorr:
+    """Drop-in for xcorrRoutines.GenXcorr (679-719)."""
+
+    def __init__(self, td_scan_range, fs, siglen):
+        self.td_scan_range = np.asarray(td_scan_range)
+        self.fs = fs
+        self.siglen = siglen
+        self.sigFreq = makeFreq(siglen, fs)
+        self.td_scan_freqBounds = None
+        self._steer = None
+
+    @property
+    def steeringvec(self):
+        if self._steer is None:
+            self._steer = makeTimeScanSteervec(self.td_scan_range, self.fs, self.siglen)
+        return self._steer
+
+    def setTDscan_freqBounds(self, td_scan_freqBounds):
+        self.td_scan_freqBounds = td_scan_freqBounds
+
+    def xcorr(self, x, y):
+        cost, idx = _time_scan(_c128(x), _c128(y), 0.0, self.td_scan_range, self.fs, self.td_scan_freqBounds, None)
+        return self.td_scan_range[idx], cost
+
+
+def calcQF2(x, y):
+    """Drop-in for xcorrRoutines.calcQF2 (833-848): QF^2 of two aligned arrays (1-D, or row-wise for 2-D) = the
+    no-frequency-search correlator at the single shift 0."""
+    if x.ndim == 1 and y.ndim == 1:
+        q, _, _, _ = _fastxcorr_call(_require_c64("x", x), _require_c64("y", y), _Shifts(np.array([0]), y.shape[0], x.shape[0], y), False)
+        return _as(q, np.float64)[0]
+    if x.ndim == 2 and y.ndim == 2:
+        rows = [calcQF2(x[i], y[i]) for i in range(x.shape[0])]
+        if _lib.is_torch(rows[0]):
+            import torch
+            return torch.stack(rows)
+        return np.array(rows)
+
+
+def convertQF2toSNR(qf2):
+    """xcorrRoutines.py:723-725."""
+    return qf2 / (1.0 - qf2)
+
+
+def convertQF2toEffSNR(qf2):
+    """xcorrRoutines.py:728-730."""
+    return 2.0 * qf2 / (1.0 - qf2)
+
+
+def convertEffSNRtoQF2(effSNR):
+    """xcorrRoutines.py:733-735."""
+    return effSNR / (2 + effSNR)
+
+
+def expectedEffSNR(snr1, snr2=np.inf, OSR=1):
+    """xcorrRoutines.py:738-755."""
+    y = 1.0 / (0.5 * (1 / snr1 + 1 / snr2 + 1 / snr1 / snr2))
+    return y / OSR
+
+
+def sigmaDTO(signalBW, noiseBW, integTime, effSNR):
+    """xcorrRoutines.py:758-764."""
+    beta = np.pi / np.sqrt(3) * signalBW
+    return 1.0 / beta / np.sqrt(noiseBW * integTime * effSNR)
+
+
+def sigmaDFO(noiseBW, integTime, effSNR):
+    """xcorrRoutines.py:767-772."""
+    return 0.55 / integTime / np.sqrt(noiseBW * integTime * effSNR)
+
+
+# ------------------------------------------------------------------------------------------------
 # 8(f): GroupXcorr / GroupXcorrGPU / GroupXcorrCZT  (xcorrRoutines.py:852-1039, 1896-2051)
 # ------------------------------------------------------------------------------------------------
 class _GroupFreqHandle:

@@ -650,3 +650,51 @@ def test_groupfreq_vs_oracle_many_tiles(xr):
     assert q.dtype == np.float32 and fi.dtype == np.int32 and int(fi[411]) == 123
     with pytest.raises(AssertionError):
         a.xcorr(rx, np.arange(K + 20))                       # reads past the end of rx (xcorrRoutines.py:923-925)
+
+
+# ---------------------------------------------------------------------------------------------
+# refinement around the peak (fineFreqTimeSearch / GenXcorr / calcQF2): FP64 kernels vs the real reference
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name,d", _load("fine_*.npz"), ids=lambda v: v if isinstance(v, str) else "")
+@pytest.mark.parametrize("space", ["host", "device"])
+def test_fine_search_golden(xr, name, d, space):
+    conv = _dev if space == "device" else (lambda a: a)
+    back = (lambda t: t.cpu().numpy()) if space == "device" else (lambda a: a)
+    x, y = conv(d["x"]), conv(d["y"])
+    bounds = d["bounds"] if "bounds" in d.files else None
+    fs = float(d["fs"])
+    ff, td, cost = xr.fineFreqTimeSearch(x, y, list(d["fineRes"]), float(d["f0"]), float(d["freqRes"]), fs, d["td"],
+                                         td_scan_freqBounds=bounds)
+    cost = back(cost)
+    if np.isnan(d["finefreq"]):
+        assert ff is None
+    else:
+        assert ff == float(d["finefreq"])                       # the same grid point, bit for bit
+    assert td == float(d["timediff"])
+    assert cost.dtype == np.complex128
+    np.testing.assert_allclose(cost, d["cost"], rtol=0, atol=5e-8)
+    g = xr.GenXcorr(d["td"], fs, d["x"].size)
+    if bounds is not None:
+        g.setTDscan_freqBounds(bounds)
+    gtd, gcost = g.xcorr(x, y)
+    assert gtd == float(d["gen_td"])
+    np.testing.assert_allclose(back(gcost), d["gen_cost"], rtol=0, atol=5e-7)       # both reference FFTs in float32 (numpy >= 2)
+    # a caller-supplied steering matrix (fineFreqTimeSearch's steeringvec argument) gives the same scan
+    S = xr.makeTimeScanSteervec(d["td"], fs, d["x"].size)
+    ff2, td2, cost2 = xr.fineFreqTimeSearch(x, y, list(d["fineRes"]), float(d["f0"]), float(d["freqRes"]), fs, d["td"],
+                                            steeringvec=conv(S), td_scan_freqBounds=bounds)
+    assert td2 == td and (ff2 == ff or (ff is None and ff2 is None))
+    np.testing.assert_allclose(back(cost2), d["cost"], rtol=0, atol=5e-8)
+    q = xr.calcQF2(x, y)
+    assert abs(float(q) - float(d["qf2"])) <= RTOL * float(d["qf2"])
+    q2 = back(xr.calcQF2(conv(np.stack([d["x"], d["y"]])), conv(np.stack([d["y"], d["y"]]))))
+    assert abs(q2[0] - float(d["qf2"])) <= RTOL * float(d["qf2"]) and abs(q2[1] - 1.0) <= RTOL
+
+
+def test_snr_helpers(xr):
+    """xcorrRoutines.py:723-772 (closed-form helpers that callers apply to the QF^2 trace)."""
+    assert xr.convertQF2toSNR(0.5) == 1.0 and xr.convertQF2toEffSNR(0.5) == 2.0
+    assert abs(xr.convertEffSNRtoQF2(xr.convertQF2toEffSNR(0.3)) - 0.3) < 1e-15
+    assert xr.expectedEffSNR(10.0, np.inf, 2) == 10.0                    # the docstring example of the reference (:744-750)
+    assert abs(xr.sigmaDFO(1e4, 0.1, 10.0) - 0.55 / 0.1 / np.sqrt(1e4 * 0.1 * 10.0)) < 1e-15
+    assert abs(xr.sigmaDTO(5e3, 1e4, 0.1, 10.0) - 1.0 / (np.pi / np.sqrt(3) * 5e3) / np.sqrt(1e4 * 0.1 * 10.0)) < 1e-18

@@ -143,3 +143,24 @@ def test_groupfreq_restatement_matches_reference(name, d):
     i = int(np.argmax(xc))
     assert i == int(d["p0"])
     assert abs(fp[i] - float(d["foff"])) <= np.min(np.abs(np.diff(np.sort(d["freqs"])))) + 1e-12
+
+
+@pytest.mark.parametrize("name,d", _load("fine_*.npz"), ids=lambda v: v if isinstance(v, str) else "")
+def test_fine_search_restatement_matches_reference(name, d):
+    """fineFreqTimeSearch (xcorrRoutines.py:583-667), GenXcorr.xcorr (697-719) and calcQF2 (833-848).  The picks
+    (fine frequency, time offset) must be identical; the cost vectors agree to 5e-8 absolute only, because numpy >= 2
+    runs np.fft.fft of the complex64 inputs in single precision when the golden vectors are generated, while the
+    restatement (like the reference under numpy 1.x) transforms in double."""
+    bounds = d["bounds"] if "bounds" in d.files else None
+    ff, td, cost = orc.fineFreqTimeSearch(d["x"], d["y"], list(d["fineRes"]), float(d["f0"]), float(d["freqRes"]),
+                                          float(d["fs"]), d["td"], td_scan_freqBounds=bounds)
+    if np.isnan(d["finefreq"]):
+        assert ff is None
+    else:
+        assert ff == float(d["finefreq"])
+    assert td == float(d["timediff"])
+    np.testing.assert_allclose(cost, d["cost"], rtol=0, atol=5e-8)
+    gtd, gcost = orc.timeScan(d["x"], d["y"], d["td"], float(d["fs"]), bounds)
+    assert gtd == float(d["gen_td"])
+    np.testing.assert_allclose(gcost, d["gen_cost"], rtol=0, atol=5e-7)       # both reference FFTs in float32 (numpy >= 2)
+    np.testing.assert_allclose(orc.calcQF2(d["x"], d["y"]), float(d["qf2"]), rtol=1e-5)
