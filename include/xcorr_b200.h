@@ -154,6 +154,13 @@ int32_t xc_groupfreq_xcorr(xc_groupfreq* handle, const void* rx, int64_t rxlen, 
                            float* qf2, uint32_t* fidx, float* caf, xc_peak* peak, int32_t where, void* stream);
 int32_t xc_groupfreq_destroy(xc_groupfreq* handle);
 
+/* ---- 8(f) rank 3: capture ingestion ---------------------------------------------------------
+ * usrpRoutines.simpleBinRead (usrpRoutines.py:51-66: np.fromfile(int16).astype(float32).view(complex64)) and the
+ * copy-then-convert-on-device finding of benchmarks/benchmark_cupyCopyAndConvert.py:15-26.  iq = nsamp interleaved
+ * (I, Q) int16 pairs, out = nsamp complex64; each side host or device (where_in / where_out).  With a host input
+ * the raw int16 samples cross PCIe (half the bytes of complex64) and are widened on the device. */
+int32_t xc_convert_i16_c64(const int16_t* iq, int64_t nsamp, void* out, int32_t where_in, int32_t where_out, void* stream);
+
 /* ---- 8(f) rank 2: refinement around a found peak -------------------------------------------
  * xcorrRoutines.fineFreqTimeSearch (xcorrRoutines.py:583-667), makeTimeScanSteervec (669-675) and
  * GenXcorr.xcorr (679-719).  complex128 (interleaved double) like the reference; x / y / steeringvec / pp / cost /

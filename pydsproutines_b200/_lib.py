@@ -60,6 +60,7 @@ SIGNATURES = {
     "xc_mt_correlate": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp, _i32, C.POINTER(xc_peak), _i32, _vp]),
     "xc_mt_destroy": (_i32, [_vp]),
     "xc_mt_uses_tensor_cores": (_i32, [_vp]),
+    "xc_convert_i16_c64": (_i32, [_vp, _i64, _vp, _i32, _i32, _vp]),
     "xc_copy_groups_c64": (_i32, [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _i32, _i32, _vp]),
     "xc_copy_slices_to_matrix_c64": (_i32, [_vp, _i64, _i64, _i64, _i64, _i64, _vp, _i32, _vp]),
     "xc_multiply_slides_normalised_c64": (_i32, [_vp, _i32, _vp, _i64, _i64, _i64, C.c_double, _vp, _i32, _vp]),
@@ -125,7 +126,7 @@ def torch_dtype(np_dtype):
     if not _TORCH_DTYPES:
         _TORCH_DTYPES.update({np.dtype(np.float32): torch.float32, np.dtype(np.float64): torch.float64,
                               np.dtype(np.complex64): torch.complex64, np.dtype(np.complex128): torch.complex128,
-                              np.dtype(np.int32): torch.int32,
+                              np.dtype(np.int32): torch.int32, np.dtype(np.int16): torch.int16,
                               np.dtype(np.int64): torch.int64, np.dtype(np.uint32): torch.int32})
     return _TORCH_DTYPES[np.dtype(np_dtype)]
 
@@ -135,7 +136,8 @@ def np_dtype_of(x):
         import torch
         return {torch.float32: np.dtype(np.float32), torch.float64: np.dtype(np.float64),
                 torch.complex64: np.dtype(np.complex64), torch.complex128: np.dtype(np.complex128),
-                torch.int32: np.dtype(np.int32), torch.int64: np.dtype(np.int64)}.get(x.dtype)
+                torch.int32: np.dtype(np.int32), torch.int64: np.dtype(np.int64),
+                torch.int16: np.dtype(np.int16)}.get(x.dtype)
     return np.asarray(x).dtype
 
 

@@ -59,6 +59,28 @@ __global__ void multiply_slides_kernel(const float2* __restrict__ x, int xlen, c
     }
 }
 
+// raw interleaved int16 I/Q -> complex64, 4 samples (16 B in, 32 B out) per thread and iteration
+__global__ void convert_i16_c64_kernel(const int16_t* __restrict__ iq, int64_t nsamp, float2* __restrict__ out) {
+    const int64_t nvec = nsamp / 4;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int4* in4 = reinterpret_cast<const int4*>(iq);
+    float4* out4 = reinterpret_cast<float4*>(out);
+    for (int64_t i = tid; i < nvec; i += stride) {
+        const int4 v = __ldg(in4 + i);
+        const int w[4] = {v.x, v.y, v.z, v.w};
+        float f[8];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            f[2 * q] = (float)(int16_t)(w[q] & 0xffff);
+            f[2 * q + 1] = (float)(int16_t)(w[q] >> 16);
+        }
+        out4[2 * i] = make_float4(f[0], f[1], f[2], f[3]);
+        out4[2 * i + 1] = make_float4(f[4], f[5], f[6], f[7]);
+    }
+    for (int64_t n = nvec * 4 + tid; n < nsamp; n += stride) out[n] = make_float2((float)iq[2 * n], (float)iq[2 * n + 1]);
+}
+
 }  // namespace xc
 
 using namespace xc;
@@ -73,6 +95,41 @@ static int32_t helpers_require_device() {
 }
 
 extern "C" {
+
+int32_t xc_convert_i16_c64(const int16_t* iq, int64_t nsamp, void* out, int32_t where_in, int32_t where_out, void* stream) {
+    if ((where_in != XC_HOST && where_in != XC_DEVICE) || (where_out != XC_HOST && where_out != XC_DEVICE))
+        return fail(XC_ERR_ARG, "where must be XC_HOST (0) or XC_DEVICE (1)");
+    if (!iq || !out) return fail(XC_ERR_ARG, "iq/out is NULL");
+    if (nsamp < 0) return fail(XC_ERR_ARG, "negative size");
+    XC_TRY(helpers_require_device());
+    if (nsamp == 0) return XC_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int16_t* din = iq;
+    float2* dout = (float2*)out;
+    if (where_in == XC_HOST) {          // the raw samples cross PCIe: half the bytes of complex64
+        int16_t* b = (int16_t*)workspace(SLOT_IN0, sizeof(int16_t) * 2 * (size_t)nsamp);
+        if (!b) return XC_ERR_NOMEM;
+        XC_CUDA_TRY(cudaMemcpyAsync(b, iq, sizeof(int16_t) * 2 * (size_t)nsamp, cudaMemcpyHostToDevice, st));
+        din = b;
+    }
+    if (where_out == XC_HOST) {
+        dout = (float2*)workspace(SLOT_OUT2, sizeof(float2) * (size_t)nsamp);
+        if (!dout) return XC_ERR_NOMEM;
+    }
+    if ((reinterpret_cast<uintptr_t>(din) & 15) || (reinterpret_cast<uintptr_t>(dout) & 15))
+        return fail(XC_ERR_ARG, "device buffers must be 16-byte aligned");
+    int64_t blocks = (nsamp / 4 + 255) / 256;
+    const int64_t cap = (int64_t)sm_count() * 16;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    convert_i16_c64_kernel<<<(unsigned)blocks, 256, 0, st>>>(din, nsamp, dout);
+    XC_LAUNCH_CHECK();
+    if (where_out == XC_HOST) {
+        XC_CUDA_TRY(cudaMemcpyAsync(out, dout, sizeof(float2) * (size_t)nsamp, cudaMemcpyDeviceToHost, st));
+        XC_CUDA_TRY(cudaStreamSynchronize(st));
+    }
+    return XC_OK;
+}
 
 int32_t xc_copy_groups_c64(const void* x, int64_t xlen, void* y, int64_t ylen, const int32_t* x_starts,
                            const int32_t* y_starts, const int32_t* lengths, int32_t G, int32_t where, void* stream) {

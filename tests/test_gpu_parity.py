@@ -698,3 +698,38 @@ def test_snr_helpers(xr):
     assert xr.expectedEffSNR(10.0, np.inf, 2) == 10.0                    # the docstring example of the reference (:744-750)
     assert abs(xr.sigmaDFO(1e4, 0.1, 10.0) - 0.55 / 0.1 / np.sqrt(1e4 * 0.1 * 10.0)) < 1e-15
     assert abs(xr.sigmaDTO(5e3, 1e4, 0.1, 10.0) - 1.0 / (np.pi / np.sqrt(3) * 5e3) / np.sqrt(1e4 * 0.1 * 10.0)) < 1e-18
+
+
+# ---------------------------------------------------------------------------------------------
+# capture ingestion: raw int16 I/Q -> complex64 on the device (usrpRoutines.simpleBinRead, bit-exact)
+# ---------------------------------------------------------------------------------------------
+def test_int16_ingestion(xr, tmp_path):
+    import torch
+    from pydsproutines_b200 import usrpRoutines as ur
+    rng = np.random.default_rng(5)
+    for n in (0, 1, 3, 4, 1001, 1 << 16):
+        iq = rng.integers(-32768, 32768, size=2 * n, dtype=np.int16)
+        ref = iq.astype(np.float32).view(np.complex64)            # usrpRoutines.py:61-64
+        assert np.array_equal(ur.convertInt16ToComplex64(iq), ref)
+        d = ur.convertInt16ToComplex64(iq, device="cuda:0")
+        assert d.is_cuda and d.dtype == torch.complex64 and np.array_equal(d.cpu().numpy(), ref)
+        if n:
+            d2 = ur.convertInt16ToComplex64(torch.from_numpy(iq).cuda())
+            assert np.array_equal(d2.cpu().numpy(), ref)
+    # file reader: sample count, byte offset, device placement, straight into the correlator
+    iq = rng.integers(-2000, 2000, size=2 * 5000, dtype=np.int16)
+    path = os.path.join(str(tmp_path), "cap.bin")
+    iq.tofile(path)
+    ref = iq.astype(np.float32).view(np.complex64)
+    assert np.array_equal(ur.simpleBinRead(path), ref)
+    assert np.array_equal(ur.simpleBinRead(path, numSamps=100, offset=4 * 7), ref[7:107])
+    rx = ur.simpleBinRead(path, device="cuda:0")
+    cut = ref[1234:1234 + 256].copy()
+    q = xr.fastXcorr(_dev(cut), rx).cpu().numpy()
+    assert int(np.argmax(q)) == 1234 and abs(q[1234] - 1.0) < 1e-4
+    both = ur.multiBinRead([path, path], 50)
+    assert np.array_equal(both, np.concatenate([ref[:50], ref[:50]]))
+    with pytest.raises(TypeError):
+        ur.simpleBinRead(path, in_dtype=np.complex64)
+    qb, fb = ur.type1ResultBlobs(np.array([0.25, 0.5], np.float32), np.array([3, 7], np.int32))
+    assert np.array_equal(np.frombuffer(qb, np.float64), [0.25, 0.5]) and np.array_equal(np.frombuffer(fb, np.uint32), [3, 7])
