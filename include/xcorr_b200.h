@@ -144,15 +144,24 @@ int32_t xc_group_destroy(xc_group* handle);
  * f / fs.  start_freq_cycles (NULL = freq_cycles) is the frequency used for the starts[g] part of the phase:
  * GroupXcorrCZT rotates the groups with the nominal grid f1 + k binWidth while its CZT bins sit at
  * f1 + k (f2 - f1 + binWidth) / nbins (spectralRoutines.py:239-262).  Shifts are the contiguous range shift0 .. shift0 + K - 1.  qf2/fidx = max / arg max over the list per
- * shift, caf = the full [K, NF] float surface; any of them may be NULL.  Runs on the tensor cores (tcgen05);
+ * shift, caf = the full [K, NF] float surface, cplx = the raw complex d[s, k] (device buffers only); any may be NULL.  Runs on the tensor cores (tcgen05);
  * XC_ERR_UNSUPPORTED on anything else. */
 typedef struct xc_groupfreq xc_groupfreq;
 int32_t xc_groupfreq_create(const void* ycat, const int64_t* starts, const int32_t* lengths, int32_t G,
                             const double* freq_cycles, const double* start_freq_cycles, int32_t NF, int32_t conj,
                             xc_groupfreq** handle);
 int32_t xc_groupfreq_xcorr(xc_groupfreq* handle, const void* rx, int64_t rxlen, int64_t shift0, int64_t K,
-                           float* qf2, uint32_t* fidx, float* caf, xc_peak* peak, int32_t where, void* stream);
+                           float* qf2, uint32_t* fidx, float* caf, void* cplx, xc_peak* peak, int32_t where,
+                           void* stream);
 int32_t xc_groupfreq_destroy(xc_groupfreq* handle);
+/* GroupXcorrCZT_Permutations (xcorrRoutines.py:1264-1690): every template of every group is correlated once
+ * (xc_groupfreq_xcorr with cplx = the raw complex surface d[s, k], complex64 [K, NF], device only), then any
+ * permutation is  caf[s, b] = |sum_g surfaces[template_idx[g], s, b]|^2 / sum_g rxnormsq[group_idx[g], s] / ynormsq
+ * (getCAF_GPU, :1452-1483).  surfaces [NTemplates, K, NB] complex64, rxnormsq [NGroups, K] float32 and caf [K, NB]
+ * float32 are DEVICE buffers; template_idx / group_idx are host arrays of G entries. */
+int32_t xc_groupperm_combine(const void* surfaces, int64_t K, int32_t NB, const int32_t* template_idx,
+                             const int32_t* group_idx, int32_t G, const float* rxnormsq, double ynormsq, float* caf,
+                             void* stream);
 
 /* ---- 8(f) rank 3: capture ingestion ---------------------------------------------------------
  * usrpRoutines.simpleBinRead (usrpRoutines.py:51-66: np.fromfile(int16).astype(float32).view(complex64)) and the

@@ -172,11 +172,39 @@ def fine_cases(ref):
     return cases
 
 
+def groupperm_cases(ref):
+    """GroupXcorrCZT_Permutations (xcorrRoutines.py:1264-1690), CPU methods xcorr + getCAF: 3 groups with 2 / 3 / 1
+    candidate templates; the permutation (1, 2, 0) is planted."""
+    rng = np.random.default_rng(61)
+    L, fs = 96, 2000.0
+    idxs = np.array([0, 0, 1, 1, 1, 2])
+    starts = np.array([0, 300, 777])
+    ygroups = signals.qpsk(rng, idxs.size * L).reshape(idxs.size, L)
+    f1, f2, bw = -20.0, 20.0, 1.0
+    K, p0, foff = 40, 13, 7.0
+    rx = signals.cnoise(rng, K + int(starts[-1]) + L + 4)
+    planted = (1, 2, 0)
+    for g in range(3):
+        k = np.argwhere(idxs == g)[planted[g]][0]
+        n = np.arange(L) + starts[g]
+        rx[p0 + starts[g]:p0 + starts[g] + L] += (0.8 * ygroups[k] * np.exp(2j * np.pi * foff * n / fs)).astype(np.complex64)
+    obj = ref.GroupXcorrCZT_Permutations(ygroups, idxs, starts, f1, f2, bw, fs)
+    shifts = np.arange(K)
+    cf = obj.xcorr(rx, shifts, numThreads=1)
+    d = dict(ygroups=ygroups, idxs=idxs, starts=starts, f1=f1, f2=f2, bw=bw, fs=fs, rx=rx, shifts=shifts, cztFreq=cf,
+             xcTemplates=obj.xcTemplates.astype(np.complex64), rxgroupNormSq=obj.rxgroupNormSq, p0=p0, foff=foff,
+             planted=np.array(planted))
+    for name, perm in (("caf_planted", planted), ("caf_other", (0, 0, 0))):
+        d[name] = obj.getCAF(np.array(perm), numThreads=1)
+    return {"g3": d}
+
+
 def main():
     ref = ref_import.load()
     os.makedirs(OUT, exist_ok=True)
     for fam, cases in (("fastxcorr", fastxcorr_cases(ref)), ("groupxcorr", group_cases(ref)), ("cztxcorr", czt_cases(ref)),
-                       ("groupfreq", groupfreq_cases(ref)), ("fine", fine_cases(ref))):
+                       ("groupfreq", groupfreq_cases(ref)), ("fine", fine_cases(ref)),
+                       ("groupperm", groupperm_cases(ref))):
         for name, d in cases.items():
             path = os.path.join(OUT, "%s_%s.npz" % (fam, name))
             np.savez_compressed(path, **d)

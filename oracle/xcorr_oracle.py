@@ -481,3 +481,48 @@ def calcQF2(x, y):
     y = np.atleast_2d(np.asarray(y, np.complex128))
     q = np.abs(np.sum(x.conj() * y, axis=1)) ** 2 / np.sum(np.abs(x) ** 2, axis=1) / np.sum(np.abs(y) ** 2, axis=1)
     return q if q.size > 1 else q[0]
+
+
+class GroupXcorrCZT_Permutations:
+    """xcorrRoutines.py:1264-1690 (CPU methods xcorr / getCAF): per-template complex surfaces
+    CZT(y_k rx[shift + start_g : + L]) * exp(-2j pi cztFreq start_g / fs), combined per permutation as
+    |sum_g surface|^2 / sum_g ||rx_g||^2 / sum_g ||y_k||^2.  The CZT is evaluated directly on CZTCached's bins."""
+
+    def __init__(self, ygroups, ygroupIdxs, groupStarts, f1, f2, binWidth, fs, autoConj=True):
+        self.ygroups = np.asarray(ygroups).conj() if autoConj else np.asarray(ygroups)
+        self.ygroupIdxs = np.asarray(ygroupIdxs)
+        self.groupStarts = np.asarray(groupStarts)
+        self.fs = fs
+        self.length = self.ygroups.shape[1]
+        self.ygroupsEnergy = np.linalg.norm(self.ygroups, axis=1) ** 2
+        k = int((f2 - f1) / binWidth + 1)
+        self.bins = f1 + np.arange(k) * (f2 - f1 + binWidth) / k
+        self.cztFreq = np.arange(f1, f2 + binWidth / 2, binWidth)
+
+    def xcorr(self, rx, shifts):
+        rx = np.asarray(rx)
+        E = np.exp(-2j * np.pi * np.outer(self.bins, np.arange(self.length)) / self.fs)
+        ph = np.exp(-2j * np.pi * self.cztFreq * self.groupStarts.reshape(-1, 1) / self.fs)
+        T, G = self.ygroups.shape[0], self.groupStarts.size
+        self.xcTemplates = np.zeros((T, len(shifts), self.bins.size), np.complex128)
+        self.rxgroupNormSq = np.zeros((G, len(shifts)))
+        for i, s in enumerate(shifts):
+            for g in range(G):
+                sl = rx[s + self.groupStarts[g]:s + self.groupStarts[g] + self.length]
+                self.rxgroupNormSq[g, i] = np.linalg.norm(sl) ** 2
+            for k in range(T):
+                g = self.ygroupIdxs[k]
+                sl = rx[s + self.groupStarts[g]:s + self.groupStarts[g] + self.length]
+                self.xcTemplates[k, i] = (E @ (self.ygroups[k] * sl).astype(np.complex128)) * ph[g]
+        return self.cztFreq
+
+    def getCAF(self, templateIdx):
+        tot = np.zeros(self.xcTemplates.shape[1:], np.complex128)
+        rn = np.zeros(self.rxgroupNormSq.shape[1])
+        yn = 0.0
+        for g in range(self.groupStarts.size):
+            k = np.argwhere(self.ygroupIdxs == g)[templateIdx[g]][0]
+            tot += self.xcTemplates[k]
+            rn += self.rxgroupNormSq[g]
+            yn += self.ygroupsEnergy[k]
+        return np.abs(tot) ** 2 / rn.reshape(-1, 1) / yn

@@ -52,7 +52,8 @@ SIGNATURES = {
     "xc_group_xcorr": (_i32, [_vp, _vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp, _vp, C.POINTER(xc_peak), _i32, _vp]),
     "xc_group_destroy": (_i32, [_vp]),
     "xc_groupfreq_create": (_i32, [_vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32, C.POINTER(_vp)]),
-    "xc_groupfreq_xcorr": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp, C.POINTER(xc_peak), _i32, _vp]),
+    "xc_groupfreq_xcorr": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp, C.POINTER(xc_peak), _i32, _vp]),
+    "xc_groupperm_combine": (_i32, [_vp, _i64, _i32, _vp, _vp, _i32, _vp, C.c_double, _vp, _vp]),
     "xc_groupfreq_destroy": (_i32, [_vp]),
     "xc_fine_freq_c128": (_i32, [_vp, _vp, _i64, _vp, _i64, _vp, _vp, _i32, _vp]),
     "xc_time_scan_c128": (_i32, [_vp, _vp, _i64, C.c_double, _vp, _i64, C.c_double, _vp, _vp, _vp, _vp, _i32, _vp]),

@@ -45,6 +45,25 @@ __global__ void groupfreq_energy_kernel(const float* __restrict__ el, int64_t el
     }
 }
 
+// caf[s, b] = |sum_g surf[tmpl[g], s, b]|^2 / sum_g en[grp[g], s] / ynormsq   (GroupXcorrCZT_Permutations.getCAF)
+__global__ void groupperm_combine_kernel(const float2* __restrict__ surf, int64_t K, int NB, const int32_t* __restrict__ sel,
+                                         int G, const float* __restrict__ en, double inv_ynormsq, float* __restrict__ caf) {
+    const int64_t total = K * NB;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
+        const int64_t s = e / NB;
+        float2 acc = make_float2(0.f, 0.f);
+        double rn = 0.0;
+        for (int g = 0; g < G; ++g) {
+            const float2 v = __ldg(surf + (size_t)sel[2 * g] * (size_t)total + e);
+            acc.x += v.x;
+            acc.y += v.y;
+            rn += (double)__ldg(en + (size_t)sel[2 * g + 1] * (size_t)K + s);
+        }
+        caf[e] = (float)(((double)acc.x * acc.x + (double)acc.y * acc.y) / rn * inv_ynormsq);
+    }
+}
+
 int32_t collect_peak(const float* d_qf2, const uint32_t* d_fidx, const int32_t* d_aux, int64_t K, int64_t shift0,
                      int64_t step, const int64_t* d_shifts, xc_peak* peak, cudaStream_t st);
 
@@ -53,6 +72,32 @@ int32_t collect_peak(const float* d_qf2, const uint32_t* d_fidx, const int32_t* 
 using namespace xc;
 
 extern "C" {
+
+int32_t xc_groupperm_combine(const void* surfaces, int64_t K, int32_t NB, const int32_t* template_idx,
+                             const int32_t* group_idx, int32_t G, const float* rxnormsq, double ynormsq, float* caf,
+                             void* stream) {
+    if (!surfaces || !template_idx || !group_idx || !rxnormsq || !caf) return fail(XC_ERR_ARG, "NULL argument");
+    if (K < 0 || NB < 1 || G < 1 || G > 4096) return fail(XC_ERR_ARG, "bad sizes");
+    if (!(ynormsq > 0.0)) return fail(XC_ERR_ARG, "template energy must be positive");
+    if (K == 0) return XC_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    int32_t* d_sel = (int32_t*)workspace(SLOT_IN2, sizeof(int32_t) * 2 * (size_t)G);
+    if (!d_sel) return XC_ERR_NOMEM;
+    std::vector<int32_t> sel(2 * (size_t)G);
+    for (int g = 0; g < G; ++g) {
+        sel[2 * g] = template_idx[g];
+        sel[2 * g + 1] = group_idx[g];
+    }
+    XC_CUDA_TRY(cudaMemcpyAsync(d_sel, sel.data(), sizeof(int32_t) * sel.size(), cudaMemcpyHostToDevice, st));
+    XC_CUDA_TRY(cudaStreamSynchronize(st));          // sel is a stack-lifetime host buffer
+    int64_t blocks = (K * NB + 255) / 256;
+    const int64_t cap = (int64_t)sm_count() * 16;
+    if (blocks > cap) blocks = cap;
+    groupperm_combine_kernel<<<(unsigned)blocks, 256, 0, st>>>(reinterpret_cast<const float2*>(surfaces), K, NB, d_sel, G,
+                                                               rxnormsq, 1.0 / ynormsq, caf);
+    XC_LAUNCH_CHECK();
+    return XC_OK;
+}
 
 int32_t xc_groupfreq_destroy(xc_groupfreq* h) {
     if (!h) return XC_OK;
@@ -173,7 +218,7 @@ int32_t xc_groupfreq_create(const void* ycat, const int64_t* starts, const int32
 }
 
 int32_t xc_groupfreq_xcorr(xc_groupfreq* h, const void* rx, int64_t rxlen, int64_t shift0, int64_t K, float* qf2,
-                           uint32_t* fidx, float* caf, xc_peak* peak, int32_t where, void* stream) {
+                           uint32_t* fidx, float* caf, void* cplx, xc_peak* peak, int32_t where, void* stream) {
     if (where != XC_HOST && where != XC_DEVICE) return fail(XC_ERR_ARG, "where must be XC_HOST (0) or XC_DEVICE (1)");
     if (!h || !rx) return fail(XC_ERR_ARG, "handle/rx is NULL");
     if (K < 0 || shift0 < 0) return fail(XC_ERR_RANGE, "shifts must be >= 0");
@@ -187,7 +232,9 @@ int32_t xc_groupfreq_xcorr(xc_groupfreq* h, const void* rx, int64_t rxlen, int64
     const size_t cafb = sizeof(float) * (size_t)K * (size_t)h->NF;
     const float2* drx = reinterpret_cast<const float2*>(rx);
     float *dq = qf2, *dcaf = caf;
+    float2* dcplx = reinterpret_cast<float2*>(cplx);
     uint32_t* df = fidx;
+    if (cplx && where == XC_HOST) return fail(XC_ERR_UNSUPPORTED, "the complex surface is a device-side output");
     if (where == XC_HOST) {
         float2* b = (float2*)workspace(SLOT_IN1, sizeof(float2) * (size_t)rxlen);
         if (!b) return XC_ERR_NOMEM;
@@ -216,7 +263,7 @@ int32_t xc_groupfreq_xcorr(xc_groupfreq* h, const void* rx, int64_t rxlen, int64
                                                                   d_energy, q > 0 ? 1 : 0);
         XC_LAUNCH_CHECK();
     }
-    XC_TRY(mt_tc_run(h->tc, drx, rxlen, shift0 + h->start0, K, d_energy, dq, reinterpret_cast<int32_t*>(df), 0, st, dcaf));
+    XC_TRY(mt_tc_run(h->tc, drx, rxlen, shift0 + h->start0, K, d_energy, dq, reinterpret_cast<int32_t*>(df), 0, st, dcaf, dcplx));
     if (where == XC_HOST) {
         if (qf2) XC_CUDA_TRY(cudaMemcpyAsync(qf2, dq, sizeof(float) * (size_t)K, cudaMemcpyDeviceToHost, st));
         if (fidx) XC_CUDA_TRY(cudaMemcpyAsync(fidx, df, sizeof(uint32_t) * (size_t)K, cudaMemcpyDeviceToHost, st));

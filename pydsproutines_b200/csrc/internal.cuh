@@ -61,6 +61,7 @@ int32_t mt_tc_prepare(const float2* d_templates, int T, int L, int L8, const flo
                       const int32_t* segs = nullptr, int nseg = 0);
 void mt_tc_release(MtTcPlan* plan);
 int32_t mt_tc_run(const MtTcPlan& plan, const float2* x, int64_t xlen, int64_t start, int64_t K, const float* xenergy,
-                  float* best, int32_t* tidx, int sqrt_out, cudaStream_t stream, float* caf = nullptr);
+                  float* best, int32_t* tidx, int sqrt_out, cudaStream_t stream, float* caf = nullptr,
+                  float2* cplx = nullptr);
 
 }  // namespace xc

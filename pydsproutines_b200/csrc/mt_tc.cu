@@ -103,7 +103,8 @@ mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_ene
              const int L32, const int Lp, const int nseg, const int32_t* __restrict__ segs, const int nstages, const int ne,
              const int np, const float2* __restrict__ x, const int64_t xlen, const int64_t start, const int64_t K,
              const float* __restrict__ xenergy, float* __restrict__ best_out, int32_t* __restrict__ tidx_out,
-             float* __restrict__ caf_out, const int caf_cols, const int sqrt_out, const int64_t ntiles,
+             float* __restrict__ caf_out, float2* __restrict__ cplx_out, const int caf_cols, const int sqrt_out,
+             const int64_t ntiles,
              const int64_t tiles_per_cta) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -225,6 +226,13 @@ mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_ene
                     tc::tmem_ld16(lane_base + 16 * c, re);
                     tc::tmem_ld16(lane_base + 256 + 16 * c, im);
                     tc::tmem_ld_wait();
+                    if (cplx_out && o < K) {   // raw complex contraction d[s, t], row = shift
+                        const int col0 = nb * NT + 16 * c;
+                        float2* dst = cplx_out + (size_t)o * (size_t)caf_cols + col0;
+#pragma unroll
+                        for (int j = 0; j < 16; ++j)
+                            if (col0 + j < caf_cols) dst[j] = make_float2(re[j], im[j]);
+                    }
 #pragma unroll
                     for (int j = 0; j < 16; ++j) {
                         const float q = fmaf(re[j], re[j], im[j] * im[j]) * inv[16 * c + j];
@@ -438,7 +446,7 @@ int32_t mt_tc_prepare(const float2* d_templates, int T, int L, int L8, const flo
 }
 
 int32_t mt_tc_run(const MtTcPlan& plan, const float2* x, int64_t xlen, int64_t start, int64_t K, const float* xenergy,
-                  float* best, int32_t* tidx, int sqrt_out, cudaStream_t stream, float* caf) {
+                  float* best, int32_t* tidx, int sqrt_out, cudaStream_t stream, float* caf, float2* cplx) {
     if (!plan.usable) return fail(XC_ERR_UNSUPPORTED, "tensor-core template plan is not usable");
     int ne = 0;
     const int nstages = tc_pick_stages(plan.Lp, plan.NT, plan.NB, plan.planes, &ne);
@@ -458,7 +466,7 @@ int32_t mt_tc_run(const MtTcPlan& plan, const float2* x, int64_t xlen, int64_t s
     mt_tc_kernel<<<(unsigned)ctas, TC_THREADS, smem, stream>>>(reinterpret_cast<const uint8_t*>(plan.d_pack),
                                                                plan.d_inv_energy, plan.NT, plan.NB, plan.L32, plan.Lp, plan.nseg,
                                                                plan.d_segs, nstages, ne, plan.planes, x, xlen, start, K, xenergy,
-                                                               best, tidx, caf, plan.T, sqrt_out, ntiles, per);
+                                                               best, tidx, caf, cplx, plan.T, sqrt_out, ntiles, per);
     profile_end(stream);
     XC_LAUNCH_CHECK();
     return XC_OK;

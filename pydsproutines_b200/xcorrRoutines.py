@@ -575,8 +575,14 @@ class _GroupFreqHandle:
         fidx = _lib.empty_like_space(rx, K, np.uint32) if want_flat else None
         caf = _lib.empty_like_space(rx, (K, self.NF), np.float32) if want_caf else None
         check(lib.xc_groupfreq_xcorr(self._h, _lib.ptr(rx), rx.shape[0], int(shift0), int(K), _lib.ptr(qf2),
-                                     _lib.ptr(fidx), _lib.ptr(caf), None, where, _lib.current_stream(rx)))
+                                     _lib.ptr(fidx), _lib.ptr(caf), None, None, where, _lib.current_stream(rx)))
         return qf2, fidx, caf
+
+    def run_complex(self, rx, shift0, K, out):
+        """raw complex surface d[s, k] into `out` (torch CUDA complex64 [K, NF]); rx must be a CUDA tensor"""
+        _select_device(rx)
+        check(_lib.load().xc_groupfreq_xcorr(self._h, _lib.ptr(rx), rx.shape[0], int(shift0), int(K), None, None, None,
+                                             _lib.ptr(out), None, XC_DEVICE, _lib.current_stream(rx)))
 
     def run_shifts(self, rx, shifts, want_flat, want_caf):
         """Any shift list: the kernel works on the covering contiguous range (a tile is 128 consecutive shifts) and
@@ -717,6 +723,122 @@ class GroupXcorrCZT:
             assert shifts[-1] + self.starts[-1] + self.lengths[-1] < rx.shape[0]                   # :1002-1004
         _, _, caf = self._handle.run_shifts(rx, np.asarray(shifts) + self._off, False, True)
         return _as(caf, np.float64), self.cztFreq
+
+
+class GroupXcorrCZT_Permutations:
+    """Drop-in for xcorrRoutines.GroupXcorrCZT_Permutations (1264-1690): every template of every group is correlated
+    once over the CZT grid (complex surfaces kept on the device), then any permutation of one template per group is
+    combined with getCAF / getCAF_GPU.  Each template is one tensor-core contraction (csrc/groupfreq.cu, complex
+    epilogue); the combination is one kernel (xc_groupperm_combine)."""
+
+    def __init__(self, ygroups, ygroupIdxs, groupStarts, f1, f2, binWidth, fs, autoConj=True):
+        ygroups = np.asarray(ygroups)
+        ygroupIdxs = np.asarray(ygroupIdxs)
+        groupStarts = np.asarray(groupStarts)
+        assert ygroups.shape[0] == ygroupIdxs.size                                       # :1298-1300
+        assert np.unique(ygroupIdxs).size == groupStarts.size                            # :1301-1303
+        self.numTemplates = ygroupIdxs.size
+        self.numGroups = groupStarts.size
+        assert np.all(np.sort(np.unique(ygroupIdxs)) == np.arange(self.numGroups))       # :1309-1311
+        self.groupStarts = groupStarts
+        self.ygroupIdxs = ygroupIdxs
+        self.fs = fs
+        self.length = ygroups.shape[1]
+        self.f1, self.f2, self.binWidth = f1, f2, binWidth
+        self.ygroups = ygroups.conj() if autoConj else ygroups                           # :1323-1324
+        self.ygroupsEnergy = np.linalg.norm(self.ygroups, axis=1) ** 2                   # :1325
+        from .spectralRoutines import CZTCached
+        cz = CZTCached(self.length, f1, f2, binWidth, fs)
+        self._cztFreq = np.arange(self.f1, self.f2 + self.binWidth / 2, self.binWidth)   # :1353
+        self._nb = cz.k
+        if self._cztFreq.size != self._nb:
+            raise ValueError("operands could not be broadcast together: %d CZT bins against %d group phases"
+                             % (self._nb, self._cztFreq.size))
+        bins = cz.f0_cycles + np.arange(self._nb) * cz.df_cycles
+        self._handles = [_GroupFreqHandle(self.ygroups[k], np.array([int(groupStarts[ygroupIdxs[k]])]),
+                                          np.array([self.length]), bins, self._cztFreq / float(fs))
+                         for k in range(self.numTemplates)]
+        self.d_xcTemplates = None
+        self.d_rxgroupNormSq = None
+
+    def _run(self, d_rx, shifts):
+        import torch
+        from .filterRoutines import slidingEnergy
+        s = np.asarray(shifts).astype(np.int64).reshape(-1)
+        lo, hi = int(s.min()), int(s.max())
+        Kc = hi - lo + 1
+        contiguous = s.size == Kc and np.all(np.diff(s) == 1)
+        pick = None if contiguous else torch.from_numpy(s - lo).to(d_rx.device)
+        surf = torch.empty((self.numTemplates, s.size, self._nb), dtype=torch.complex64, device=d_rx.device)
+        tmp = None if contiguous else torch.empty((Kc, self._nb), dtype=torch.complex64, device=d_rx.device)
+        for k, h in enumerate(self._handles):
+            if contiguous:
+                h.run_complex(d_rx, lo, Kc, surf[k])
+            else:
+                h.run_complex(d_rx, lo, Kc, tmp)
+                surf[k] = tmp[pick]
+        en = torch.empty((self.numGroups, s.size), dtype=torch.float32, device=d_rx.device)
+        for g in range(self.numGroups):
+            a = lo + int(self.groupStarts[g])
+            e = slidingEnergy(d_rx[a:a + Kc + self.length - 1], self.length)
+            en[g] = e if contiguous else e[pick]
+        self.d_xcTemplates, self.d_rxgroupNormSq = surf, en
+
+    def xcorrGPU(self, rx, shifts, batchSz=32):
+        """rx: CUDA tensor (complex64).  Fills d_xcTemplates (T, K, nbins) complex64 and d_rxgroupNormSq (G, K); returns
+        the CZT frequencies as numpy (:1327-1450)."""
+        if not _lib.is_device(rx):
+            raise TypeError("rx must be a CUDA tensor (the reference requires a cupy array here)")
+        if _lib.np_dtype_of(rx) != np.dtype(np.complex64):
+            raise TypeError("rx must be complex64")
+        assert shifts[-1] + self.groupStarts[-1] + self.length < rx.shape[0]             # :1337
+        self._run(_lib.contiguous(rx), shifts)
+        return self._cztFreq
+
+    def _combine(self, templateIdx):
+        import torch
+        templateIdx = np.asarray(templateIdx)
+        assert templateIdx.size == self.numGroups                                         # :1453
+        tsel = np.array([np.argwhere(self.ygroupIdxs == g)[templateIdx[g]][0] for g in range(self.numGroups)], np.int32)
+        gsel = np.arange(self.numGroups, dtype=np.int32)
+        ynormsq = float(np.sum(self.ygroupsEnergy[tsel]))
+        surf = self.d_xcTemplates
+        K = surf.shape[1]
+        caf = torch.empty((K, self._nb), dtype=torch.float32, device=surf.device)
+        check(_lib.load().xc_groupperm_combine(_lib.ptr(surf), K, self._nb, _lib.ptr(tsel), _lib.ptr(gsel), self.numGroups,
+                                               _lib.ptr(self.d_rxgroupNormSq), ynormsq, _lib.ptr(caf),
+                                               _lib.current_stream(surf)))
+        return caf
+
+    def getCAF_GPU(self, templateIdx):
+        """(K, nbins) float64 CUDA tensor (:1452-1483)."""
+        return _as(self._combine(templateIdx), np.float64)
+
+    def xcorr(self, rx, shifts=None, numThreads=1):
+        """Host-array variant (:1485-1547): same kernels, rx staged to the device once; returns the CZT frequencies."""
+        import torch
+        if _lib.np_dtype_of(rx) != np.dtype(np.complex64):
+            raise TypeError("rx must be complex64")
+        if shifts is None:
+            shifts = np.arange(rx.shape[0] - (int(self.groupStarts[-1]) + self.length) + 1)   # :1487
+        else:
+            assert shifts[-1] + self.groupStarts[-1] + self.length < rx.shape[0]              # :1489-1491
+        d_rx = rx if _lib.is_device(rx) else torch.from_numpy(np.ascontiguousarray(rx)).cuda()
+        self._run(d_rx.contiguous(), shifts)
+        return self._cztFreq
+
+    @property
+    def xcTemplates(self):
+        """(T, K, nbins) complex128 numpy like the reference's attribute (:1493-1500)."""
+        return self.d_xcTemplates.cpu().numpy().astype(np.complex128)
+
+    @property
+    def rxgroupNormSq(self):
+        return self.d_rxgroupNormSq.cpu().numpy().astype(np.float64)
+
+    def getCAF(self, templateIdx, numThreads=4):
+        """(K, nbins) float64 numpy (:1549-1585)."""
+        return self._combine(templateIdx).cpu().numpy().astype(np.float64)
 
 
 # ------------------------------------------------------------------------------------------------

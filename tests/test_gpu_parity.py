@@ -733,3 +733,32 @@ def test_int16_ingestion(xr, tmp_path):
         ur.simpleBinRead(path, in_dtype=np.complex64)
     qb, fb = ur.type1ResultBlobs(np.array([0.25, 0.5], np.float32), np.array([3, 7], np.int32))
     assert np.array_equal(np.frombuffer(qb, np.float64), [0.25, 0.5]) and np.array_equal(np.frombuffer(fb, np.uint32), [3, 7])
+
+
+@pytest.mark.parametrize("name,d", _load("groupperm_*.npz"), ids=lambda v: v if isinstance(v, str) else "")
+def test_groupperm_golden(xr, name, d):
+    """GroupXcorrCZT_Permutations (xcorrRoutines.py:1264-1690): per-template complex surfaces from the tensor-core
+    contraction, permutations combined on the device; host (xcorr / getCAF) and device (xcorrGPU / getCAF_GPU) methods."""
+    obj = xr.GroupXcorrCZT_Permutations(d["ygroups"], d["idxs"], d["starts"], float(d["f1"]), float(d["f2"]), float(d["bw"]),
+                                        float(d["fs"]))
+    cf = obj.xcorr(d["rx"], d["shifts"])
+    assert np.array_equal(cf, d["cztFreq"])
+    scale = np.abs(d["xcTemplates"]).max()
+    assert obj.xcTemplates.dtype == np.complex128
+    np.testing.assert_allclose(obj.xcTemplates, d["xcTemplates"], rtol=0, atol=3e-5 * scale)
+    np.testing.assert_allclose(obj.rxgroupNormSq, d["rxgroupNormSq"], rtol=1e-5)
+    for key, perm in (("caf_planted", tuple(d["planted"])), ("caf_other", (0, 0, 0))):
+        caf = obj.getCAF(np.array(perm))
+        assert caf.dtype == np.float64 and caf.shape == d[key].shape
+        np.testing.assert_allclose(caf, d[key], rtol=RTOL, atol=2e-6 * d[key].max())
+    i, b = np.unravel_index(int(np.argmax(caf := obj.getCAF(d["planted"]))), caf.shape)
+    assert i == int(d["p0"]) and cf[b] == float(d["foff"])
+    # device methods, strided shifts
+    sh = d["shifts"][1::3]
+    cf2 = obj.xcorrGPU(_dev(d["rx"]), sh)
+    assert np.array_equal(cf2, d["cztFreq"])
+    g = obj.getCAF_GPU(d["planted"])
+    assert g.is_cuda and g.cpu().numpy().dtype == np.float64
+    np.testing.assert_allclose(g.cpu().numpy(), d["caf_planted"][1::3], rtol=RTOL, atol=2e-6 * d["caf_planted"].max())
+    with pytest.raises(TypeError):
+        obj.xcorrGPU(d["rx"], sh)

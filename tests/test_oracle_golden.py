@@ -164,3 +164,20 @@ def test_fine_search_restatement_matches_reference(name, d):
     assert gtd == float(d["gen_td"])
     np.testing.assert_allclose(gcost, d["gen_cost"], rtol=0, atol=5e-7)       # both reference FFTs in float32 (numpy >= 2)
     np.testing.assert_allclose(orc.calcQF2(d["x"], d["y"]), float(d["qf2"]), rtol=1e-5)
+
+
+@pytest.mark.parametrize("name,d", _load("groupperm_*.npz"), ids=lambda v: v if isinstance(v, str) else "")
+def test_groupperm_restatement_matches_reference(name, d):
+    """GroupXcorrCZT_Permutations.xcorr + getCAF (xcorrRoutines.py:1485-1585)."""
+    o = orc.GroupXcorrCZT_Permutations(d["ygroups"], d["idxs"], d["starts"], float(d["f1"]), float(d["f2"]), float(d["bw"]),
+                                       float(d["fs"]))
+    cf = o.xcorr(d["rx"], d["shifts"])
+    assert np.array_equal(cf, d["cztFreq"])
+    scale = np.abs(d["xcTemplates"]).max()
+    np.testing.assert_allclose(o.xcTemplates, d["xcTemplates"], rtol=0, atol=2e-6 * scale)    # golden stored as complex64
+    np.testing.assert_allclose(o.rxgroupNormSq, d["rxgroupNormSq"], rtol=1e-6)
+    for key, perm in (("caf_planted", tuple(d["planted"])), ("caf_other", (0, 0, 0))):
+        np.testing.assert_allclose(o.getCAF(np.array(perm)), d[key], rtol=1e-6, atol=1e-9 * d[key].max())
+    caf = o.getCAF(d["planted"])
+    i, b = np.unravel_index(int(np.argmax(caf)), caf.shape)
+    assert i == int(d["p0"]) and cf[b] == float(d["foff"]) and caf.max() > 3 * d["caf_other"].max()

@@ -8,7 +8,7 @@ timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/${tag}_pytest.log 
 tail -3 gpurun_out/${tag}_pytest.log
 timeout 600 python bench.py --steps 10 --warmup 3 > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench rc=$?"
 cat gpurun_out/${tag}_bench.json
-timeout 600 python tools/bench_configs.py c1 c3 c4 > gpurun_out/${tag}_configs.jsonl 2> gpurun_out/${tag}_configs.err; echo "configs rc=$?"
+timeout 600 python tools/bench_configs.py c1 c3 c4 c6 > gpurun_out/${tag}_configs.jsonl 2> gpurun_out/${tag}_configs.err; echo "configs rc=$?"
 cat gpurun_out/${tag}_configs.jsonl
 if [ -z "$SKIP_NCU" ]; then
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${tag}_launches.csv \
