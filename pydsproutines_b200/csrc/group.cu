@@ -73,18 +73,16 @@ struct GroupLoader {
 
     size_t dyn_smem() const { return y_smem_off >= 0 ? sizeof(float2) * (size_t)rows * PL::TG + sizeof(int32_t) * (size_t)rows + 16 : 0; }   // weights, row bases, alignment slack
 
-    // shared-memory tables: slot_base[V + 1], then the list of non-empty slots ne[V] and their count
-    __host__ __device__ static constexpr size_t smem_bytes() { return ((sizeof(int32_t) * (2 * PL::V + 2) + 15) / 16) * 16; }
+    // shared-memory table: one int4 {slot, first row, end row, -} per NON-EMPTY register slot, then their count
+    __host__ __device__ static constexpr size_t smem_bytes() { return sizeof(int4) * (PL::V + 1); }
 
     __device__ __forceinline__ void prepare(int tid, int nthreads, unsigned char* smem) const {
-        int32_t* slot_base = reinterpret_cast<int32_t*>(smem);
-        for (int i = tid; i <= PL::V; i += nthreads) slot_base[i] = slot_base_g[i];
         if (tid == 0) {
-            int32_t* ne = slot_base + PL::V + 1;
+            int4* tab = reinterpret_cast<int4*>(smem);
             int n = 0;
             for (int c = 0; c < PL::V; ++c)
-                if (slot_base_g[c + 1] > slot_base_g[c]) ne[n++] = c;
-            ne[PL::V] = n;
+                if (slot_base_g[c + 1] > slot_base_g[c]) tab[n++] = make_int4(c, slot_base_g[c], slot_base_g[c + 1], 0);
+            tab[PL::V] = make_int4(n, 0, 0, 0);
         }
         if (y_smem_off >= 0) {      // the weights never change: keep them next to the FFT buffers
             float2* ys = reinterpret_cast<float2*>(smem + y_smem_off);
@@ -103,8 +101,7 @@ struct GroupLoader {
     // The gather is ONE rolled loop over the non-empty register slots (the code of a fully unrolled slot loop
     // does not fit the instruction cache); the finished sum is steered into its register by a uniform switch.
     __device__ __forceinline__ bool load(float2* v, int t, int64_t i, const unsigned char* smem) const {
-        const int32_t* slot_base = reinterpret_cast<const int32_t*>(smem);
-        const int32_t* ne = slot_base + PL::V + 1;
+        const int4* tab = reinterpret_cast<const int4*>(smem);
         const int64_t s = shifts ? shifts[i] : shift0 + i * step;
         if (s + lo < 0 || s + hi > rxlen) return false;
         const float2* x = rx + s;
@@ -112,12 +109,15 @@ struct GroupLoader {
         const float2* const yp = (y_smem_off >= 0) ? reinterpret_cast<const float2*>(smem + y_smem_off) : ell_y;
 #pragma unroll
         for (int c = 0; c < PL::V; ++c) v[c] = make_float2(0.f, 0.f);
-        const int n_ne = ne[PL::V];
+        const int n_ne = tab[PL::V].x;
+        int4 nxt = tab[0];                  // the next slot's entry is fetched one iteration ahead
 #pragma unroll 1
         for (int k = 0; k < n_ne; ++k) {
-            const int c = ne[k];
+            const int4 ent = nxt;
+            nxt = tab[k + 1];
+            const int c = ent.x;
             float2 acc = make_float2(0.f, 0.f);
-            const int j0 = slot_base[c], j1 = slot_base[c + 1];
+            const int j0 = ent.y, j1 = ent.z;
             // lists are padded to a multiple of ELL_UNROLL (zero weights): all index / weight / sample loads
             // of a batch are issued before the first dependent one is used
             if (row_base) {
