@@ -762,3 +762,26 @@ def test_groupperm_golden(xr, name, d):
     np.testing.assert_allclose(g.cpu().numpy(), d["caf_planted"][1::3], rtol=RTOL, atol=2e-6 * d["caf_planted"].max())
     with pytest.raises(TypeError):
         obj.xcorrGPU(d["rx"], sh)
+
+
+def test_groupfreq_and_fine_limits(xr):
+    """error behaviour of the 8(f) rows: dtype checks, empty shift lists, unsupported sizes fail loudly"""
+    rng = np.random.default_rng(3)
+    y = signals.qpsk(rng, 300)
+    starts, lengths = np.array([0, 150]), np.array([64, 100])
+    rx = signals.cnoise(rng, 600)
+    a = xr.GroupXcorr(y, starts, lengths, np.linspace(-0.01, 0.01, 9), 1.0)
+    with pytest.raises(TypeError):
+        a.xcorr(rx.astype(np.complex128))
+    with pytest.raises(IndexError):                 # the reference indexes shifts[-1] (xcorrRoutines.py:923)
+        a.xcorr(rx, np.array([], dtype=np.int64))
+    one, f1 = a.xcorr(rx, np.array([17]))
+    ref, rf = orc.GroupXcorr(y, starts, lengths, np.linspace(-0.01, 0.01, 9), 1.0).xcorr(rx, np.array([17]))
+    assert_qf2(one, ref) and f1[0] == rf[0]
+    with pytest.raises(NotImplementedError):
+        xr.GroupXcorr(y, starts, lengths, np.linspace(-0.1, 0.1, 3000), 1.0)          # > 2048 frequencies
+    with pytest.raises(AssertionError):
+        xr.fineFreqTimeSearch(rx[:100], rx[:99], [], 0.0, 0.0, 1.0, np.arange(-1, 1, 0.1))
+    # a one-sample-long "signal" and a single time offset still work
+    ff, td, cost = xr.fineFreqTimeSearch(rx[:1], rx[:1], [], 0.0, 0.0, 1.0, np.array([0.0]))
+    assert ff is None and td == 0.0 and abs(cost[0] - 1.0) < 1e-12
