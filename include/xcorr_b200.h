@@ -163,6 +163,12 @@ int32_t xc_groupperm_combine(const void* surfaces, int64_t K, int32_t NB, const 
                              const int32_t* group_idx, int32_t G, const float* rxnormsq, double ynormsq, float* caf,
                              void* stream);
 
+/* stand-alone chirp-z transform, spectralRoutines.CZTCached(GPU).run / runMany (spectralRoutines.py:263-306, 347-391):
+ * out[r, k] = sum_n x[r, n] exp(-j 2 pi (f0_cycles + k df_cycles) n), x = [rows, m] complex64, out = [rows, nbins]
+ * complex64.  m + nbins - 1 <= 16384 (the transform runs inside the fused correlation kernel). */
+int32_t xc_czt_c64(const void* x, int32_t m, int64_t rows, double f0_cycles, double df_cycles, int32_t nbins, void* out,
+                   int32_t where, void* stream);
+
 /* ---- 8(f) rank 3: capture ingestion ---------------------------------------------------------
  * usrpRoutines.simpleBinRead (usrpRoutines.py:51-66: np.fromfile(int16).astype(float32).view(complex64)) and the
  * copy-then-convert-on-device finding of benchmarks/benchmark_cupyCopyAndConvert.py:15-26.  iq = nsamp interleaved

@@ -199,12 +199,27 @@ def groupperm_cases(ref):
     return {"g3": d}
 
 
+def czt_run_cases(ref):
+    """spectralRoutines.CZTCached.run / runMany (the reference's own chirp-z convolution, complex128)."""
+    import spectralRoutines as sr            # the reference's module (sys.path set by ref_import.load())
+    cases = {}
+    for name, seed, m, rows, f1, f2, bw, fs in (("m100", 71, 100, 3, -5.0, 5.0, 0.25, 100.0),
+                                                ("m1000", 72, 1000, 2, 100.0, 140.0, 0.5, 8000.0)):
+        rng = np.random.default_rng(seed)
+        x = signals.cnoise(rng, rows * m).reshape(rows, m)
+        x[-1] = 0                              # an all-zero row transforms to zeros
+        c = sr.CZTCached(m, f1, f2, bw, fs)
+        cases[name] = dict(x=x, f1=f1, f2=f2, bw=bw, fs=fs, many=c.runMany(x), one=c.run(x[0]), freq=c.getFreq())
+    return cases
+
+
 def main():
     ref = ref_import.load()
     os.makedirs(OUT, exist_ok=True)
     for fam, cases in (("fastxcorr", fastxcorr_cases(ref)), ("groupxcorr", group_cases(ref)), ("cztxcorr", czt_cases(ref)),
                        ("groupfreq", groupfreq_cases(ref)), ("fine", fine_cases(ref)),
-                       ("groupperm", groupperm_cases(ref))):
+                       ("groupperm", groupperm_cases(ref)),
+                       ("cztrun", czt_run_cases(ref))):
         for name, d in cases.items():
             path = os.path.join(OUT, "%s_%s.npz" % (fam, name))
             np.savez_compressed(path, **d)

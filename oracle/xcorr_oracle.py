@@ -526,3 +526,12 @@ class GroupXcorrCZT_Permutations:
             rn += self.rxgroupNormSq[g]
             yn += self.ygroupsEnergy[k]
         return np.abs(tot) ** 2 / rn.reshape(-1, 1) / yn
+
+
+def cztRun(xmany, f1, f2, binWidth, fs):
+    """CZTCached.runMany (spectralRoutines.py:239-306) evaluated directly: X[r, k] = sum_n x[r, n] exp(-2j pi f_k n / fs)
+    on the bins f_k = f1 + k (f2 - f1 + binWidth) / K, K = int((f2 - f1) / binWidth + 1)."""
+    x = np.atleast_2d(np.asarray(xmany)).astype(np.complex128)
+    K = int((f2 - f1) / binWidth + 1)
+    fk = f1 + np.arange(K) * (f2 - f1 + binWidth) / K
+    return x @ np.exp(-2j * np.pi * np.outer(np.arange(x.shape[1]), fk) / fs)

@@ -61,6 +61,7 @@ SIGNATURES = {
     "xc_mt_correlate": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp, _i32, C.POINTER(xc_peak), _i32, _vp]),
     "xc_mt_destroy": (_i32, [_vp]),
     "xc_mt_uses_tensor_cores": (_i32, [_vp]),
+    "xc_czt_c64": (_i32, [_vp, _i32, _i64, C.c_double, C.c_double, _i32, _vp, _i32, _vp]),
     "xc_convert_i16_c64": (_i32, [_vp, _i64, _vp, _i32, _i32, _vp]),
     "xc_copy_groups_c64": (_i32, [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _i32, _i32, _vp]),
     "xc_copy_slices_to_matrix_c64": (_i32, [_vp, _i64, _i64, _i64, _i64, _i64, _vp, _i32, _vp]),

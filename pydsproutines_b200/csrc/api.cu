@@ -385,6 +385,57 @@ int32_t xc_cztxcorr_c64(const void* cutout, int32_t N, const void* rx, int64_t r
     return finish(where, st);
 }
 
+// ---- stand-alone chirp-z transform of the rows of a matrix (CZTCached.run / runMany, spectralRoutines.py:263-306) ----
+// The correlator kernel with an all-ones cutout computes X_r[k] / (sqrt(m) ||x_r||) for every row; the window energies
+// it leaves in the workspace undo the normalisation.
+namespace xc {
+__global__ void czt_ones_kernel(float2* p, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = make_float2(1.f, 0.f);
+}
+__global__ void czt_unscale_kernel(float2* out, int64_t rows, int nbins, const float* __restrict__ energy, float sqrt_m) {
+    const int64_t total = rows * nbins;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
+        const float en = energy[e / nbins];
+        const float sc = sqrt_m * sqrtf(en);
+        const float2 v = out[e];
+        out[e] = (en > 0.f) ? make_float2(v.x * sc, v.y * sc) : make_float2(0.f, 0.f);
+    }
+}
+}  // namespace xc
+
+int32_t xc_czt_c64(const void* x, int32_t m, int64_t rows, double f0_cycles, double df_cycles, int32_t nbins, void* out,
+                   int32_t where, void* stream) {
+    XC_TRY(check_where(where));
+    if (!x || !out) return fail(XC_ERR_ARG, "x/out is NULL");
+    if (m < 2 || nbins < 1 || rows < 0) return fail(XC_ERR_ARG, "need m >= 2, nbins >= 1, rows >= 0");
+    XC_TRY(require_device());
+    if (rows == 0) return XC_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t ob = sizeof(float2) * (size_t)rows * (size_t)nbins;
+    int32_t status = XC_OK;
+    const float2* dx = (const float2*)stage_in(SLOT_IN1, x, sizeof(float2) * (size_t)rows * (size_t)m, where, st, &status);
+    float2* dout = (float2*)stage_out(SLOT_OUT2, out, ob, where, &status);
+    XC_TRY(status);
+    float2* d_ones = (float2*)workspace(SLOT_TMP3, sizeof(float2) * (size_t)m);
+    if (!d_ones) return XC_ERR_NOMEM;
+    czt_ones_kernel<<<(m + 255) / 256, 256, 0, st>>>(d_ones, m);
+    XC_LAUNCH_CHECK();
+    ShiftList sl{0, (int64_t)m, rows, nullptr};                       // row r = the window at shift r * m
+    const CztSpec spec{nbins, f0_cycles, df_cycles};
+    XC_TRY(fastxcorr_freq_device(d_ones, m, dx, rows * (int64_t)m, sl, nullptr, nullptr, nullptr, dout, 1, st, &spec));
+    const float* d_energy = (const float*)workspace(SLOT_TMP1, sizeof(float) * (size_t)rows);   // left there by the call above
+    if (!d_energy) return XC_ERR_NOMEM;
+    int64_t blocks = ((int64_t)rows * nbins + 255) / 256;
+    const int64_t cap = (int64_t)sm_count() * 16;
+    if (blocks > cap) blocks = cap;
+    czt_unscale_kernel<<<(unsigned)blocks, 256, 0, st>>>(dout, rows, nbins, d_energy, sqrtf((float)m));
+    XC_LAUNCH_CHECK();
+    XC_TRY(fetch_out(out, dout, ob, where, st));
+    return finish(where, st);
+}
+
 int32_t xc_row_argmax_c64(const void* x, int64_t rows, int64_t cols, int32_t use_normsq, uint32_t* idx, float* val,
                           int32_t where, void* stream) {
     XC_TRY(check_where(where));

@@ -1,7 +1,11 @@
 """The part of the reference's spectralRoutines.py the detection path touches: the cached chirp-z transform object
-(spectralRoutines.py:239-391) that cztXcorr and cp_fastXcorr_v2(cztObj=...) take.  Here it is only the description
-of the frequency grid -- the transform itself runs inside the fused correlation kernel (xc_cztxcorr_c64)."""
+(spectralRoutines.py:239-391) that cztXcorr and cp_fastXcorr_v2(cztObj=...) take.  It describes the frequency grid; the
+transform itself runs inside the fused correlation kernel (xc_cztxcorr_c64), and run / runMany call the same kernel
+stand-alone (xc_czt_c64)."""
 import numpy as np
+
+from . import _lib
+from ._lib import check
 
 
 class CZTCached:
@@ -15,6 +19,7 @@ class CZTCached:
         self.fs = fs
         self.k = int((f2 - f1) / binWidth + 1)
         self.m = int(xlength)
+        self.convertTo32fc = convertTo32fc
         if self.k < 1:
             raise ValueError("empty frequency range")
 
@@ -30,11 +35,27 @@ class CZTCached:
     def df_cycles(self):
         return float(self.f2 - self.f1 + self.binWidth) / self.k / float(self.fs)
 
-    def run(self, x):
-        raise NotImplementedError("the stand-alone transform is not part of the detection path; use cztXcorr or "
-                                  "cp_fastXcorr_v2(cztObj=...)")
+    def runMany(self, xmany, out=None):
+        """CZT of every row of xmany (rows, m) -> (rows, k); complex64 in, complex128 out like the reference (complex64
+        with convertTo32fc / for CUDA tensors, spectralRoutines.py:272-306, 361-391)."""
+        if _lib.np_dtype_of(xmany) != np.dtype(np.complex64):
+            raise TypeError("x must be complex64, got %s" % _lib.np_dtype_of(xmany))
+        x = _lib.contiguous(xmany)
+        if x.ndim != 2 or x.shape[1] != self.m:
+            raise ValueError("expected rows of %d samples" % self.m)
+        if _lib.is_device(x):
+            check(_lib.load().xc_set_device(x.device.index or 0))
+        g = _lib.empty_like_space(x, (x.shape[0], self.k), np.complex64)
+        check(_lib.load().xc_czt_c64(_lib.ptr(x), self.m, x.shape[0], self.f0_cycles, self.df_cycles, self.k, _lib.ptr(g),
+                                     _lib.where_of(x), _lib.current_stream(x)))
+        if not _lib.is_torch(g) and not self.convertTo32fc:
+            g = g.astype(np.complex128)
+        if out is None:
+            return g
+        out[...] = g
 
-    runMany = run
+    def run(self, x):
+        return self.runMany(x.reshape(1, -1))[0]
 
 
 CZTCachedGPU = CZTCached

@@ -785,3 +785,27 @@ def test_groupfreq_and_fine_limits(xr):
     # a one-sample-long "signal" and a single time offset still work
     ff, td, cost = xr.fineFreqTimeSearch(rx[:1], rx[:1], [], 0.0, 0.0, 1.0, np.array([0.0]))
     assert ff is None and td == 0.0 and abs(cost[0] - 1.0) < 1e-12
+
+
+@pytest.mark.parametrize("name,d", _load("cztrun_*.npz"), ids=lambda v: v if isinstance(v, str) else "")
+@pytest.mark.parametrize("space", ["host", "device"])
+def test_czt_run_golden(xr, name, d, space):
+    """stand-alone CZTCached.run / runMany (spectralRoutines.py:239-306) through the fused correlation kernel"""
+    from pydsproutines_b200.spectralRoutines import CZTCached
+    conv = _dev if space == "device" else (lambda a: a)
+    back = (lambda t: t.cpu().numpy()) if space == "device" else (lambda a: a)
+    x = d["x"]
+    c = CZTCached(x.shape[1], float(d["f1"]), float(d["f2"]), float(d["bw"]), float(d["fs"]))
+    assert np.array_equal(c.getFreq(), d["freq"])
+    many = back(c.runMany(conv(x)))
+    assert many.shape == d["many"].shape
+    if space == "host":
+        assert many.dtype == np.complex128
+    # float32 transform of m samples: error relative to the row's spectrum scale
+    scale = np.abs(d["many"]).max()
+    np.testing.assert_allclose(many, d["many"], rtol=0, atol=2e-5 * scale)
+    assert np.all(many[-1] == 0)
+    one = back(c.run(conv(x[0])))
+    np.testing.assert_allclose(one, d["one"], rtol=0, atol=2e-5 * scale)
+    with pytest.raises(TypeError):
+        c.runMany(x.astype(np.complex128))

@@ -181,3 +181,13 @@ def test_groupperm_restatement_matches_reference(name, d):
     caf = o.getCAF(d["planted"])
     i, b = np.unravel_index(int(np.argmax(caf)), caf.shape)
     assert i == int(d["p0"]) and cf[b] == float(d["foff"]) and caf.max() > 3 * d["caf_other"].max()
+
+
+@pytest.mark.parametrize("name,d", _load("cztrun_*.npz"), ids=lambda v: v if isinstance(v, str) else "")
+def test_czt_run_restatement_matches_reference(name, d):
+    """CZTCached.run / runMany (spectralRoutines.py:239-306): direct evaluation against the chirp-z convolution."""
+    many = orc.cztRun(d["x"], float(d["f1"]), float(d["f2"]), float(d["bw"]), float(d["fs"]))
+    scale = np.abs(d["many"]).max()
+    np.testing.assert_allclose(many, d["many"], rtol=0, atol=1e-9 * scale)
+    np.testing.assert_allclose(many[0], d["one"], rtol=0, atol=1e-9 * scale)
+    assert np.all(many[-1] == 0)
