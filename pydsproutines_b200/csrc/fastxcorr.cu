@@ -11,6 +11,7 @@
 
 #include "bluestein.cuh"
 #include "fused_fft_kernel.cuh"
+#include "fused_fft_dual.cuh"
 #include "internal.cuh"
 #include "plans.cuh"
 
@@ -72,6 +73,26 @@ struct CutoutLoader {
 #pragma unroll
                 for (int q = 0; q < NQ; ++q)
                     v[q * PL::R1 + n1] = pcmulc(v[q * PL::R1 + n1], __ldg(cg + input_index<PL>(0, q, n1)));
+        }
+    }
+    // two windows at once (fused_fft_dual_kernel): every conj(cutout) value is read once for both products
+    __device__ __forceinline__ void finish2(float2* v0, float2* v1, int t, const unsigned char* smem) const {
+        constexpr int NQ = PL::V / PL::R1;
+        if (CUT_SMEM) {
+            const float2* cc = reinterpret_cast<const float2*>(smem) + t;
+#pragma unroll
+            for (int n1 = 0; n1 < PL::R1; ++n1) {
+#pragma unroll
+                for (int q = 0; q < NQ; ++q) {
+                    const float2 c = cc[input_index<PL>(0, q, n1)];
+                    v0[q * PL::R1 + n1] = pcmul(v0[q * PL::R1 + n1], c);
+                    v1[q * PL::R1 + n1] = pcmul(v1[q * PL::R1 + n1], c);
+                }
+                if (((n1 + 1) * NQ) % 8 == 0) asm volatile("" ::: "memory");
+            }
+        } else {
+            finish(v0, t, smem);
+            finish(v1, t, smem);
         }
     }
     __device__ __forceinline__ bool load(float2* v, int t, int64_t i, const unsigned char* smem) const {
@@ -160,6 +181,11 @@ struct FreqRunner {
         using PF = PlanFor<LOG2N>;
         using LD = CutoutLoader<typename PF::PL, PF::CS>;
         LD ld{rx, rxlen, cutout, sl.shift0, sl.step, sl.shifts};
+        if constexpr (LOG2N == 13) {
+            // two FFTs per thread (fused_fft_dual.cuh) for the (max, arg max) outputs; XC_DUAL=0 keeps the B = 2 layout
+            static const bool dual = [] { const char* e = getenv("XC_DUAL"); return e && e[0] == '1'; }();
+            if (dual && !out.caf && !out.cplx) return launch_fused_dual<typename PF::PL, LD>(ld, out, sl.K, stream);
+        }
         return launch_fused<typename PF::PL, PF::B, LD>(ld, out, sl.K, stream);
     }
 };

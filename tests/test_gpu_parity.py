@@ -809,3 +809,28 @@ def test_czt_run_golden(xr, name, d, space):
     np.testing.assert_allclose(one, d["one"], rtol=0, atol=2e-5 * scale)
     with pytest.raises(TypeError):
         c.runMany(x.astype(np.complex128))
+
+
+def test_dual_layout_subprocess():
+    """XC_DUAL=1 (two FFTs per thread, csrc/fused_fft_dual.cuh) is an opt-in layout of the N = 8192 search: same results
+    as the default layout, odd and even shift counts, windows that leave rx."""
+    import subprocess
+    import sys
+    code = r'''
+import numpy as np, torch
+from pydsproutines_b200 import signals
+import pydsproutines_b200.xcorrRoutines as xr
+from oracle import xcorr_oracle as orc
+cutout, rx = signals.make_fastxcorr_case(16, 8192, 8192 + 300, 123, 1234, amp=0.7)
+for shifts in (None, np.arange(100, 141), np.arange(0, 300, 7)):
+    q, f = xr.fastXcorr(cutout, rx, freqsearch=True, shifts=shifts)
+    rq, rf = orc.fastXcorr(cutout, rx, freqsearch=True, shifts=shifts)
+    assert np.allclose(q, rq, rtol=1e-4, atol=1e-6 * rq.max()), "qf2"
+    assert (np.asarray(f) == np.asarray(rf)).mean() > 0.98, "bins"
+    i = int(np.argmax(q)); assert f[i] == rf[i] and i == int(np.argmax(rq))
+print("dual ok")
+'''
+    env = dict(os.environ, XC_DUAL="1")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], env=env, cwd=root, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "dual ok" in r.stdout, r.stdout + r.stderr
