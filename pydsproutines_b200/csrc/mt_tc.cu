@@ -104,7 +104,7 @@ mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_ene
              const int np, const float2* __restrict__ x, const int64_t xlen, const int64_t start, const int64_t K,
              const float* __restrict__ xenergy, float* __restrict__ best_out, int32_t* __restrict__ tidx_out,
              float* __restrict__ caf_out, float2* __restrict__ cplx_out, const int caf_cols, const int sqrt_out,
-             const int64_t ntiles,
+             const int seg_per_flush, float* __restrict__ scratch, const int64_t ntiles,
              const int64_t tiles_per_cta) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -211,48 +211,74 @@ mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_ene
             const int64_t o = (tile0 + i) * TC_M + warp * 32 + lane;
             const float inv_ex = (o < K) ? 1.f / xenergy[o] : 0.f;
             for (int nb = 0; nb < NB; ++nb) {
-                // keep the tile builder one job ahead of the MMAs
-                if (nseg > 1) {
-                    for (int sg = 0; sg < nseg; ++sg) ensure((i * NB + nb) * nseg + sg + 2);
-                } else if (nb == 0) {
-                    ensure(i + 2);
-                }
-                tc::mbar_wait(bar_tfull, gen & 1u);
-                tc::tc_fence_after();
-                const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
-                const float* inv = sInv + nb * NT;
-                for (int c = 0; c < NT / 16; ++c) {
-                    float re[16], im[16];
-                    tc::tmem_ld16(lane_base + 16 * c, re);
-                    tc::tmem_ld16(lane_base + 256 + 16 * c, im);
-                    tc::tmem_ld_wait();
-                    if (cplx_out && o < K) {   // raw complex contraction d[s, t], row = shift
-                        const int col0 = nb * NT + 16 * c;
-                        float2* dst = cplx_out + (size_t)o * (size_t)caf_cols + col0;
-#pragma unroll
-                        for (int j = 0; j < 16; ++j)
-                            if (col0 + j < caf_cols) dst[j] = make_float2(re[j], im[j]);
+                // Long contractions are accumulated in chunks: the tensor core truncates the FP32 accumulator on every
+                // read-modify-write (a bias of ~3e-8 of the sum per MMA), so after seg_per_flush segments the partial
+                // sums leave TMEM and continue in an L2-resident FP32 scratch ([re|im][column][row] per CTA).
+                const int nchunks = (nseg > 1 && seg_per_flush > 0) ? (nseg + seg_per_flush - 1) / seg_per_flush : 1;
+                float* const sc_re = scratch + (size_t)blockIdx.x * 2 * NT * TC_M + (warp * 32 + lane);
+                float* const sc_im = sc_re + (size_t)NT * TC_M;
+                int sg = 0;
+                for (int ch = 0; ch < nchunks; ++ch) {
+                    // keep the tile builder one job ahead of the MMAs
+                    if (nseg > 1) {
+                        const int sg_end = (nchunks == 1) ? nseg : min(nseg, (ch + 1) * seg_per_flush);
+                        for (; sg < sg_end; ++sg) ensure((i * NB + nb) * nseg + sg + 2);
+                    } else if (nb == 0) {
+                        ensure(i + 2);
                     }
+                    const bool first = (ch == 0), last = (ch == nchunks - 1);
+                    tc::mbar_wait(bar_tfull, gen & 1u);
+                    tc::tc_fence_after();
+                    const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+                    const float* inv = sInv + nb * NT;
+                    for (int c = 0; c < NT / 16; ++c) {
+                        float re[16], im[16];
+                        tc::tmem_ld16(lane_base + 16 * c, re);
+                        tc::tmem_ld16(lane_base + 256 + 16 * c, im);
+                        tc::tmem_ld_wait();
+                        if (!first) {
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        const float q = fmaf(re[j], re[j], im[j] * im[j]) * inv[16 * c + j];
-                        if (q > bestv) {       // strict '>' keeps the lowest template on ties
-                            bestv = q;
-                            besti = nb * NT + 16 * c + j;
+                            for (int j = 0; j < 16; ++j) {
+                                re[j] += sc_re[(size_t)(16 * c + j) * TC_M];
+                                im[j] += sc_im[(size_t)(16 * c + j) * TC_M];
+                            }
                         }
-                        re[j] = q * inv_ex;
-                    }
-                    if (caf_out && o < K) {    // full surface: row = shift, column = template
-                        const int col0 = nb * NT + 16 * c;
-                        float* dst = caf_out + (size_t)o * (size_t)caf_cols + col0;
+                        if (!last) {
 #pragma unroll
-                        for (int j = 0; j < 16; ++j)
-                            if (col0 + j < caf_cols) dst[j] = re[j];
+                            for (int j = 0; j < 16; ++j) {
+                                sc_re[(size_t)(16 * c + j) * TC_M] = re[j];
+                                sc_im[(size_t)(16 * c + j) * TC_M] = im[j];
+                            }
+                            continue;
+                        }
+                        if (cplx_out && o < K) {   // raw complex contraction d[s, t], row = shift
+                            const int col0 = nb * NT + 16 * c;
+                            float2* dst = cplx_out + (size_t)o * (size_t)caf_cols + col0;
+#pragma unroll
+                            for (int j = 0; j < 16; ++j)
+                                if (col0 + j < caf_cols) dst[j] = make_float2(re[j], im[j]);
+                        }
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) {
+                            const float q = fmaf(re[j], re[j], im[j] * im[j]) * inv[16 * c + j];
+                            if (q > bestv) {       // strict '>' keeps the lowest template on ties
+                                bestv = q;
+                                besti = nb * NT + 16 * c + j;
+                            }
+                            re[j] = q * inv_ex;
+                        }
+                        if (caf_out && o < K) {    // full surface: row = shift, column = template
+                            const int col0 = nb * NT + 16 * c;
+                            float* dst = caf_out + (size_t)o * (size_t)caf_cols + col0;
+#pragma unroll
+                            for (int j = 0; j < 16; ++j)
+                                if (col0 + j < caf_cols) dst[j] = re[j];
+                        }
                     }
+                    tc::tc_fence_before();
+                    tc::mbar_arrive(bar_tempty);                      // TMEM may be overwritten
+                    ++gen;
                 }
-                tc::tc_fence_before();
-                tc::mbar_arrive(bar_tempty);                          // TMEM may be overwritten
-                ++gen;
             }
             if (o < K) {
                 const float q = bestv * inv_ex;
@@ -289,10 +315,14 @@ mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_ene
             int job = 0;
             for (int i = 0; i < ntl; ++i) {
                 for (int nb = 0; nb < NB; ++nb) {
-                    tc::mbar_wait(bar_tempty, (gen & 1u) ^ 1u);       // the epilogue has drained the accumulators
-                    tc::tc_fence_after();
+                    const int per = (nseg > 1 && seg_per_flush > 0) ? seg_per_flush : nseg;     // segments per accumulator generation
                     bool first = true;
                     for (int sg = 0; sg < nseg; ++sg) {
+                        if (sg % per == 0) {
+                            tc::mbar_wait(bar_tempty, (gen & 1u) ^ 1u);       // the epilogue has drained the accumulators
+                            tc::tc_fence_after();
+                            first = true;
+                        }
                         const int b = job % ne;
                         const uint32_t use = (uint32_t)(job / ne);
                         if (nseg > 1 || nb == 0) tc::mbar_wait(bar_efull + 8 * b, use & 1u);
@@ -333,9 +363,11 @@ mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_ene
                             tc::umma_commit(bar_eempty + 8 * b);      // x tile buffer free
                             ++job;
                         }
+                        if ((sg + 1) % per == 0 || sg == nseg - 1) {
+                            tc::umma_commit(bar_tfull);               // accumulators of this generation complete
+                            ++gen;
+                        }
                     }
-                    tc::umma_commit(bar_tfull);                       // accumulators complete
-                    ++gen;
                 }
             }
             if (job > 0)      // every commit has landed before the CTA tears down
@@ -462,11 +494,22 @@ int32_t mt_tc_run(const MtTcPlan& plan, const float2* x, int64_t xlen, int64_t s
     if (ctas > ntiles) ctas = ntiles;
     const int64_t per = (ntiles + ctas - 1) / ctas;
     ctas = (ntiles + per - 1) / per;
+    // accumulator generations of at most ~64 K steps for long segmented contractions (see the kernel's epilogue)
+    int seg_per_flush = 0;
+    float* scratch = nullptr;
+    const int rmw = (plan.planes == 4) ? 6 : 4;                     // accumulator read-modify-writes per K step
+    if (plan.nseg > 1 && (plan.L32 / TC_SUB) * rmw > 768) {
+        static const int flush_ks = [] { const char* e = getenv("XC_TC_FLUSH_KS"); return e ? atoi(e) : 64; }();
+        seg_per_flush = flush_ks / (plan.Lp / TC_SUB);
+        if (seg_per_flush < 1) seg_per_flush = 1;
+        scratch = reinterpret_cast<float*>(workspace(SLOT_TMP3, sizeof(float) * 2 * (size_t)plan.NT * TC_M * (size_t)ctas));
+        if (!scratch) return XC_ERR_NOMEM;
+    }
     profile_begin(stream);
     mt_tc_kernel<<<(unsigned)ctas, TC_THREADS, smem, stream>>>(reinterpret_cast<const uint8_t*>(plan.d_pack),
                                                                plan.d_inv_energy, plan.NT, plan.NB, plan.L32, plan.Lp, plan.nseg,
                                                                plan.d_segs, nstages, ne, plan.planes, x, xlen, start, K, xenergy,
-                                                               best, tidx, caf, cplx, plan.T, sqrt_out, ntiles, per);
+                                                               best, tidx, caf, cplx, plan.T, sqrt_out, seg_per_flush, scratch, ntiles, per);
     profile_end(stream);
     XC_LAUNCH_CHECK();
     return XC_OK;

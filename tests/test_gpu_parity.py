@@ -834,3 +834,29 @@ print("dual ok")
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, "-c", code], env=env, cwd=root, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "dual ok" in r.stdout, r.stdout + r.stderr
+
+
+def test_groupfreq_large_planted_and_sampled(xr):
+    """C3's groups (64 x 128 at 1024 g) against 256 frequencies over 2^17 shifts: the planted (shift, frequency) is the
+    global peak, and 48 randomly sampled shifts agree with the oracle (size-independent checks at bench-like size)."""
+    c = signals.config_c3(log2_shifts=17)
+    F = c["F"]
+    NFQ = 256
+    freqs = (np.arange(NFQ) - 100) * (1.0 / F) + c["k0"] / F - 28.0 / F          # contains k0 / F exactly at index 128
+    k_true = int(np.argmin(np.abs(freqs - c["k0"] / F)))
+    y = np.zeros(int(c["starts"][-1]) + 128, np.complex64)
+    for g in range(64):
+        y[int(c["starts"][g]):int(c["starts"][g]) + 128] = c["ygroups"][g]
+    lengths = np.full(64, 128)
+    a = xr.GroupXcorr(y, c["starts"], lengths, freqs, 1.0)
+    K = c["K"]
+    xc, fp = a.xcorr(_dev(c["rx"]), np.arange(K))
+    xc, fp = xc.cpu().numpy(), fp.cpu().numpy()
+    i = int(np.argmax(xc))
+    assert i == c["p0"] and fp[i] == freqs[k_true] and xc[i] > 0.3
+    o = orc.GroupXcorr(y, c["starts"], lengths, freqs, 1.0)
+    rng = np.random.default_rng(9)
+    sample = np.unique(np.concatenate([rng.integers(0, K, 47), [c["p0"]]]))
+    rxc, rfp = o.xcorr(c["rx"], sample)
+    assert_qf2(xc[sample], rxc)
+    assert (fp[sample] == rfp).mean() > 0.95
