@@ -148,6 +148,7 @@ __global__ void __launch_bounds__(PL::TG) fused_fft_staged_kernel(const StagedAr
     unsigned int* const binmin = reinterpret_cast<unsigned int*>(smem_raw + L::OFF_BIN);
     float* const pend = reinterpret_cast<float*>(smem_raw + L::OFF_PEND);
     if (t < 2) binmin[t] = 0xffffffffu;
+    if (t < 4) reinterpret_cast<unsigned int*>(wmax)[t] = 0u;
 
     // this CTA owns shift-list entries [i0, i0 + 2 * chunk), taken in pairs
     const int64_t i0 = (int64_t)blockIdx.x * 2 * (int64_t)chunk;
@@ -220,24 +221,19 @@ __global__ void __launch_bounds__(PL::TG) fused_fft_staged_kernel(const StagedAr
             tmax0 = fmaxf(tmax0, cnorm2(v0[j]));
             tmax1 = fmaxf(tmax1, cnorm2(v1[j]));
         }
-        float m0 = tmax0, m1 = tmax1;
-#pragma unroll
-        for (int sh = 16; sh >= 1; sh >>= 1) {
-            m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, sh));
-            m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, sh));
-        }
+        // |X|^2 >= +0, so the float order is the order of the bit patterns: one REDUX per warp, one shared atomic
+        // per warp into the slot of this iteration's parity (the other slot is cleared for the next iteration)
+        unsigned int* const gm = reinterpret_cast<unsigned int*>(wmax) + 2 * (it & 1);
+        const unsigned int u0 = __reduce_max_sync(0xffffffffu, __float_as_uint(tmax0));
+        const unsigned int u1 = __reduce_max_sync(0xffffffffu, __float_as_uint(tmax1));
         if ((t & 31) == 0) {
-            wmax[t >> 5] = m0;
-            wmax[NW + (t >> 5)] = m1;
+            atomicMax(gm, u0);
+            atomicMax(gm + 1, u1);
         }
-        __syncthreads();   // all last-pass loads done (buffer free) + warp maxima visible
-        m0 = wmax[0];
-        m1 = wmax[NW];
-#pragma unroll
-        for (int w = 1; w < NW; ++w) {
-            m0 = fmaxf(m0, wmax[w]);
-            m1 = fmaxf(m1, wmax[NW + w]);
-        }
+        __syncthreads();   // all last-pass loads done (buffer free) + group maxima complete
+        const float m0 = __uint_as_float(gm[0]);
+        const float m1 = __uint_as_float(gm[1]);
+        if (t < 2) reinterpret_cast<unsigned int*>(wmax)[2 * ((it & 1) ^ 1) + t] = 0u;
         if (ok0 && tmax0 == m0) {
             unsigned int mybin = 0xffffffffu;
 #pragma unroll
