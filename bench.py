@@ -32,9 +32,9 @@ N_CUT = 8192
 K_C2 = 1 << 20
 K_RANK_MULTI = 1 << 23
 ALGO_BYTES_PER_SHIFT = 16.0        # one new rx sample (8 B) + one result (f32 qf2 + u32 bin)
-# dram__bytes_read.sum + dram__bytes_write.sum of one C2 launch of fused_fft_kernel<8192>, from the ncu --set full
-# capture summarised in profiles/r1_c2_fused_ncu.md (12.77 MB read, 0 written: the 8 MB of results stay in L2)
-NCU_DRAM_BYTES_C2 = 12.77e6
+# dram__bytes_read.sum + dram__bytes_write.sum of one C2 launch of fused_fft_staged_kernel<8192>, from the ncu --set full
+# capture summarised in profiles/r1_c2_staged_ncu.md (12.89 MB read, 0 written: the 8 MB of results stay in L2)
+NCU_DRAM_BYTES_C2 = 12.89e6
 FLOPS_PER_CELL = 75.0              # 5*log2(8192) + 10
 
 
@@ -300,9 +300,9 @@ def run_ours(args, rank, world, local_rank):
                            "wall_s_timed_loop": t_wall},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                              "frac": achieved / hbm_peak, "traffic": NCU_DRAM_BYTES_C2 if world == 1 else None,
-                             "traffic_source": "profiles/r1_c2_fused_ncu.md (ncu --set full, per launch)" if world == 1 else None,
+                             "traffic_source": "profiles/r1_c2_staged_ncu.md (ncu --set full, per launch)" if world == 1 else None,
                              "peak_source": peak_src,
-                             "kernel": "fused_fft_kernel<8192>", "kernel_ms": kms,
+                             "kernel": "fused_fft_staged_kernel<8192>", "kernel_ms": kms,
                              "algorithmic_bytes_per_launch": algo_bytes,
                              "note": "the path is FP32/issue bound, not HBM bound (SURVEY.md 8d); see fp32"},
                 "fp32": {"achieved_tflops": fp32_ach, "peak_tflops_measured_ffma": fp32_peak,

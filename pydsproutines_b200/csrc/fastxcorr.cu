@@ -186,9 +186,10 @@ struct FreqRunner {
             // two FFTs per thread (fused_fft_dual.cuh) for the (max, arg max) outputs; XC_DUAL=0 keeps the B = 2 layout
             static const bool dual = [] { const char* e = getenv("XC_DUAL"); return e && e[0] == '1'; }();
             if (dual && !out.caf && !out.cplx) return launch_fused_dual<typename PF::PL, LD>(ld, out, sl.K, stream);
-            // contiguous shift range: rx window resident in shared memory (fused_fft_staged.cuh); XC_STAGED=1 opts in
-            static const bool staged = [] { const char* e = getenv("XC_STAGED"); return e && e[0] == '1'; }();
-            if (staged && !out.caf && !out.cplx && !sl.shifts && sl.step == 1)
+            // contiguous shift range: rx window resident in shared memory (fused_fft_staged.cuh); XC_STAGED=0 keeps
+            // the B = 2 layout.  Short ranges stay on the B = 2 layout too (a refill per CTA would dominate).
+            static const bool staged = [] { const char* e = getenv("XC_STAGED"); return !(e && e[0] == '0'); }();
+            if (staged && !out.caf && !out.cplx && !sl.shifts && sl.step == 1 && sl.K >= 16 * (int64_t)sm_count())
                 return launch_fused_staged<typename PF::PL>(StagedArgs{rx, rxlen, cutout, sl.shift0}, out, sl.K, stream);
         }
         return launch_fused<typename PF::PL, PF::B, LD>(ld, out, sl.K, stream);

@@ -36,13 +36,21 @@ struct StagedLayout {
 // Both FFTs through one exchange buffer.  On entry v0 / v1 hold the products in input_index() order, on return the
 // bins of output_bin().  Three CTA-wide barriers inside; the caller's epilogue barrier frees the buffer.
 template <class PL>
-__device__ __forceinline__ void block_fft_dual_1buf(float2* v0, float2* v1, const float2* tab, float2* buf, int t) {
+__device__ __forceinline__ void block_fft_dual_1buf(float2* v0, float2* v1, const float2* x, const float2* c, const float2* tab,
+                                                    float2* buf, int t) {
     static_assert(PL::P == 3 && PL::WARP_LOCAL_X2, "staged layout: three passes, warp-local second exchange");
     constexpr int RL = PL::RL, ROW = PL::ROW;
     constexpr int K1STEP = (PL::M1 / RL) * ROW;
-    // ---- pass 1 ----
+    // ---- products of both windows (x = stage + offset + t, c = conj(cutout) + t) and pass 1, column by column ----
 #pragma unroll
     for (int q = 0; q < PL::V / PL::R1; ++q) {
+#pragma unroll
+        for (int n1 = 0; n1 < PL::R1; ++n1) {
+            const int n = input_index<PL>(0, q, n1);
+            const float2 cv = c[n];
+            v0[q * PL::R1 + n1] = pcmul(x[n], cv);
+            v1[q * PL::R1 + n1] = pcmul(x[n + 1], cv);
+        }
         codelet_fft<PL::R1>(v0 + q * PL::R1);
         codelet_fft<PL::R1>(v1 + q * PL::R1);
     }
@@ -112,6 +120,8 @@ __device__ __forceinline__ void block_fft_dual_1buf(float2* v0, float2* v1, cons
     for (int q = 0; q < PL::V / PL::R2; ++q)
 #pragma unroll
         for (int j = 0; j < PL::R2; ++j) buf[o2 + q * QSTEP2 + bitrev(j, ilog2(PL::R2)) * ROW] = v1[q * PL::R2 + j];
+#pragma unroll
+    for (int q = 0; q < PL::V / RL; ++q) codelet_fft<RL>(v0 + q * RL);   // under the stores / loads of FFT 1
     __syncwarp();
 #pragma unroll
     for (int q = 0; q < PL::V / RL; ++q)
@@ -122,10 +132,7 @@ __device__ __forceinline__ void block_fft_dual_1buf(float2* v0, float2* v1, cons
             v1[q * RL + 2 * d2 + 1] = make_float2(x.z, x.w);
         }
 #pragma unroll
-    for (int q = 0; q < PL::V / RL; ++q) {
-        codelet_fft<RL>(v0 + q * RL);
-        codelet_fft<RL>(v1 + q * RL);
-    }
+    for (int q = 0; q < PL::V / RL; ++q) codelet_fft<RL>(v1 + q * RL);
 }
 
 template <class PL>
@@ -133,7 +140,7 @@ __global__ void __launch_bounds__(PL::TG) fused_fft_staged_kernel(const StagedAr
                                                                   const int chunk) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     using L = StagedLayout<PL>;
-    constexpr int TG = PL::TG, V = PL::V, NW = TG / 32, W = L::W, NQ = PL::V / PL::R1;
+    constexpr int TG = PL::TG, V = PL::V, NW = TG / 32, W = L::W;
     const int t = threadIdx.x;
     float2* const cc = reinterpret_cast<float2*>(smem_raw + L::OFF_CUT);
     for (int n = t; n < PL::N; n += TG) {
@@ -176,32 +183,11 @@ __global__ void __launch_bounds__(PL::TG) fused_fft_staged_kernel(const StagedAr
         const int64_t s0 = s_first + e0;
         const bool ok0 = e0 < n_act && s0 >= 0 && s0 + PL::N <= a.rxlen;
         const bool ok1 = e1 < n_act && s0 + 1 >= 0 && s0 + 1 + PL::N <= a.rxlen;
-        {
-            const float2* const x = stage + o + t;
-            const float2* const c = cc + t;
-#pragma unroll
-            for (int n1 = 0; n1 < PL::R1; ++n1) {
-#pragma unroll
-                for (int q = 0; q < NQ; ++q) {
-                    const int n = input_index<PL>(0, q, n1);
-                    const float2 cv = c[n];
-                    v0[q * PL::R1 + n1] = pcmul(x[n], cv);
-                    v1[q * PL::R1 + n1] = pcmul(x[n + 1], cv);
-                }
-                if (((n1 + 1) * NQ) % 8 == 0) asm volatile("" ::: "memory");
-            }
-        }
-        if (!ok0) {
-#pragma unroll
-            for (int j = 0; j < V; ++j) v0[j] = make_float2(0.f, 0.f);
-        }
-        if (!ok1) {
-#pragma unroll
-            for (int j = 0; j < V; ++j) v1[j] = make_float2(0.f, 0.f);
-        }
+        // windows that leave the record still run (the stage is zero filled there); their results are dropped below
+        const float2* const xw = stage + o + t;
         o += 2;
         // the barriers inside also order the previous pair's bin-minimum atomics before thread 0 reads them below
-        block_fft_dual_1buf<PL>(v0, v1, tab, buf, t);
+        block_fft_dual_1buf<PL>(v0, v1, xw, cc + t, tab, buf, t);
         if (t == 0 && it > 0) {                      // results of the previous pair
             const int p0 = 2 * (it - 1);
 #pragma unroll

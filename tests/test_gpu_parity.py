@@ -836,6 +836,47 @@ print("dual ok")
     assert r.returncode == 0 and "dual ok" in r.stdout, r.stdout + r.stderr
 
 
+def test_staged_layout_matches_b2_layout_subprocess(xr):
+    """Contiguous N = 8192 searches of >= 16 shifts per SM run the staged layout (csrc/fused_fft_staged.cuh: rx window in
+    shared memory, two FFTs per thread through one exchange buffer); XC_STAGED=0 keeps the B = 2 layout.  Both must give
+    the same bits on a record long enough for several window refills per CTA, with windows that leave rx on both sides
+    (CyIppXcorrFFT's zero rule, IppXcorrFFT.cpp:125-130), odd and even counts, and the oracle must agree at the peak."""
+    import hashlib
+    import subprocess
+    import sys
+    code = r'''
+import hashlib, numpy as np
+from pydsproutines_b200 import signals
+import pydsproutines_b200.xcorrRoutines as xr
+cutout, rx = signals.make_fastxcorr_case(21, 8192, 8192 + 300000, 123456, 4321, amp=0.7)
+h = hashlib.sha1()
+for a, b in ((-50, 300101), (7, 290000), (100, 2601)):
+    q, f = xr.CyIppXcorrFFT(cutout).xcorr(rx, a, b, 1)
+    h.update(np.ascontiguousarray(q).tobytes()); h.update(np.ascontiguousarray(f).tobytes())
+print("digest", h.hexdigest())
+'''
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    digests = []
+    for flag in ("1", "0"):
+        env = dict(os.environ, XC_STAGED=flag)
+        r = subprocess.run([sys.executable, "-c", code], env=env, cwd=root, capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0 and "digest" in r.stdout, r.stdout + r.stderr
+        digests.append(r.stdout.split("digest")[1].split()[0])
+    assert digests[0] == digests[1]
+    # and against the oracle in this process (staged is the default): zeros outside, peak where planted
+    from pydsproutines_b200 import signals
+    cutout, rx = signals.make_fastxcorr_case(21, 8192, 8192 + 300000, 123456, 4321, amp=0.7)
+    q, f = xr.CyIppXcorrFFT(cutout).xcorr(rx, -50, 300101, 1)
+    assert q.dtype == np.float32 and f.dtype == np.int32 and q.size == 300151
+    assert not q[:50].any() and not f[:50].any() and not q[-100:].any() and q[50] > 0 and q[-101] > 0
+    i = int(np.argmax(q))
+    assert i == 123456 + 50 and f[i] == 4321
+    idx = np.r_[np.arange(0, 40), np.arange(123456 - 20, 123456 + 21), np.arange(299960, 300001)]
+    rq, rf = orc.fastXcorr(cutout, rx, freqsearch=True, shifts=idx)
+    assert_qf2(q[idx + 50], rq)
+    assert (f[idx + 50] == rf).mean() > 0.97 and f[123456 + 50] == rf[60]
+
+
 def test_groupfreq_large_planted_and_sampled(xr):
     """C3's groups (64 x 128 at 1024 g) against 256 frequencies over 2^17 shifts: the planted (shift, frequency) is the
     global peak, and 48 randomly sampled shifts agree with the oracle (size-independent checks at bench-like size)."""
