@@ -13,7 +13,7 @@ cat gpurun_out/${tag}_configs.jsonl
 if [ -z "$SKIP_NCU" ]; then
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${tag}_launches.csv \
    python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/${tag}_ncu_launch.log 2>&1; echo "ncu launches rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:fused_fft_kernel -s 3 -c 1 -f -o gpurun_out/${tag}_fused \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:fused_fft_staged -s 3 -c 1 -f -o gpurun_out/${tag}_fused \
    python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/${tag}_ncu_full.log 2>&1; echo "ncu full rc=$?"
 fi
 if [ -n "$REF_ARM" ]; then

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""A/B of the N = 8192 frequency-search layouts on the GPU box: default (B = 2), XC_DUAL=1, XC_STAGED=1.
+"""A/B of the N = 8192 frequency-search layouts on the GPU box: B = 2 (XC_STAGED=0), XC_DUAL=1, staged (the default).
 Each layout runs in its own process (the switch is read once per process) on the C2 record and on a short record
 with windows that leave rx; results are compared bit for bit with the default layout, times are CUDA-event medians."""
 import json
@@ -40,7 +40,7 @@ np.savez(out, q=np.asarray(q.cpu() if hasattr(q, "cpu") else q), f=np.asarray(f.
 def main():
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     res = {}
-    for name, env in (("default", {}), ("dual", {"XC_DUAL": "1"}), ("staged", {"XC_STAGED": "1"})):
+    for name, env in (("default", {"XC_STAGED": "0"}), ("dual", {"XC_DUAL": "1", "XC_STAGED": "0"}), ("staged", {"XC_STAGED": "1"})):
         out = os.path.join(ROOT, "gpurun_out", "ab_%s.npz" % name)
         e = dict(os.environ, **env)
         r = subprocess.run([sys.executable, "-c", CHILD, out], env=e, cwd=ROOT, capture_output=True, text=True, timeout=600)
