@@ -4,7 +4,9 @@
 NVCC      ?= /usr/local/cuda/bin/nvcc
 ARCH      := -gencode arch=compute_100a,code=sm_100a
 NVCCFLAGS := -O3 -std=c++17 -lineinfo $(ARCH) -Xcompiler -fPIC \
-             --expt-relaxed-constexpr -Xptxas -v
+             --expt-relaxed-constexpr -Xptxas -v $(EXTRA)
+# EXTRA=-DXC_EXPERIMENTS keeps the earlier layouts of the N = 8192 search selectable (XC_LAYOUT=b2|dual|staged|pp)
+# for A/B runs; the shipped library is built without it.
 CSRC      := pydsproutines_b200/csrc
 BUILD     := build
 SRCS      := $(wildcard $(CSRC)/*.cu)

@@ -68,6 +68,31 @@ int32_t release_workspace();
 int sm_count();
 int max_smem_optin();
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is per device: one flag per (kernel instantiation, device).
+constexpr int XC_MAX_DEVICES = 64;
+struct KernelOnce {
+    bool done[XC_MAX_DEVICES] = {};
+    int occ[XC_MAX_DEVICES] = {};
+    // opts the kernel into `smem_bytes` of dynamic shared memory on the current device (first call per device)
+    template <class Kern>
+    int32_t configure(Kern kern, int smem_bytes, int* first = nullptr) {
+        int dev = 0;
+        XC_CUDA_TRY(cudaGetDevice(&dev));
+        if (dev < 0 || dev >= XC_MAX_DEVICES) return fail(XC_ERR_UNSUPPORTED, "device ordinal %d out of range", dev);
+        if (first) *first = done[dev] ? 0 : 1;
+        if (!done[dev]) {
+            XC_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+            done[dev] = true;
+        }
+        return XC_OK;
+    }
+    int& occupancy() {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        return occ[(dev >= 0 && dev < XC_MAX_DEVICES) ? dev : 0];
+    }
+};
+
 // ---------------------------------------------------------------------------------------------
 // complex helpers (float2 = interleaved complex64)
 // ---------------------------------------------------------------------------------------------

@@ -13,6 +13,7 @@
 #include "fused_fft_kernel.cuh"
 #include "fused_fft_dual.cuh"
 #include "fused_fft_staged.cuh"
+#include "fused_fft_pp.cuh"
 #include "internal.cuh"
 #include "plans.cuh"
 
@@ -170,6 +171,25 @@ bool fastxcorr_fft_supported(int N) {
     return N >= 3 && bluestein_log2m(N) <= MAX_LOG2N;
 }
 
+// Layout of the N = 8192 search.  The product always runs LAYOUT_PP; a build with -DXC_EXPERIMENTS keeps the
+// earlier layouts selectable through XC_LAYOUT=b2|dual|staged|pp for A/B runs (tools/staged_check.py).
+enum { LAYOUT_B2 = 0, LAYOUT_DUAL, LAYOUT_STAGED, LAYOUT_PP };
+static int search_layout() {
+#ifdef XC_EXPERIMENTS
+    static const int layout = [] {
+        const char* e = getenv("XC_LAYOUT");
+        if (!e) return (int)LAYOUT_PP;
+        if (!strcmp(e, "b2")) return (int)LAYOUT_B2;
+        if (!strcmp(e, "dual")) return (int)LAYOUT_DUAL;
+        if (!strcmp(e, "staged")) return (int)LAYOUT_STAGED;
+        return (int)LAYOUT_PP;
+    }();
+    return layout;
+#else
+    return LAYOUT_PP;
+#endif
+}
+
 struct FreqRunner {
     const float2* cutout;
     const float2* rx;
@@ -183,14 +203,19 @@ struct FreqRunner {
         using LD = CutoutLoader<typename PF::PL, PF::CS>;
         LD ld{rx, rxlen, cutout, sl.shift0, sl.step, sl.shifts};
         if constexpr (LOG2N == 13) {
-            // two FFTs per thread (fused_fft_dual.cuh) for the (max, arg max) outputs; XC_DUAL=0 keeps the B = 2 layout
-            static const bool dual = [] { const char* e = getenv("XC_DUAL"); return e && e[0] == '1'; }();
-            if (dual && !out.caf && !out.cplx) return launch_fused_dual<typename PF::PL, LD>(ld, out, sl.K, stream);
-            // contiguous shift range: rx window resident in shared memory (fused_fft_staged.cuh); XC_STAGED=0 keeps
-            // the B = 2 layout.  Short ranges stay on the B = 2 layout too (a refill per CTA would dominate).
-            static const bool staged = [] { const char* e = getenv("XC_STAGED"); return !(e && e[0] == '0'); }();
-            if (staged && !out.caf && !out.cplx && !sl.shifts && sl.step == 1 && sl.K >= 16 * (int64_t)sm_count())
+            // contiguous shift range, (max, arg max) outputs: two free-running thread groups per SM over one staged
+            // rx window, constants in tensor memory (fused_fft_pp.cuh).  Short ranges, shift lists with a step or a
+            // gather table and the CAF / complex outputs stay on the B = 2 layout below.
+            const int layout = search_layout();
+            const bool plain = !out.caf && !out.cplx;
+            const bool contiguous = !sl.shifts && sl.step == 1 && sl.K >= 16 * (int64_t)sm_count();
+            if (layout == LAYOUT_PP && plain && contiguous)
+                return launch_fused_pp<FftPlan<13, 128, 8, 32, 32>, 2>(StagedArgs{rx, rxlen, cutout, sl.shift0}, out, sl.K, stream);
+#ifdef XC_EXPERIMENTS
+            if (layout == LAYOUT_STAGED && plain && contiguous)
                 return launch_fused_staged<typename PF::PL>(StagedArgs{rx, rxlen, cutout, sl.shift0}, out, sl.K, stream);
+            if (layout == LAYOUT_DUAL && plain) return launch_fused_dual<typename PF::PL, LD>(ld, out, sl.K, stream);
+#endif
         }
         return launch_fused<typename PF::PL, PF::B, LD>(ld, out, sl.K, stream);
     }

@@ -244,13 +244,13 @@ int32_t launch_fused_dual(const Loader& loader, const FusedOut& out, int64_t K, 
     auto kern = fused_fft_dual_kernel<PL, Loader>;
     const size_t smem = fused_dual_smem_bytes<PL, Loader>();
     if ((int)smem > max_smem_optin()) return fail(XC_ERR_UNSUPPORTED, "dual fused kernel needs %zu B of shared memory", smem);
-    static bool configured = false;
-    static int occ = 1;
-    if (!configured) {
-        XC_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_optin()));
+    static KernelOnce once;
+    int first = 0;
+    XC_TRY(once.configure(kern, max_smem_optin(), &first));
+    int& occ = once.occupancy();
+    if (first) {
         XC_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, PL::TG, smem));
         if (occ < 1) return fail(XC_ERR_CUDA, "dual fused kernel does not fit on an SM (smem %zu B)", smem);
-        configured = true;
     }
     const int64_t pairs = (K + 1) / 2;
     int64_t ctas = (int64_t)sm_count() * occ;

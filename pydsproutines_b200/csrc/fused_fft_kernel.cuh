@@ -182,16 +182,15 @@ int32_t launch_fused_variant(const Loader& loader, const FusedOut& out, int64_t 
     const size_t dyn = loader.dyn_smem();
     const size_t smem = fused_smem_bytes<PL, B, Loader>() + dyn;
     if ((int)smem > max_smem_optin()) return fail(XC_ERR_UNSUPPORTED, "fused kernel needs %zu B of shared memory", smem);
-    static bool configured = false;   // per instantiation
-    static int occ0 = 1;
-    int occ = occ0;
-    if (!configured) {
-        XC_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_optin()));
+    static KernelOnce once;           // per instantiation, flags per device
+    int first = 0;
+    XC_TRY(once.configure(kern, max_smem_optin(), &first));
+    int& occ0 = once.occupancy();
+    if (first) {
         XC_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ0, kern, PL::TG * B, fused_smem_bytes<PL, B, Loader>()));
         if (occ0 < 1) return fail(XC_ERR_CUDA, "fused kernel does not fit on an SM (smem %zu B)", smem);
-        configured = true;
-        occ = occ0;
     }
+    int occ = occ0;
     if (dyn > 0) {
         XC_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, PL::TG * B, smem));
         if (occ < 1) return fail(XC_ERR_CUDA, "fused kernel does not fit on an SM (smem %zu B)", smem);

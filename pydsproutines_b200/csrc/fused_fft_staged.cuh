@@ -261,11 +261,8 @@ int32_t launch_fused_staged(const StagedArgs& a, const FusedOut& out, int64_t K,
     auto kern = fused_fft_staged_kernel<PL>;
     constexpr size_t smem = StagedLayout<PL>::BYTES;
     if ((int)smem > max_smem_optin()) return fail(XC_ERR_UNSUPPORTED, "staged fused kernel needs %zu B of shared memory", smem);
-    static bool configured = false;
-    if (!configured) {
-        XC_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_optin()));
-        configured = true;
-    }
+    static KernelOnce once;
+    XC_TRY(once.configure(kern, max_smem_optin()));
     const int64_t pairs = (K + 1) / 2;
     int64_t ctas = (int64_t)sm_count();
     if (ctas > pairs) ctas = pairs;

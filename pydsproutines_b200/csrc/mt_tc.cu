@@ -484,11 +484,9 @@ int32_t mt_tc_run(const MtTcPlan& plan, const float2* x, int64_t xlen, int64_t s
     const int nstages = tc_pick_stages(plan.Lp, plan.NT, plan.NB, plan.planes, &ne);
     const TcSmem lay = tc_smem_layout(plan.Lp, plan.NT, plan.NB, nstages, ne, plan.planes);
     const size_t smem = lay.total + 128;
-    static size_t configured = 0;
-    if (smem > configured) {
-        XC_CUDA_TRY(cudaFuncSetAttribute(mt_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    if ((int)smem > max_smem_optin()) return fail(XC_ERR_UNSUPPORTED, "tensor-core template kernel needs %zu B of shared memory", smem);
+    static KernelOnce once;
+    XC_TRY(once.configure(mt_tc_kernel, max_smem_optin()));
     const int64_t ntiles = (K + TC_M - 1) / TC_M;
     int64_t ctas = sm_count();
     if (ctas > ntiles) ctas = ntiles;

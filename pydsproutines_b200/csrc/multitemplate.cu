@@ -242,11 +242,9 @@ int32_t xc_mt_correlate(xc_mt* h, const void* x, int64_t xlen, int64_t start, in
         XC_TRY(mt_tc_run(h->tc, dx, xlen, start, K, d_energy, db, dt, sqrt_out, st));
     } else {
         const size_t smem = mt_smem_bytes(h->L8);
-        static size_t configured = 0;
-        if (smem > configured) {
-            XC_CUDA_TRY(cudaFuncSetAttribute(mt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            configured = smem;
-        }
+        if ((int)smem > max_smem_optin()) return fail(XC_ERR_UNSUPPORTED, "template kernel needs %zu B of shared memory", smem);
+        static KernelOnce once;
+        XC_TRY(once.configure(mt_kernel, max_smem_optin()));
         const int64_t blocks = (K + MT_TS - 1) / MT_TS;
         mt_kernel<<<(unsigned)blocks, MT_THREADS, smem, st>>>(h->d_templates, h->T, h->L8, h->d_energies, dx, xlen, start,
                                                               K, d_energy, db, dt, dfull, sqrt_out);

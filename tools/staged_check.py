@@ -1,7 +1,8 @@
 #!/usr/bin/env python
-"""A/B of the N = 8192 frequency-search layouts on the GPU box: B = 2 (XC_STAGED=0), XC_DUAL=1, staged (the default).
-Each layout runs in its own process (the switch is read once per process) on the C2 record and on a short record
-with windows that leave rx; results are compared bit for bit with the default layout, times are CUDA-event medians."""
+"""A/B of the N = 8192 frequency-search layouts on the GPU box (library built with EXTRA=-DXC_EXPERIMENTS):
+XC_LAYOUT = b2 | dual | staged | pp.  Each layout runs in its own process (the switch is read once per process) on the
+C2 record and on a short record with windows that leave rx; results are compared bit for bit with the B = 2 layout,
+times are CUDA-event medians."""
 import json
 import os
 import subprocess
@@ -40,7 +41,8 @@ np.savez(out, q=np.asarray(q.cpu() if hasattr(q, "cpu") else q), f=np.asarray(f.
 def main():
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     res = {}
-    for name, env in (("default", {"XC_STAGED": "0"}), ("dual", {"XC_DUAL": "1", "XC_STAGED": "0"}), ("staged", {"XC_STAGED": "1"})):
+    names = sys.argv[1:] or ["b2", "staged", "pp"]
+    for name, env in [(n, {"XC_LAYOUT": n}) for n in names]:
         out = os.path.join(ROOT, "gpurun_out", "ab_%s.npz" % name)
         e = dict(os.environ, **env)
         r = subprocess.run([sys.executable, "-c", CHILD, out], env=e, cwd=ROOT, capture_output=True, text=True, timeout=600)
@@ -48,7 +50,7 @@ def main():
             print(name, "FAILED", r.stderr[-2000:])
             continue
         res[name] = np.load(out)
-    ref = res["default"]
+    ref = res[names[0]]
     for name, d in res.items():
         line = {"layout": name, "c2_ms": float(d["ms"])}
         for k in ("q", "f", "q2", "f2", "q3", "f3"):
