@@ -13,11 +13,13 @@
 #include "fused_fft_kernel.cuh"
 #include "fused_fft_dual.cuh"
 #include "fused_fft_staged.cuh"
-#include "fused_fft_pp.cuh"
 #include "internal.cuh"
 #include "plans.cuh"
 
 namespace xc {
+
+// search_pp.cu: the ping-pong layout of the N = 8192 search (fused_fft_pp.cuh); fold = 1 is the shipped variant
+int32_t search_pp_device(const StagedArgs& a, const FusedOut& out, int64_t K, int fold, cudaStream_t stream);
 
 // ---------------------------------------------------------------------------------------------
 // loader of the fused kernel: v[n] = rx[s + n] * conj(cutout[n])
@@ -172,8 +174,8 @@ bool fastxcorr_fft_supported(int N) {
 }
 
 // Layout of the N = 8192 search.  The product always runs LAYOUT_PP; a build with -DXC_EXPERIMENTS keeps the
-// earlier layouts selectable through XC_LAYOUT=b2|dual|staged|pp for A/B runs (tools/staged_check.py).
-enum { LAYOUT_B2 = 0, LAYOUT_DUAL, LAYOUT_STAGED, LAYOUT_PP };
+// earlier layouts selectable through XC_LAYOUT=b2|dual|staged|ppchain|pp for A/B runs (tools/staged_check.py).
+enum { LAYOUT_B2 = 0, LAYOUT_DUAL, LAYOUT_STAGED, LAYOUT_PP_CHAIN, LAYOUT_PP };
 static int search_layout() {
 #ifdef XC_EXPERIMENTS
     static const int layout = [] {
@@ -182,6 +184,7 @@ static int search_layout() {
         if (!strcmp(e, "b2")) return (int)LAYOUT_B2;
         if (!strcmp(e, "dual")) return (int)LAYOUT_DUAL;
         if (!strcmp(e, "staged")) return (int)LAYOUT_STAGED;
+        if (!strcmp(e, "ppchain")) return (int)LAYOUT_PP_CHAIN;
         return (int)LAYOUT_PP;
     }();
     return layout;
@@ -210,8 +213,10 @@ struct FreqRunner {
             const bool plain = !out.caf && !out.cplx;
             const bool contiguous = !sl.shifts && sl.step == 1 && sl.K >= 16 * (int64_t)sm_count();
             if (layout == LAYOUT_PP && plain && contiguous)
-                return launch_fused_pp<FftPlan<13, 128, 8, 32, 32>, 2>(StagedArgs{rx, rxlen, cutout, sl.shift0}, out, sl.K, stream);
+                return search_pp_device(StagedArgs{rx, rxlen, cutout, sl.shift0}, out, sl.K, 1, stream);
 #ifdef XC_EXPERIMENTS
+            if (layout == LAYOUT_PP_CHAIN && plain && contiguous)
+                return search_pp_device(StagedArgs{rx, rxlen, cutout, sl.shift0}, out, sl.K, 0, stream);
             if (layout == LAYOUT_STAGED && plain && contiguous)
                 return launch_fused_staged<typename PF::PL>(StagedArgs{rx, rxlen, cutout, sl.shift0}, out, sl.K, stream);
             if (layout == LAYOUT_DUAL && plain) return launch_fused_dual<typename PF::PL, LD>(ld, out, sl.K, stream);

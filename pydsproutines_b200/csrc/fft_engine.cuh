@@ -68,11 +68,12 @@ __device__ __forceinline__ void dit_butterfly(float2& u, float2& v, int idx) {
 // on return.  Decimation in time on the virtual array b[i] = a[bitrev(i)] (so its bit-reversed input
 // order is the natural order of a); all index arithmetic folds at compile time.
 // 194 packed instructions for R = 32, 26 for R = 8.
-template <int R>
+// H0 > 1 skips the stages below H0 (the caller has run them, see folded_butterfly()).
+template <int R, int H0 = 1>
 __device__ __forceinline__ void codelet_fft(float2* a) {
     constexpr int LG = ilog2(R);
 #pragma unroll
-    for (int h = 1; h < R; h <<= 1) {
+    for (int h = H0; h < R; h <<= 1) {
 #pragma unroll
         for (int blk = 0; blk < R; blk += 2 * h) {
 #pragma unroll
@@ -82,7 +83,18 @@ __device__ __forceinline__ void codelet_fft(float2* a) {
     }
 }
 template <>
-__device__ __forceinline__ void codelet_fft<1>(float2*) {}
+__device__ __forceinline__ void codelet_fft<1, 1>(float2*) {}
+
+// First stage (h = 1) of codelet_fft<R> with a pending twiddle on every input: the stage pairs a[i] with a[i + R/2]
+// (w = 1), so (a[i], a[i + R/2]) <- (wu a[i] + wv a[i + R/2], wu a[i] - wv a[i + R/2]) costs five packed
+// instructions (P = wu u; S = P + wv v; D = 2 P - S) instead of two complex multiplies and a butterfly (six).
+__device__ __forceinline__ void folded_butterfly(float2& u, float2& v, float2 wu, float2 wv) {
+    const float2 P = pcmul(u, wu);
+    float2 S = pfma(v, make_float2(wv.x, wv.x), P);
+    S = pfma(make_float2(v.y, v.x), make_float2(-wv.y, wv.y), S);
+    v = pfma(P, make_float2(2.f, 2.f), make_float2(-S.x, -S.y));
+    u = S;
+}
 
 // multiply the bit-reversed outputs of a codelet by successive powers of w: a[bitrev(k)] *= w^k
 template <int R>

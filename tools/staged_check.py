@@ -56,8 +56,12 @@ def main():
         for k in ("q", "f", "q2", "f2", "q3", "f3"):
             line["same_" + k] = bool(np.array_equal(d[k], ref[k]))
             if not line["same_" + k]:
-                line["maxdiff_" + k] = float(np.max(np.abs(d[k].astype(np.float64) - ref[k].astype(np.float64))))
+                a, b = d[k].astype(np.float64), ref[k].astype(np.float64)
                 line["ndiff_" + k] = int(np.sum(d[k] != ref[k]))
+                if k.startswith("q"):
+                    line["maxrel_" + k] = float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-30)))
+                else:
+                    line["maxdiff_" + k] = float(np.max(np.abs(a - b)))
         print(json.dumps(line))
 
 
