@@ -44,13 +44,13 @@ __device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, uint32_t* u) {
           "=r"(u[9]), "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15])
         : "r"(taddr));
 }
-// waits for every outstanding tcgen05.ld of this thread; the "+r" operands tie the consumers of `u` behind it
+// waits for every outstanding tcgen05.ld of this thread; the "+r" operands tie the consumers of `u` behind it.
+// No "memory" clobber: the tables in tensor memory are written once per kernel (behind tcgen05.wait::st and a
+// CTA barrier), and a clobber would pin every shared-memory load / store of the FFT to its side of the wait.
 __device__ __forceinline__ void tmem_ld_wait16(uint32_t* u) {
     asm volatile("tcgen05.wait::ld.sync.aligned;"
                  : "+r"(u[0]), "+r"(u[1]), "+r"(u[2]), "+r"(u[3]), "+r"(u[4]), "+r"(u[5]), "+r"(u[6]), "+r"(u[7]),
-                   "+r"(u[8]), "+r"(u[9]), "+r"(u[10]), "+r"(u[11]), "+r"(u[12]), "+r"(u[13]), "+r"(u[14]), "+r"(u[15])
-                 :
-                 : "memory");
+                   "+r"(u[8]), "+r"(u[9]), "+r"(u[10]), "+r"(u[11]), "+r"(u[12]), "+r"(u[13]), "+r"(u[14]), "+r"(u[15]));
 }
 }  // namespace tc
 
@@ -180,17 +180,53 @@ __device__ __forceinline__ void pp_block_fft_fold(float2* v, const float2* x, co
     const int o1 = (t / RL) * ROW + (t % RL);
     uint32_t cu[2][16];
     tc::tmem_ld16_issue(tb + L::COL_CUT, cu[0]);
+#ifndef XC_PP_NOPIPE
+    // explicit software pipeline: the window samples and the conj(cutout) chunk of column q + 1 are requested before
+    // the arithmetic of column q (volatile loads keep their order; the empty asm ties column q's arithmetic behind them)
+    float2 xs[2][R1];
+    const uint32_t xa = tc::smem_u32(x);
+#pragma unroll
+    for (int n1 = 0; n1 < R1; ++n1) xs[0][n1] = x[input_index<PL>(0, 0, n1)];
+#endif
     tc::tmem_ld_wait16(cu[0]);
     // ---- products + pass 1 + first-exchange stores (raw), column by column ----
 #pragma unroll
     for (int q = 0; q < NQ1; ++q) {
-        if (q + 1 < NQ1) tc::tmem_ld16_issue(tb + L::COL_CUT + 16 * (q + 1), cu[(q + 1) & 1]);
+        if (q + 1 < NQ1) {
+            tc::tmem_ld16_issue(tb + L::COL_CUT + 16 * (q + 1), cu[(q + 1) & 1]);
+#ifndef XC_PP_NOPIPE
+#pragma unroll
+            for (int n1 = 0; n1 < R1; ++n1)
+                asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];"
+                             : "=f"(xs[(q + 1) & 1][n1].x), "=f"(xs[(q + 1) & 1][n1].y)
+                             : "r"(xa + 8u * (uint32_t)(n1 * PL::M1 + PL::TG * (q + 1))));
+            asm volatile("" : "+r"(cu[q & 1][0]));
+#endif
+        }
+        float2 c8[R1], x8[R1];
 #pragma unroll
         for (int n1 = 0; n1 < R1; ++n1) {
-            const float2 cv = make_float2(__uint_as_float(cu[q & 1][2 * n1]), __uint_as_float(cu[q & 1][2 * n1 + 1]));
-            v[q * R1 + n1] = pcmul(x[input_index<PL>(0, q, n1)], cv);
+            c8[n1] = make_float2(__uint_as_float(cu[q & 1][2 * n1]), __uint_as_float(cu[q & 1][2 * n1 + 1]));
+#ifndef XC_PP_NOPIPE
+            x8[n1] = xs[q & 1][n1];
+#else
+            x8[n1] = x[input_index<PL>(0, q, n1)];
+#endif
         }
+#ifdef XC_PP_NOFOLD0
+#pragma unroll
+        for (int n1 = 0; n1 < R1; ++n1) v[q * R1 + n1] = pcmul(x8[n1], c8[n1]);
         codelet_fft<R1>(v + q * R1);
+#else
+        // the products ride on the first butterfly stage of the radix-8 codelet (pairs n1, n1 + 4)
+#pragma unroll
+        for (int n1 = 0; n1 < R1 / 2; ++n1) {
+            v[q * R1 + n1] = x8[n1];
+            v[q * R1 + n1 + R1 / 2] = x8[n1 + R1 / 2];
+            folded_butterfly(v[q * R1 + n1], v[q * R1 + n1 + R1 / 2], c8[n1], c8[n1 + R1 / 2]);
+        }
+        codelet_fft<R1, 2>(v + q * R1);
+#endif
 #pragma unroll
         for (int j = 0; j < R1; ++j) buf[o1 + bitrev(j, ilog2(R1)) * K1STEP + q * QSTEP1] = v[q * R1 + j];
         if (q + 1 < NQ1) tc::tmem_ld_wait16(cu[(q + 1) & 1]);
