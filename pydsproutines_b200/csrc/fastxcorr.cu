@@ -11,8 +11,10 @@
 
 #include "bluestein.cuh"
 #include "fused_fft_kernel.cuh"
+#ifdef XC_EXPERIMENTS   // earlier layouts of the N = 8192 search, kept for A/B runs only (tools/staged_check.py)
 #include "fused_fft_dual.cuh"
 #include "fused_fft_staged.cuh"
+#endif
 #include "internal.cuh"
 #include "plans.cuh"
 

@@ -36,6 +36,14 @@ struct FusedOut {
     const float* refnormsq;  // device scalar: ||cutout||^2 (or ||ygroups||^2)
 };
 
+// arguments of the layouts that search a CONTIGUOUS shift range from a staged window (fused_fft_pp.cuh)
+struct StagedArgs {
+    const float2* rx;
+    int64_t rxlen;
+    const float2* cutout;
+    int64_t shift0;       // the shift of entry i is shift0 + i
+};
+
 // Loader concept (all const; the kernel argument is never copied into registers):
 //   static constexpr size_t smem_bytes()
 //   __device__ void prepare(int tid_in_cta, int nthreads, unsigned char* smem) const   -- once per CTA

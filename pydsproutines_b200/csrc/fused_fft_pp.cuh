@@ -20,7 +20,7 @@
 // Results are bit-identical to fused_fft_kernel / fused_fft_staged_kernel (same codelets, same twiddle values,
 // same operation order per point).  (max, arg max) outputs only.
 #pragma once
-#include "fused_fft_staged.cuh"
+#include "fused_fft_kernel.cuh"
 #include "mt_tc.cuh"
 
 namespace xc {

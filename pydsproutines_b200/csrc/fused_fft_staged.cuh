@@ -13,13 +13,6 @@
 
 namespace xc {
 
-struct StagedArgs {
-    const float2* rx;
-    int64_t rxlen;
-    const float2* cutout;
-    int64_t shift0;       // the shift of entry i is shift0 + i
-};
-
 template <class PL>
 struct StagedLayout {
     static constexpr int W = 1792;                                        // extra samples behind the window (even)
