@@ -21,7 +21,7 @@ $(BUILD)/%.o: $(CSRC)/%.cu $(HDRS)
 	$(NVCC) $(NVCCFLAGS) -c $< -o $@ 2> $(BUILD)/$*.ptxas.log || (cat $(BUILD)/$*.ptxas.log; exit 1)
 
 $(LIB): $(OBJS)
-	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -cudart static
+	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -cudart static -ldl
 
 clean:
 	rm -rf $(BUILD) $(LIB)

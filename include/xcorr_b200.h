@@ -53,6 +53,9 @@ int32_t xc_version(void);
 const char* xc_last_error(void);
 int32_t xc_device_count(void);
 int32_t xc_set_device(int32_t device);
+/* ordinal of the device that owns `p` (device or managed memory), -1 for host pointers: lets the Python side adopt any
+ * object exposing __cuda_array_interface__ (the reference's gate is cupyHelpers.py:80-83 requireCupyArray) */
+int32_t xc_pointer_device(const void* p);
 /* frees the cached device workspace of the current device */
 int32_t xc_release_workspace(void);
 /* device properties the bench reports: out[0]=SM count, out[1]=max smem/block (opt-in), out[2]=clock kHz,
@@ -247,6 +250,21 @@ int32_t xc_row_argmax_c64(const void* x, int64_t rows, int64_t cols, int32_t use
  * stored (count still reports how many exist); sorted != 0 returns them in ascending order */
 int32_t xc_find_local_maxima_f32(const float* x, int64_t n, float min_height, int32_t* idx, int32_t cap,
                                  int32_t* count, int32_t sorted, int32_t where, void* stream);
+
+/* ---- 8e: the one exchange step of the shift-sharded multi-GPU search ---------------------------------------
+ * (the reference has no multi-GPU code; north_star: work is partitioned by shift range, only the per-rank peak
+ * tuples are combined with one small NCCL allgather).  One process per GPU: xc_set_device() first, rank 0 makes the
+ * 128-byte NCCL unique id and hands it to the other ranks by any host channel, every rank calls xc_dist_init().
+ * xc_dist_allgather_peak(): `mine` (host) -> `all` (host, world entries, rank-ordered; .rank filled in); *best_rank
+ * (optional) = the winner of the deterministic reduction (largest QF^2, lowest shift on ties, negative shift = empty
+ * shard).  The copies and the ncclAllGather are enqueued on `stream`; the call returns when `all` is host-visible.
+ * NCCL is loaded at run time (libnccl.so.2); XC_ERR_UNSUPPORTED when it is absent.  xc_peak_argmax() is the same
+ * reduction on caller-gathered tuples (what pydsproutines_b200/dist.py uses after torch.distributed's allgather). */
+int32_t xc_dist_unique_id(void* out128);
+int32_t xc_dist_init(int32_t rank, int32_t world, const void* unique_id128);
+int32_t xc_dist_allgather_peak(const xc_peak* mine, xc_peak* all, int32_t* best_rank, void* stream);
+int32_t xc_dist_finalize(void);
+int32_t xc_peak_argmax(const xc_peak* all, int32_t world);
 
 #ifdef __cplusplus
 }

@@ -33,6 +33,7 @@ SIGNATURES = {
     "xc_last_error": (C.c_char_p, []),
     "xc_device_count": (_i32, []),
     "xc_set_device": (_i32, [_i32]),
+    "xc_pointer_device": (_i32, [_vp]),
     "xc_release_workspace": (_i32, []),
     "xc_device_info": (_i32, [C.POINTER(_i32)]),
     "xc_launch_count": (_i64, []),
@@ -67,6 +68,11 @@ SIGNATURES = {
     "xc_copy_slices_to_matrix_c64": (_i32, [_vp, _i64, _i64, _i64, _i64, _i64, _vp, _i32, _vp]),
     "xc_multiply_slides_normalised_c64": (_i32, [_vp, _i32, _vp, _i64, _i64, _i64, C.c_double, _vp, _i32, _vp]),
     "xc_row_argmax_c64": (_i32, [_vp, _i64, _i64, _i32, _vp, _vp, _i32, _vp]),
+    "xc_dist_unique_id": (_i32, [_vp]),
+    "xc_dist_init": (_i32, [_i32, _i32, _vp]),
+    "xc_dist_allgather_peak": (_i32, [C.POINTER(xc_peak), C.POINTER(xc_peak), C.POINTER(_i32), _vp]),
+    "xc_dist_finalize": (_i32, []),
+    "xc_peak_argmax": (_i32, [C.POINTER(xc_peak), _i32]),
     "xc_find_local_maxima_f32": (_i32, [_vp, _i64, _f32, _vp, _i32, _vp, _i32, _i32, _vp]),
 }
 
@@ -168,12 +174,73 @@ def contiguous(x):
     return np.ascontiguousarray(x)
 
 
+PINNED_MIN_BYTES = 1 << 16
+
+
+def host_empty(shape, np_dtype):
+    """Host output buffer.  Large results come from torch's caching pinned-memory allocator (when a CUDA device
+    is there), so that the library's device-to-host copies run at PCIe speed and overlap the kernels of the
+    pipelined host path; small ones are plain numpy arrays."""
+    shape = tuple(int(v) for v in np.atleast_1d(shape))
+    nbytes = int(np.prod(shape, dtype=np.int64)) * np.dtype(np_dtype).itemsize
+    if nbytes >= PINNED_MIN_BYTES:
+        try:
+            import torch
+            if torch.cuda.is_available():
+                t = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+                return t.numpy().view(np_dtype).reshape(shape)      # keeps `t` alive through .base
+        except Exception:
+            pass
+    return np.empty(shape, dtype=np_dtype)
+
+
 def empty_like_space(ref, shape, np_dtype):
     """Output buffer in the memory space of `ref`."""
     if is_device(ref):
         import torch
         return torch.empty(shape, dtype=torch_dtype(np_dtype), device=ref.device)
-    return np.empty(shape, dtype=np_dtype)
+    return host_empty(shape, np_dtype)
+
+
+# ------------------------------------------------------------------------------------------------
+# foreign device arrays: anything that exposes __cuda_array_interface__ (CuPy, Numba, ...) is adopted
+# zero-copy as a torch tensor on the device that owns the pointer (cupyHelpers.py:80-83 requireCupyArray is
+# the reference's gate; the protocol, not a framework, is what a drop-in has to accept).  Results come back
+# as torch CUDA tensors, which expose the same protocol (cupy.asarray(t) / numba.cuda.as_cuda_array(t)).
+# ------------------------------------------------------------------------------------------------
+def adopt(x):
+    if x is None or isinstance(x, (np.ndarray, np.generic, int, float, complex, str, bool, list, tuple)) or is_torch(x):
+        return x
+    cai = getattr(x, "__cuda_array_interface__", None)
+    if cai is None:
+        return x
+    import torch
+    dev = load().xc_pointer_device(C.c_void_p(int(cai["data"][0]))) if cai["data"][0] else 0
+    if dev < 0:
+        raise TypeError("__cuda_array_interface__ object does not point to device memory")
+    return torch.as_tensor(x, device=torch.device("cuda", dev))
+
+
+def adopting(fn):
+    """Decorator of the public entry points: adopts foreign device arrays among the arguments."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapper(*args, **kwargs):
+        return fn(*[adopt(a) for a in args], **{k: adopt(v) for k, v in kwargs.items()})
+    return wrapper
+
+
+def adopt_module(namespace, names):
+    """Wraps the listed functions / the public methods of the listed classes of a module in `adopting`."""
+    for name in names:
+        obj = namespace[name]
+        if isinstance(obj, type):
+            for attr, val in list(vars(obj).items()):
+                if callable(val) and (not attr.startswith("_") or attr == "__init__"):
+                    setattr(obj, attr, adopting(val))
+        else:
+            namespace[name] = adopting(obj)
 
 
 def current_stream(ref):

@@ -27,50 +27,63 @@ int32_t fail(int32_t code, const char* fmt, ...) {
 }
 void count_launch(int n) { g_launches += n; }
 
-static bool g_prof_on = false, g_prof_valid = false;
-static cudaEvent_t g_prof_e0 = nullptr, g_prof_e1 = nullptr;
-void profile_begin(cudaStream_t st) {
-    if (!g_prof_on) return;
-    if (!g_prof_e0) {
-        cudaEventCreate(&g_prof_e0);
-        cudaEventCreate(&g_prof_e1);
-    }
-    cudaEventRecord(g_prof_e0, st);
-}
-void profile_end(cudaStream_t st) {
-    if (!g_prof_on) return;
-    cudaEventRecord(g_prof_e1, st);
-    g_prof_valid = true;
+std::recursive_mutex& api_mutex() {
+    static std::recursive_mutex m;
+    return m;
 }
 
-// ---- workspace -----------------------------------------------------------------------------------
+// ---- per-device state ----------------------------------------------------------------------------
 struct SlotBuf {
     void* ptr = nullptr;
     size_t bytes = 0;
 };
-static SlotBuf g_slots[SLOT_COUNT];
-static int g_sm_count = 0, g_smem_optin = 0, g_dev = -1;
+constexpr int PIPE_MAX = 16;      // chunks of the pipelined host path
+struct DeviceState {
+    SlotBuf slots[SLOT_COUNT];
+    int sm_count = 0, smem_optin = 0;
+    cudaEvent_t prof_e0 = nullptr, prof_e1 = nullptr;
+    bool prof_valid = false;
+    // host pipeline (XC_HOST frequency search): copy-in / copy-out streams and per-chunk events
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    cudaEvent_t ev_in[PIPE_MAX] = {}, ev_k[PIPE_MAX] = {};
+};
+static DeviceState g_devs[XC_MAX_DEVICES];
+static bool g_prof_on = false;
 
-static void refresh_device() {
+static DeviceState& dev_state() {
     int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess) return;
-    if (dev == g_dev && g_sm_count) return;
-    if (g_dev != -1 && dev != g_dev) release_workspace();
-    g_dev = dev;
-    cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
-    cudaDeviceGetAttribute(&g_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= XC_MAX_DEVICES) dev = 0;
+    DeviceState& d = g_devs[dev];
+    if (!d.sm_count) {
+        cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, dev);
+        cudaDeviceGetAttribute(&d.smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    }
+    return d;
 }
+
+void profile_begin(cudaStream_t st) {
+    if (!g_prof_on) return;
+    DeviceState& d = dev_state();
+    if (!d.prof_e0) {
+        cudaEventCreate(&d.prof_e0);
+        cudaEventCreate(&d.prof_e1);
+    }
+    cudaEventRecord(d.prof_e0, st);
+}
+void profile_end(cudaStream_t st) {
+    if (!g_prof_on) return;
+    DeviceState& d = dev_state();
+    cudaEventRecord(d.prof_e1, st);
+    d.prof_valid = true;
+}
+
 int sm_count() {
-    refresh_device();
-    return g_sm_count > 0 ? g_sm_count : 1;
+    const int n = dev_state().sm_count;
+    return n > 0 ? n : 1;
 }
-int max_smem_optin() {
-    refresh_device();
-    return g_smem_optin;
-}
+int max_smem_optin() { return dev_state().smem_optin; }
 void* workspace(Slot slot, size_t bytes) {
-    refresh_device();
-    SlotBuf& s = g_slots[slot];
+    SlotBuf& s = dev_state().slots[slot];
     if (bytes == 0) bytes = 256;
     if (s.bytes >= bytes) return s.ptr;
     if (s.ptr) {
@@ -96,11 +109,15 @@ void* workspace(Slot slot, size_t bytes) {
     s.bytes = want;
     return s.ptr;
 }
+void release_plan_caches();   // fastxcorr.cu: Bluestein / chirp-z plans of the current device
 int32_t release_workspace() {
+    DeviceState& d = dev_state();
+    cudaDeviceSynchronize();
     for (int i = 0; i < SLOT_COUNT; ++i) {
-        if (g_slots[i].ptr) cudaFree(g_slots[i].ptr);
-        g_slots[i] = SlotBuf();
+        if (d.slots[i].ptr) cudaFree(d.slots[i].ptr);
+        d.slots[i] = SlotBuf();
     }
+    release_plan_caches();
     return XC_OK;
 }
 
@@ -173,6 +190,9 @@ int32_t collect_peak(const float* d_qf2, const uint32_t* d_fidx, const int32_t* 
     return XC_OK;
 }
 
+static int32_t fastxcorr_host_pipelined(const float2* cutout, int32_t N, const float2* rx, int64_t rxlen, int64_t shift0,
+                                        int64_t K, float* qf2, uint32_t* fidx, xc_peak* peak, cudaStream_t st);
+
 }  // namespace xc
 
 using namespace xc;
@@ -182,6 +202,7 @@ extern "C" {
 int32_t xc_version(void) { return 100; }
 const char* xc_last_error(void) { return g_err; }
 int32_t xc_device_count(void) {
+    XC_API_GUARD;
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess) {
         cudaGetLastError();
@@ -190,12 +211,25 @@ int32_t xc_device_count(void) {
     return n;
 }
 int32_t xc_set_device(int32_t device) {
+    XC_API_GUARD;
     XC_TRY(require_device());
     XC_CUDA_TRY(cudaSetDevice(device));
     return XC_OK;
 }
-int32_t xc_release_workspace(void) { return release_workspace(); }
+int32_t xc_pointer_device(const void* p) {
+    cudaPointerAttributes a;
+    if (!p || cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return -1;
+    }
+    return (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) ? a.device : -1;
+}
+int32_t xc_release_workspace(void) {
+    XC_API_GUARD;
+    return release_workspace();
+}
 int32_t xc_device_info(int32_t* out4) {
+    XC_API_GUARD;
     if (!out4) return fail(XC_ERR_ARG, "out4 is NULL");
     XC_TRY(require_device());
     int dev = 0, clock = 0, major = 0, minor = 0;
@@ -211,19 +245,23 @@ int32_t xc_device_info(int32_t* out4) {
 }
 int64_t xc_launch_count(void) { return g_launches.load(); }
 int32_t xc_profile_enable(int32_t on) {
+    XC_API_GUARD;
     g_prof_on = on != 0;
-    g_prof_valid = false;
+    dev_state().prof_valid = false;
     return XC_OK;
 }
 double xc_profile_last_ms(void) {
-    if (!g_prof_valid) return -1.0;
-    if (cudaEventSynchronize(g_prof_e1) != cudaSuccess) return -1.0;
+    XC_API_GUARD;
+    DeviceState& d = dev_state();
+    if (!d.prof_valid) return -1.0;
+    if (cudaEventSynchronize(d.prof_e1) != cudaSuccess) return -1.0;
     float ms = 0.f;
-    if (cudaEventElapsedTime(&ms, g_prof_e0, g_prof_e1) != cudaSuccess) return -1.0;
+    if (cudaEventElapsedTime(&ms, d.prof_e0, d.prof_e1) != cudaSuccess) return -1.0;
     return (double)ms;
 }
 
 int32_t xc_sliding_energy_c64(const void* x, int64_t n, int32_t L, float* out, int32_t where, void* stream) {
+    XC_API_GUARD;
     XC_TRY(check_where(where));
     if (!x || !out) return fail(XC_ERR_ARG, "x/out is NULL");
     if (L < 1 || n < L) return fail(XC_ERR_ARG, "need 1 <= L <= n (L=%d, n=%lld)", L, (long long)n);
@@ -241,6 +279,7 @@ int32_t xc_sliding_energy_c64(const void* x, int64_t n, int32_t L, float* out, i
 
 int32_t xc_moving_average_f32(const float* x, int64_t n, int32_t L, int32_t sum_instead, float* out, int32_t where,
                               void* stream) {
+    XC_API_GUARD;
     XC_TRY(check_where(where));
     if (!x || !out) return fail(XC_ERR_ARG, "x/out is NULL");
     if (L < 1) return fail(XC_ERR_ARG, "avgLength must be >= 1");
@@ -257,6 +296,7 @@ int32_t xc_moving_average_f32(const float* x, int64_t n, int32_t L, int32_t sum_
 }
 
 int32_t xc_complex_magnsq_c64(const void* x, int64_t n, void* out, int32_t out_f64, int32_t where, void* stream) {
+    XC_API_GUARD;
     XC_TRY(check_where(where));
     if (!x || !out) return fail(XC_ERR_ARG, "x/out is NULL");
     if (n <= 0) return XC_OK;
@@ -292,18 +332,22 @@ static int32_t check_shift_args(int32_t N, int64_t rxlen, int64_t shift0, int64_
 int32_t xc_fastxcorr_c64(const void* cutout, int32_t N, const void* rx, int64_t rxlen, int64_t shift0, int64_t step,
                          int64_t K, const int64_t* shifts, int32_t freqsearch, int32_t flags, float* qf2,
                          uint32_t* fidx, void* cplx, xc_peak* peak, int32_t where, void* stream) {
+    XC_API_GUARD;
     XC_TRY(check_where(where));
     if (!cutout || !rx) return fail(XC_ERR_ARG, "cutout/rx is NULL");
     if (!qf2 && !cplx) return fail(XC_ERR_ARG, "qf2 and cplx are both NULL");
     XC_TRY(check_shift_args(N, rxlen, shift0, step, K, shifts, flags));
     if (freqsearch && !fastxcorr_fft_supported(N))
-        return fail(XC_ERR_UNSUPPORTED, "fused frequency search supports power-of-two cutout lengths up to 16384, got %d", N);
+        return fail(XC_ERR_UNSUPPORTED, "fused frequency search does not take a cutout of %d samples", N);
     XC_TRY(require_device());
     if (K == 0) {
         if (peak) { memset(peak, 0, sizeof(*peak)); peak->index = -1; }
         return XC_OK;
     }
     cudaStream_t st = (cudaStream_t)stream;
+    if (where == XC_HOST && freqsearch && !shifts && step == 1 && !cplx && K >= (1 << 17) && shift0 >= 0 &&
+        shift0 + K - 1 + N <= rxlen && fft_length_pow2(N))
+        return fastxcorr_host_pipelined((const float2*)cutout, N, (const float2*)rx, rxlen, shift0, K, qf2, fidx, peak, st);
     int32_t status = XC_OK;
     const float2* dc = (const float2*)stage_in(SLOT_IN0, cutout, sizeof(float2) * (size_t)N, where, st, &status);
     const float2* drx = (const float2*)stage_in(SLOT_IN1, rx, sizeof(float2) * (size_t)rxlen, where, st, &status);
@@ -329,14 +373,82 @@ int32_t xc_fastxcorr_c64(const void* cutout, int32_t N, const void* rx, int64_t 
     return finish(where, st);
 }
 
+}  // extern "C" (reopened below)
+
+namespace xc {
+// XC_HOST frequency search over a contiguous in-range shift list, pipelined: the shift range is cut into chunks and
+// H2D(rx part of chunk i + 1) | kernels(chunk i) | D2H(results of chunk i - 1) run on three streams, so that only the
+// first copy-in and the last copy-out are exposed (pinned caller buffers overlap fully; pageable ones are staged by
+// the driver and still copy while the previous chunk computes).  One cudaMemcpyAsync per chunk and direction.
+static int32_t ensure_pipe(DeviceState& d) {
+    if (d.s_in) return XC_OK;
+    XC_CUDA_TRY(cudaStreamCreateWithFlags(&d.s_in, cudaStreamNonBlocking));
+    XC_CUDA_TRY(cudaStreamCreateWithFlags(&d.s_out, cudaStreamNonBlocking));
+    for (int i = 0; i < PIPE_MAX; ++i) {
+        XC_CUDA_TRY(cudaEventCreateWithFlags(&d.ev_in[i], cudaEventDisableTiming));
+        XC_CUDA_TRY(cudaEventCreateWithFlags(&d.ev_k[i], cudaEventDisableTiming));
+    }
+    return XC_OK;
+}
+
+static int32_t fastxcorr_host_pipelined(const float2* cutout, int32_t N, const float2* rx, int64_t rxlen, int64_t shift0,
+                                        int64_t K, float* qf2, uint32_t* fidx, xc_peak* peak, cudaStream_t st) {
+    DeviceState& d = dev_state();
+    XC_TRY(ensure_pipe(d));
+    int nch = (int)(K >> 18);                    // about 2^18 shifts (2 ms of search at N = 8192) per chunk
+    if (nch < 2) nch = 2;
+    if (nch > PIPE_MAX) nch = PIPE_MAX;
+    float2* dc = (float2*)workspace(SLOT_IN0, sizeof(float2) * (size_t)N);
+    float2* drx = (float2*)workspace(SLOT_IN1, sizeof(float2) * (size_t)rxlen);
+    float* dq = (float*)workspace(SLOT_OUT0, sizeof(float) * (size_t)K);
+    uint32_t* df = (uint32_t*)workspace(SLOT_OUT1, sizeof(uint32_t) * (size_t)K);
+    if (!dc || !drx || !dq || !df) return XC_ERR_NOMEM;
+    // earlier work of the caller's stream may still read the staging slots
+    XC_CUDA_TRY(cudaEventRecord(d.ev_k[0], st));
+    XC_CUDA_TRY(cudaStreamWaitEvent(d.s_in, d.ev_k[0], 0));
+    XC_CUDA_TRY(cudaStreamWaitEvent(d.s_out, d.ev_k[0], 0));
+    XC_CUDA_TRY(cudaMemcpyAsync(dc, cutout, sizeof(float2) * (size_t)N, cudaMemcpyHostToDevice, d.s_in));
+    int64_t k0[PIPE_MAX + 1];
+    for (int c = 0; c <= nch; ++c) k0[c] = (K * c) / nch;
+    int64_t copied = shift0;                     // rx[shift0, copied) is on its way
+    for (int c = 0; c < nch; ++c) {
+        const int64_t need = shift0 + k0[c + 1] + N - 1;     // chunk c reads rx[shift0 + k0[c], need)
+        if (need > copied) {
+            XC_CUDA_TRY(cudaMemcpyAsync(drx + copied, rx + copied, sizeof(float2) * (size_t)(need - copied),
+                                        cudaMemcpyHostToDevice, d.s_in));
+            copied = need;
+        }
+        XC_CUDA_TRY(cudaEventRecord(d.ev_in[c], d.s_in));
+    }
+    for (int c = 0; c < nch; ++c) {
+        const int64_t kc = k0[c + 1] - k0[c];
+        if (kc <= 0) continue;
+        XC_CUDA_TRY(cudaStreamWaitEvent(st, d.ev_in[c], 0));
+        ShiftList sl{shift0 + k0[c], 1, kc, nullptr};
+        XC_TRY(fastxcorr_freq_device(dc, N, drx, rxlen, sl, dq + k0[c], df + k0[c], nullptr, nullptr, 0, st));
+        XC_CUDA_TRY(cudaEventRecord(d.ev_k[c], st));
+        XC_CUDA_TRY(cudaStreamWaitEvent(d.s_out, d.ev_k[c], 0));
+        if (qf2) XC_CUDA_TRY(cudaMemcpyAsync(qf2 + k0[c], dq + k0[c], sizeof(float) * (size_t)kc, cudaMemcpyDeviceToHost, d.s_out));
+        if (fidx) XC_CUDA_TRY(cudaMemcpyAsync(fidx + k0[c], df + k0[c], sizeof(uint32_t) * (size_t)kc, cudaMemcpyDeviceToHost, d.s_out));
+    }
+    if (peak) XC_TRY(collect_peak(dq, df, nullptr, K, shift0, 1, nullptr, peak, st));
+    XC_CUDA_TRY(cudaStreamSynchronize(d.s_out));
+    XC_CUDA_TRY(cudaStreamSynchronize(st));
+    return XC_OK;
+}
+}  // namespace xc
+
+extern "C" {
+
 int32_t xc_fastxcorr_caf_c64(const void* cutout, int32_t N, const void* rx, int64_t rxlen, int64_t shift0,
                              int64_t step, int64_t K, const int64_t* shifts, void* caf, int32_t complex_out,
                              int32_t where, void* stream) {
+    XC_API_GUARD;
     XC_TRY(check_where(where));
     if (!cutout || !rx || !caf) return fail(XC_ERR_ARG, "cutout/rx/caf is NULL");
     XC_TRY(check_shift_args(N, rxlen, shift0, step, K, shifts, 0));
     if (!fastxcorr_fft_supported(N))
-        return fail(XC_ERR_UNSUPPORTED, "fused frequency search supports power-of-two cutout lengths up to 16384, got %d", N);
+        return fail(XC_ERR_UNSUPPORTED, "fused frequency search does not take a cutout of %d samples", N);
     XC_TRY(require_device());
     if (K == 0) return XC_OK;
     cudaStream_t st = (cudaStream_t)stream;
@@ -356,6 +468,7 @@ int32_t xc_fastxcorr_caf_c64(const void* cutout, int32_t N, const void* rx, int6
 int32_t xc_cztxcorr_c64(const void* cutout, int32_t N, const void* rx, int64_t rxlen, int64_t shift0, int64_t step,
                         int64_t K, const int64_t* shifts, double f0_cycles, double df_cycles, int32_t nbins, float* qf2,
                         uint32_t* fidx, void* cplx, float* caf, int32_t where, void* stream) {
+    XC_API_GUARD;
     XC_TRY(check_where(where));
     if (!cutout || !rx) return fail(XC_ERR_ARG, "cutout/rx is NULL");
     if (!qf2 && !cplx && !caf) return fail(XC_ERR_ARG, "qf2, cplx and caf are all NULL");
@@ -407,6 +520,7 @@ __global__ void czt_unscale_kernel(float2* out, int64_t rows, int nbins, const f
 
 int32_t xc_czt_c64(const void* x, int32_t m, int64_t rows, double f0_cycles, double df_cycles, int32_t nbins, void* out,
                    int32_t where, void* stream) {
+    XC_API_GUARD;
     XC_TRY(check_where(where));
     if (!x || !out) return fail(XC_ERR_ARG, "x/out is NULL");
     if (m < 2 || nbins < 1 || rows < 0) return fail(XC_ERR_ARG, "need m >= 2, nbins >= 1, rows >= 0");
@@ -438,6 +552,7 @@ int32_t xc_czt_c64(const void* x, int32_t m, int64_t rows, double f0_cycles, dou
 
 int32_t xc_row_argmax_c64(const void* x, int64_t rows, int64_t cols, int32_t use_normsq, uint32_t* idx, float* val,
                           int32_t where, void* stream) {
+    XC_API_GUARD;
     XC_TRY(check_where(where));
     if (!x || !idx) return fail(XC_ERR_ARG, "x/idx is NULL");
     if (rows < 0 || cols < 1) return fail(XC_ERR_ARG, "need rows >= 0 and cols >= 1");
@@ -457,6 +572,7 @@ int32_t xc_row_argmax_c64(const void* x, int64_t rows, int64_t cols, int32_t use
 
 int32_t xc_find_local_maxima_f32(const float* x, int64_t n, float min_height, int32_t* idx, int32_t cap, int32_t* count,
                                  int32_t sorted, int32_t where, void* stream) {
+    XC_API_GUARD;
     (void)sorted;   // the compaction is ordered, so the result is always ascending
     XC_TRY(check_where(where));
     if (!x || !idx || !count) return fail(XC_ERR_ARG, "x/idx/count is NULL");

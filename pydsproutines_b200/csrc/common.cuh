@@ -6,6 +6,8 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "../../include/xcorr_b200.h"
 
 namespace xc {
@@ -45,9 +47,14 @@ void profile_end(cudaStream_t st);
         xc::count_launch();                                                                      \
     } while (0)
 
+// Every extern "C" entry takes this lock: the workspace slots, plan caches and profiling events are shared
+// process state, and ctypes releases the GIL around a call.  Recursive because entries call one another.
+std::recursive_mutex& api_mutex();
+#define XC_API_GUARD std::lock_guard<std::recursive_mutex> xc_api_guard_(xc::api_mutex())
+
 // ---------------------------------------------------------------------------------------------
-// device workspace: grow-only named slots, per process (one device per process is the model;
-// switching device releases the slots)
+// device workspace: grow-only named slots PER DEVICE (indexed by the current device); calls on one
+// device are serialised by the API lock and by stream order, see xcorr_b200.h "Threading"
 // ---------------------------------------------------------------------------------------------
 enum Slot {
     SLOT_IN0 = 0,  // staged inputs (host mode)

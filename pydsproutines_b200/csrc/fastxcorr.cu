@@ -170,6 +170,7 @@ static int bluestein_log2m(int N) {
 }
 
 // power-of-two lengths run the plain fused kernel; every other length 2 <= N <= 2^(MAX_LOG2N - 1) the Bluestein one
+bool fft_length_pow2(int N) { return fft_length_supported(N); }
 bool fastxcorr_fft_supported(int N) {
     if (fft_length_supported(N)) return true;
     return N >= 3 && bluestein_log2m(N) <= MAX_LOG2N;
@@ -243,7 +244,34 @@ struct BluePlan {
     float2* d_post = nullptr;       // [nbins]: exp(+i 2 pi w k^2 / 2); X[k] = conj(d_post[k] v) / M
 };
 // keyed by (device, length, bins, start frequency a, frequency step w) -- a, w in cycles per sample
-static std::map<std::tuple<int, int, int, double, double>, BluePlan> g_blue;
+typedef std::tuple<int, int, int, double, double> BlueKey;
+static std::map<BlueKey, BluePlan> g_blue;
+static std::vector<BlueKey> g_blue_order;         // insertion order: the cache keeps the BLUE_CACHE_MAX newest plans
+constexpr size_t BLUE_CACHE_MAX = 16;
+
+static void blue_free(BluePlan& p) {
+    if (p.d_b) cudaFree(p.d_b);
+    if (p.d_bhat_perm) cudaFree(p.d_bhat_perm);
+    if (p.d_post) cudaFree(p.d_post);
+    p = BluePlan();
+}
+// xc_release_workspace(): drops the plans of the current device (the device is idle: the caller synchronised)
+void release_plan_caches() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return;
+    for (auto it = g_blue.begin(); it != g_blue.end();) {
+        if (std::get<0>(it->first) == dev) {
+            blue_free(it->second);
+            it = g_blue.erase(it);
+        } else {
+            ++it;
+        }
+    }
+    std::vector<BlueKey> keep;
+    for (const BlueKey& k : g_blue_order)
+        if (std::get<0>(k) != dev) keep.push_back(k);
+    g_blue_order.swap(keep);
+}
 
 // exp(+i 2 pi (lin + w d^2 / 2)); the DFT case (w = 1/N) reduces d^2 modulo 2N exactly
 static cd chirp_phase(double lin_cycles, double w, long long d, int exact_n) {
@@ -341,6 +369,17 @@ static int32_t blue_plan_for(int N, const CztSpec* spec, const BluePlan** out) {
     XC_CUDA_TRY(cudaMemcpy(p.d_b, hb.data(), sizeof(float2) * M, cudaMemcpyHostToDevice));
     XC_CUDA_TRY(cudaMemcpy(p.d_bhat_perm, perm.data(), sizeof(float2) * M, cudaMemcpyHostToDevice));
     XC_CUDA_TRY(cudaMemcpy(p.d_post, post.data(), sizeof(float2) * nbins, cudaMemcpyHostToDevice));
+    if (g_blue_order.size() >= BLUE_CACHE_MAX) {
+        // callers that move the chirp-z window per detection would otherwise grow the cache without bound
+        cudaDeviceSynchronize();              // the oldest plan may still be read by enqueued kernels
+        auto old = g_blue.find(g_blue_order.front());
+        if (old != g_blue.end()) {
+            blue_free(old->second);
+            g_blue.erase(old);
+        }
+        g_blue_order.erase(g_blue_order.begin());
+    }
+    g_blue_order.push_back(key);
     *out = &(g_blue[key] = p);
     return XC_OK;
 }

@@ -216,6 +216,7 @@ extern "C" {
 
 int32_t xc_fine_freq_c128(const void* x, const void* y, int64_t N, const double* freq_cycles, int64_t NF, void* pp,
                           int64_t* best, int32_t where, void* stream) {
+    XC_API_GUARD;
     if (where != XC_HOST && where != XC_DEVICE) return fail(XC_ERR_ARG, "where must be XC_HOST (0) or XC_DEVICE (1)");
     if (!x || !y || !freq_cycles || !pp) return fail(XC_ERR_ARG, "NULL argument");
     if (N < 1 || NF < 1 || NF > (int64_t(1) << 30)) return fail(XC_ERR_ARG, "need at least one sample and one frequency");
@@ -260,6 +261,7 @@ int32_t xc_fine_freq_c128(const void* x, const void* y, int64_t N, const double*
 int32_t xc_time_scan_c128(const void* x, const void* y, int64_t N, double shift_cycles, const double* td, int64_t NT,
                           double fs, const double* freq_bounds, const void* steeringvec, void* cost, int64_t* best,
                           int32_t where, void* stream) {
+    XC_API_GUARD;
     if (where != XC_HOST && where != XC_DEVICE) return fail(XC_ERR_ARG, "where must be XC_HOST (0) or XC_DEVICE (1)");
     if (!x || !y || !cost || (!td && !steeringvec)) return fail(XC_ERR_ARG, "NULL argument");
     if (N < 1 || NT < 1 || NT > (int64_t(1) << 30)) return fail(XC_ERR_ARG, "need at least one sample and one time offset");

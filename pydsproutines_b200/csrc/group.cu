@@ -335,6 +335,7 @@ extern "C" {
 
 int32_t xc_group_create(const void* ygroups, int32_t G, int32_t L, const int64_t* starts, int32_t F, int32_t auto_conj,
                         xc_group** handle) {
+    XC_API_GUARD;
     if (!ygroups || !starts || !handle) return fail(XC_ERR_ARG, "ygroups/starts/handle is NULL");
     if (G < 1 || L < 1) return fail(XC_ERR_ARG, "need at least one group of at least one sample");
     if (F < L) return fail(XC_ERR_ARG, "INVALID_FFTLEN: fftlen %d is shorter than the group length %d", F, L);   // GroupXcorrFFT.cpp:11-14
@@ -401,6 +402,7 @@ int32_t xc_group_create(const void* ygroups, int32_t G, int32_t L, const int64_t
 }
 
 int32_t xc_group_destroy(xc_group* h) {
+    XC_API_GUARD;
     if (!h) return XC_OK;
     cudaFree(h->d_ell_y);
     cudaFree(h->d_ell_off);
@@ -415,6 +417,7 @@ int32_t xc_group_destroy(xc_group* h) {
 int32_t xc_group_xcorr(xc_group* h, const void* rx, int64_t rxlen, int64_t shift0, int64_t step, int64_t K,
                        const int64_t* shifts, float* qf2, uint32_t* fidx, float* caf, xc_peak* peak, int32_t where,
                        void* stream) {
+    XC_API_GUARD;
     if (where != XC_HOST && where != XC_DEVICE) return fail(XC_ERR_ARG, "where must be XC_HOST (0) or XC_DEVICE (1)");
     if (!h || !rx) return fail(XC_ERR_ARG, "handle/rx is NULL");
     if (!qf2 && !caf) return fail(XC_ERR_ARG, "qf2 and caf are both NULL");

@@ -76,6 +76,7 @@ extern "C" {
 int32_t xc_groupperm_combine(const void* surfaces, int64_t K, int32_t NB, const int32_t* template_idx,
                              const int32_t* group_idx, int32_t G, const float* rxnormsq, double ynormsq, float* caf,
                              void* stream) {
+    XC_API_GUARD;
     if (!surfaces || !template_idx || !group_idx || !rxnormsq || !caf) return fail(XC_ERR_ARG, "NULL argument");
     if (K < 0 || NB < 1 || G < 1 || G > 4096) return fail(XC_ERR_ARG, "bad sizes");
     if (!(ynormsq > 0.0)) return fail(XC_ERR_ARG, "template energy must be positive");
@@ -100,6 +101,7 @@ int32_t xc_groupperm_combine(const void* surfaces, int64_t K, int32_t NB, const 
 }
 
 int32_t xc_groupfreq_destroy(xc_groupfreq* h) {
+    XC_API_GUARD;
     if (!h) return XC_OK;
     mt_tc_release(&h->tc);
     cudaFree(h->d_templates);
@@ -112,6 +114,7 @@ int32_t xc_groupfreq_destroy(xc_groupfreq* h) {
 int32_t xc_groupfreq_create(const void* ycat, const int64_t* starts, const int32_t* lengths, int32_t G,
                             const double* freq_cycles, const double* start_freq_cycles, int32_t NF, int32_t conj,
                             xc_groupfreq** handle) {
+    XC_API_GUARD;
     if (!ycat || !starts || !lengths || !freq_cycles || !handle) return fail(XC_ERR_ARG, "NULL argument");
     if (G < 1 || NF < 1) return fail(XC_ERR_ARG, "need at least one group and one frequency");
     int ndev = 0;
@@ -219,6 +222,7 @@ int32_t xc_groupfreq_create(const void* ycat, const int64_t* starts, const int32
 
 int32_t xc_groupfreq_xcorr(xc_groupfreq* h, const void* rx, int64_t rxlen, int64_t shift0, int64_t K, float* qf2,
                            uint32_t* fidx, float* caf, void* cplx, xc_peak* peak, int32_t where, void* stream) {
+    XC_API_GUARD;
     if (where != XC_HOST && where != XC_DEVICE) return fail(XC_ERR_ARG, "where must be XC_HOST (0) or XC_DEVICE (1)");
     if (!h || !rx) return fail(XC_ERR_ARG, "handle/rx is NULL");
     if (K < 0 || shift0 < 0) return fail(XC_ERR_RANGE, "shifts must be >= 0");

@@ -97,6 +97,7 @@ static int32_t helpers_require_device() {
 extern "C" {
 
 int32_t xc_convert_i16_c64(const int16_t* iq, int64_t nsamp, void* out, int32_t where_in, int32_t where_out, void* stream) {
+    XC_API_GUARD;
     if ((where_in != XC_HOST && where_in != XC_DEVICE) || (where_out != XC_HOST && where_out != XC_DEVICE))
         return fail(XC_ERR_ARG, "where must be XC_HOST (0) or XC_DEVICE (1)");
     if (!iq || !out) return fail(XC_ERR_ARG, "iq/out is NULL");
@@ -133,6 +134,7 @@ int32_t xc_convert_i16_c64(const int16_t* iq, int64_t nsamp, void* out, int32_t 
 
 int32_t xc_copy_groups_c64(const void* x, int64_t xlen, void* y, int64_t ylen, const int32_t* x_starts,
                            const int32_t* y_starts, const int32_t* lengths, int32_t G, int32_t where, void* stream) {
+    XC_API_GUARD;
     if (where != XC_HOST && where != XC_DEVICE) return fail(XC_ERR_ARG, "where must be XC_HOST (0) or XC_DEVICE (1)");
     if (!x || !y || !x_starts || !y_starts || !lengths) return fail(XC_ERR_ARG, "NULL argument");
     if (G < 0 || xlen < 0 || ylen < 0) return fail(XC_ERR_ARG, "negative size");
@@ -165,6 +167,7 @@ int32_t xc_copy_groups_c64(const void* x, int64_t xlen, void* y, int64_t ylen, c
 
 int32_t xc_copy_slices_to_matrix_c64(const void* x, int64_t xlen, int64_t start, int64_t increment, int64_t row_length,
                                      int64_t num_rows, void* out, int32_t where, void* stream) {
+    XC_API_GUARD;
     if (where != XC_HOST && where != XC_DEVICE) return fail(XC_ERR_ARG, "where must be XC_HOST (0) or XC_DEVICE (1)");
     if (!x || !out) return fail(XC_ERR_ARG, "x/out is NULL");
     if (xlen < 0 || row_length < 0 || num_rows < 0) return fail(XC_ERR_ARG, "negative size");
@@ -195,6 +198,7 @@ int32_t xc_copy_slices_to_matrix_c64(const void* x, int64_t xlen, int64_t start,
 
 int32_t xc_multiply_slides_normalised_c64(const void* x, int32_t xlen, const void* y, int64_t ylen, int64_t start,
                                           int64_t idxlen, double coefficient, void* out, int32_t where, void* stream) {
+    XC_API_GUARD;
     if (where != XC_HOST && where != XC_DEVICE) return fail(XC_ERR_ARG, "where must be XC_HOST (0) or XC_DEVICE (1)");
     if (!x || !y || !out) return fail(XC_ERR_ARG, "x/y/out is NULL");
     if (xlen < 1) return fail(XC_ERR_ARG, "the template needs at least one sample");

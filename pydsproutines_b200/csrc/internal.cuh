@@ -19,6 +19,7 @@ struct ShiftList {
     const int64_t* shifts;   // device pointer or NULL
 };
 bool fastxcorr_fft_supported(int N);
+bool fft_length_pow2(int N);   // a power of two with a block-FFT plan
 // chirp-z frequency grid: bins k < nbins at (a_cycles + k * w_cycles) cycles per sample
 struct CztSpec {
     int nbins;

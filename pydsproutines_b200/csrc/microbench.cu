@@ -26,6 +26,7 @@ __global__ void __launch_bounds__(256) ffma_kernel(float* out, int iters, float 
 using namespace xc;
 
 extern "C" int32_t xc_measure_fp32_tflops(double ms, double* tflops) {
+    XC_API_GUARD;
     if (!tflops) return fail(XC_ERR_ARG, "tflops is NULL");
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {

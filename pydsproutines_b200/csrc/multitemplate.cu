@@ -147,6 +147,7 @@ using namespace xc;
 extern "C" {
 
 int32_t xc_mt_create(const void* templates, int32_t T, int32_t L, int32_t conj, const float* energies, xc_mt** handle) {
+    XC_API_GUARD;
     if (!templates || !handle) return fail(XC_ERR_ARG, "templates/handle is NULL");
     if (T < 1 || L < 1) return fail(XC_ERR_ARG, "need at least one template of at least one sample");
     int ndev = 0;
@@ -194,6 +195,7 @@ int32_t xc_mt_create(const void* templates, int32_t T, int32_t L, int32_t conj, 
 }
 
 int32_t xc_mt_destroy(xc_mt* h) {
+    XC_API_GUARD;
     if (!h) return XC_OK;
     mt_tc_release(&h->tc);
     cudaFree(h->d_templates);
@@ -206,6 +208,7 @@ int32_t xc_mt_uses_tensor_cores(const xc_mt* h) { return (h && h->tc.usable) ? 1
 
 int32_t xc_mt_correlate(xc_mt* h, const void* x, int64_t xlen, int64_t start, int64_t K, float* best, int32_t* tidx,
                         void* full, int32_t sqrt_out, xc_peak* peak, int32_t where, void* stream) {
+    XC_API_GUARD;
     if (where != XC_HOST && where != XC_DEVICE) return fail(XC_ERR_ARG, "where must be XC_HOST (0) or XC_DEVICE (1)");
     if (!h || !x) return fail(XC_ERR_ARG, "handle/x is NULL");
     if (start < 0) return fail(XC_ERR_RANGE, "startIdx should be >= 0.");                                   // cupyExtensions.py:584-586

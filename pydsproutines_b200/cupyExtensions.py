@@ -155,3 +155,6 @@ def multiplySlidesNormalised(d_x, d_y, startIdx, idxlen, THREADS_PER_BLOCK=128, 
                                                         int(startIdx), int(idxlen), coef, _lib.ptr(out),
                                                         _lib.where_of(d_x, d_y), _lib.current_stream(d_y)))
     return out
+
+
+_lib.adopt_module(globals(), ['cupyComplexMagnSq', 'cupyArgmaxAbsRows_complex64', 'multiTemplateSlidingDotProduct', 'cupyFindLocalMaxima', 'cupyCopyGroups32fc', 'cupyCopyIncrementalEqualSlicesToMatrix_32fc', 'multiplySlidesNormalised'])

@@ -37,3 +37,6 @@ def slidingEnergy(x, L):
     check(_lib.load().xc_sliding_energy_c64(_lib.ptr(x), n, int(L), _lib.ptr(out), _lib.where_of(x),
                                             _lib.current_stream(x)))
     return out
+
+
+_lib.adopt_module(globals(), ['cupyMovingAverage', 'slidingEnergy'])

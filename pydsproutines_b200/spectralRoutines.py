@@ -59,3 +59,6 @@ class CZTCached:
 
 
 CZTCachedGPU = CZTCached
+
+
+_lib.adopt_module(globals(), ['CZTCached'])

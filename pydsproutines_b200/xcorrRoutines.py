@@ -944,3 +944,6 @@ class TemplateCrossCorrelator:
             import torch
             return best, tidx.to(torch.int64)
         return best, tidx.astype(np.int64)                                               # cp.argmax dtype (:367)
+
+
+_lib.adopt_module(globals(), ['fastXcorr', 'cztXcorr', 'fastXcorrPeak', 'cp_fastXcorr', 'cp_fastXcorr_v2', 'CyIppXcorrFFT', 'GroupXcorrFFT', 'GroupXcorr', 'GroupXcorrGPU', 'GroupXcorrCZT', 'GroupXcorrCZT_Permutations', 'CyGroupXcorrFFT', 'TemplateCrossCorrelator', 'fineFreqTimeSearch', 'GenXcorr', 'calcQF2'])
