@@ -1,19 +1,25 @@
 #!/usr/bin/env python
 """bench.py -- CAF cells/s of the fused frequency-search fastXcorr on B200 (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1|c3|c4]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1|c3|c4|c6]
 
 A "step" is one pass of the hot path over one synthetic batch:
-  N = 1 : BASELINE.json configs[1] (C2): 8192-sample cutout, 2^20 shifts, 8192-bin FFT per shift.
-  N > 1 : configs[4] (C5) scaled weakly: every rank searches 2^23 shifts of a shard (block + 8191-sample
-          halo) of one N*2^23-sample record, so N = 8 is exactly the 2^26-sample C5 record; the only
-          exchange is the allgather of the per-rank peak tuples (NCCL).
-`value` = cells (shifts x bins) of all ranks / device time with inputs resident in HBM (CUDA events,
-max over ranks); `e2e` = the same through the public API with pinned HOST buffers (H2D + D2H inside).
-The reference arm (`--impl reference`) times the CPU restatement of the reference's numpy/scipy path
-(oracle/) on all host cores on a bounded sample of the same workload.
+  N = 1 : BASELINE.json configs[1] (C2): 8192-sample cutout, 2^20 shifts, 8192-bin FFT per shift (the headline).
+          The line also carries `configs`: device-timed C1, C3, C4 (and C6) with their own rooflines, and
+          `config.strong`: the 2^26-sample C5 record on this one GPU.
+  N > 1 : configs[4] (C5) sharded by shift range.  `value` is the weak line (every rank searches 2^23 shifts of a
+          shard = block + 8191-sample halo of one N*2^23-sample record, so N = 8 is exactly the 2^26-sample C5 record);
+          `config.strong` is the FIXED 2^26-sample record split N ways.  A half-amplitude decoy sits in rank 0's
+          block, the only exchange is the allgather of the per-rank peak tuples (NCCL), every rank checks one 256-shift
+          window of its results against the oracle outside the timed region.
+`value` = cells (shifts x bins) of all ranks / device time with inputs resident in HBM (CUDA events, max over ranks);
+`e2e` = the same through the public API with pinned HOST buffers (H2D + D2H inside the timed region).
+`--workload` makes another config the headline of a single-GPU run (its own metric unit stays cells/s).
+The reference arm (`--impl reference`) times the CPU restatement of the reference's numpy/scipy path (oracle/) on all
+host cores on a bounded sample of the same workload.
 """
 import argparse
+import ctypes
 import json
 import os
 import subprocess
@@ -30,12 +36,16 @@ METRIC = "caf_cells_per_sec"
 UNIT = "cells/s"
 N_CUT = 8192
 K_C2 = 1 << 20
-K_RANK_MULTI = 1 << 23
+K_RANK_WEAK = 1 << 23
+LOG2_C5 = 26
 ALGO_BYTES_PER_SHIFT = 16.0        # one new rx sample (8 B) + one result (f32 qf2 + u32 bin)
-# dram__bytes_read.sum + dram__bytes_write.sum of one C2 launch of fused_fft_staged_kernel<8192>, from the ncu --set full
-# capture summarised in profiles/r1_c2_staged_ncu.md (12.89 MB read, 0 written: the 8 MB of results stay in L2)
-NCU_DRAM_BYTES_C2 = 12.89e6
 FLOPS_PER_CELL = 75.0              # 5*log2(8192) + 10
+# dram__bytes_read.sum + dram__bytes_write.sum of one C2 launch of fused_fft_pp_kernel, from this round's
+# `ncu --set full` capture of this very command (profiles/r2_c2_pp_ncu.md): 12.78 MB read, 0 written (the 8 MB of
+# results stay in the 126 MB L2)
+NCU_DRAM_BYTES_C2 = 12.78e6
+NCU_TRAFFIC_SOURCE = "profiles/r2_c2_pp_ncu.md (ncu --set full of this command, per launch)"
+FP32_NOMINAL_TFLOPS = 74.4         # 148 SMs x 128 lanes x 2 x 1.965 GHz
 
 
 def measured_peaks():
@@ -43,8 +53,9 @@ def measured_peaks():
     if os.path.isfile(p):
         with open(p) as f:
             d = json.load(f)
-        return float(d.get("hbm_gbs", 6650.0)), "measured"
-    return 6650.0, "fallback"
+        d["_source"] = "measured"
+        return d
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "_source": "fallback"}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -56,19 +67,26 @@ def noise_block(seed, b, n):
     return (np.float32(np.sqrt(0.5)) * w).view(np.complex64)
 
 
-def make_shard(seed, rank, world, k_rank, N, p0, k0):
-    """rx[rank*k_rank : (rank+1)*k_rank + N - 1] of the global record + the QPSK cutout."""
+NOISE_BLOCK = 1 << 22      # samples per seeded noise block of the sharded record
+
+
+def record_slice(seed, first, n, N, plants):
+    """rx[first : first + n] of the global record (noise in seeded 2^22-sample blocks + the planted copies of the
+    cutout: (position, amplitude, bin) each) and the QPSK cutout.  Every rank builds only its own slice."""
     from pydsproutines_b200 import signals
     cutout = signals.qpsk(np.random.default_rng([seed, 10 ** 6]), N)
-    first = rank * k_rank
-    a = noise_block(seed, rank, k_rank)
-    b = noise_block(seed, rank + 1, k_rank)[:N - 1]
-    rx = np.concatenate((a, b))
-    lo, hi = max(p0, first), min(p0 + N, first + rx.size)
-    if hi > lo:
-        planted = cutout * signals.tone(N, k0, N)
-        rx[lo - first:hi - first] += planted[lo - p0:hi - p0]
-    return cutout, rx, first
+    rx = np.empty(n, np.complex64)
+    b0, b1 = first // NOISE_BLOCK, (first + n - 1) // NOISE_BLOCK
+    for b in range(b0, b1 + 1):
+        blk = noise_block(seed, b, NOISE_BLOCK)
+        lo, hi = max(first, b * NOISE_BLOCK), min(first + n, (b + 1) * NOISE_BLOCK)
+        rx[lo - first:hi - first] = blk[lo - b * NOISE_BLOCK:hi - b * NOISE_BLOCK]
+    for pos, amp, k in plants:
+        lo, hi = max(pos, first), min(pos + N, first + n)
+        if hi > lo:
+            planted = np.complex64(amp) * cutout * signals.tone(N, k, N)
+            rx[lo - first:hi - first] += planted[lo - pos:hi - pos]
+    return cutout, rx
 
 
 class ClockSampler:
@@ -152,6 +170,11 @@ def cpu_time_sample(n_shifts, procs):
     return per * procs * N_CUT / wall, per * procs
 
 
+CPU_NOTE = ("oracle/xcorr_oracle.fastXcorr = the reference's per-shift numpy + scipy.fft loop (xcorrRoutines.py:511-531), "
+            "bit-identical to it on the golden vectors; conj(cutout) is hoisted out of the loop (the reference "
+            "recomputes it per shift), which favours the CPU arm")
+
+
 def run_reference(args, rank):
     if rank != 0:
         return
@@ -168,10 +191,11 @@ def run_reference(args, rank):
             "warmup": args.warmup, "ms_per_step": 1e3 * sample * N_CUT / value, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
             "config": {"workload": "C2 fastXcorr freqsearch: 8192-sample cutout, 8192-bin FFT per shift "
-                                   "(bounded sample of the 2^20 shifts)", "cutout": N_CUT, "shifts_per_step": sample},
+                                   "(bounded sample of the 2^20 shifts)", "cutout": N_CUT, "shifts_per_step": sample,
+                       "host_cores": cores},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": procs, "kind": "port",
-                             "sample": "%d shifts per step split over %d processes (oracle/xcorr_oracle.fastXcorr, "
-                                       "numpy+scipy.fft, the reference's own per-shift loop)" % (sample, procs)},
+                             "sample": "%d shifts per step split over %d processes of %d host cores; %s"
+                                       % (sample, procs, cores, CPU_NOTE)},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -180,11 +204,222 @@ def run_reference(args, rank):
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
+def event_times(fn, steps, warmup, flush=None):
+    """Per-step CUDA-event times (ms) of fn() on torch's current stream (the stream the library enqueues on)."""
+    import torch
+    for _ in range(warmup):
+        if flush is not None:
+            flush.zero_()
+        fn()
+    torch.cuda.synchronize()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for a, b in ev:
+        if flush is not None:
+            flush.zero_()
+        a.record()
+        fn()
+        b.record()
+    torch.cuda.synchronize()
+    return [a.elapsed_time(b) for a, b in ev]
+
+
+def fp32_peak(lib):
+    tf = ctypes.c_double(0.0)
+    if lib.xc_measure_fp32_tflops(300.0, tf) == 0 and tf.value > 0:
+        return tf.value, "measured (register-resident FFMA loop, xc_measure_fp32_tflops)"
+    return FP32_NOMINAL_TFLOPS, "nominal 148 x 128 x 2 x 1.965 GHz"
+
+
+def fp32_roofline(flops, ms, peak, src, kernel, hbm_bytes, peaks, traffic=None, traffic_source=None):
+    ach = flops / (ms * 1e-3) / 1e12
+    hbm = hbm_bytes / (ms * 1e-3) / 1e9
+    return {"bound": "fp32", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "peak_source": src,
+            "frac_of_nominal_74.4": ach / FP32_NOMINAL_TFLOPS, "kernel": kernel, "kernel_ms": ms,
+            "algorithmic_flops_per_launch": flops, "traffic": traffic, "traffic_source": traffic_source,
+            "hbm": {"achieved": hbm, "peak": float(peaks["hbm_gbs"]), "unit": "GB/s", "frac": hbm / float(peaks["hbm_gbs"]),
+                    "algorithmic_bytes_per_launch": hbm_bytes, "peak_source": peaks["_source"],
+                    "note": "SURVEY.md 8d: the path is FP32 bound, the HBM fraction is ~1e-4 by construction"}}
+
+
+def config_line(which, lib, peaks, p32, p32src, steps):
+    """Device-timed line of one non-headline config (inputs resident in HBM, answer checked)."""
+    import torch
+    from pydsproutines_b200 import signals
+    from pydsproutines_b200 import xcorrRoutines as xr
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    lib.xc_profile_enable(0)
+    if which == "c1":
+        c = signals.config_c1()
+        cu, rx = dev(c["cutout"]), dev(c["rx"])
+        K = c["rx"].size - 4096 + 1
+        sh = xr._Shifts(None, rx.shape[0], 4096, rx)
+        q = xr._fastxcorr_call(cu, rx, sh, False)[0]
+        assert int(torch.argmax(q)) == c["p0"], "C1 lost the planted peak"
+        ms = float(np.median(event_times(lambda: xr._fastxcorr_call(cu, rx, sh, False), steps, 2, flush)))
+        flops = K * (8.0 * 4096 + 10)
+        return {"workload": "C1 fastXcorr no freqsearch: 4096-sample cutout, 2^20-sample rx, step 1", "ms": ms,
+                "cells_per_s": K / (ms * 1e-3), "peak_checked": [c["p0"]],
+                "roofline": fp32_roofline(flops, ms, p32, p32src, "nofreq_tiled_kernel", 16.0 * K, peaks)}
+    if which == "c3":
+        c = signals.config_c3()
+        obj = xr.GroupXcorrFFT(c["ygroups"], c["starts"], 1, fftlen=c["F"])
+        rx = dev(c["rx"])
+        shl = xr._group_shifts(np.arange(c["K"]), rx)
+        q, f = obj._handle.run(rx, shl, True, False)[:2]
+        p = int(torch.argmax(q))
+        assert p == c["p0"] and int(f[p]) == c["k0"], "C3 lost the planted peak"
+        ms = float(np.median(event_times(lambda: obj._handle.run(rx, shl, True, False), steps, 2, flush)))
+        flops = c["K"] * c["F"] * 80.0
+        return {"workload": "C3 GroupXcorrFFT: 64 groups x 128, fftlen 4096, 2^22 shifts", "ms": ms,
+                "cells_per_s": c["K"] * c["F"] / (ms * 1e-3), "peak_checked": [c["p0"], c["k0"]],
+                "roofline": fp32_roofline(flops, ms, p32, p32src, "group search kernel", 16.0 * c["K"], peaks)}
+    if which in ("c4", "c6"):
+        if which == "c4":
+            c = signals.config_c4()
+            h = xr._MtHandle(c["templates"].conj(), False)
+            x = dev(c["x"])
+            best, tidx = h.run(x, 0, c["K"], True, False, False)[:2]
+            for pos, t, _ in c["plants"]:
+                assert int(tidx[pos]) == t, "C4 lost a planted template"
+            ms = float(np.median(event_times(lambda: h.run(x, 0, c["K"], True, False, False), steps, 1, flush)))
+            cells, flops, passes = c["K"] * 256, c["K"] * 256 * 8.0 * 1024, 2
+            name = "C4 multi-template: 256 templates x 1024 vs 2^24 samples"
+            checked = [list(p[:2]) for p in c["plants"]]
+            tcores = bool(h.uses_tensor_cores)
+        else:
+            c = signals.config_c3(log2_shifts=20)
+            NFQ = 256
+            freqs = (np.arange(NFQ) - NFQ // 2) * (1.0 / 65536.0)
+            y = np.zeros(int(c["starts"][-1]) + 128, np.complex64)
+            for g in range(64):
+                y[int(c["starts"][g]):int(c["starts"][g]) + 128] = c["ygroups"][g]
+            h = xr.GroupXcorr(y, c["starts"], np.full(64, 128), freqs, 1.0)._handle
+            x = dev(c["rx"])
+            ms = float(np.median(event_times(lambda: h.run(x, 0, c["K"], True, False), steps, 1, flush)))
+            cells, flops, passes = c["K"] * NFQ, c["K"] * NFQ * 8.0 * 64 * 128, 3
+            name = "C6 GroupXcorr (frequency list, SURVEY 8f): 64 groups x 128, 256 frequencies, 2^20 shifts"
+            checked, tcores = None, True
+        peak = float(peaks.get("bf16_tflops", 1590.0))
+        ach = passes * flops / (ms * 1e-3) / 1e12
+        return {"workload": name, "ms": ms, "cells_per_s": cells / (ms * 1e-3), "peak_checked": checked,
+                "tensor_cores": tcores,
+                "roofline": {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                             "peak_source": peaks["_source"] + " (cuBLAS bf16 burst)", "precision_passes": passes,
+                             "algorithmic_frac": flops / (ms * 1e-3) / 1e12 / peak, "kernel": "mt_tc_kernel",
+                             "kernel_ms": ms, "traffic": None}}
+    raise SystemExit("unknown workload %r" % which)
+
+
+def sharded_search(world, rank, dev, k_rank, seed, plants, expect, steps, warmup, lib, flush, host_pass):
+    """One sharded run: every rank searches k_rank shifts of its slice (block + halo) of the record; peak allgather.
+    Returns dict(ms (max over ranks), e2e_ms, launches, kern_ms, h2d, d2h, oracle window result)."""
+    import torch
+    import torch.distributed as dist
+    from pydsproutines_b200 import dist as xdist
+    from pydsproutines_b200 import xcorrRoutines as xr
+    first = rank * k_rank
+    cutout, rx = record_slice(seed, first, k_rank + N_CUT - 1, N_CUT, plants)
+    cutout_d, rx_d = torch.from_numpy(cutout).to(dev), torch.from_numpy(rx).to(dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_device():
+        qf2, fidx, peak = xr.fastXcorrPeak(cutout_d, rx_d, freqsearch=True)
+        row = xdist.peak_to_row(peak.qf2, peak.fidx, first + peak.shift, 0, rank)
+        return qf2, fidx, peak, xdist.global_peak(xdist.allgather_peak(row, dev))
+
+    for _ in range(max(warmup, 1)):
+        flush.zero_()
+        qf2, fidx, lpeak, gp = step_device()
+    assert gp["shift"] == expect[0] and gp["fidx"] == expect[1], "wrong global peak: %r (expected %r)" % (gp, expect)
+    out = {"global_peak": [gp["shift"], gp["fidx"], gp["rank"]]}
+    # a decoy planted in this rank's block must be this rank's LOCAL peak unless the true peak is here too
+    found = -1
+    for pos, amp, k in plants[1:]:
+        if first <= pos < first + k_rank and not (first <= expect[0] < first + k_rank):
+            assert first + lpeak.shift == pos and lpeak.fidx == k, "rank %d did not find its decoy" % rank
+            found = rank
+    # one 256-shift window of this rank's results against the oracle (outside the timed region)
+    from oracle import xcorr_oracle as orc
+    w0 = (k_rank // 3) & ~255
+    pk = expect[0] - first
+    if 0 <= pk < k_rank:
+        w0 = max(0, min(k_rank - 256, pk - 128))
+    qo, fo = orc.fastXcorr(cutout, rx[w0:w0 + 256 + N_CUT - 1], freqsearch=True)
+    qg, fg = qf2[w0:w0 + 256].cpu().numpy(), fidx[w0:w0 + 256].cpu().numpy().astype(np.uint32)
+    assert np.allclose(qg, qo, rtol=1e-4, atol=1e-7), "rank %d: QF2 window differs from the oracle" % rank
+    bad = np.nonzero(fg != fo)[0]
+    for i in bad:       # a differing bin must be a float32 near-tie of the float64 spectrum
+        X = np.fft.fft(rx[w0 + i:w0 + i + N_CUT].astype(np.complex128) * np.conj(cutout).astype(np.complex128))
+        a, b = abs(X[fg[i]]) ** 2, abs(X[fo[i]]) ** 2
+        assert abs(a - b) <= 1e-5 * max(a, b), "rank %d: bin differs from the oracle at shift %d" % (rank, first + w0 + i)
+    out["oracle_window"] = {"rank": rank, "first_shift": first + w0, "shifts": 256, "bins_differing_near_ties": int(bad.size)}
+    if world > 1:       # which rank saw the decoy as its local peak (max over ranks; -1 = none)
+        t = torch.tensor([found], dtype=torch.int64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        found = int(t.item())
+    out["decoy_found_by_rank"] = found if found >= 0 else None
+
+    lib.xc_profile_enable(1)
+    barrier()
+    launches0 = lib.xc_launch_count()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    kern_ms = []
+    for i in range(steps):
+        flush.zero_()
+        ev[i][0].record()
+        step_device()
+        ev[i][1].record()
+        kern_ms.append(lib.xc_profile_last_ms())
+    barrier()
+    out["launches"] = int(lib.xc_launch_count() - launches0)
+    lib.xc_profile_enable(0)
+    ms_total = sum(a.elapsed_time(b) for a, b in ev)
+    if world > 1:
+        t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    out["ms"] = ms_total / steps
+    out["kern_ms"] = float(np.mean([k for k in kern_ms if k > 0])) if any(k > 0 for k in kern_ms) else out["ms"]
+    if host_pass:
+        cutout_h = torch.from_numpy(cutout).pin_memory().numpy()
+        rx_h = torch.from_numpy(rx).pin_memory().numpy()
+
+        def step_host():
+            q, f, peak = xr.fastXcorrPeak(cutout_h, rx_h, freqsearch=True)
+            row = xdist.peak_to_row(peak.qf2, peak.fidx, first + peak.shift, 0, rank)
+            return xdist.global_peak(xdist.allgather_peak(row, dev)), q.nbytes + f.nbytes
+        for _ in range(2):
+            step_host()
+        barrier()
+        e2e_ms, d2h = [], 0
+        for i in range(steps):
+            flush.zero_()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            gph, d2h = step_host()
+            e2e_ms.append((time.perf_counter() - t0) * 1e3)
+        barrier()
+        assert gph["shift"] == expect[0] and gph["fidx"] == expect[1]
+        e2e = float(np.mean(e2e_ms))
+        if world > 1:
+            t = torch.tensor([e2e], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e2e = float(t.item())
+        out.update(e2e_ms=e2e, h2d=int(rx.nbytes + cutout.nbytes), d2h=int(d2h + 32))
+    del rx_d, cutout_d
+    torch.cuda.empty_cache()
+    return out
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
-    from pydsproutines_b200 import _lib, dist as xdist
-    from pydsproutines_b200 import xcorrRoutines as xr
+    from pydsproutines_b200 import _lib
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; pydsproutines_b200 has no CPU fallback "
@@ -195,134 +430,86 @@ def run_ours(args, rank, world, local_rank):
         dist.init_process_group("nccl", device_id=dev)
     lib = _lib.load()
     _lib.check(lib.xc_set_device(local_rank))
+    peaks = measured_peaks()
+    warmup = max(args.warmup, 3)
 
+    if world == 1 and args.workload != "c2":
+        p32, p32src = fp32_peak(lib)
+        cl = config_line(args.workload, lib, peaks, p32, p32src, args.steps)
+        line = {"metric": METRIC, "value": cl["cells_per_s"], "unit": UNIT, "n_gpus": 1, "steps": args.steps,
+                "warmup": 2, "ms_per_step": cl["ms"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32" if cl["roofline"]["bound"] == "fp32" else "bf16 hi/lo split, f32 accumulate",
+                "data": "synthetic", "config": {"workload": cl["workload"], "l2": "256 MiB device memset between timed steps",
+                                                "peak_checked": cl["peak_checked"]},
+                "roofline": cl["roofline"], "gpu_launches": None}
+        print(json.dumps(line), flush=True)
+        return
+
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
+    sampler = ClockSampler(local_rank) if rank == 0 else None
     if world == 1:
-        k_rank, seed, p0, k0 = K_C2, 1002, 600001, 1234
+        k_rank, seed, plants, expect = K_C2, 1002, [(600001, 1.0, 1234)], (600001, 1234)
         workload = "C2 fastXcorr freqsearch: 8192-sample cutout, 2^20 shifts, 8192-bin FFT per shift"
     else:
-        k_rank, seed, k0 = K_RANK_MULTI, 1005, 4321
+        k_rank, seed = K_RANK_WEAK, 1005
         p0 = int(50000017 * world / 8)
-        workload = ("C5 freqsearch CAF sharded by shift range: 8192-sample cutout, %d x 2^23 shifts "
-                    "(block + 8191-sample halo per rank), peak allgather" % world)
-    cutout, rx, first = make_shard(seed, rank, world, k_rank, N_CUT, p0, k0)
-    cells_rank = float(k_rank) * N_CUT
-    cutout_d = torch.from_numpy(cutout).to(dev)
-    rx_d = torch.from_numpy(rx).to(dev)
-    cutout_pin = torch.from_numpy(cutout).pin_memory()
-    rx_pin = torch.from_numpy(rx).pin_memory()
-    cutout_h, rx_h = cutout_pin.numpy(), rx_pin.numpy()
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
-
-    def step_device():
-        qf2, fidx, peak = xr.fastXcorrPeak(cutout_d, rx_d, freqsearch=True)
-        row = xdist.peak_to_row(peak.qf2, peak.fidx, first + peak.shift, 0, rank)
-        return xdist.global_peak(xdist.allgather_peak(row, dev))
-
-    def step_host():
-        qf2, fidx, peak = xr.fastXcorrPeak(cutout_h, rx_h, freqsearch=True)
-        row = xdist.peak_to_row(peak.qf2, peak.fidx, first + peak.shift, 0, rank)
-        return xdist.global_peak(xdist.allgather_peak(row, dev)), qf2.nbytes + fidx.nbytes
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    # ---- warm-up (also checks the answer) ----
-    for _ in range(max(args.warmup, 3)):
-        flush.zero_()
-        gp = step_device()
-    assert gp["shift"] == p0 and gp["fidx"] == k0, "wrong peak: %r (expected shift %d bin %d)" % (gp, p0, k0)
-
-    # ---- timed region: device-resident inputs ----
-    lib.xc_profile_enable(1)
-    sampler = ClockSampler(local_rank) if rank == 0 else None
-    barrier()
-    launches0 = lib.xc_launch_count()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    kern_ms = []
-    t_wall0 = time.perf_counter()
-    for i in range(args.steps):
-        flush.zero_()
-        ev[i][0].record()
-        step_device()
-        ev[i][1].record()
-        kern_ms.append(lib.xc_profile_last_ms())
-    barrier()
-    t_wall = time.perf_counter() - t_wall0
-    launches = lib.xc_launch_count() - launches0
+        plants, expect = [(p0, 1.0, 4321), (1000003, 0.5, (4321 * 3) % N_CUT)], (p0, 4321)
+        workload = ("C5 freqsearch CAF sharded by shift range (weak): 8192-sample cutout, %d x 2^23 shifts "
+                    "(block + 8191-sample halo per rank), half-amplitude decoy in rank 0, peak allgather" % world)
+    main = sharded_search(world, rank, dev, k_rank, seed, plants, expect, args.steps, warmup, lib, flush, True)
     clocks = sampler.stop() if sampler else None
-    lib.xc_profile_enable(0)
-    ms_total = sum(a.elapsed_time(b) for a, b in ev)
-    if world > 1:
-        t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_total = float(t.item())
-    ms_step = ms_total / args.steps
-    value = cells_rank * world / (ms_step * 1e-3)
+    cells_rank = float(k_rank) * N_CUT
+    value = cells_rank * world / (main["ms"] * 1e-3)
 
-    # ---- end to end through the public API with pinned host buffers ----
-    for _ in range(2):
-        step_host()
-    barrier()
-    e2e_ms = []
-    d2h = 0
-    for i in range(args.steps):
-        flush.zero_()
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        _, d2h = step_host()
-        e2e_ms.append((time.perf_counter() - t0) * 1e3)
-    barrier()
-    e2e_step = float(np.mean(e2e_ms))
-    if world > 1:
-        t = torch.tensor([e2e_step], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_step = float(t.item())
-    e2e_value = cells_rank * world / (e2e_step * 1e-3)
+    # ---- strong scaling: the fixed 2^26-sample C5 record split `world` ways ----
+    strong = None
+    if not args.no_strong:
+        k_strong = (1 << LOG2_C5) // world
+        p0s = 50000017
+        strong = sharded_search(world, rank, dev, k_strong, 1005, [(p0s, 1.0, 4321), (1000003, 0.5, (4321 * 3) % N_CUT)],
+                                (p0s, 4321), max(1, min(args.steps, 3)), 1, lib, flush, False)
 
     if rank == 0:
-        hbm_peak, peak_src = measured_peaks()
-        kms = float(np.mean([k for k in kern_ms if k > 0])) if any(k > 0 for k in kern_ms) else ms_step
-        algo_bytes = ALGO_BYTES_PER_SHIFT * k_rank
-        achieved = algo_bytes / (kms * 1e-3) / 1e9
-        tf = C_double()
-        fp32_peak = None
-        if lib.xc_measure_fp32_tflops(300.0, tf) == 0:
-            fp32_peak = tf.value
-        fp32_ach = FLOPS_PER_CELL * cells_rank / (kms * 1e-3) / 1e12
+        p32, p32src = fp32_peak(lib)
+        roof = fp32_roofline(FLOPS_PER_CELL * cells_rank, main["kern_ms"], p32, p32src,
+                             "fused_fft_pp_kernel<8192> (two thread groups per SM, constants in tensor memory)",
+                             ALGO_BYTES_PER_SHIFT * k_rank, peaks,
+                             NCU_DRAM_BYTES_C2 if world == 1 else None, NCU_TRAFFIC_SOURCE if world == 1 else None)
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-                "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+                "warmup": warmup, "ms_per_step": main["ms"], "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": workload, "cutout": N_CUT, "shifts_per_rank": k_rank, "bins": N_CUT,
                            "l2": "256 MiB device memset between timed steps (outside the per-step CUDA events)",
                            "timing": "sum of per-step CUDA-event times on the launching stream, max over ranks",
-                           "wall_s_timed_loop": t_wall},
-                "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                             "frac": achieved / hbm_peak, "traffic": NCU_DRAM_BYTES_C2 if world == 1 else None,
-                             "traffic_source": "profiles/r1_c2_staged_ncu.md (ncu --set full, per launch)" if world == 1 else None,
-                             "peak_source": peak_src,
-                             "kernel": "fused_fft_staged_kernel<8192>", "kernel_ms": kms,
-                             "algorithmic_bytes_per_launch": algo_bytes,
-                             "note": "the path is FP32/issue bound, not HBM bound (SURVEY.md 8d); see fp32"},
-                "fp32": {"achieved_tflops": fp32_ach, "peak_tflops_measured_ffma": fp32_peak,
-                         "frac": (fp32_ach / fp32_peak) if fp32_peak else None,
-                         "flops_per_cell": FLOPS_PER_CELL},
-                "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_step,
-                        "h2d_bytes_per_step": int(rx.nbytes + cutout.nbytes), "d2h_bytes_per_step": int(d2h + 32)},
-                "gpu_launches": int(launches), "clocks": clocks}
+                           "global_peak": main["global_peak"], "oracle_window": main["oracle_window"],
+                           "decoy_found_by_rank": main.get("decoy_found_by_rank")},
+                "roofline": roof,
+                "e2e": {"value": cells_rank * world / (main["e2e_ms"] * 1e-3), "unit": UNIT, "ms_per_step": main["e2e_ms"],
+                        "h2d_bytes_per_step": main["h2d"], "d2h_bytes_per_step": main["d2h"],
+                        "path": "xcorrRoutines.fastXcorrPeak(numpy, numpy): pinned host buffers, chunked H2D | search | D2H pipeline"},
+                "gpu_launches": main["launches"], "clocks": clocks}
+        if strong is not None:
+            line["config"]["strong"] = {
+                "workload": "C5: fixed 2^26-sample record, %d shifts per rank" % k_strong, "ms_per_step": strong["ms"],
+                "value": float(k_strong) * world * N_CUT / (strong["ms"] * 1e-3), "unit": UNIT,
+                "global_peak": strong["global_peak"], "decoy_found_by_rank": strong.get("decoy_found_by_rank"),
+                "oracle_window": strong["oracle_window"]}
         if world == 1 and not args.no_cpu:
             v, n = cpu_time_sample(1 << 14, 1)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
-                                    "sample": "%d of the 2^20 shifts, single thread (oracle/xcorr_oracle.fastXcorr)" % n}
+                                    "sample": "%d of the 2^20 shifts, single thread of %d host cores; %s"
+                                              % (n, os.cpu_count() or 1, CPU_NOTE)}
+        if world == 1 and not args.no_configs:
+            line["configs"] = []
+            for w in ("c1", "c3", "c4", "c6"):
+                try:
+                    line["configs"].append(config_line(w, lib, peaks, p32, p32src, 3))
+                except Exception as e:                      # a config failure must not hide the headline
+                    line["configs"].append({"workload": w, "error": repr(e)})
         print(json.dumps(line), flush=True)
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
-
-
-def C_double():
-    import ctypes
-    return ctypes.c_double(0.0)
 
 
 def main():
@@ -331,7 +518,11 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "c1", "c3", "c4", "c6"],
+                    help="single-GPU headline config (default C2, BASELINE.json's metric config)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-configs", action="store_true", help="skip the C1 / C3 / C4 / C6 lines of the N = 1 run")
+    ap.add_argument("--no-strong", action="store_true", help="skip the fixed-size C5 (strong scaling) leg")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

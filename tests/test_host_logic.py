@@ -149,3 +149,23 @@ def test_sharded_peak_exchange_gloo_world2(tmp_path):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
     assert "rank0-ok" in r.stdout and "rank1-ok" in r.stdout
+
+
+def test_peak_argmax_rule(lib):
+    """The deterministic cross-rank reduction of the C-ABI (largest QF^2, lowest shift on ties, negative shift = empty
+    shard) agrees with pydsproutines_b200.dist.global_peak."""
+    from pydsproutines_b200 import _lib, dist as xdist
+    rows = [(0.5, 3, 900), (0.75, 4, 5000), (0.75, 9, 4000), (0.9, 1, -1)]
+    arr = (_lib.xc_peak * len(rows))()
+    for i, (q, f, s) in enumerate(rows):
+        arr[i] = _lib.xc_peak(qf2=q, fidx=f, index=0, shift=s, aux=0, rank=i)
+    assert lib.xc_peak_argmax(arr, len(rows)) == 2
+    gp = xdist.global_peak([xdist.peak_to_row(q, f, s, 0, i) for i, (q, f, s) in enumerate(rows)])
+    assert gp["rank"] == 2 and gp["shift"] == 4000
+    assert lib.xc_peak_argmax(arr, 1) == 0 and lib.xc_peak_argmax(None, 0) == -1
+
+
+def test_foreign_arrays_without_the_interface_are_left_alone():
+    from pydsproutines_b200 import _lib
+    a = np.ones(4, np.complex64)
+    assert _lib.adopt(a) is a and _lib.adopt(None) is None and _lib.adopt(3) == 3
