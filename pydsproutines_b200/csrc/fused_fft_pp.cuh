@@ -415,6 +415,7 @@ __global__ void __launch_bounds__(PL::TG* B, 1) fused_fft_pp_kernel(const Staged
         }
         // ---- |X|^2 and the group maximum: |X|^2 >= +0, so the float order is the order of the bit patterns:
         // one REDUX per warp, one shared atomic per warp into the slot of this iteration's parity ----
+#ifdef XC_PP_FLATSEARCH
         float tmax = 0.f;
 #pragma unroll
         for (int j = 0; j < V; ++j) tmax = fmaxf(tmax, cnorm2(v[j]));
@@ -432,6 +433,39 @@ __global__ void __launch_bounds__(PL::TG* B, 1) fused_fft_pp_kernel(const Staged
                     if (cnorm2(v[q * PL::RL + j]) == m) mybin = min(mybin, (unsigned int)output_bin<PL>(t, q, j));
             atomicMin(binmin, mybin);
         }
+#else
+        // maxima of chunks of 8 registers first: the one thread that holds the group maximum then only searches the
+        // chunk(s) that reach it (about 40 instead of 160 instructions on the critical path of its warp)
+        float nv[V], m8[V / 8];
+#pragma unroll
+        for (int j = 0; j < V; ++j) nv[j] = cnorm2(v[j]);
+        float tmax = 0.f;
+#pragma unroll
+        for (int c = 0; c < V / 8; ++c) {
+            m8[c] = fmaxf(fmaxf(fmaxf(nv[8 * c], nv[8 * c + 1]), fmaxf(nv[8 * c + 2], nv[8 * c + 3])),
+                          fmaxf(fmaxf(nv[8 * c + 4], nv[8 * c + 5]), fmaxf(nv[8 * c + 6], nv[8 * c + 7])));
+            tmax = fmaxf(tmax, m8[c]);
+        }
+        const unsigned int u = __reduce_max_sync(0xffffffffu, __float_as_uint(tmax));
+        if ((t & 31) == 0) atomicMax(gmax + (it & 1), u);
+        bar();   // all last-pass loads done (buffer free) + group maximum complete
+        const float m = __uint_as_float(gmax[it & 1]);
+        if (t == 0) gmax[(it & 1) ^ 1] = 0u;
+        if (ok && tmax == m) {
+            unsigned int mybin = 0xffffffffu;
+#pragma unroll
+            for (int c = 0; c < V / 8; ++c) {
+                if (m8[c] == m) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int j = 8 * c + i;
+                        if (nv[j] == m) mybin = min(mybin, (unsigned int)output_bin<PL>(t, j / PL::RL, j % PL::RL));
+                    }
+                }
+            }
+            atomicMin(binmin, mybin);
+        }
+#endif
         if (t == 0) pend = (ok) ? m / *out.refnormsq / out.energy[i0 + e] : 0.f;
     }
     bar();
