@@ -19,6 +19,7 @@ sys.path.insert(0, HERE)
 sys.path.insert(0, ROOT)
 
 import ref_import  # noqa: E402
+from recipes import big_inputs  # noqa: E402
 from pydsproutines_b200 import signals  # noqa: E402
 
 OUT = os.path.join(ROOT, "tests", "golden")
@@ -213,14 +214,58 @@ def czt_run_cases(ref):
     return cases
 
 
+def big_cases(ref):
+    """fastXcorr(freqsearch=True) of the real reference for cutouts beyond one block FFT: a power of two (2^17), lengths
+    that are not (9001, 20000 with a stepped shift list, 100000).  Inputs are stored as recipes (see big_inputs)."""
+    cases = {}
+    specs = [
+        ("n9001", 81, 9001, 9001 + 6, 3, 4500, None, True),
+        ("n20000_step", 82, 20000, 20000 + 300, 120, 19999, np.arange(0, 300, 12), False),
+        ("n32768", 83, 32768, 32768 + 11, 7, 12345, None, False),
+        ("n100000", 84, 100000, 100000 + 20, 13, 31337, None, False),
+        ("n131072", 85, 131072, 131072 + 24, 9, 70001, None, False),
+    ]
+    for name, seed, N, rxlen, p0, k0, shifts, full in specs:
+        recipe = dict(seed=seed, N=N, rxlen=rxlen, p0=p0, k0=k0)
+        cutout, rx = big_inputs(recipe)
+        d = dict(recipe)
+        if shifts is not None:
+            d["shifts"] = shifts
+        q, f = ref.fastXcorr(cutout, rx, freqsearch=True, shifts=shifts)
+        d["qf2_freq"], d["fidx_freq"] = q, f
+        z, fz = ref.fastXcorr(cutout, rx, freqsearch=True, shifts=shifts, absResult=False)
+        d["cplx_freq"], d["cplx_fidx"] = z.astype(np.complex64), fz
+        if full:
+            d["caf"] = ref.fastXcorr(cutout, rx, freqsearch=True, outputCAF=True, shifts=shifts).astype(np.float32)
+        cases[name] = d
+    return cases
+
+
+def bigczt_cases(ref):
+    """cztXcorr with cutout length + bins - 1 beyond 16384 points."""
+    cases = {}
+    for name, seed, N, rxlen, p0, foff, fs, f1, f2, step in (("n20000", 91, 20000, 20000 + 30, 11, 1.37, 1000.0, -5.0, 5.0, 0.05),):
+        recipe = dict(seed=seed, N=N, rxlen=rxlen, p0=p0, foff=foff, fs=fs)
+        cutout, rx = big_inputs(recipe)
+        shifts = np.arange(max(p0 - 6, 0), min(p0 + 6, rxlen - N + 1))
+        res, freqs = ref.cztXcorr(cutout, rx, f1, f2, fs, cztStep=step, shifts=shifts)
+        caf, fsearch = ref.cztXcorr(cutout, rx, f1, f2, fs, cztStep=step, outputCAF=True, shifts=shifts)
+        cases[name] = dict(recipe, shifts=shifts, f1=f1, f2=f2, step=step, res=res, freqs=freqs, caf=caf.astype(np.float32),
+                           fsearch=fsearch)
+    return cases
+
+
 def main():
     ref = ref_import.load()
     os.makedirs(OUT, exist_ok=True)
+    only = sys.argv[1:]
     for fam, cases in (("fastxcorr", fastxcorr_cases(ref)), ("groupxcorr", group_cases(ref)), ("cztxcorr", czt_cases(ref)),
                        ("groupfreq", groupfreq_cases(ref)), ("fine", fine_cases(ref)),
                        ("groupperm", groupperm_cases(ref)),
-                       ("cztrun", czt_run_cases(ref))):
+                       ("cztrun", czt_run_cases(ref)), ("bigxcorr", big_cases(ref)), ("bigczt", bigczt_cases(ref))):
         for name, d in cases.items():
+            if only and fam not in only:
+                continue
             path = os.path.join(OUT, "%s_%s.npz" % (fam, name))
             np.savez_compressed(path, **d)
             print(path, os.path.getsize(path))

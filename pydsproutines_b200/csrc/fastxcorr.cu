@@ -171,10 +171,12 @@ static int bluestein_log2m(int N) {
 
 // power-of-two lengths run the plain fused kernel; every other length 2 <= N <= 2^(MAX_LOG2N - 1) the Bluestein one
 bool fft_length_pow2(int N) { return fft_length_supported(N); }
-bool fastxcorr_fft_supported(int N) {
+// one block FFT per shift (powers of two up to 2^14, Bluestein up to 2^13 - 1 points) or the four-step path of bigfft.cu
+static bool fused_length(int N) {
     if (fft_length_supported(N)) return true;
-    return N >= 3 && bluestein_log2m(N) <= MAX_LOG2N;
+    return N >= 3 && N <= (1 << (MAX_LOG2N - 1)) && bluestein_log2m(N) <= MAX_LOG2N;
 }
+bool fastxcorr_fft_supported(int N) { return fused_length(N) || bigfft_supported(N, nullptr); }
 
 // Layout of the N = 8192 search.  The product always runs LAYOUT_PP; a build with -DXC_EXPERIMENTS keeps the
 // earlier layouts selectable through XC_LAYOUT=b2|dual|staged|ppchain|pp for A/B runs (tools/staged_check.py).
@@ -271,6 +273,7 @@ void release_plan_caches() {
     for (const BlueKey& k : g_blue_order)
         if (std::get<0>(k) != dev) keep.push_back(k);
     g_blue_order.swap(keep);
+    release_big_plan_caches();
 }
 
 // exp(+i 2 pi (lin + w d^2 / 2)); the DFT case (w = 1/N) reduces d^2 modulo 2N exactly
@@ -428,13 +431,16 @@ struct BlueRunner {
 int32_t fastxcorr_freq_device(const float2* cutout, int N, const float2* rx, int64_t rxlen, const ShiftList& sl,
                               float* qf2, uint32_t* fidx, float2* cplx, void* caf, int caf_complex,
                               cudaStream_t stream, const CztSpec* czt) {
+    bool big = false;
     if (czt) {
-        if (N < 1 || czt->nbins < 1 || czt_log2m(N, czt->nbins) > MAX_LOG2N)
-            return fail(XC_ERR_UNSUPPORTED, "chirp-z search: cutout length + frequency bins - 1 must be <= %d, got %d + %d",
-                        1 << MAX_LOG2N, N, czt->nbins);
-    } else if (!fastxcorr_fft_supported(N))
-        return fail(XC_ERR_UNSUPPORTED, "fused frequency search supports cutout lengths 2..%d (powers of two up to %d), got %d",
-                    1 << (MAX_LOG2N - 1), 1 << MAX_LOG2N, N);
+        if (N < 1 || czt->nbins < 1) return fail(XC_ERR_ARG, "chirp-z search needs N >= 1 and at least one bin");
+        big = (int64_t)N + czt->nbins - 1 > (1 << MAX_LOG2N);
+        if (big && !bigfft_supported(N, czt))
+            return fail(XC_ERR_UNSUPPORTED, "chirp-z search: cutout length + frequency bins - 1 must be <= 2^28, got %d + %d", N, czt->nbins);
+    } else {
+        big = !fused_length(N);
+        if (big && !bigfft_supported(N, nullptr)) return fail(XC_ERR_UNSUPPORTED, "frequency search does not take a cutout of %d samples", N);
+    }
     if (sl.K <= 0) return XC_OK;
     // normalisation terms: ||cutout||^2 (device scalar) and the window energies
     float* d_refn = reinterpret_cast<float*>(workspace(SLOT_TMP0, 256));
@@ -447,6 +453,7 @@ int32_t fastxcorr_freq_device(const float2* cutout, int N, const float2* rx, int
         XC_TRY(window_energy_device(rx, rxlen, N, sl.shift0, sl.step, sl.shifts, sl.K, d_energy, stream));
     }
     FusedOut out{qf2, fidx, cplx, reinterpret_cast<float*>(caf), caf_complex, d_energy, d_refn};
+    if (big) return bigfft_freq_device(cutout, N, rx, rxlen, sl, out, czt, stream);   // beyond one block FFT per shift
     if (czt || !fft_length_supported(N)) {
         // not a power of two, or a chirp-z frequency grid: Bluestein inside the fused kernel
         const BluePlan* plan = nullptr;

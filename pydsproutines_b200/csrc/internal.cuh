@@ -32,6 +32,13 @@ int32_t fastxcorr_freq_device(const float2* cutout, int N, const float2* rx, int
 int32_t fastxcorr_nofreq_device(const float2* cutout, int N, const float2* rx, int64_t rxlen, const ShiftList& sl,
                                 float* qf2, float2* cplx, cudaStream_t stream);
 
+// bigfft.cu: four-step frequency search for lengths beyond one block FFT (any N, chirp-z grids), FusedOut-style outputs
+struct FusedOut;
+bool bigfft_supported(int64_t N, const CztSpec* czt);
+int32_t bigfft_freq_device(const float2* cutout, int64_t N, const float2* rx, int64_t rxlen, const ShiftList& sl,
+                           const FusedOut& out, const CztSpec* czt, cudaStream_t stream);
+void release_big_plan_caches();
+
 // Bluestein tables of a transform length that is not a power of two (cached per length): padded plan length and
 // FFT_M(chirp) laid out for the block FFT's output registers
 int32_t bluestein_tables(int N, int* log2m, const float2** d_bhat_perm, const float2** d_chirp);

@@ -552,8 +552,9 @@ def test_cztxcorr_golden(xr, name, d, space):
 def test_cztxcorr_limits(xr):
     rng = np.random.default_rng(3)
     c, rx = signals.qpsk(rng, 9000), signals.cnoise(rng, 9100)
-    with pytest.raises(NotImplementedError):       # N + bins - 1 > 16384
-        xr.cztXcorr(c, rx, -1.0, 1.0, 100.0, cztStep=0.0002)
+    # N + bins - 1 > 16384 takes the four-step path (tests/test_gpu_big.py pins it to the reference)
+    caf, fsearch = xr.cztXcorr(c, rx, -1.0, 1.0, 100.0, cztStep=0.0002, outputCAF=True, shifts=np.arange(3))
+    assert caf.shape == (3, fsearch.size) and fsearch.size == 10001 and np.isfinite(caf).all()
     with pytest.raises(TypeError):
         xr.cztXcorr(c.astype(np.complex128), rx, -1.0, 1.0, 100.0)
 

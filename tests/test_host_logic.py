@@ -35,7 +35,10 @@ def test_library_exports_every_declared_symbol(lib):
     assert lib.xc_version() >= 100
     assert ctypes.sizeof(_lib.xc_peak) == 32
     assert lib.xc_fastxcorr_supported(8192) == 1 and lib.xc_fastxcorr_supported(100) == 1      # any length (Bluestein)
-    assert lib.xc_fastxcorr_supported(16384) == 1 and lib.xc_fastxcorr_supported(8193) == 0 and lib.xc_fastxcorr_supported(1) == 0
+    assert lib.xc_fastxcorr_supported(16384) == 1 and lib.xc_fastxcorr_supported(1) == 0
+    # beyond one block FFT: the four-step path, powers of two to 2^28, any other length while 2 N - 1 <= 2^28
+    assert lib.xc_fastxcorr_supported(8193) == 1 and lib.xc_fastxcorr_supported(1000000) == 1
+    assert lib.xc_fastxcorr_supported(1 << 28) == 1 and lib.xc_fastxcorr_supported((1 << 28) + 1) == 0
 
 
 def test_no_cpu_fallback(lib):

@@ -191,3 +191,34 @@ def test_czt_run_restatement_matches_reference(name, d):
     np.testing.assert_allclose(many, d["many"], rtol=0, atol=1e-9 * scale)
     np.testing.assert_allclose(many[0], d["one"], rtol=0, atol=1e-9 * scale)
     assert np.all(many[-1] == 0)
+
+
+# ---------------------------------------------------------------------------------------------
+# cutouts beyond one block FFT (tests/golden/big*.npz hold recipes + the real reference's outputs)
+# ---------------------------------------------------------------------------------------------
+def _big(pattern):
+    import glob
+    return sorted(glob.glob(os.path.join(GOLDEN, pattern)))
+
+
+@pytest.mark.parametrize("path", _big("bigxcorr_*.npz"), ids=os.path.basename)
+def test_oracle_large_cutouts_bit_exact(path):
+    from oracle.recipes import big_inputs
+    d = np.load(path)
+    cutout, rx = big_inputs(d)
+    shifts = d["shifts"] if "shifts" in d.files else None
+    q, f = orc.fastXcorr(cutout, rx, freqsearch=True, shifts=shifts)
+    assert np.array_equal(q, d["qf2_freq"]) and np.array_equal(f, d["fidx_freq"])
+    k = int(np.argmax(q))
+    sh = np.arange(q.size) if shifts is None else shifts
+    assert sh[k] == int(d["p0"]) and int(f[k]) == int(d["k0"])
+
+
+@pytest.mark.parametrize("path", _big("bigczt_*.npz"), ids=os.path.basename)
+def test_oracle_large_chirpz(path):
+    from oracle.recipes import big_inputs
+    d = np.load(path)
+    cutout, rx = big_inputs(d)
+    res, fr = orc.cztXcorr(cutout, rx, float(d["f1"]), float(d["f2"]), float(d["fs"]), cztStep=float(d["step"]), shifts=d["shifts"])
+    assert np.array_equal(fr, d["freqs"])
+    np.testing.assert_allclose(res, d["res"], rtol=0, atol=1e-6 * np.abs(d["res"]).max())
