@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- CAF cells/s of the fused frequency-search fastXcorr on B200 (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1|c3|c4|c6]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1|c3|c4|c6|bx|bx10]
 
 A "step" is one pass of the hot path over one synthetic batch:
   N = 1 : BASELINE.json configs[1] (C2): 8192-sample cutout, 2^20 shifts, 8192-bin FFT per shift (the headline).
@@ -308,6 +308,47 @@ def config_line(which, lib, peaks, p32, p32src, steps):
                              "peak_source": peaks["_source"] + " (cuBLAS bf16 burst)", "precision_passes": passes,
                              "algorithmic_frac": flops / (ms * 1e-3) / 1e12 / peak, "kernel": "mt_tc_kernel",
                              "kernel_ms": ms, "traffic": None}}
+    if which in ("bx", "bx10"):
+        # the reference's own published benchmark: `python benchmarks/benchmark_xcorrs.py 1000000 128` (README.md:3-23):
+        # cutout = x[10000 : 10000 + N], shifts 0..127, cp_fastXcorr on device arrays, results copied to the host
+        from oracle import xcorr_oracle as orc
+        N, K = (1000000, 128) if which == "bx" else (10000000, 128)
+        rng = np.random.default_rng(7)
+        x = (rng.standard_normal(10000 + N + K, dtype=np.float32) + 1j * rng.standard_normal(10000 + N + K, dtype=np.float32)).astype(np.complex64)
+        cutout = x[10000:10000 + N].copy()
+        shifts = np.arange(K)
+        d_c, d_x = dev(cutout), dev(x)
+        q, f = xr.cp_fastXcorr(d_c, d_x, freqsearch=True, shifts=shifts, BATCH=128)
+        for i in (0, K - 1):                                   # two shifts against the oracle (numpy, float32 FFT)
+            qo, fo = orc.fastXcorr(cutout, x[i:i + N], freqsearch=True)
+            assert abs(q[i] - qo[0]) <= 1e-4 * qo[0] + 1e-9, "benchmark_xcorrs workload: QF2 differs from the oracle"
+            if f[i] != fo[0]:
+                X = np.abs(np.fft.fft(x[i:i + N].astype(np.complex128) * np.conj(cutout).astype(np.complex128))) ** 2
+                assert abs(X[f[i]] - X[fo[0]]) <= 1e-5 * X[fo[0]], "benchmark_xcorrs workload: bin differs from the oracle"
+        lib.xc_profile_enable(0)
+        wall = []
+        for i in range(2 + steps):
+            flush.zero_()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            xr.cp_fastXcorr(d_c, d_x, freqsearch=True, shifts=shifts, BATCH=128)
+            wall.append((time.perf_counter() - t0) * 1e3)
+        ms = float(np.median(wall[2:]))
+        log2l = int(np.ceil(np.log2(2 * N - 1)))
+        L = 1 << log2l
+        form_bytes = K * (8.0 * N + 6 * 8.0 * L)                # one read of the window + six passes over the 8 L-byte work array
+        pub = {"bx": {"numpy_s": 15.9, "cython_ipp_4thr_s": 3.9, "cupy_s": 0.29}, "bx10": {"numpy_s": 192.0, "cython_ipp_4thr_s": 62.0, "cupy_s": 3.0}}[which]
+        ach = form_bytes / (ms * 1e-3) / 1e9
+        return {"workload": "benchmark_xcorrs.py %d 128 (reference's published benchmark): %d-sample cutout, 128 shifts, cp_fastXcorr "
+                            "on device arrays, results on the host" % (N, N), "ms": ms, "cells_per_s": K * float(N) / (ms * 1e-3),
+                "peak_checked": None, "published_reference": dict(pub, source="benchmarks/README.md:3-23, unnamed hardware"),
+                "speedup_vs_published_cupy": pub["cupy_s"] * 1e3 / ms, "vs_baseline": K * float(N) / (ms * 1e-3) / (K * float(N) / pub["cupy_s"]),
+                "roofline": {"bound": "hbm", "achieved": ach, "peak": float(peaks["hbm_gbs"]), "unit": "GB/s", "frac": ach / float(peaks["hbm_gbs"]),
+                             "peak_source": peaks["_source"], "kernel": "big_cols_kernel / big_rows_kernel (four-step Bluestein, L = 2^%d)" % log2l,
+                             "kernel_ms": ms, "formulation_bytes_per_call": form_bytes, "traffic": None,
+                             "note": "bytes of the four-step formulation (window read + 6 passes over 8 L bytes per shift); the "
+                                     "work arrays of a batch (about 1 GB) do not stay in the 126 MB L2 -- an L2-sized batch measured "
+                                     "slower (12.5 vs 9.9 ms at N = 1e6), see bigfft.cu"}}
     raise SystemExit("unknown workload %r" % which)
 
 
@@ -437,8 +478,8 @@ def run_ours(args, rank, world, local_rank):
         p32, p32src = fp32_peak(lib)
         cl = config_line(args.workload, lib, peaks, p32, p32src, args.steps)
         line = {"metric": METRIC, "value": cl["cells_per_s"], "unit": UNIT, "n_gpus": 1, "steps": args.steps,
-                "warmup": 2, "ms_per_step": cl["ms"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "f32" if cl["roofline"]["bound"] == "fp32" else "bf16 hi/lo split, f32 accumulate",
+                "warmup": 2, "ms_per_step": cl["ms"], "higher_is_better": True, "scaling": "weak", "vs_baseline": cl.get("vs_baseline"),
+                "dtype": "bf16 hi/lo split, f32 accumulate" if cl["roofline"]["bound"] == "tensor" else "f32",
                 "data": "synthetic", "config": {"workload": cl["workload"], "l2": "256 MiB device memset between timed steps",
                                                 "peak_checked": cl["peak_checked"]},
                 "roofline": cl["roofline"], "gpu_launches": None}
@@ -501,7 +542,7 @@ def run_ours(args, rank, world, local_rank):
                                               % (n, os.cpu_count() or 1, CPU_NOTE)}
         if world == 1 and not args.no_configs:
             line["configs"] = []
-            for w in ("c1", "c3", "c4", "c6"):
+            for w in ("c1", "c3", "c4", "c6", "bx"):
                 try:
                     line["configs"].append(config_line(w, lib, peaks, p32, p32src, 3))
                 except Exception as e:                      # a config failure must not hide the headline
@@ -518,7 +559,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=["c2", "c1", "c3", "c4", "c6"],
+    ap.add_argument("--workload", default="c2", choices=["c2", "c1", "c3", "c4", "c6", "bx", "bx10"],
                     help="single-GPU headline config (default C2, BASELINE.json's metric config)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-configs", action="store_true", help="skip the C1 / C3 / C4 / C6 lines of the N = 1 run")

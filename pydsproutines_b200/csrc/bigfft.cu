@@ -10,8 +10,8 @@
 // Bluestein (any length N, and chirp-z grids): L >= N + bins - 1; second transform with the roles swapped
 // (k = k2 R + k1: its "columns" are the contiguous rows the first transform left, no transpose pass in between):
 //   columns(R; product) -> rows(C; times FFT_L(chirp), conj) -> columns(C) -> rows(R; |.|^2 for k < bins, arg max).
-// Per shift the intermediate (8 L bytes) is written and read once per step; a batch of shifts is sized to stay
-// around 2 x 512 MB of workspace.  This path is memory bound (about 7 x 8 L bytes per shift for Bluestein, 3 x for a
+// Per shift the intermediate (8 L bytes) is written and read once per step; a batch of shifts takes about 1 GB of
+// workspace.  This path is memory bound (about 7 x 8 L bytes per shift for Bluestein, 3 x for a
 // power of two), unlike the fused single-SM kernels.
 #include <math.h>
 
@@ -597,8 +597,14 @@ int32_t bigfft_freq_device(const float2* cutout, int64_t N, const float2* rx, in
     const int R = 1 << log2R, C = 1 << log2C;
     const BigTw* tw = nullptr;
     XC_TRY(big_twiddles(log2L, &tw));
-    // shifts per batch: two work arrays of batch * L points, about 512 MB each
-    int64_t batch = (1ll << 26) / L;
+    // shifts per batch: about 1 GB of work arrays (one for a power of two, two for Bluestein).  Measured on the
+    // reference's benchmark (N = 1e6, 128 shifts): 1 GB 9.9 ms, 200 MB 11.0, 96 MB (L2 resident) 12.5, 4 GB 11.2 --
+    // the parallelism of a large batch is worth more than L2 residency.  A debug build takes XC_BIG_BATCH_MB.
+    int64_t budget = 1024ll << 20;
+#ifdef XC_EXPERIMENTS
+    if (const char* e = getenv("XC_BIG_BATCH_MB")) budget = (int64_t)atoll(e) << 20;
+#endif
+    int64_t batch = budget / ((pow2 ? 1 : 2) * (int64_t)sizeof(float2) * L);
     if (batch < 1) batch = 1;
     if (batch > 16384) batch = 16384;
     if (batch > sl.K) batch = sl.K;
