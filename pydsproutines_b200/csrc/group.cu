@@ -33,6 +33,7 @@ struct xc_group {
     int32_t blue;            // F is not a power of two: chirped weights, two FFTs per shift (bluestein.cuh)
     const float2* d_bhat_perm;   // Bluestein: FFT_M(chirp) in register order (owned by the per-length cache)
     const float2* d_chirp;       // Bluestein: b[k] = exp(+i pi k^2 / F), k < F
+    xc::GroupPPPlan pp;          // ping-pong layout for contiguous shift ranges (group_pp.cuh), usable or not
 };
 
 namespace xc {
@@ -322,6 +323,16 @@ struct GroupRunner {
     }
 };
 
+// a build with -DXC_EXPERIMENTS keeps the round-1 kernel selectable (XC_GROUP_LAYOUT=ell) for A/B runs
+static bool group_layout_pp() {
+#ifdef XC_EXPERIMENTS
+    static const bool pp = [] { const char* e = getenv("XC_GROUP_LAYOUT"); return !(e && !strcmp(e, "ell")); }();
+    return pp;
+#else
+    return true;
+#endif
+}
+
 }  // namespace xc
 
 using namespace xc;
@@ -385,6 +396,7 @@ int32_t xc_group_create(const void* ygroups, int32_t G, int32_t L, const int64_t
         nsq += (double)yin[i].x * yin[i].x + (double)yin[i].y * yin[i].y;
     }
     int32_t st = dispatch_log2(h->log2m, GroupBuilder{y.data(), starts, h});
+    if (st == XC_OK && !blue) st = group_pp_build(y.data(), starts, G, L, F, &h->pp);
     if (st == XC_OK) {
         const float nf = (float)nsq;
         cudaError_t e = cudaMalloc(&h->d_refn, 256);
@@ -410,6 +422,7 @@ int32_t xc_group_destroy(xc_group* h) {
     cudaFree(h->d_row_base);
     cudaFree(h->d_refn);
     cudaFree(h->d_starts);
+    group_pp_release(&h->pp);
     delete h;
     return XC_OK;
 }
@@ -468,7 +481,10 @@ int32_t xc_group_xcorr(xc_group* h, const void* rx, int64_t rxlen, int64_t shift
     // the fused kernel either reduces to (max, arg max) or writes CAF rows; both wanted = two passes
     if (dq || df) {
         FusedOut out{dq, df, nullptr, nullptr, 0, d_energy, h->d_refn};
-        XC_TRY(dispatch_log2(h->log2m, GroupRunner{h, drx, rxlen, sl, out, st}));
+        if (h->pp.usable && !dsh && step == 1 && K >= 16 * (int64_t)sm_count() && group_layout_pp())
+            XC_TRY(group_pp_run(h->pp, h->d_starts, drx, rxlen, shift0, K, h->min_start, h->span, out, st));
+        else
+            XC_TRY(dispatch_log2(h->log2m, GroupRunner{h, drx, rxlen, sl, out, st}));
     }
     if (dcaf) {
         FusedOut out{nullptr, nullptr, nullptr, dcaf, 0, d_energy, h->d_refn};

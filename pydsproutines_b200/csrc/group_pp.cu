@@ -1,0 +1,113 @@
+// group_pp.cu -- plan builder and launcher of the ping-pong GroupXcorrFFT kernel (group_pp.cuh).
+#include <vector>
+
+#include "group_pp.cuh"
+#include "internal.cuh"
+
+namespace xc {
+
+using GPPL = FftPlan<12, 128, 4, 32, 32>;
+
+#ifndef XC_GP_B
+#define XC_GP_B 3
+#endif
+constexpr int GP_B = XC_GP_B;          // thread groups per SM
+
+void group_pp_release(GroupPPPlan* p) {
+    if (p->d_w) cudaFree(p->d_w);
+    if (p->d_off) cudaFree(p->d_off);
+    memset(p, 0, sizeof(*p));
+}
+
+// y: host weights [G][L] (conjugation already applied); the plan is usable when the fold fits the kernel's limits
+int32_t group_pp_build(const float2* y, const int64_t* starts, int G, int L, int F, GroupPPPlan* p) {
+    memset(p, 0, sizeof(*p));
+    if (F != GPPL::N) return XC_OK;
+    using LY = GroupPPLayout<GPPL, GP_B>;
+    // window slack: the largest multiple of B (at most 252) that fits shared memory
+    int W = ((int)(((int64_t)max_smem_optin() - (int64_t)LY::OFF_STAGE) / (int64_t)(sizeof(float2) * (size_t)G)) - L) / GP_B * GP_B;
+    if (W > 252 / GP_B * GP_B) W = 252 / GP_B * GP_B;
+    if (W < 4 * GP_B) return XC_OK;
+    constexpr int TG = GPPL::TG, V = GPPL::V, R1 = GPPL::R1;
+    struct Contrib { uint32_t off; float2 w; };
+    std::vector<std::vector<Contrib>> cells(F);
+    const int SW = L + W;
+    for (int g = 0; g < G; ++g)
+        for (int n = 0; n < L; ++n) {
+            const int64_t a = starts[g] + n;
+            const int64_t m = ((a % F) + F) % F;
+            cells[(size_t)m].push_back(Contrib{(uint32_t)(((int64_t)g * SW + n) * 8), y[(size_t)g * L + n]});
+        }
+    int base[V + 1];
+    base[0] = 0;
+    int qtop = 0;
+    for (int c = 0; c < V; ++c) {
+        const int q = c / R1, n1 = c % R1;
+        size_t len = 0;
+        for (int t = 0; t < TG; ++t) {
+            const size_t m = (size_t)(n1 * GPPL::M1 + t + TG * q);
+            if (cells[m].size() > len) len = cells[m].size();
+        }
+        len = (len + GP_CH - 1) / GP_CH * GP_CH;
+        if (len > 248) return XC_OK;
+        if (len > 0) qtop = q;
+        p->lens[c] = (unsigned char)len;
+        base[c + 1] = base[c] + (int)len;
+    }
+    const int NC = base[V];
+    if (NC == 0 || NC > GP_MAX_NC) {
+        memset(p, 0, sizeof(*p));
+        return XC_OK;
+    }
+    int nq = 1;
+    while (nq < qtop + 1) nq <<= 1;
+    std::vector<float2> hw((size_t)NC * TG, make_float2(0.f, 0.f));
+    std::vector<uint32_t> ho((size_t)NC * TG, 0u);
+    for (int c = 0; c < V; ++c) {
+        const int q = c / R1, n1 = c % R1;
+        for (int t = 0; t < TG; ++t) {
+            const size_t m = (size_t)(n1 * GPPL::M1 + t + TG * q);
+            for (size_t j = 0; j < cells[m].size(); ++j) {
+                hw[((size_t)base[c] + j) * TG + t] = cells[m][j].w;
+                ho[((size_t)base[c] + j) * TG + t] = cells[m][j].off;
+            }
+        }
+    }
+    XC_CUDA_TRY(cudaMalloc(&p->d_w, sizeof(float2) * hw.size()));
+    XC_CUDA_TRY(cudaMalloc(&p->d_off, sizeof(uint32_t) * ho.size()));
+    XC_CUDA_TRY(cudaMemcpy(p->d_w, hw.data(), sizeof(float2) * hw.size(), cudaMemcpyHostToDevice));
+    XC_CUDA_TRY(cudaMemcpy(p->d_off, ho.data(), sizeof(uint32_t) * ho.size(), cudaMemcpyHostToDevice));
+    p->G = G;
+    p->L = L;
+    p->W = W;
+    p->NC = NC;
+    p->nq_live = nq;
+    p->usable = 1;
+    return XC_OK;
+}
+
+int32_t group_pp_run(const GroupPPPlan& p, const int64_t* d_starts, const float2* rx, int64_t rxlen, int64_t shift0, int64_t K,
+                     int64_t lo, int64_t hi, const FusedOut& out, cudaStream_t stream) {
+    using LY = GroupPPLayout<GPPL, GP_B>;
+    auto kern = group_pp_kernel<GPPL, GP_B>;
+    const size_t smem = LY::bytes(p.G, p.L, p.W);
+    if ((int)smem > max_smem_optin()) return fail(XC_ERR_UNSUPPORTED, "group search kernel needs %zu B of shared memory", smem);
+    static KernelOnce once;
+    XC_TRY(once.configure(kern, max_smem_optin()));
+    GroupPPArgs a{rx, rxlen, shift0, lo, hi, d_starts, p.d_w, p.d_off, p.G, p.L, p.NC, p.nq_live, p.W};
+    GroupPPLens lens;
+    memcpy(lens.len, p.lens, sizeof(lens.len));
+    const int64_t per = (K + GP_B - 1) / GP_B;
+    int64_t ctas = (int64_t)sm_count();
+    if (ctas > per) ctas = per;
+    if (ctas < 1) ctas = 1;
+    const int64_t chunk = (per + ctas - 1) / ctas;
+    if (chunk >= (1ll << 29)) return fail(XC_ERR_UNSUPPORTED, "too many shifts per thread group");
+    profile_begin(stream);
+    kern<<<(unsigned)ctas, GPPL::TG * GP_B, smem, stream>>>(a, lens, out, K, (int)chunk);
+    profile_end(stream);
+    XC_LAUNCH_CHECK();
+    return XC_OK;
+}
+
+}  // namespace xc

@@ -1,0 +1,358 @@
+// group_pp.cuh -- GroupXcorrFFT over a CONTIGUOUS shift range in the ping-pong layout of fused_fft_pp.cuh
+// (B free-running thread groups per SM, per-thread constants in tensor memory), for fftlen 4096.
+//
+// The folded formulation of group.cu (one F-point FFT of the products folded into F cells) with three changes:
+//   * the per-group rx windows rx[s + s_g, s + s_g + L + W) are staged in shared memory (G x (L + W) samples,
+//     refilled every W / B iterations), so the gather of the G L products per shift reads LDS instead of L2
+//     (profiles/r1_c3_group_ncu.md: 33 % of the samples sat in that loop with long-scoreboard stalls);
+//   * the contributor lists of a thread (weight, stage offset) live in tensor memory next to the twiddle tables:
+//     nothing per thread is re-read from shared or global memory;
+//   * zero padding is not transformed: when the folded groups only reach the first 128 nq cells of each 1024-cell
+//     quarter (nq in {1, 2, 4}; C3: 64 groups x 128 at starts 1024 g -> nq = 1), pass 1 runs nq of its 8 columns and
+//     pass 2 is a radix-32 codelet with 4 nq non-zero inputs (copy stages cost nothing).
+// Folds that do not fit (more than 96 padded contributors per thread, windows larger than the shared-memory budget,
+// Bluestein lengths, shift lists with a step) stay on fused_fft_kernel<GroupLoader>.
+#pragma once
+#include "fused_fft_pp.cuh"
+
+namespace xc {
+
+constexpr int GP_MAX_NC = 96;      // padded contributors per thread (tensor-memory columns: 3 per contributor)
+constexpr int GP_CH = 8;           // contributors per tcgen05.ld pair
+
+struct GroupPPLens {
+    unsigned char len[32];         // padded list length of register slot c (multiple of GP_CH), uniform over the threads
+};
+
+struct GroupPPArgs {
+    const float2* rx;
+    int64_t rxlen;
+    int64_t shift0;                // the shift of entry i is shift0 + i
+    int64_t lo, hi;                // valid shifts satisfy s + lo >= 0 and s + hi <= rxlen
+    const int64_t* starts;         // [G] device
+    const float2* w;               // [NC][TG] weights (conj applied), device
+    const uint32_t* off;           // [NC][TG] byte offsets into the stage at iteration offset 0
+    int G, L, NC, nq_live, W;
+};
+
+namespace tc {
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t* r) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr), "r"(r[0]), "r"(r[1]),
+                 "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_ld8_issue(uint32_t taddr, uint32_t* u) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7])
+                 : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait8(uint32_t* u) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(u[0]), "+r"(u[1]), "+r"(u[2]), "+r"(u[3]), "+r"(u[4]), "+r"(u[5]), "+r"(u[6]), "+r"(u[7]));
+}
+}  // namespace tc
+
+// stages h >= H0 of codelet_fft<R> when only the first NZ inputs are non-zero: a stage whose partner distance
+// R / (2 h) is >= NZ adds a zero, i.e. it copies (u + w 0, u - w 0) = (u, u)
+template <int R, int NZ, int H0>
+__device__ __forceinline__ void codelet_fft_pruned(float2* a) {
+    constexpr int LG = ilog2(R);
+#pragma unroll
+    for (int h = H0; h < R; h <<= 1) {
+#pragma unroll
+        for (int blk = 0; blk < R; blk += 2 * h) {
+#pragma unroll
+            for (int j = 0; j < h; ++j) {
+                if (R / (2 * h) >= NZ) {
+                    a[bitrev(blk + j + h, LG)] = a[bitrev(blk + j, LG)];
+                } else {
+                    dit_butterfly(a[bitrev(blk + j, LG)], a[bitrev(blk + j + h, LG)], j * (16 / h));
+                }
+            }
+        }
+    }
+}
+
+template <class PL, int B>
+struct GroupPPLayout {
+    static_assert(PL::P == 3 && PL::R2 == 32 && PL::R3 == 32 && PL::V == 32 && PL::TG == 128, "4096-point plan: 128 threads x 32 points");
+    static constexpr size_t OFF_BUF = 0;
+    static constexpr size_t OFF_GMAX = sizeof(float2) * (size_t)PL::BUF * B;          // [B][2]
+    static constexpr size_t OFF_BIN = OFF_GMAX + sizeof(unsigned int) * 2 * B;        // [B]
+    static constexpr size_t OFF_TADDR = OFF_BIN + sizeof(unsigned int) * B;
+    static constexpr size_t OFF_STAGE = (OFF_TADDR + 16 + 15) / 16 * 16;              // G x (L + W) samples
+    __host__ __device__ static constexpr size_t bytes(int G, int L, int W) { return OFF_STAGE + sizeof(float2) * (size_t)G * (size_t)(L + W); }
+    // tensor-memory columns of one thread
+    static constexpr int COL_W = 0;                       // weights, 2 columns per contributor
+    static constexpr int COL_O = 2 * GP_MAX_NC;           // stage byte offsets
+    static constexpr int COL_T1 = 3 * GP_MAX_NC;          // pass-2 input twiddles, chunk layout of fused_fft_pp.cuh
+    static constexpr int COL_T2 = COL_T1 + 64;            // pass-3 input twiddles
+    static constexpr int TMEM_COLS = 512;
+    static_assert(COL_T2 + 64 <= 512, "tensor memory holds 512 columns");
+};
+
+// pass 2 with NZ = 4 nq non-zero inputs (the columns c < 128 nq of the first exchange): loads, folded first stage,
+// pruned tail, in-place stores
+template <class PL, int NZ>
+__device__ __forceinline__ void gp_pass2(float2* v, float2* buf, const int o2, const uint32_t t1) {
+    constexpr int ROW = PL::ROW, R2 = PL::R2;
+    uint32_t cu[2][16];
+    tc::tmem_ld16_issue(t1, cu[0]);
+#pragma unroll
+    for (int n2 = 0; n2 < R2; ++n2) v[n2] = (n2 < NZ) ? buf[o2 + n2 * ROW] : make_float2(0.f, 0.f);
+    if (NZ == R2) {
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+            tc::tmem_ld_wait16(cu[m & 1]);
+            if (m + 1 < 4) tc::tmem_ld16_issue(t1 + 16 * (m + 1), cu[(m + 1) & 1]);
+            folded_stage_chunk(v, m, cu[m & 1]);
+        }
+        codelet_fft<R2, 2>(v);
+    } else {
+        // a[i + 16] = 0: the first stage is a[i] = a[i + 16] = T1[i] a[i]
+#pragma unroll
+        for (int m = 0; m < NZ / 4; ++m) {
+            tc::tmem_ld_wait16(cu[m & 1]);
+            if (m + 1 < NZ / 4) tc::tmem_ld16_issue(t1 + 16 * (m + 1), cu[(m + 1) & 1]);
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const int i = 4 * m + r;
+                v[i] = pcmul(v[i], make_float2(__uint_as_float(cu[m & 1][4 * r]), __uint_as_float(cu[m & 1][4 * r + 1])));
+                v[i + 16] = v[i];
+            }
+        }
+        codelet_fft_pruned<R2, NZ, 2>(v);
+    }
+#pragma unroll
+    for (int j = 0; j < R2; ++j) buf[o2 + bitrev(j, ilog2(R2)) * ROW] = v[j];
+}
+
+template <class PL, int B>
+__global__ void __launch_bounds__(PL::TG* B, 1) group_pp_kernel(const GroupPPArgs a, const GroupPPLens lens, const FusedOut out,
+                                                                const int64_t K, const int chunk) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    using LY = GroupPPLayout<PL, B>;
+    const int W = a.W;                    // extra samples behind every group window (a multiple of B)
+    constexpr int TG = PL::TG, V = PL::V, RL = PL::RL, ROW = PL::ROW, R1 = PL::R1;
+    const int g = threadIdx.x / TG;       // thread group within the CTA
+    const int t = threadIdx.x % TG;
+    const int warp_cta = threadIdx.x >> 5;
+    float2* const buf = reinterpret_cast<float2*>(smem_raw + LY::OFF_BUF) + (size_t)g * PL::BUF;
+    float2* const stage = reinterpret_cast<float2*>(smem_raw + LY::OFF_STAGE);
+    unsigned int* const gmax = reinterpret_cast<unsigned int*>(smem_raw + LY::OFF_GMAX) + 2 * g;
+    unsigned int* const binmin = reinterpret_cast<unsigned int*>(smem_raw + LY::OFF_BIN) + g;
+    uint32_t* const taddr_slot = reinterpret_cast<uint32_t*>(smem_raw + LY::OFF_TADDR);
+    if (warp_cta == 0) tc::tmem_alloc(tc::smem_u32(taddr_slot), LY::TMEM_COLS);
+    if (t == 0) {
+        *binmin = 0xffffffffu;
+        gmax[0] = 0u;
+        gmax[1] = 0u;
+    }
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+    const uint32_t tmem0 = *taddr_slot;
+    const uint32_t tb = tmem0 + (((uint32_t)(warp_cta & 3) * 32u) << 16);
+    if (g == 0) {
+        // ---- per-thread constants -> tensor memory (read by the same in-group thread of every group) ----
+        for (int e0 = 0; e0 < a.NC; e0 += GP_CH) {
+            float r[16];
+            uint32_t o[8];
+#pragma unroll
+            for (int i = 0; i < GP_CH; ++i) {
+                const float2 w = a.w[(size_t)(e0 + i) * TG + t];
+                r[2 * i] = w.x;
+                r[2 * i + 1] = w.y;
+                o[i] = a.off[(size_t)(e0 + i) * TG + t];
+            }
+            tc::tmem_st16(tb + LY::COL_W + 2 * e0, r);
+            tc::tmem_st8(tb + LY::COL_O + e0, o);
+        }
+        float r[16];
+        const int k1 = t / PL::M2, d = t % PL::M2;
+#pragma unroll 1
+        for (int m = 0; m < 4; ++m) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int n2 = 4 * m + (i >> 1) + 16 * (i & 1);
+                const float2 w = unit_root(((n2 * PL::M2 + d) * k1) % PL::N, PL::N);
+                r[2 * i] = w.x;
+                r[2 * i + 1] = w.y;
+            }
+            tc::tmem_st16(tb + LY::COL_T1 + 16 * m, r);
+        }
+        const int k2 = t % PL::R2;
+#pragma unroll 1
+        for (int m = 0; m < 4; ++m) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int dd = 4 * m + (i >> 1) + 16 * (i & 1);
+                const float2 w = unit_root((dd * k2) % PL::M1, PL::M1);
+                r[2 * i] = w.x;
+                r[2 * i + 1] = w.y;
+            }
+            tc::tmem_st16(tb + LY::COL_T2 + 16 * m, r);
+        }
+        tc::tmem_st_wait();
+    }
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+
+    // this CTA owns shift-list entries [i0, i0 + B * chunk); group g takes i0 + B * it + g
+    const int64_t i0 = (int64_t)blockIdx.x * B * (int64_t)chunk;
+    int64_t n_left = K - i0;
+    if (n_left < 0) n_left = 0;
+    if (n_left > B * (int64_t)chunk) n_left = B * (int64_t)chunk;
+    const int n_act = (int)n_left;
+    const int64_t s_first = a.shift0 + i0;
+    const GroupBar<TG, B> bar{1 + g};
+    const int SW = a.L + W;
+    const int nstage = a.G * SW;
+    const uint32_t stage_s = tc::smem_u32(stage);
+    constexpr int K1STEP = (PL::M1 / RL) * ROW;
+    constexpr int QSTEP1 = (TG / RL) * ROW;
+    const int o1 = (t / RL) * ROW + (t % RL);
+    const int o2 = (t / PL::M2) * K1STEP + (t % PL::M2);
+    float2 v[V];
+    float pend = 0.f;
+    int o = W;
+
+    for (int it = 0; it < chunk; ++it) {
+        const int e = B * it + g;
+        if (o == W) {
+            // refill: stage[gi (L + W) + j] = rx[s + s_gi + j] (zero outside the record)
+            __syncthreads();
+            const int64_t base = s_first + (int64_t)B * it;
+            for (int i = threadIdx.x; i < nstage; i += TG * B) {
+                const int gi = i / SW, j = i - gi * SW;
+                const int64_t p = base + __ldg(a.starts + gi) + j;
+                stage[i] = (p >= 0 && p < a.rxlen) ? __ldg(a.rx + p) : make_float2(0.f, 0.f);
+            }
+            o = 0;
+            __syncthreads();
+        }
+        const int64_t s = s_first + e;
+        const bool ok = e < n_act && s + a.lo >= 0 && s + a.hi <= a.rxlen;
+        const uint32_t xs = stage_s + 8u * (uint32_t)(o + g);
+        o += B;
+        // ---- gather: v[c] = sum_j w[c][j] x[off[c][j]] over the contributor list of register slot c ----
+        {
+            uint32_t cw = tb + LY::COL_W, co = tb + LY::COL_O;
+#pragma unroll
+            for (int c = 0; c < V; ++c) {
+                float2 acc = make_float2(0.f, 0.f);
+                const int n_c = lens.len[c];
+#pragma unroll 1
+                for (int j = 0; j < n_c; j += GP_CH) {
+                    uint32_t wv[16], ov[8];
+                    tc::tmem_ld16_issue(cw, wv);
+                    tc::tmem_ld8_issue(co, ov);
+                    cw += 2 * GP_CH;
+                    co += GP_CH;
+                    tc::tmem_ld_wait8(ov);
+                    float2 x[GP_CH];
+#pragma unroll
+                    for (int u = 0; u < GP_CH; ++u)
+                        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(x[u].x), "=f"(x[u].y) : "r"(xs + ov[u]));
+                    tc::tmem_ld_wait16(wv);
+#pragma unroll
+                    for (int u = 0; u < GP_CH; ++u) {
+                        const float2 y = make_float2(__uint_as_float(wv[2 * u]), __uint_as_float(wv[2 * u + 1]));
+                        acc = pfma(make_float2(x[u].y, x[u].x), make_float2(-y.y, y.y), pfma(x[u], make_float2(y.x, y.x), acc));
+                    }
+                }
+                v[c] = acc;
+            }
+        }
+        // ---- pass 1: radix-4 columns q < nq_live (the others are all zero), raw stores ----
+#pragma unroll
+        for (int q = 0; q < V / R1; ++q) {
+            if (q < a.nq_live) {
+                codelet_fft<R1>(v + q * R1);
+#pragma unroll
+                for (int j = 0; j < R1; ++j) buf[o1 + bitrev(j, ilog2(R1)) * K1STEP + q * QSTEP1] = v[q * R1 + j];
+            }
+        }
+        bar();
+        // ---- pass 2 (in place, warp local from here on) ----
+        if (a.nq_live == 1) gp_pass2<PL, 4>(v, buf, o2, tb + LY::COL_T1);
+        else if (a.nq_live == 2) gp_pass2<PL, 8>(v, buf, o2, tb + LY::COL_T1);
+        else if (a.nq_live == 4) gp_pass2<PL, 16>(v, buf, o2, tb + LY::COL_T1);
+        else gp_pass2<PL, 32>(v, buf, o2, tb + LY::COL_T1);
+        __syncwarp();
+        // ---- pass 3 ----
+        {
+            uint32_t cu[2][16];
+            tc::tmem_ld16_issue(tb + LY::COL_T2, cu[0]);
+            const float4* const b3 = reinterpret_cast<const float4*>(buf + t * ROW);
+#pragma unroll
+            for (int d2 = 0; d2 < RL / 2; ++d2) {
+                const float4 y = b3[d2];
+                v[2 * d2] = make_float2(y.x, y.y);
+                v[2 * d2 + 1] = make_float2(y.z, y.w);
+            }
+#pragma unroll
+            for (int m = 0; m < 4; ++m) {
+                tc::tmem_ld_wait16(cu[m & 1]);
+                if (m + 1 < 4) tc::tmem_ld16_issue(tb + LY::COL_T2 + 16 * (m + 1), cu[(m + 1) & 1]);
+                folded_stage_chunk(v, m, cu[m & 1]);
+            }
+            codelet_fft<RL, 2>(v);
+        }
+        if (t == 0 && it > 0) {                        // results of the previous FFT of this group
+            const int p = e - B;
+            if (p < n_act) {
+                const unsigned int b = *binmin;
+                if (out.qf2) out.qf2[i0 + p] = pend;
+                if (out.fidx) out.fidx[i0 + p] = (b == 0xffffffffu) ? 0u : b;
+            }
+            *binmin = 0xffffffffu;
+        }
+        // ---- |X|^2, group maximum, lowest arg max (as fused_fft_pp_kernel) ----
+        float nv[V], m8[V / 8];
+#pragma unroll
+        for (int j = 0; j < V; ++j) nv[j] = cnorm2(v[j]);
+        float tmax = 0.f;
+#pragma unroll
+        for (int c = 0; c < V / 8; ++c) {
+            m8[c] = fmaxf(fmaxf(fmaxf(nv[8 * c], nv[8 * c + 1]), fmaxf(nv[8 * c + 2], nv[8 * c + 3])),
+                          fmaxf(fmaxf(nv[8 * c + 4], nv[8 * c + 5]), fmaxf(nv[8 * c + 6], nv[8 * c + 7])));
+            tmax = fmaxf(tmax, m8[c]);
+        }
+        const unsigned int u = __reduce_max_sync(0xffffffffu, __float_as_uint(tmax));
+        if ((t & 31) == 0) atomicMax(gmax + (it & 1), u);
+        bar();   // all last-pass loads done (buffer free) + group maximum complete
+        const float m = __uint_as_float(gmax[it & 1]);
+        if (t == 0) gmax[(it & 1) ^ 1] = 0u;
+        if (ok && tmax == m) {
+            unsigned int mybin = 0xffffffffu;
+#pragma unroll
+            for (int c = 0; c < V / 8; ++c) {
+                if (m8[c] == m) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int j = 8 * c + i;
+                        if (nv[j] == m) mybin = min(mybin, (unsigned int)output_bin<PL>(t, j / RL, j % RL));
+                    }
+                }
+            }
+            atomicMin(binmin, mybin);
+        }
+        if (t == 0) pend = ok ? m / *out.refnormsq / out.energy[i0 + e] : 0.f;
+    }
+    bar();
+    if (t == 0 && chunk > 0) {
+        const int p = B * (chunk - 1) + g;
+        if (p < n_act) {
+            const unsigned int b = *binmin;
+            if (out.qf2) out.qf2[i0 + p] = pend;
+            if (out.fidx) out.fidx[i0 + p] = (b == 0xffffffffu) ? 0u : b;
+        }
+    }
+    tc::tc_fence_before();
+    __syncthreads();
+    if (warp_cta == 0) tc::tmem_dealloc(tmem0, LY::TMEM_COLS);
+}
+
+}  // namespace xc

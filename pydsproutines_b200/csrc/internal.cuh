@@ -39,6 +39,19 @@ int32_t bigfft_freq_device(const float2* cutout, int64_t N, const float2* rx, in
                            const FusedOut& out, const CztSpec* czt, cudaStream_t stream);
 void release_big_plan_caches();
 
+// group_pp.cu: ping-pong GroupXcorrFFT kernel for fftlen 4096 over contiguous shifts (POD: lives inside xc_group)
+struct GroupPPPlan {
+    int usable;
+    int G, L, W, NC, nq_live;
+    unsigned char lens[32];
+    float2* d_w;
+    uint32_t* d_off;
+};
+int32_t group_pp_build(const float2* y, const int64_t* starts, int G, int L, int F, GroupPPPlan* p);
+void group_pp_release(GroupPPPlan* p);
+int32_t group_pp_run(const GroupPPPlan& p, const int64_t* d_starts, const float2* rx, int64_t rxlen, int64_t shift0, int64_t K,
+                     int64_t lo, int64_t hi, const FusedOut& out, cudaStream_t stream);
+
 // Bluestein tables of a transform length that is not a power of two (cached per length): padded plan length and
 // FFT_M(chirp) laid out for the block FFT's output registers
 int32_t bluestein_tables(int N, int* log2m, const float2** d_bhat_perm, const float2** d_chirp);
