@@ -48,14 +48,14 @@ int32_t group_pp_build(const float2* y, const int64_t* starts, int G, int L, int
             const size_t m = (size_t)(n1 * GPPL::M1 + t + TG * q);
             if (cells[m].size() > len) len = cells[m].size();
         }
-        len = (len + GP_CH - 1) / GP_CH * GP_CH;
+        len = (len + 2 * GP_CH - 1) / (2 * GP_CH) * (2 * GP_CH);
         if (len > 248) return XC_OK;
         if (len > 0) qtop = q;
         p->lens[c] = (unsigned char)len;
         base[c + 1] = base[c] + (int)len;
     }
-    const int NC = base[V];
-    if (NC == 0 || NC > GP_MAX_NC) {
+    const int NC = base[V] + GP_CH;                       // one chunk of padding: the gather prefetches one chunk ahead
+    if (base[V] == 0 || NC > GP_MAX_NC) {
         memset(p, 0, sizeof(*p));
         return XC_OK;
     }
@@ -89,11 +89,13 @@ int32_t group_pp_build(const float2* y, const int64_t* starts, int G, int L, int
 int32_t group_pp_run(const GroupPPPlan& p, const int64_t* d_starts, const float2* rx, int64_t rxlen, int64_t shift0, int64_t K,
                      int64_t lo, int64_t hi, const FusedOut& out, cudaStream_t stream) {
     using LY = GroupPPLayout<GPPL, GP_B>;
-    auto kern = group_pp_kernel<GPPL, GP_B>;
+    void (*kern)(const GroupPPArgs, const GroupPPLens, const FusedOut, const int64_t, const int) =
+        p.nq_live == 1 ? group_pp_kernel<GPPL, GP_B, 1> : p.nq_live == 2 ? group_pp_kernel<GPPL, GP_B, 2>
+        : p.nq_live == 4 ? group_pp_kernel<GPPL, GP_B, 4> : group_pp_kernel<GPPL, GP_B, 8>;
     const size_t smem = LY::bytes(p.G, p.L, p.W);
     if ((int)smem > max_smem_optin()) return fail(XC_ERR_UNSUPPORTED, "group search kernel needs %zu B of shared memory", smem);
-    static KernelOnce once;
-    XC_TRY(once.configure(kern, max_smem_optin()));
+    static KernelOnce once[4];
+    XC_TRY(once[p.nq_live == 1 ? 0 : p.nq_live == 2 ? 1 : p.nq_live == 4 ? 2 : 3].configure(kern, max_smem_optin()));
     GroupPPArgs a{rx, rxlen, shift0, lo, hi, d_starts, p.d_w, p.d_off, p.G, p.L, p.NC, p.nq_live, p.W};
     GroupPPLens lens;
     memcpy(lens.len, p.lens, sizeof(lens.len));

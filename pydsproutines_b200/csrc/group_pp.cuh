@@ -17,8 +17,8 @@
 
 namespace xc {
 
-constexpr int GP_MAX_NC = 96;      // padded contributors per thread (tensor-memory columns: 3 per contributor)
-constexpr int GP_CH = 8;           // contributors per tcgen05.ld pair
+constexpr int GP_MAX_NC = 96;      // padded contributors per thread incl. one chunk of padding (tensor-memory columns: 3 each)
+constexpr int GP_CH = 8;           // contributors per tcgen05.ld pair (lists are padded to 2 GP_CH)
 
 struct GroupPPLens {
     unsigned char len[32];         // padded list length of register slot c (multiple of GP_CH), uniform over the threads
@@ -127,7 +127,9 @@ __device__ __forceinline__ void gp_pass2(float2* v, float2* buf, const int o2, c
     for (int j = 0; j < R2; ++j) buf[o2 + bitrev(j, ilog2(R2)) * ROW] = v[j];
 }
 
-template <class PL, int B>
+// NQ = number of live pass-1 columns (1, 2, 4 or 8 = all): a template parameter, so that the gather is only unrolled
+// over the 4 NQ register slots that can have contributors and the code of one variant stays inside the instruction cache
+template <class PL, int B, int NQ>
 __global__ void __launch_bounds__(PL::TG* B, 1) group_pp_kernel(const GroupPPArgs a, const GroupPPLens lens, const FusedOut out,
                                                                 const int64_t K, const int chunk) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -236,39 +238,53 @@ __global__ void __launch_bounds__(PL::TG* B, 1) group_pp_kernel(const GroupPPArg
         const bool ok = e < n_act && s + a.lo >= 0 && s + a.hi <= a.rxlen;
         const uint32_t xs = stage_s + 8u * (uint32_t)(o + g);
         o += B;
-        // ---- gather: v[c] = sum_j w[c][j] x[off[c][j]] over the contributor list of register slot c ----
+        // ---- gather: v[c] = sum_j w[c][j] x[off[c][j]] over the contributor list of register slot c; the chunk of 8
+        // (weights, offsets) after the current one is already on its way from tensor memory, four partial sums ----
         {
             uint32_t cw = tb + LY::COL_W, co = tb + LY::COL_O;
+            uint32_t wv[2][16], ov[2][8];
+            tc::tmem_ld16_issue(cw, wv[0]);
+            tc::tmem_ld8_issue(co, ov[0]);
+            int par = 0;                               // runtime parity of the chunk ring: kept uniform by two code copies
 #pragma unroll
-            for (int c = 0; c < V; ++c) {
-                float2 acc = make_float2(0.f, 0.f);
+            for (int c = 0; c < R1 * NQ; ++c) {
+                float2 acc[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) acc[i] = make_float2(0.f, 0.f);
                 const int n_c = lens.len[c];
 #pragma unroll 1
-                for (int j = 0; j < n_c; j += GP_CH) {
-                    uint32_t wv[16], ov[8];
-                    tc::tmem_ld16_issue(cw, wv);
-                    tc::tmem_ld8_issue(co, ov);
-                    cw += 2 * GP_CH;
-                    co += GP_CH;
-                    tc::tmem_ld_wait8(ov);
-                    float2 x[GP_CH];
+                for (int j = 0; j < n_c; j += 2 * GP_CH) {
+                    // lists are padded to a multiple of 16 contributors: two chunks per trip, static register parity
 #pragma unroll
-                    for (int u = 0; u < GP_CH; ++u)
-                        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(x[u].x), "=f"(x[u].y) : "r"(xs + ov[u]));
-                    tc::tmem_ld_wait16(wv);
+                    for (int h = 0; h < 2; ++h) {
+                        tc::tmem_ld_wait8(ov[h]);
+                        float2 x[GP_CH];
 #pragma unroll
-                    for (int u = 0; u < GP_CH; ++u) {
-                        const float2 y = make_float2(__uint_as_float(wv[2 * u]), __uint_as_float(wv[2 * u + 1]));
-                        acc = pfma(make_float2(x[u].y, x[u].x), make_float2(-y.y, y.y), pfma(x[u], make_float2(y.x, y.x), acc));
+                        for (int u = 0; u < GP_CH; ++u)
+                            asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(x[u].x), "=f"(x[u].y) : "r"(xs + ov[h][u]));
+                        tc::tmem_ld_wait16(wv[h]);
+                        cw += 2 * GP_CH;
+                        co += GP_CH;
+                        tc::tmem_ld16_issue(cw, wv[h ^ 1]);      // the next chunk (one chunk of padding follows the last list)
+                        tc::tmem_ld8_issue(co, ov[h ^ 1]);
+#pragma unroll
+                        for (int u = 0; u < GP_CH; ++u) {
+                            const float2 y = make_float2(__uint_as_float(wv[h][2 * u]), __uint_as_float(wv[h][2 * u + 1]));
+                            acc[u & 3] = pfma(make_float2(x[u].y, x[u].x), make_float2(-y.y, y.y), pfma(x[u], make_float2(y.x, y.x), acc[u & 3]));
+                        }
                     }
                 }
-                v[c] = acc;
+                v[c] = padd(padd(acc[0], acc[1]), padd(acc[2], acc[3]));
             }
+            (void)par;
+            tc::tmem_ld_wait8(ov[0]);                  // drain the last prefetch
+#pragma unroll
+            for (int c = R1 * NQ; c < V; ++c) v[c] = make_float2(0.f, 0.f);
         }
         // ---- pass 1: radix-4 columns q < nq_live (the others are all zero), raw stores ----
 #pragma unroll
         for (int q = 0; q < V / R1; ++q) {
-            if (q < a.nq_live) {
+            if (q < NQ) {
                 codelet_fft<R1>(v + q * R1);
 #pragma unroll
                 for (int j = 0; j < R1; ++j) buf[o1 + bitrev(j, ilog2(R1)) * K1STEP + q * QSTEP1] = v[q * R1 + j];
@@ -276,10 +292,7 @@ __global__ void __launch_bounds__(PL::TG* B, 1) group_pp_kernel(const GroupPPArg
         }
         bar();
         // ---- pass 2 (in place, warp local from here on) ----
-        if (a.nq_live == 1) gp_pass2<PL, 4>(v, buf, o2, tb + LY::COL_T1);
-        else if (a.nq_live == 2) gp_pass2<PL, 8>(v, buf, o2, tb + LY::COL_T1);
-        else if (a.nq_live == 4) gp_pass2<PL, 16>(v, buf, o2, tb + LY::COL_T1);
-        else gp_pass2<PL, 32>(v, buf, o2, tb + LY::COL_T1);
+        gp_pass2<PL, 4 * NQ>(v, buf, o2, tb + LY::COL_T1);
         __syncwarp();
         // ---- pass 3 ----
         {
