@@ -273,7 +273,7 @@ def config_line(which, lib, peaks, p32, p32src, steps):
         flops = c["K"] * c["F"] * 80.0
         return {"workload": "C3 GroupXcorrFFT: 64 groups x 128, fftlen 4096, 2^22 shifts", "ms": ms,
                 "cells_per_s": c["K"] * c["F"] / (ms * 1e-3), "peak_checked": [c["p0"], c["k0"]],
-                "roofline": fp32_roofline(flops, ms, p32, p32src, "group search kernel", 16.0 * c["K"], peaks)}
+                "roofline": fp32_roofline(flops, ms, p32, p32src, "group_pp_kernel<4096> (staged group windows, contributor lists in tensor memory, pruned transform)", 16.0 * c["K"], peaks)}
     if which in ("c4", "c6"):
         if which == "c4":
             c = signals.config_c4()
