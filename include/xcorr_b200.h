@@ -199,9 +199,13 @@ int32_t xc_time_scan_c128(const void* x, const void* y, int64_t N, double shift_
 /* ---- a9, a10: (multi-)template correlator -------------------------------------------------
  * xcorrRoutines.TemplateCrossCorrelator (xcorrRoutines.py:277-371) and
  * cupyExtensions.multiTemplateSlidingDotProduct (cupyExtensions.py:563-642 -> multiplySlices.cu:251-399).
- * templates: complex64 (T, L) HOST memory; conj != 0 conjugates them inside (TemplateCrossCorrelator
- * semantics), conj == 0 uses them as given (multiTemplateSlidingDotProduct semantics).
+ * templates: complex64 (T, L) HOST memory; conj is a flag word: XC_MT_CONJ conjugates them inside
+ * (TemplateCrossCorrelator semantics; without it they are used as given, multiTemplateSlidingDotProduct semantics),
+ * XC_MT_FP32 keeps the contraction on the FP32 SIMT kernel instead of the tensor cores (BF16 hi/lo split, FP32
+ * accumulate; both agree to 1e-5 -- the flag exists for callers who want plain FP32 products and for A/B runs).
  * energies: optional float32[T] template energies (NULL = computed inside). */
+#define XC_MT_CONJ 1
+#define XC_MT_FP32 2
 typedef struct xc_mt xc_mt;
 int32_t xc_mt_create(const void* templates, int32_t T, int32_t L, int32_t conj, const float* energies,
                      xc_mt** handle);

@@ -251,12 +251,24 @@ mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_ene
                             }
                             continue;
                         }
-                        if (cplx_out && o < K) {   // raw complex contraction d[s, t], row = shift
+                        if (cplx_out && o < K) {
                             const int col0 = nb * NT + 16 * c;
-                            float2* dst = cplx_out + (size_t)o * (size_t)caf_cols + col0;
+                            if (sqrt_out & 2) {
+                                // normalised complex QF, template-major (T, K): TemplateCrossCorrelator.correlate
+                                // (returnMax=False), xcorrRoutines.py:352-362; a warp writes 32 consecutive shifts per template
+                                const float sx = sqrtf(inv_ex);
 #pragma unroll
-                            for (int j = 0; j < 16; ++j)
-                                if (col0 + j < caf_cols) dst[j] = make_float2(re[j], im[j]);
+                                for (int j = 0; j < 16; ++j)
+                                    if (col0 + j < caf_cols) {
+                                        const float sc = sqrtf(inv[16 * c + j]) * sx;
+                                        cplx_out[(size_t)(col0 + j) * (size_t)K + (size_t)o] = make_float2(re[j] * sc, im[j] * sc);
+                                    }
+                            } else {               // raw complex contraction d[s, t], row = shift
+                                float2* dst = cplx_out + (size_t)o * (size_t)caf_cols + col0;
+#pragma unroll
+                                for (int j = 0; j < 16; ++j)
+                                    if (col0 + j < caf_cols) dst[j] = make_float2(re[j], im[j]);
+                            }
                         }
 #pragma unroll
                         for (int j = 0; j < 16; ++j) {
@@ -282,7 +294,7 @@ mt_tc_kernel(const uint8_t* __restrict__ pack, const float* __restrict__ inv_ene
             }
             if (o < K) {
                 const float q = bestv * inv_ex;
-                if (best_out) best_out[o] = sqrt_out ? sqrtf(q) : q;
+                if (best_out) best_out[o] = (sqrt_out & 1) ? sqrtf(q) : q;
                 if (tidx_out) tidx_out[o] = besti;
             }
         }
@@ -435,9 +447,6 @@ int32_t mt_tc_prepare(const float2* d_templates, int T, int L, int L8, const flo
     }
     plan->NT = (T >= 256) ? 256 : (T + 15) / 16 * 16;
     plan->NB = (T + plan->NT - 1) / plan->NT;
-    if (const char* e = getenv("XC_MT_FP32")) {
-        if (e[0] == '1') return XC_OK;            // A/B switch: force the FP32 SIMT kernel
-    }
     if (plan->NB * plan->NT > TC_MAX_TEMPLATES) return XC_OK;
     int ne_probe = 0;
     if (tc_pick_stages(plan->Lp, plan->NT, plan->NB, 4, &ne_probe) < 2) return XC_OK;
@@ -497,7 +506,11 @@ int32_t mt_tc_run(const MtTcPlan& plan, const float2* x, int64_t xlen, int64_t s
     float* scratch = nullptr;
     const int rmw = (plan.planes == 4) ? 6 : 4;                     // accumulator read-modify-writes per K step
     if (plan.nseg > 1 && (plan.L32 / TC_SUB) * rmw > 768) {
+#ifdef XC_EXPERIMENTS
         static const int flush_ks = [] { const char* e = getenv("XC_TC_FLUSH_KS"); return e ? atoi(e) : 64; }();
+#else
+        constexpr int flush_ks = 64;          // K steps per accumulator generation (tools/prec_groupfreq.py)
+#endif
         seg_per_flush = flush_ks / (plan.Lp / TC_SUB);
         if (seg_per_flush < 1) seg_per_flush = 1;
         scratch = reinterpret_cast<float*>(workspace(SLOT_TMP3, sizeof(float) * 2 * (size_t)plan.NT * TC_M * (size_t)ctas));

@@ -166,7 +166,7 @@ int32_t xc_mt_create(const void* templates, int32_t T, int32_t L, int32_t conj, 
         double e = 0.0;
         for (int n = 0; n < L; ++n) {
             const float2 v = in[(size_t)t * L + n];
-            padded[(size_t)t * L8 + n] = conj ? make_float2(v.x, -v.y) : v;
+            padded[(size_t)t * L8 + n] = (conj & XC_MT_CONJ) ? make_float2(v.x, -v.y) : v;
             e += (double)v.x * v.x + (double)v.y * v.y;
         }
         en[t] = energies ? energies[t] : (float)e;
@@ -183,7 +183,7 @@ int32_t xc_mt_create(const void* templates, int32_t T, int32_t L, int32_t conj, 
         xc_mt_destroy(h);
         return fail(e == cudaErrorMemoryAllocation ? XC_ERR_NOMEM : XC_ERR_CUDA, "template upload failed: %s", cudaGetErrorString(e));
     }
-    {
+    if (!(conj & XC_MT_FP32)) {          // XC_MT_FP32: keep the FP32 SIMT kernel (the tensor-core plan stays unusable)
         const int32_t st = mt_tc_prepare(h->d_templates, T, L, L8, h->d_energies, &h->tc);
         if (st != XC_OK) {
             xc_mt_destroy(h);
@@ -240,9 +240,10 @@ int32_t xc_mt_correlate(xc_mt* h, const void* x, int64_t xlen, int64_t start, in
     float* d_energy = (float*)workspace(SLOT_TMP1, sizeof(float) * (size_t)K);
     if (!d_energy) return XC_ERR_NOMEM;
     XC_TRY(sliding_sum_device(dx + start, true, xlen - start, 0, h->L, K, d_energy, 0, st));
-    if (h->tc.usable && !dfull) {
-        // dense complex contraction on the tensor cores (tcgen05), templates exact in BF16
-        XC_TRY(mt_tc_run(h->tc, dx, xlen, start, K, d_energy, db, dt, sqrt_out, st));
+    if (h->tc.usable) {
+        // dense complex contraction on the tensor cores (tcgen05); the full (T, K) complex QF comes out of the same
+        // kernel's complex epilogue (flag 2), normalised and template-major
+        XC_TRY(mt_tc_run(h->tc, dx, xlen, start, K, d_energy, db, dt, (sqrt_out ? 1 : 0) | (dfull ? 2 : 0), st, nullptr, dfull));
     } else {
         const size_t smem = mt_smem_bytes(h->L8);
         if ((int)smem > max_smem_optin()) return fail(XC_ERR_UNSUPPORTED, "template kernel needs %zu B of shared memory", smem);

@@ -874,7 +874,7 @@ class CyGroupXcorrFFT:
 # a9: TemplateCrossCorrelator  (xcorrRoutines.py:277-371)
 # ------------------------------------------------------------------------------------------------
 class _MtHandle:
-    def __init__(self, templates, conj, energies=None):
+    def __init__(self, templates, conj, energies=None, fp32=False):
         lib = _lib.load()
         if _lib.is_torch(templates):
             templates = templates.detach().cpu().numpy()
@@ -886,11 +886,12 @@ class _MtHandle:
             e = np.ascontiguousarray(energies, dtype=np.float32)
         self.T, self.L = t.shape
         self._h = C.c_void_p()
-        check(lib.xc_mt_create(_lib.ptr(t), self.T, self.L, 1 if conj else 0, _lib.ptr(e), C.byref(self._h)))
+        flags = (_lib.XC_MT_CONJ if conj else 0) | (_lib.XC_MT_FP32 if fp32 else 0)
+        check(lib.xc_mt_create(_lib.ptr(t), self.T, self.L, flags, _lib.ptr(e), C.byref(self._h)))
 
     @property
     def uses_tensor_cores(self):
-        """True when the returnMax / multiTemplateSlidingDotProduct path of this template set runs on tcgen05."""
+        """True when this template set runs on tcgen05 (every output: max / arg max and the full (T, K) complex QF)."""
         return bool(_lib.load().xc_mt_uses_tensor_cores(self._h))
 
     def run(self, x, start, K, want_best, want_full, sqrt_out, want_peak=False):

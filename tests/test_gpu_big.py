@@ -83,7 +83,11 @@ def test_large_chirpz_golden(xr, name, d):
     args = (cutout, rx, float(d["f1"]), float(d["f2"]), float(d["fs"]), float(d["step"]))
     res, freqs = xr.cztXcorr(*args, shifts=d["shifts"])
     same = freqs == d["freqs"]
-    assert same.mean() > 0.9
+    for i in np.nonzero(~same)[0]:                 # a differing pick must be a near-tie of the reference's own surface
+        row = d["caf"][i].astype(np.float64)
+        ka, kb = int(np.argmin(np.abs(d["fsearch"] - freqs[i]))), int(np.argmin(np.abs(d["fsearch"] - d["freqs"][i])))
+        assert abs(row[ka] - row[kb]) <= 1e-4 * row[kb], "frequency pick at %d is not a near-tie" % i
+    assert same.sum() >= same.size - max(1, same.size // 50)
     np.testing.assert_allclose(res[same], d["res"][same], rtol=0, atol=5e-5 * np.abs(d["res"]).max())
     i = int(np.argmax(np.abs(res)))
     assert d["shifts"][i] == int(d["p0"]) and freqs[i] == d["freqs"][i]
