@@ -77,3 +77,57 @@ def sharded_fastxcorr_peak(cutout, rx_shard, shard_first_shift, rank, device=Non
         row = peak_to_row(0.0, 0, -1, 0, rank)
     rows = allgather_peak(row, device)
     return qf2, fidx, global_peak(rows)
+
+
+def sharded_peak(local, shard_first_shift, rank, device=None):
+    """The exchange step shared by the three sharded correlators.  `local` = (QF^2, index (frequency bin or template),
+    shift inside the shard) of the rank's best shift, or None for an empty shard."""
+    if local is None:
+        row = peak_to_row(0.0, 0, -1, 0, rank)
+    else:
+        q, k, s = local
+        row = peak_to_row(q, k, shard_first_shift + int(s), 0, rank)
+    return global_peak(allgather_peak(row, device))
+
+
+def group_window(starts, L):
+    """Samples one shift of a GroupXcorrFFT needs behind it: starts[-1] - starts[0] + L (the halo is one less)."""
+    starts = np.asarray(starts, dtype=np.int64)
+    return int(starts.max() - starts.min()) + int(L)
+
+
+def sharded_group_peak(obj, rx_shard, shard_first_shift, rank, device=None, search=None):
+    """One rank's part of a shift-sharded GroupXcorrFFT search (halo = starts[-1] + L - 1 samples):
+    searches every shift of its shard (block + halo) and exchanges peaks.  `obj` is a GroupXcorrFFT; `search(rx, shifts)`
+    -> (QF^2[K], bins[K]) replaces obj.xcorr in the CPU test.  Returns (qf2_local, fidx_local, global_peak_dict)."""
+    window = group_window(obj.starts, obj.ygroupLen)
+    K_local = int(rx_shard.shape[0]) - window + 1
+    if K_local <= 0:
+        return None, None, sharded_peak(None, shard_first_shift, rank, device)
+    shifts = np.arange(K_local)
+    if search is None:
+        qf2, fidx, peak = obj.xcorrPeak(rx_shard, shifts)
+        local = (peak.qf2, peak.fidx, peak.shift)
+    else:
+        qf2, fidx = search(rx_shard, shifts)
+        k = int(np.argmax(qf2))
+        local = (qf2[k], fidx[k], k)
+    return qf2, fidx, sharded_peak(local, shard_first_shift, rank, device)
+
+
+def sharded_mt_peak(correlator, x_shard, shard_first_shift, rank, device=None, search=None):
+    """One rank's part of a shift-sharded multi-template search (halo = L - 1 samples).  `correlator` is a
+    TemplateCrossCorrelator (its handle gives QF^2 and the template index per shift); `search(x)` -> (QF^2[K], tidx[K])
+    replaces it in the CPU test.  The peak tuple carries the template index in `fidx`."""
+    L = int(correlator._templateLength)
+    K_local = int(x_shard.shape[0]) - L + 1
+    if K_local <= 0:
+        return None, None, sharded_peak(None, shard_first_shift, rank, device)
+    if search is None:
+        best, tidx, _, peak = correlator._handle.run(x_shard, 0, K_local, True, False, False, want_peak=True)
+        local = (peak.qf2, peak.aux, peak.shift)
+    else:
+        best, tidx = search(x_shard)
+        k = int(np.argmax(best))
+        local = (best[k], tidx[k], k)
+    return best, tidx, sharded_peak(local, shard_first_shift, rank, device)

@@ -725,6 +725,102 @@ class GroupXcorrCZT:
         return _as(caf, np.float64), self.cztFreq
 
 
+class pbIppGroupXcorrCZT:
+    """Drop-in for the reference's pybind class pbIppGroupXcorrCZT (pybinds/ippGroupXcorrCZT/pbGroupXcorrCZT.cpp:8-33,
+    GroupXcorrCZT.cpp): groups are added one by one (or sliced from a long array), xcorr(x, shiftStart, shiftStep,
+    numShifts) returns the float32 (numShifts, k) CAF with k = int((f2 - f1) / fstep + 1).  Same checks and messages
+    (pybind11 turns std::range_error / std::invalid_argument into ValueError).  The segmented tensor-core contraction of
+    GroupXcorrCZT is rebuilt lazily whenever the set of groups changed."""
+
+    def __init__(self, maxlen, f1, f2, fstep, fs, NUM_THREADS=1):
+        if NUM_THREADS < 1:
+            raise ValueError("Number of threads must be greater than 0")          # GroupXcorrCZT.cpp:32
+        self._N, self._f1, self._f2, self._fstep, self._fs = int(maxlen), float(f1), float(f2), float(fstep), float(fs)
+        self._k = int((self._f2 - self._f1) / self._fstep + 1)                    # GroupXcorrCZT.cpp:13
+        self._threads = int(NUM_THREADS)
+        self._starts, self._groups, self._energies = [], [], []
+        self._handle = None
+
+    def getNumThreads(self):
+        return self._threads
+
+    def addGroup(self, start, group, autoConj=True):
+        group = np.asarray(group)
+        if group.ndim != 1:
+            raise ValueError("Input must be 1d")
+        start, length = int(start), int(group.shape[0])
+        for gs, g in zip(self._starts, self._groups):                              # GroupXcorrCZT.cpp:45-59
+            ge = gs + g.size
+            if gs <= start < ge:
+                raise ValueError("Group start overlaps with existing group! [%d,%d)" % (gs, ge))
+            if gs <= start + length < ge:
+                raise ValueError("Group end overlaps with existing group! [%d,%d)" % (gs, ge))
+        if length > self._N:
+            raise ValueError("Length of group exceeds maximum length")
+        g = np.ascontiguousarray(group, dtype=np.complex64)
+        self._starts.append(start)
+        self._groups.append(g.conj() if autoConj else g.copy())
+        self._energies.append(float(np.linalg.norm(g) ** 2))
+        self._handle = None
+
+    def addGroupsFromArray(self, starts, lengths, arr, autoConj=True):
+        starts, lengths, arr = np.asarray(starts), np.asarray(lengths), np.asarray(arr)
+        if arr.ndim != 1:
+            raise ValueError("Input must be 1d")
+        if starts.ndim != 1:
+            raise ValueError("Starts must be 1d")
+        if lengths.ndim != 1:
+            raise ValueError("Lengths must be 1d")
+        if lengths.shape[0] != starts.shape[0]:
+            raise ValueError("Lengths must be same size as starts")
+        m = int(starts.min())                                                       # GroupXcorrCZT.cpp:84-95
+        for s0, n in zip(starts, lengths):
+            self.addGroup(int(s0) - m, arr[int(s0):int(s0) + int(n)], autoConj)
+
+    def printGroups(self):
+        for i, (gs, g, e) in enumerate(zip(self._starts, self._groups, self._energies)):
+            print("Group %d: [%d, %d)" % (i, gs, gs + g.size))
+            print("Energy = %f" % e)
+
+    def resetGroups(self):
+        self._starts, self._groups, self._energies = [], [], []
+        self._handle = None
+
+    def _build(self):
+        from .spectralRoutines import CZTCached
+        order = np.argsort(np.asarray(self._starts, dtype=np.int64), kind="stable")
+        starts = np.asarray(self._starts, dtype=np.int64)[order]
+        lengths = np.array([self._groups[i].size for i in order], dtype=np.int32)
+        ycat = np.hstack([self._groups[i] for i in order])
+        cz = CZTCached(self._N, self._f1, self._f2, self._fstep, self._fs)
+        bins = cz.f0_cycles + np.arange(cz.k) * cz.df_cycles
+        nominal = (self._f1 + np.arange(self._k) * self._fstep) / self._fs         # ippe Slope(f1, fstep), GroupXcorrCZT.cpp:340-345
+        self._off = int(starts.min())
+        self._handle = _GroupFreqHandle(ycat, starts - self._off, lengths, bins, nominal)
+
+    def xcorr(self, x, shiftStart, shiftStep, numShifts):
+        if shiftStep < 0:
+            raise ValueError("shiftStep cannot be negative")                       # GroupXcorrCZT.cpp:111-112
+        if not self._starts:
+            raise ValueError("No groups have been defined!")
+        if _lib.np_dtype_of(x) != np.dtype(np.complex64):
+            raise TypeError("x must be complex64")
+        x = _lib.contiguous(x)
+        for gs, g in zip(self._starts, self._groups):                              # GroupXcorrCZT.cpp:153-163
+            xi = int(shiftStart) + gs
+            if xi < 0:
+                raise ValueError("Shifts accesses negative indices!")
+            if xi + int(numShifts) * int(shiftStep) + g.size >= x.shape[0]:
+                raise ValueError("Input length is insufficient for search range!")
+        if self._handle is None:
+            self._build()
+        shifts = int(shiftStart) + np.arange(int(numShifts), dtype=np.int64) * max(int(shiftStep), 0) + self._off
+        if int(shiftStep) == 0:
+            shifts = np.full(int(numShifts), int(shiftStart) + self._off, dtype=np.int64)
+        _, _, caf = self._handle.run_shifts(x, shifts, False, True)
+        return caf
+
+
 class GroupXcorrCZT_Permutations:
     """Drop-in for xcorrRoutines.GroupXcorrCZT_Permutations (1264-1690): every template of every group is correlated
     once over the CZT grid (complex surfaces kept on the device), then any permutation of one template per group is
@@ -947,4 +1043,4 @@ class TemplateCrossCorrelator:
         return best, tidx.astype(np.int64)                                               # cp.argmax dtype (:367)
 
 
-_lib.adopt_module(globals(), ['fastXcorr', 'cztXcorr', 'fastXcorrPeak', 'cp_fastXcorr', 'cp_fastXcorr_v2', 'CyIppXcorrFFT', 'GroupXcorrFFT', 'GroupXcorr', 'GroupXcorrGPU', 'GroupXcorrCZT', 'GroupXcorrCZT_Permutations', 'CyGroupXcorrFFT', 'TemplateCrossCorrelator', 'fineFreqTimeSearch', 'GenXcorr', 'calcQF2'])
+_lib.adopt_module(globals(), ['fastXcorr', 'cztXcorr', 'fastXcorrPeak', 'cp_fastXcorr', 'cp_fastXcorr_v2', 'CyIppXcorrFFT', 'GroupXcorrFFT', 'GroupXcorr', 'GroupXcorrGPU', 'GroupXcorrCZT', 'GroupXcorrCZT_Permutations', 'pbIppGroupXcorrCZT', 'CyGroupXcorrFFT', 'TemplateCrossCorrelator', 'fineFreqTimeSearch', 'GenXcorr', 'calcQF2'])

@@ -134,3 +134,65 @@ def test_c_abi_nccl_peak_exchange(tmp_path):
     outs = [p.communicate(timeout=240)[0] for p in procs]
     for r, (p, o) in enumerate(zip(procs, outs)):
         assert p.returncode == 0 and ("rank %d ok" % r) in o, o[-2000:]
+
+
+def test_pbIppGroupXcorrCZT_call_surface(xr):
+    """The incremental add-group class of the reference's pybind module (pbGroupXcorrCZT.cpp:8-33) against golden vectors
+    of the real GroupXcorrCZT (same mathematics, GroupXcorrCZT.cpp:106-330), plus its argument checks."""
+    import glob
+    golden = os.path.join(ROOT, "tests", "golden")
+    for path in sorted(glob.glob(os.path.join(golden, "groupfreq_*.npz"))):
+        d = np.load(path)
+        y, starts, lengths, rx = d["y"], d["starts"], d["lengths"], d["rx"]
+        K = int(d["shifts"].size)
+        pb = xr.pbIppGroupXcorrCZT(int(lengths.max()), float(d["f1"]), float(d["f2"]), float(d["bw"]), float(d["fs"]), 4)
+        assert pb.getNumThreads() == 4
+        pb.addGroupsFromArray(starts.astype(np.int32), lengths.astype(np.int32), y)
+        out = pb.xcorr(rx, 0, 1, K)
+        assert out.dtype == np.float32 and out.shape == d["caf"].shape
+        np.testing.assert_allclose(out, d["caf"], rtol=1e-4, atol=2e-6 * d["caf"].max())
+        # groups added one by one in another order, a stepped shift list, device input
+        pb.resetGroups()
+        z = starts - starts.min()
+        for g in reversed(range(starts.size)):
+            pb.addGroup(int(z[g]), y[starts[g]:starts[g] + lengths[g]])
+        out2 = pb.xcorr(_dev(rx), 1, 3, (K - 1) // 3)
+        np.testing.assert_allclose(out2.cpu().numpy(), d["caf"][1:1 + 3 * ((K - 1) // 3):3], rtol=1e-4, atol=2e-6 * d["caf"].max())
+    pb = xr.pbIppGroupXcorrCZT(12, -0.1, 0.1, 0.1, 100.0)
+    data = np.arange(200).astype(np.float32).view(np.complex64)               # the reference's own test.py
+    with pytest.raises(ValueError, match="No groups"):
+        pb.xcorr(data, 0, 1, 3)
+    pb.addGroup(0, data[10:20])
+    pb.addGroup(60, data[70:82])
+    with pytest.raises(ValueError, match="overlaps"):
+        pb.addGroup(65, data[75:85])
+    with pytest.raises(ValueError, match="maximum length"):
+        pb.addGroup(20, data[0:13])
+    with pytest.raises(ValueError, match="negative"):
+        pb.xcorr(data, 9, -1, 3)
+    with pytest.raises(ValueError, match="insufficient"):
+        pb.xcorr(data, 9, 1, 30)
+    with pytest.raises(ValueError, match="greater than 0"):
+        xr.pbIppGroupXcorrCZT(12, -0.1, 0.1, 0.1, 100.0, 0)
+    assert pb.xcorr(data, 9, 1, 3).shape == (3, 3)
+
+
+def test_sharded_group_and_template_drivers_on_the_device(xr):
+    """dist.sharded_group_peak / sharded_mt_peak with the real searches (world size 1: the allgather is the identity)."""
+    from oracle import xcorr_oracle as orc
+    from pydsproutines_b200 import dist as xd
+    c = signals.config_c3(log2_shifts=13)
+    obj = xr.GroupXcorrFFT(c["ygroups"], c["starts"], 1, fftlen=c["F"])
+    window = xd.group_window(obj.starts, obj.ygroupLen)
+    rx = c["rx"][:c["K"] + window - 1]
+    q, f, g = xd.sharded_group_peak(obj, _dev(rx), 1000, 0)
+    assert q.shape[0] == c["K"] and g["shift"] == 1000 + c["p0"] and g["fidx"] == c["k0"] and g["rank"] == 0
+    rng = np.random.default_rng(12)
+    templates = signals.qpsk(rng, 5 * 64).reshape(5, 64)
+    x = signals.cnoise(rng, 3000)
+    x[1234:1234 + 64] += 2.0 * templates[3]
+    tcc = xr.TemplateCrossCorrelator(templates, x.size)
+    best, tidx, g = xd.sharded_mt_peak(tcc, _dev(x), 50, 0)
+    assert best.shape[0] == 3000 - 63 and g["shift"] == 50 + 1234 and g["fidx"] == 3
+    ti_ref, q_ref = orc.multiTemplateSlidingDotProduct(x, templates.conj(), 0, 3000 - 63)
+    np.testing.assert_allclose(best.cpu().numpy(), q_ref, rtol=1e-4, atol=1e-6 * q_ref.max())

@@ -154,6 +154,74 @@ def test_sharded_peak_exchange_gloo_world2(tmp_path):
     assert "rank0-ok" in r.stdout and "rank1-ok" in r.stdout
 
 
+_GLOO_WORKER_GROUP_MT = r"""
+import os, sys, types
+import numpy as np
+sys.path.insert(0, %(root)r)
+import torch.distributed as dist
+from pydsproutines_b200 import dist as xd, signals
+from oracle import xcorr_oracle as orc     # the CPU checker stands in for the GPU search in this host-logic test
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+rng = np.random.default_rng(5)
+# ---- GroupXcorrFFT: 4 groups x 16, fftlen 64, halo = starts[-1] + L - 1; peak in rank 1, weaker decoy in rank 0 ----
+G, L, F, K = 4, 16, 64, 240
+starts = np.array([0, 40, 80, 120])
+y = signals.qpsk(rng, G * L).reshape(G, L)
+window = xd.group_window(starts, L)
+rx = signals.cnoise(rng, K + window - 1)
+for p0, k0, amp in ((170, 5, 1.0), (30, 11, 0.5)):
+    for g in range(G):
+        a = p0 + int(starts[g])
+        rx[a:a + L] += np.complex64(amp) * y[g] * signals.tone(L, k0, F, offset=int(starts[g]))
+first, n = xd.shard_samples(K, window, rank, world)
+spec = types.SimpleNamespace(starts=starts, ygroupLen=L)
+ref = orc.GroupXcorrFFT(y, starts, 1, fftlen=F)
+pad = np.zeros(F + 1, np.complex64)          # the reference asserts fftlen samples of slack behind the last window (:1143)
+q, f, g = xd.sharded_group_peak(spec, rx[first:first + n], first, rank, search=lambda r, sh: ref.xcorr(np.concatenate([r, pad]), sh))
+assert g["shift"] == 170 and g["fidx"] == 5 and g["rank"] == 1, g
+qa, fa = ref.xcorr(np.concatenate([rx, pad]), np.arange(K))
+lo, hi = xd.shard_range(K, rank, world)
+assert np.array_equal(q, qa[lo:hi]) and np.array_equal(f, fa[lo:hi])
+if rank == 0:
+    assert int(np.argmax(q)) == 30 and f[30] == 11                      # the decoy wins locally, loses globally
+# ---- multi-template: 6 templates x 32, halo = L - 1; template 4 planted in rank 0, decoy template 1 in rank 1 ----
+T, L, n_x = 6, 32, 400
+templates = signals.qpsk(rng, T * L).reshape(T, L)
+x = signals.cnoise(rng, n_x)
+x[60:60 + L] += 2.0 * templates[4]
+x[300:300 + L] += 1.0 * templates[1]
+K = n_x - L + 1
+first, n = xd.shard_samples(K, L, rank, world)
+spec = types.SimpleNamespace(_templateLength=L)
+def search(xs):
+    ti, q = orc.multiTemplateSlidingDotProduct(xs, templates.conj(), 0, xs.size - L + 1)
+    return q, ti
+best, tidx, g = xd.sharded_mt_peak(spec, x[first:first + n], first, rank, search=search)
+assert g["shift"] == 60 and g["fidx"] == 4 and g["rank"] == 0, g
+if rank == 1:
+    k = int(np.argmax(best)); assert first + k == 300 and tidx[k] == 1
+# an empty shard never wins
+_, _, g2 = xd.sharded_mt_peak(spec, x[:L - 1] if rank == 1 else x[first:first + n], first, rank, search=search)
+assert g2["rank"] == 0 and g2["shift"] == 60
+dist.destroy_process_group()
+sys.stdout.write("rank" + str(rank) + "-ok\n")
+"""
+
+
+def test_sharded_group_and_template_search_gloo_world2(tmp_path):
+    """SURVEY.md 8e halos of the other two correlators (starts[-1] + L - 1 for GroupXcorrFFT, L - 1 for the template
+    correlator): shards reproduce the unsharded search exactly and the cross-rank reduction rejects a local decoy."""
+    script = tmp_path / "worker2.py"
+    script.write_text(_GLOO_WORKER_GROUP_MT % {"root": ROOT})
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29519", str(script)]
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    assert "rank0-ok" in r.stdout and "rank1-ok" in r.stdout
+
+
 def test_peak_argmax_rule(lib):
     """The deterministic cross-rank reduction of the C-ABI (largest QF^2, lowest shift on ties, negative shift = empty
     shard) agrees with pydsproutines_b200.dist.global_peak."""
