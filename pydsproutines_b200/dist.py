@@ -106,7 +106,12 @@ def sharded_group_peak(obj, rx_shard, shard_first_shift, rank, device=None, sear
         return None, None, sharded_peak(None, shard_first_shift, rank, device)
     shifts = np.arange(K_local)
     if search is None:
-        qf2, fidx, peak = obj.xcorrPeak(rx_shard, shifts)
+        # the handle, not obj.xcorr: the reference's argument check wants fftlen samples of slack behind the last window
+        # (xcorrRoutines.py:1143), which a halo of window - 1 samples does not have -- the kernels only read the windows
+        from . import xcorrRoutines as xr
+        from ._lib import contiguous
+        rx_shard = contiguous(rx_shard)
+        qf2, fidx, _, peak = obj._handle.run(rx_shard, xr._group_shifts(shifts, rx_shard), True, False, want_peak=True)
         local = (peak.qf2, peak.fidx, peak.shift)
     else:
         qf2, fidx = search(rx_shard, shifts)
