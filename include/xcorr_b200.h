@@ -11,7 +11,12 @@
  *     (a cudaStream_t, NULL = default stream) and does NOT synchronise;
  *   - every function returns an int32 status (XC_OK == 0, negative on error) and leaves a
  *     thread-local message readable through xc_last_error(); no C++ exception crosses the ABI;
- *   - there is no CPU fallback: without a CUDA device every compute call returns XC_ERR_CUDA.
+ *   - there is no CPU fallback: without a CUDA device every compute call returns XC_ERR_CUDA;
+ *   - threading: every entry point takes one process-wide lock (calls from several host threads are serialised); the
+ *     device workspace, the plan caches and the kernel attributes are kept PER DEVICE (xc_set_device() then calls on
+ *     another device of the same process work); the workspace slots of a device are shared by all its streams, so
+ *     keep ONE stream per device in flight (XC_DEVICE calls only enqueue; a second stream would reuse the
+ *     normalisation scratch while the first still reads it).
  *
  * Each entry point cites the reference interface it replaces (file:line in pydsproutines @ e005737).
  */
