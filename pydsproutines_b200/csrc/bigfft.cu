@@ -131,19 +131,32 @@ __global__ void __launch_bounds__(PL::TG* B) big_cols_kernel(const BigColsArgs a
                 v[q * PL::R1 + n1] = x;
             }
         block_fft<PL>(v, th, tab, buf, t, bar);
-        if (col < a.NC) {
-            float2* const o = a.out + (int64_t)b * a.L + col;
+        // ---- twiddle, then the transposed store through the exchange buffers: group g leaves its R outputs in natural
+        // order in its own buffer (skewed by SK g cells against bank conflicts), and the whole CTA writes, for every k,
+        // the B adjacent columns as one contiguous run of 8 B bytes (full 32-byte sectors instead of 8 bytes per lane at
+        // a stride of NC samples) ----
+        bar();                                                     // last-pass loads of the group are done
+        constexpr int SK = (B > 1 && (PL::BUF - PL::N) / (B - 1) >= 4) ? 4 : ((B > 1 && (PL::BUF - PL::N) / (B - 1) >= 1) ? 1 : 0);
 #pragma unroll
-            for (int q = 0; q < V / PL::RL; ++q)
+        for (int q = 0; q < V / PL::RL; ++q)
 #pragma unroll
-                for (int j = 0; j < PL::RL; ++j) {
-                    const int k = output_bin<PL>(t, q, j);
-                    const int64_t x = (int64_t)k * col;            // < L: no reduction needed
-                    const float2 w = cmul(__ldg(a.twa + (x >> TWB_BITS)), __ldg(a.twb + (x & ((1 << TWB_BITS) - 1))));
-                    o[(int64_t)k * a.NC] = cmul(v[q * PL::RL + j], w);
-                }
+            for (int j = 0; j < PL::RL; ++j) {
+                const int k = output_bin<PL>(t, q, j);
+                const int64_t x = (int64_t)k * (col < a.NC ? col : 0);     // < L: no reduction needed
+                const float2 w = cmul(__ldg(a.twa + (x >> TWB_BITS)), __ldg(a.twb + (x & ((1 << TWB_BITS) - 1))));
+                buf[k + SK * g] = cmul(v[q * PL::RL + j], w);
+            }
+        __syncthreads();
+        {
+            const float2* const bufs = reinterpret_cast<const float2*>(smem_raw + PL::TABLE_BYTES);
+            float2* const o = a.out + (int64_t)b * a.L + (int64_t)tile * B;
+            const int ncol = (a.NC - tile * B < B) ? (a.NC - tile * B) : B;
+            for (int i = threadIdx.x; i < PL::N * B; i += TG * B) {
+                const int k = i / B, gg = i % B;
+                if (gg < ncol) o[(int64_t)k * a.NC + gg] = bufs[(size_t)gg * PL::BUF + k + SK * gg];
+            }
         }
-        bar();   // the exchange buffer is free for the next tile
+        __syncthreads();                                           // buffers free for the next tile
     }
 }
 
