@@ -10,11 +10,13 @@ namespace xc {
 
 // one CTA per group: y[yStarts[g] + i] = x[xStarts[g] + i], i < lengths[g]
 __global__ void copy_groups_kernel(const float2* __restrict__ x, float2* __restrict__ y, const int32_t* __restrict__ xs,
-                                   const int32_t* __restrict__ ys, const int32_t* __restrict__ len) {
+                                   const int32_t* __restrict__ ys, const int32_t* __restrict__ len, int64_t xlen, int64_t ylen) {
     const int g = blockIdx.x;
-    const float2* src = x + xs[g];
-    float2* dst = y + ys[g];
+    const int64_t a = xs[g], b = ys[g];
     const int n = len[g];
+    if (n <= 0 || a < 0 || b < 0 || a + n > xlen || b + n > ylen) return;   // a group that leaves either buffer is skipped
+    const float2* src = x + a;
+    float2* dst = y + b;
     for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
 }
 
@@ -145,6 +147,14 @@ int32_t xc_copy_groups_c64(const void* x, int64_t xlen, void* y, int64_t ylen, c
     float2* dy = (float2*)y;
     const int32_t *dxs = x_starts, *dys = y_starts, *dl = lengths;
     if (where == XC_HOST) {
+        // the three index arrays are host memory here: a bad start or length would write into neighbouring workspace
+        // blocks (XC_DEVICE callers get the same check per group inside the kernel)
+        for (int g = 0; g < G; ++g) {
+            if (lengths[g] < 0 || x_starts[g] < 0 || y_starts[g] < 0 || (int64_t)x_starts[g] + lengths[g] > xlen ||
+                (int64_t)y_starts[g] + lengths[g] > ylen)
+                return fail(XC_ERR_RANGE, "group %d: [%d, %d) of x (%lld samples) -> [%d, %d) of y (%lld samples) is out of bounds", g,
+                            x_starts[g], x_starts[g] + lengths[g], (long long)xlen, y_starts[g], y_starts[g] + lengths[g], (long long)ylen);
+        }
         float2* bx = (float2*)workspace(SLOT_IN0, sizeof(float2) * (size_t)xlen);
         float2* by = (float2*)workspace(SLOT_OUT0, sizeof(float2) * (size_t)ylen);
         int32_t* bi = (int32_t*)workspace(SLOT_IN2, sizeof(int32_t) * 3 * (size_t)G);
@@ -156,7 +166,7 @@ int32_t xc_copy_groups_c64(const void* x, int64_t xlen, void* y, int64_t ylen, c
         XC_CUDA_TRY(cudaMemcpyAsync(bi + 2 * (size_t)G, lengths, sizeof(int32_t) * (size_t)G, cudaMemcpyHostToDevice, st));
         dx = bx; dy = by; dxs = bi; dys = bi + G; dl = bi + 2 * (size_t)G;
     }
-    copy_groups_kernel<<<(unsigned)G, 256, 0, st>>>(dx, dy, dxs, dys, dl);
+    copy_groups_kernel<<<(unsigned)G, 256, 0, st>>>(dx, dy, dxs, dys, dl, xlen, ylen);
     XC_LAUNCH_CHECK();
     if (where == XC_HOST) {
         XC_CUDA_TRY(cudaMemcpyAsync(y, dy, sizeof(float2) * (size_t)ylen, cudaMemcpyDeviceToHost, st));

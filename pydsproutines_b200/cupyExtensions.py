@@ -78,9 +78,38 @@ def multiTemplateSlidingDotProduct(d_x, d_templates, startIdx, idxlen, d_templat
         cupyRequireDtype(np.float32, d_templateEnergies)
         if int(np.prod(d_templateEnergies.shape)) != T:
             raise ValueError("d_templateEnergies should have 1 value per template.")
-    h = _MtHandle(d_templates, False, d_templateEnergies)
+    h = _mt_handle_for(d_templates, d_templateEnergies)
     best, tidx, _, _ = h.run(_lib.contiguous(d_x), startIdx, idxlen, True, False, False)
     return tidx, best
+
+
+# The reference calls multiTemplateSlidingDotProduct once per batch with the same device templates; building a handle
+# costs a device-to-host copy of the templates, the BF16 exactness check and the repack.  The last few handles are kept,
+# keyed on the template buffer (address, shape, torch version counter) and the energies buffer.
+_MT_CACHE = []
+_MT_CACHE_MAX = 4
+
+
+def _buffer_key(a):
+    if a is None:
+        return None
+    if _lib.is_torch(a):
+        return ("t", a.data_ptr(), tuple(a.shape), a._version, str(a.device))
+    return ("n", a.__array_interface__["data"][0], a.shape, hash(a.tobytes()) if a.size <= 1 << 16 else None)
+
+
+def _mt_handle_for(templates, energies):
+    key = (_buffer_key(templates), _buffer_key(energies))
+    cacheable = all(k is None or k[-1] is not None or k[0] == "t" for k in key)
+    if cacheable:
+        for k, h, _, _ in _MT_CACHE:
+            if k == key:
+                return h
+    h = _MtHandle(templates, False, energies)
+    if cacheable:
+        _MT_CACHE.append((key, h, templates, energies))     # the references keep the buffers (and their addresses) alive
+        del _MT_CACHE[:-_MT_CACHE_MAX]
+    return h
 
 
 def cupyFindLocalMaxima(x, minHeight, numOutputPerBlk=32, THREADS_PER_BLK=32, maxNumPeaks=10000):
