@@ -21,7 +21,8 @@
 namespace xc {
 
 // search_pp.cu: the ping-pong layout of the N = 8192 search (fused_fft_pp.cuh); fold = 1 is the shipped variant
-int32_t search_pp_device(const StagedArgs& a, const FusedOut& out, int64_t K, int fold, cudaStream_t stream);
+int32_t search_pp_device(const StagedArgs& a, const FusedOut& out, int64_t K, int N, int fold, cudaStream_t stream);
+bool search_pp_takes(int N);
 
 // ---------------------------------------------------------------------------------------------
 // loader of the fused kernel: v[n] = rx[s + n] * conj(cutout[n])
@@ -210,21 +211,23 @@ struct FreqRunner {
         using PF = PlanFor<LOG2N>;
         using LD = CutoutLoader<typename PF::PL, PF::CS>;
         LD ld{rx, rxlen, cutout, sl.shift0, sl.step, sl.shifts};
-        if constexpr (LOG2N == 13) {
-            // contiguous shift range, (max, arg max) outputs: two free-running thread groups per SM over one staged
-            // rx window, constants in tensor memory (fused_fft_pp.cuh).  Short ranges, shift lists with a step or a
-            // gather table and the CAF / complex outputs stay on the B = 2 layout below.
+        if constexpr (LOG2N >= 11 && LOG2N <= 13) {
+            // contiguous shift range, (max, arg max) outputs, 2048 / 4096 / 8192 points: free-running thread groups per SM
+            // over one staged rx window, constants in tensor memory (fused_fft_pp.cuh).  Short ranges, shift lists with
+            // a step or a gather table and the CAF / complex outputs stay on the B-groups-per-CTA layout below.
             const int layout = search_layout();
             const bool plain = !out.caf && !out.cplx;
             const bool contiguous = !sl.shifts && sl.step == 1 && sl.K >= 16 * (int64_t)sm_count();
             if (layout == LAYOUT_PP && plain && contiguous)
-                return search_pp_device(StagedArgs{rx, rxlen, cutout, sl.shift0}, out, sl.K, 1, stream);
+                return search_pp_device(StagedArgs{rx, rxlen, cutout, sl.shift0}, out, sl.K, 1 << LOG2N, 1, stream);
 #ifdef XC_EXPERIMENTS
-            if (layout == LAYOUT_PP_CHAIN && plain && contiguous)
-                return search_pp_device(StagedArgs{rx, rxlen, cutout, sl.shift0}, out, sl.K, 0, stream);
-            if (layout == LAYOUT_STAGED && plain && contiguous)
-                return launch_fused_staged<typename PF::PL>(StagedArgs{rx, rxlen, cutout, sl.shift0}, out, sl.K, stream);
-            if (layout == LAYOUT_DUAL && plain) return launch_fused_dual<typename PF::PL, LD>(ld, out, sl.K, stream);
+            if constexpr (LOG2N == 13) {
+                if (layout == LAYOUT_PP_CHAIN && plain && contiguous)
+                    return search_pp_device(StagedArgs{rx, rxlen, cutout, sl.shift0}, out, sl.K, 1 << LOG2N, 0, stream);
+                if (layout == LAYOUT_STAGED && plain && contiguous)
+                    return launch_fused_staged<typename PF::PL>(StagedArgs{rx, rxlen, cutout, sl.shift0}, out, sl.K, stream);
+                if (layout == LAYOUT_DUAL && plain) return launch_fused_dual<typename PF::PL, LD>(ld, out, sl.K, stream);
+            }
 #endif
         }
         return launch_fused<typename PF::PL, PF::B, LD>(ld, out, sl.K, stream);

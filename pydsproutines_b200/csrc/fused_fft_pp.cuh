@@ -63,8 +63,12 @@ __device__ __forceinline__ void tmem_ld_wait16(uint32_t* u) {
 template <class PL, int B, bool FOLD>
 struct PPLayout {
     static_assert(PL::P == 3 && PL::R2 == 32 && PL::R3 == 32 && PL::V % 32 == 0, "three passes, radix-32 tail");
-    static_assert(PL::TG % 128 == 0, "a group must cover the four TMEM lane quarters");
-    static_assert(PL::R1 == 8, "one tcgen05.ld.x16 = the 8 conj(cutout) values of one pass-1 column");
+    static_assert(PL::TG == 64 || PL::TG % 128 == 0, "groups of 64 threads pair up over the four TMEM lane quarters");
+    static_assert(PL::R1 == 8 || PL::R1 == 4 || PL::R1 == 2, "one tcgen05.ld.x16 = the 8 conj(cutout) values of 8 / R1 pass-1 columns");
+    static_assert(FOLD || PL::R1 == 8, "the power-chain variant exists for the 8192-point plan only");
+    // groups whose warps cover all four lane quarters between them write the constants (1 group of >= 128 threads,
+    // 2 groups of 64); every other group reads the lanes of the writer with the same warp position
+    static constexpr int WRITERS = (PL::TG >= 128) ? 1 : 128 / PL::TG;
     static constexpr int W = 2048;                                        // extra samples behind the window
     static_assert(W % B == 0, "refills happen at the same iteration in every group");
     static constexpr size_t OFF_BUF = 0;
@@ -76,12 +80,12 @@ struct PPLayout {
     // tensor-memory columns of one thread (32-bit each)
     static constexpr int NQ1 = PL::V / PL::R1;                            // pass-1 columns per thread
     static constexpr int NQ2 = PL::V / PL::R2;                            // pass-2 / pass-3 columns per thread
-    static_assert(NQ1 <= 8, "the pass-1 base twiddles fit one x16 load");
+    static_assert(FOLD || NQ1 <= 8, "the pass-1 base twiddles fit one x16 load");
     static constexpr int COL_CUT = 0;                                     // conj(cutout): slot j = q * R1 + n1
     static constexpr int COL_TW1 = 2 * PL::V;                             // !FOLD: W_N^(t + TG q), q < NQ1; FOLD: T1[q][.]
     static constexpr int COL_TW2 = COL_TW1 + (FOLD ? 2 * PL::R2 * NQ2 : 16);   // !FOLD: W_M1^(d k2), k2 < 32; FOLD: T2[.]
     static constexpr int CW = COL_TW2 + 2 * PL::R2;
-    static constexpr int COPIES = PL::TG / 128;                           // warps of a group per lane quarter
+    static constexpr int COPIES = (PL::TG >= 128) ? PL::TG / 128 : 1;     // warps of a group per lane quarter
     static constexpr int TMEM_COLS = (CW * COPIES <= 32) ? 32 : (CW * COPIES <= 64) ? 64 : (CW * COPIES <= 128) ? 128 : (CW * COPIES <= 256) ? 256 : 512;
     static_assert(CW * COPIES <= 512, "tensor memory holds 512 columns");
 };
@@ -180,56 +184,45 @@ __device__ __forceinline__ void pp_block_fft_fold(float2* v, const float2* x, co
     const int o1 = (t / RL) * ROW + (t % RL);
     uint32_t cu[2][16];
     tc::tmem_ld16_issue(tb + L::COL_CUT, cu[0]);
-#ifndef XC_PP_NOPIPE
-    // explicit software pipeline: the window samples and the conj(cutout) chunk of column q + 1 are requested before
-    // the arithmetic of column q (volatile loads keep their order; the empty asm ties column q's arithmetic behind them)
-    float2 xs[2][R1];
+    // A chunk = 8 conj(cutout) values (one tcgen05.ld.x16) = CPC = 8 / R1 pass-1 columns.  Explicit software pipeline: the
+    // window samples and the conj(cutout) chunk after the current one are requested before the arithmetic of the current
+    // chunk (volatile loads keep their order; the empty asm ties the arithmetic behind them).
+    constexpr int CPC = 8 / R1, NCH = PL::V / 8;
+    float2 xs[2][8];
     const uint32_t xa = tc::smem_u32(x);
 #pragma unroll
-    for (int n1 = 0; n1 < R1; ++n1) xs[0][n1] = x[input_index<PL>(0, 0, n1)];
-#endif
+    for (int i = 0; i < 8; ++i) xs[0][i] = x[input_index<PL>(0, i / R1, i % R1)];
     tc::tmem_ld_wait16(cu[0]);
-    // ---- products + pass 1 + first-exchange stores (raw), column by column ----
+    // ---- products + pass 1 + first-exchange stores (raw), chunk by chunk ----
 #pragma unroll
-    for (int q = 0; q < NQ1; ++q) {
-        if (q + 1 < NQ1) {
-            tc::tmem_ld16_issue(tb + L::COL_CUT + 16 * (q + 1), cu[(q + 1) & 1]);
-#ifndef XC_PP_NOPIPE
+    for (int c = 0; c < NCH; ++c) {
+        if (c + 1 < NCH) {
+            tc::tmem_ld16_issue(tb + L::COL_CUT + 16 * (c + 1), cu[(c + 1) & 1]);
 #pragma unroll
-            for (int n1 = 0; n1 < R1; ++n1)
+            for (int i = 0; i < 8; ++i)
                 asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];"
-                             : "=f"(xs[(q + 1) & 1][n1].x), "=f"(xs[(q + 1) & 1][n1].y)
-                             : "r"(xa + 8u * (uint32_t)(n1 * PL::M1 + PL::TG * (q + 1))));
-            asm volatile("" : "+r"(cu[q & 1][0]));
-#endif
+                             : "=f"(xs[(c + 1) & 1][i].x), "=f"(xs[(c + 1) & 1][i].y)
+                             : "r"(xa + 8u * (uint32_t)((i % R1) * PL::M1 + PL::TG * ((c + 1) * CPC + i / R1))));
+            asm volatile("" : "+r"(cu[c & 1][0]));
         }
-        float2 c8[R1], x8[R1];
 #pragma unroll
-        for (int n1 = 0; n1 < R1; ++n1) {
-            c8[n1] = make_float2(__uint_as_float(cu[q & 1][2 * n1]), __uint_as_float(cu[q & 1][2 * n1 + 1]));
-#ifndef XC_PP_NOPIPE
-            x8[n1] = xs[q & 1][n1];
-#else
-            x8[n1] = x[input_index<PL>(0, q, n1)];
-#endif
+        for (int qq = 0; qq < CPC; ++qq) {
+            const int q = c * CPC + qq;
+            // the products ride on the first butterfly stage of the radix-R1 codelet (pairs n1, n1 + R1 / 2)
+#pragma unroll
+            for (int n1 = 0; n1 < R1 / 2; ++n1) {
+                const int i0 = qq * R1 + n1, i1 = i0 + R1 / 2;
+                v[q * R1 + n1] = xs[c & 1][i0];
+                v[q * R1 + n1 + R1 / 2] = xs[c & 1][i1];
+                folded_butterfly(v[q * R1 + n1], v[q * R1 + n1 + R1 / 2],
+                                 make_float2(__uint_as_float(cu[c & 1][2 * i0]), __uint_as_float(cu[c & 1][2 * i0 + 1])),
+                                 make_float2(__uint_as_float(cu[c & 1][2 * i1]), __uint_as_float(cu[c & 1][2 * i1 + 1])));
+            }
+            codelet_fft<R1, 2>(v + q * R1);
+#pragma unroll
+            for (int j = 0; j < R1; ++j) buf[o1 + bitrev(j, ilog2(R1)) * K1STEP + q * QSTEP1] = v[q * R1 + j];
         }
-#ifdef XC_PP_NOFOLD0
-#pragma unroll
-        for (int n1 = 0; n1 < R1; ++n1) v[q * R1 + n1] = pcmul(x8[n1], c8[n1]);
-        codelet_fft<R1>(v + q * R1);
-#else
-        // the products ride on the first butterfly stage of the radix-8 codelet (pairs n1, n1 + 4)
-#pragma unroll
-        for (int n1 = 0; n1 < R1 / 2; ++n1) {
-            v[q * R1 + n1] = x8[n1];
-            v[q * R1 + n1 + R1 / 2] = x8[n1 + R1 / 2];
-            folded_butterfly(v[q * R1 + n1], v[q * R1 + n1 + R1 / 2], c8[n1], c8[n1 + R1 / 2]);
-        }
-        codelet_fft<R1, 2>(v + q * R1);
-#endif
-#pragma unroll
-        for (int j = 0; j < R1; ++j) buf[o1 + bitrev(j, ilog2(R1)) * K1STEP + q * QSTEP1] = v[q * R1 + j];
-        if (q + 1 < NQ1) tc::tmem_ld_wait16(cu[(q + 1) & 1]);
+        if (c + 1 < NCH) tc::tmem_ld_wait16(cu[(c + 1) & 1]);
     }
     tc::tmem_ld16_issue(tb + L::COL_TW1, cu[0]);      // first chunk of T1, in flight across the barrier
     bar();
@@ -301,7 +294,7 @@ __global__ void __launch_bounds__(PL::TG* B, 1) fused_fft_pp_kernel(const Staged
     const uint32_t tmem0 = *taddr_slot;
     // lane quarter of this warp, column block of the warps of a group that share a quarter
     const uint32_t tb = tmem0 + (((uint32_t)(warp_cta & 3) * 32u) << 16) + (uint32_t)((t >> 7) * L::CW);
-    if (g == 0) {
+    if (g < L::WRITERS) {
         // ---- per-thread constants -> tensor memory (read by the same in-group thread of every group) ----
         float r[16];
 #pragma unroll

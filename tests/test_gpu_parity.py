@@ -866,6 +866,29 @@ def test_czt_run_golden(xr, name, d, space):
         c.runMany(x.astype(np.complex128))
 
 
+@pytest.mark.parametrize("N", [2048, 4096])
+def test_pingpong_layout_other_lengths(xr, N):
+    """The ping-pong layout at 2048 points (eight groups of 64 threads per SM) and 4096 points (four groups of 128): one
+    contiguous call against calls of < 16 shifts per SM (B-groups-per-CTA layout) and against the oracle."""
+    K = 40000
+    cutout, rx = signals.make_fastxcorr_case(31 + N, N, N + K - 1, 23456, N - 5, amp=0.7)
+    q, f = xr.fastXcorr(_dev(cutout), _dev(rx), freqsearch=True)
+    q, f = q.cpu().numpy(), f.cpu().numpy()
+    assert int(np.argmax(q)) == 23456 and int(f[23456]) == N - 5
+    qs, fs = [], []
+    for lo in range(0, K, 2000):
+        qq, ff = xr.fastXcorr(_dev(cutout), _dev(rx), freqsearch=True, shifts=np.arange(lo, min(lo + 2000, K)))
+        qs.append(qq.cpu().numpy())
+        fs.append(ff.cpu().numpy())
+    q2, f2 = np.concatenate(qs), np.concatenate(fs)
+    np.testing.assert_allclose(q, q2, rtol=2e-6, atol=1e-9)
+    assert_bins(f, f2, lambda i: _spec64(cutout, rx, i))
+    idx = np.r_[np.arange(0, 64), np.arange(23456 - 32, 23456 + 32), np.arange(K - 64, K)]
+    rq, rf = orc.fastXcorr(cutout, rx, freqsearch=True, shifts=idx)
+    assert_qf2(q[idx], rq)
+    assert_bins(f[idx], rf, lambda i: _spec64(cutout, rx, int(idx[i])))
+
+
 def test_pingpong_layout_matches_b2_layout(xr):
     """Contiguous N = 8192 searches of >= 16 shifts per SM run the ping-pong layout (csrc/fused_fft_pp.cuh: two thread
     groups per SM over one staged rx window, constants in tensor memory, exact twiddles folded into the butterflies);
