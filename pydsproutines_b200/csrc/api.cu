@@ -174,19 +174,17 @@ int32_t collect_peak(const float* d_qf2, const uint32_t* d_fidx, const int32_t* 
     if (K <= 0) return XC_OK;
     unsigned long long* d_packed = reinterpret_cast<unsigned long long*>(workspace(SLOT_TMP3, 256));
     if (!d_packed) return XC_ERR_NOMEM;
-    XC_TRY(peak_reduce_device(d_qf2, d_fidx, d_aux, K, d_packed, st));
-    unsigned long long packed = 0;
-    XC_CUDA_TRY(cudaMemcpyAsync(&packed, d_packed, sizeof(packed), cudaMemcpyDeviceToHost, st));
+    // one reduction, one 24-byte copy-out: {packed (value bits, ~index), (fidx, aux), shifts[index]}
+    XC_TRY(peak_reduce_device(d_qf2, d_fidx, d_aux, K, d_packed, st, d_shifts));
+    unsigned long long rec[3] = {0, 0, 0};
+    XC_CUDA_TRY(cudaMemcpyAsync(rec, d_packed, sizeof(rec), cudaMemcpyDeviceToHost, st));
     XC_CUDA_TRY(cudaStreamSynchronize(st));
-    const uint32_t vb = (uint32_t)(packed >> 32);
+    const uint32_t vb = (uint32_t)(rec[0] >> 32);
     memcpy(&peak->qf2, &vb, 4);
-    peak->index = (int64_t)(0xffffffffu - (uint32_t)(packed & 0xffffffffull));
-    if (d_fidx) XC_CUDA_TRY(cudaMemcpy(&peak->fidx, d_fidx + peak->index, 4, cudaMemcpyDeviceToHost));
-    if (d_aux) XC_CUDA_TRY(cudaMemcpy(&peak->aux, d_aux + peak->index, 4, cudaMemcpyDeviceToHost));
-    if (d_shifts)
-        XC_CUDA_TRY(cudaMemcpy(&peak->shift, d_shifts + peak->index, 8, cudaMemcpyDeviceToHost));
-    else
-        peak->shift = shift0 + peak->index * step;
+    peak->index = (int64_t)(0xffffffffu - (uint32_t)(rec[0] & 0xffffffffull));
+    peak->fidx = (uint32_t)(rec[1] & 0xffffffffull);
+    peak->aux = (int32_t)(uint32_t)(rec[1] >> 32);
+    peak->shift = d_shifts ? (int64_t)rec[2] : shift0 + peak->index * step;
     return XC_OK;
 }
 

@@ -58,7 +58,7 @@ int32_t bluestein_tables(int N, int* log2m, const float2** d_bhat_perm, const fl
 
 // misc.cu
 int32_t peak_reduce_device(const float* qf2, const uint32_t* fidx, const int32_t* aux, int64_t K,
-                           unsigned long long* d_packed, cudaStream_t stream);
+                           unsigned long long* d_packed, cudaStream_t stream, const int64_t* shifts = nullptr);
 int32_t row_argmax_device(const float2* x, int64_t rows, int64_t cols, int use_normsq, uint32_t* idx, float* val,
                           cudaStream_t stream);
 int32_t local_maxima_device(const float* x, int64_t n, float min_height, int32_t* idx, int32_t cap, int32_t* count,

@@ -27,8 +27,18 @@ __global__ void peak_reduce_kernel(const float* __restrict__ qf2, int64_t K, uns
     if ((threadIdx.x & 31) == 0) atomicMax(packed, best);
 }
 
-int32_t peak_reduce_device(const float* qf2, const uint32_t*, const int32_t*, int64_t K, unsigned long long* d_packed,
-                           cudaStream_t stream) {
+// record[0] = packed (value bits, ~index); record[1] = {fidx, aux}; record[2] = shifts[index]: one 24-byte copy-out
+__global__ void peak_fetch_kernel(unsigned long long* __restrict__ rec, const uint32_t* __restrict__ fidx,
+                                  const int32_t* __restrict__ aux, const int64_t* __restrict__ shifts) {
+    const unsigned long long i = 0xffffffffull - (rec[0] & 0xffffffffull);
+    const unsigned long long f = fidx ? (unsigned long long)fidx[i] : 0ull;
+    const unsigned long long a = aux ? (unsigned long long)(uint32_t)aux[i] : 0ull;
+    rec[1] = f | (a << 32);
+    rec[2] = shifts ? (unsigned long long)shifts[i] : 0ull;
+}
+
+int32_t peak_reduce_device(const float* qf2, const uint32_t* fidx, const int32_t* aux, int64_t K, unsigned long long* d_packed,
+                           cudaStream_t stream, const int64_t* shifts) {
     if (K >= (1ll << 32)) return fail(XC_ERR_UNSUPPORTED, "peak reduction supports fewer than 2^32 shifts");
     XC_CUDA_TRY(cudaMemsetAsync(d_packed, 0, sizeof(unsigned long long), stream));
     if (K <= 0) return XC_OK;
@@ -36,6 +46,8 @@ int32_t peak_reduce_device(const float* qf2, const uint32_t*, const int32_t*, in
     const int64_t cap = (int64_t)sm_count() * 8;
     if (blocks > cap) blocks = cap;
     peak_reduce_kernel<<<(unsigned)blocks, 256, 0, stream>>>(qf2, K, d_packed);
+    XC_LAUNCH_CHECK();
+    peak_fetch_kernel<<<1, 1, 0, stream>>>(d_packed, fidx, aux, shifts);
     XC_LAUNCH_CHECK();
     return XC_OK;
 }
