@@ -120,6 +120,105 @@ __global__ void __launch_bounds__(FT) dft_kernel(const double2* __restrict__ a, 
     if (threadIdx.x == 0) out[m] = t;
 }
 
+// ---------------------------------------------------------------------------------------------
+// FP64 transform of any length above FINE_DFT_MAX: radix-2 Stockham passes through global memory for a power of two,
+// Bluestein (three such transforms of M >= 2 N - 1 points) otherwise.  The exact O(N^2) DFT above stays for short arrays.
+// ---------------------------------------------------------------------------------------------
+constexpr int64_t FINE_DFT_MAX = 1 << 14;
+
+// one autosort pass: out[(j / Ns) 2 Ns + k (+ Ns)] = in[j] +- in[j + n / 2] exp(-i pi k / Ns), k = j mod Ns
+__global__ void stockham_pass_kernel(const double2* __restrict__ in, double2* __restrict__ out, int64_t n, int64_t Ns) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x, half = n >> 1;
+    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < half; j += stride) {
+        const int64_t k = j & (Ns - 1);
+        const double2 w = unit_phase(0.5 * (double)k / (double)Ns);           // exp(-i pi k / Ns)
+        const double2 u = in[j], v = zmul(in[j + half], w);
+        const int64_t j0 = ((j - k) << 1) + k;
+        out[j0] = make_double2(u.x + v.x, u.y + v.y);
+        out[j0 + Ns] = make_double2(u.x - v.x, u.y - v.y);
+    }
+}
+// chirp w[n] = exp(-i pi n^2 / N) (n^2 reduced modulo 2 N exactly): A = x w (zero padded), B = conj(w) wrapped around M
+__global__ void blue64_setup_kernel(const double2* __restrict__ x, int64_t N, int64_t M, double2* __restrict__ A, double2* __restrict__ Bw) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < M; i += stride) {
+        double2 a = make_double2(0.0, 0.0), b = make_double2(0.0, 0.0);
+        const int64_t d = (i < N) ? i : ((M - i < N) ? M - i : -1);
+        if (d >= 0) {
+            const unsigned long long r = ((unsigned long long)d * (unsigned long long)d) % (unsigned long long)(2 * N);
+            const double2 w = unit_phase(0.5 * (double)r / (double)N);            // exp(-i pi r / N)
+            b = make_double2(w.x, -w.y);
+            if (i < N) a = zmul(x[i], w);
+        }
+        A[i] = a;
+        Bw[i] = b;
+    }
+}
+// P = conj(FA FB) (input of the inverse transform as a forward one)
+__global__ void blue64_mul_kernel(const double2* __restrict__ FA, const double2* __restrict__ FB, int64_t M, double2* __restrict__ P) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < M; i += stride) {
+        const double2 p = zmul(FA[i], FB[i]);
+        P[i] = make_double2(p.x, -p.y);
+    }
+}
+// X[k] = w[k] conj(q[k]) / M, k < N
+__global__ void blue64_finish_kernel(const double2* __restrict__ q, int64_t N, int64_t M, double2* __restrict__ X) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const double inv = 1.0 / (double)M;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < N; k += stride) {
+        const unsigned long long r = ((unsigned long long)k * (unsigned long long)k) % (unsigned long long)(2 * N);
+        const double2 w = unit_phase(0.5 * (double)r / (double)N);            // exp(-i pi r / N)
+        const double2 v = zmul(w, make_double2(q[k].x, -q[k].y));
+        X[k] = make_double2(v.x * inv, v.y * inv);
+    }
+}
+
+unsigned grid_for(int64_t n);
+
+// in-place-capable power-of-two transform: result ends in `dst` (a and b are two work arrays of n points, src may be a)
+static int32_t stockham64(const double2* src, double2* a, double2* b, double2* dst, int64_t n, cudaStream_t st) {
+    int passes = 0;
+    for (int64_t Ns = 1; Ns < n; Ns <<= 1) ++passes;
+    const double2* in = src;
+    int p = 0;
+    for (int64_t Ns = 1; Ns < n; Ns <<= 1, ++p) {
+        double2* out = (p == passes - 1) ? dst : ((in == a) ? b : a);
+        if (out == in) out = (in == a) ? b : a;      // never in place
+        stockham_pass_kernel<<<grid_for(n / 2), FT, 0, st>>>(in, out, n, Ns);
+        XC_LAUNCH_CHECK();
+        in = out;
+    }
+    if (in != dst) XC_CUDA_TRY(cudaMemcpyAsync(dst, in, sizeof(double2) * (size_t)n, cudaMemcpyDeviceToDevice, st));
+    return XC_OK;
+}
+
+// X = DFT_N(x) in FP64 for any N
+static int32_t fine_transform(const double2* x, int64_t N, double2* X, cudaStream_t st) {
+    if (N <= FINE_DFT_MAX) {
+        dft_kernel<<<(unsigned)N, FT, 0, st>>>(x, N, X);
+        XC_LAUNCH_CHECK();
+        return XC_OK;
+    }
+    int64_t M = 1;
+    const bool pow2 = (N & (N - 1)) == 0;
+    while (M < (pow2 ? N : 2 * N - 1)) M <<= 1;
+    double2* w = (double2*)workspace(SLOT_BIG, sizeof(double2) * (size_t)M * 5);
+    if (!w) return XC_ERR_NOMEM;
+    double2 *A = w, *T1 = w + M, *T2 = w + 2 * M, *FB = w + 3 * M, *FA = w + 4 * M;
+    if (pow2) return stockham64(x, T1, T2, X, N, st);
+    blue64_setup_kernel<<<grid_for(M), FT, 0, st>>>(x, N, M, A, T1);
+    XC_LAUNCH_CHECK();
+    XC_TRY(stockham64(T1, T1, T2, FB, M, st));          // FFT of the wrapped chirp
+    XC_TRY(stockham64(A, T1, T2, FA, M, st));           // FFT of the chirped input
+    blue64_mul_kernel<<<grid_for(M), FT, 0, st>>>(FA, FB, M, A);
+    XC_LAUNCH_CHECK();
+    XC_TRY(stockham64(A, T1, T2, FA, M, st));
+    blue64_finish_kernel<<<grid_for(N), FT, 0, st>>>(FA, N, M, X);
+    XC_LAUNCH_CHECK();
+    return XC_OK;
+}
+
 // r[m] = X[m] conj(Y[m]) (0 outside [bounds[0], bounds[1]) of makeFreq(N, fs));  norms[0] += |X|^2, norms[1] += |Y|^2
 __global__ void __launch_bounds__(FT) spectrum_product_kernel(const double2* __restrict__ X, const double2* __restrict__ Y,
                                                               int64_t N, double fs, const double* __restrict__ bounds,
@@ -316,10 +415,8 @@ int32_t xc_time_scan_c128(const void* x, const void* y, int64_t N, double shift_
         XC_LAUNCH_CHECK();
         dx = dxs;
     }
-    dft_kernel<<<(unsigned)N, FT, 0, st>>>(dx, N, dX);
-    XC_LAUNCH_CHECK();
-    dft_kernel<<<(unsigned)N, FT, 0, st>>>(dy, N, dY);
-    XC_LAUNCH_CHECK();
+    XC_TRY(fine_transform(dx, N, dX, st));          // exact DFT up to 2^14 samples, Stockham / Bluestein in FP64 above
+    XC_TRY(fine_transform(dy, N, dY, st));
     spectrum_product_kernel<<<grid_for(N), FT, 0, st>>>(dX, dY, N, fs, dbounds, dr, dnorms);
     XC_LAUNCH_CHECK();
     if (dS) {

@@ -196,3 +196,37 @@ def test_sharded_group_and_template_drivers_on_the_device(xr):
     assert best.shape[0] == 3000 - 63 and g["shift"] == 50 + 1234 and g["fidx"] == 3
     ti_ref, q_ref = orc.multiTemplateSlidingDotProduct(x, templates.conj(), 0, 3000 - 63)
     np.testing.assert_allclose(best.cpu().numpy(), q_ref, rtol=1e-4, atol=1e-6 * q_ref.max())
+
+
+@pytest.mark.parametrize("N", [1 << 16, 50000, 1 << 20])
+def test_fine_search_long_arrays_fft(xr, N):
+    """fineFreqTimeSearch above 2^14 samples transforms with the FP64 Stockham / Bluestein kernels (the exact O(N^2) DFT
+    below): same time-offset pick as the oracle, cost within the single-precision noise of the reference's np.fft.fft on
+    complex64 inputs, and N = 2^20 well inside 50 ms on the device."""
+    import time
+    import torch
+    from oracle import xcorr_oracle as orc
+    rng = np.random.default_rng(N % 1000)
+    base = rng.standard_normal(N) + 1j * rng.standard_normal(N)
+    Bf = np.fft.fft(base)
+    fvec = np.fft.fftfreq(N)
+    Bf[np.abs(fvec) > 0.25] = 0
+    x = np.fft.ifft(Bf)
+    y = np.fft.ifft(Bf * np.exp(-2j * np.pi * fvec * 0.3))
+    xn = (x + 0.05 * (rng.standard_normal(N) + 1j * rng.standard_normal(N))).astype(np.complex64)
+    yn = (y + 0.05 * (rng.standard_normal(N) + 1j * rng.standard_normal(N))).astype(np.complex64)
+    td = np.arange(-1.0, 1.0, 0.05)
+    ff, tdiff, cost = xr.fineFreqTimeSearch(xn, yn, [], 0.0, 0.0, 1.0, td)
+    if N <= (1 << 16):
+        ffo, tdo, costo = orc.fineFreqTimeSearch(xn, yn, [], 0.0, 0.0, 1.0, td)
+        assert tdiff == tdo
+        np.testing.assert_allclose(np.asarray(cost), costo, rtol=0, atol=5e-6)
+    assert abs(tdiff - 0.3) < 0.051
+    if N == (1 << 20):
+        dx, dy = _dev(xn), _dev(yn)
+        xr.fineFreqTimeSearch(dx, dy, [], 0.0, 0.0, 1.0, td)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        xr.fineFreqTimeSearch(dx, dy, [], 0.0, 0.0, 1.0, td)
+        torch.cuda.synchronize()
+        assert (time.perf_counter() - t0) < 0.05
