@@ -547,9 +547,11 @@ __global__ void __launch_bounds__(ND_THREADS) nofreq_tiled_kernel(const float2* 
 #pragma unroll
                 for (int j = 0; j < ND_R; ++j) {
                     const float2 x = w[u + j];
-                    // conj(x) * c
-                    acc[j].x = fmaf(x.x, c[u].x, fmaf(x.y, c[u].y, acc[j].x));
-                    acc[j].y = fmaf(x.x, c[u].y, fmaf(-x.y, c[u].x, acc[j].y));
+                    // acc += conj(x) * c in two packed instructions (the kernel is issue bound with scalar FFMA:
+                    // profiles/r2_c1_c4_c6_ncu.md): (c.x, c.y) x.x + (c.y, -c.x) x.y -- the half swap with one negation
+                    // and the scalar broadcast are operand modifiers
+                    acc[j] = pfma(c[u], make_float2(x.x, x.x), acc[j]);
+                    acc[j] = pfma(make_float2(c[u].y, -c[u].x), make_float2(x.y, x.y), acc[j]);
                 }
 #pragma unroll
             for (int j = 0; j < 8; ++j) w[j] = w[8 + j];
