@@ -82,6 +82,17 @@ int sm_count() {
     return n > 0 ? n : 1;
 }
 int max_smem_optin() { return dev_state().smem_optin; }
+int current_device() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) dev = 0;
+    return dev;
+}
+int32_t check_handle_device(int handle_device, const char* what) {
+    const int dev = current_device();
+    if (dev != handle_device)
+        return fail(XC_ERR_ARG, "%s handle was created on device %d, the current device is %d (xc_set_device)", what, handle_device, dev);
+    return XC_OK;
+}
 void* workspace(Slot slot, size_t bytes) {
     SlotBuf& s = dev_state().slots[slot];
     if (bytes == 0) bytes = 256;

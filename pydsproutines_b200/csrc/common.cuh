@@ -75,6 +75,9 @@ void* workspace(Slot slot, size_t bytes);
 int32_t release_workspace();
 int sm_count();
 int max_smem_optin();
+int current_device();
+// handles own device memory: using one on another device than the one it was created on is an error, not a fault
+int32_t check_handle_device(int handle_device, const char* what);
 
 // cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is per device: one flag per (kernel instantiation, device).
 constexpr int XC_MAX_DEVICES = 64;

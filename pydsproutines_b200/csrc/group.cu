@@ -33,6 +33,7 @@ struct xc_group {
     int32_t blue;            // F is not a power of two: chirped weights, two FFTs per shift (bluestein.cuh)
     const float2* d_bhat_perm;   // Bluestein: FFT_M(chirp) in register order (owned by the per-length cache)
     const float2* d_chirp;       // Bluestein: b[k] = exp(+i pi k^2 / F), k < F
+    int32_t device;              // the device that owns the arrays of this handle
     xc::GroupPPPlan pp;          // ping-pong layout for contiguous shift ranges (group_pp.cuh), usable or not
 };
 
@@ -375,6 +376,7 @@ int32_t xc_group_create(const void* ygroups, int32_t G, int32_t L, const int64_t
     xc_group* h = new xc_group();
     memset(h, 0, sizeof(*h));
     h->G = G; h->L = L; h->F = F;
+    h->device = current_device();
     if (blue) {
         const int32_t bs = bluestein_tables(F, &log2m, &d_bhat_perm, &d_chirp);
         if (bs != XC_OK) {
@@ -433,6 +435,7 @@ int32_t xc_group_xcorr(xc_group* h, const void* rx, int64_t rxlen, int64_t shift
     XC_API_GUARD;
     if (where != XC_HOST && where != XC_DEVICE) return fail(XC_ERR_ARG, "where must be XC_HOST (0) or XC_DEVICE (1)");
     if (!h || !rx) return fail(XC_ERR_ARG, "handle/rx is NULL");
+    XC_TRY(check_handle_device(h->device, "GroupXcorrFFT"));
     if (!qf2 && !caf) return fail(XC_ERR_ARG, "qf2 and caf are both NULL");
     if (K < 0 || rxlen < h->L) return fail(XC_ERR_ARG, "need K >= 0 and rx at least one group long");
     if (K == 0) {

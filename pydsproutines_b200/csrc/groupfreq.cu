@@ -23,6 +23,7 @@ struct xc_groupfreq {
     float2* d_templates;             // [NF, Lcat] (released after the BF16 pack is built)
     float* d_energies;               // [NF] all = ||y||^2
     xc::MtTcPlan tc;
+    int32_t device = 0;              // the device that owns the arrays of this handle
     // window energies: one sliding-sum pass per distinct group length
     std::vector<int32_t> lens;
     std::vector<int64_t*> d_starts;  // per distinct length: device start list
@@ -177,6 +178,7 @@ int32_t xc_groupfreq_create(const void* ycat, const int64_t* starts, const int32
             }
     }
     xc_groupfreq* h = new xc_groupfreq();
+    h->device = current_device();
     h->G = G; h->NF = NF; h->Lcat = Lcat; h->max_end = max_end;
     h->d_templates = nullptr; h->d_energies = nullptr;
     std::vector<float> en(NF, (float)ynorm);
@@ -225,6 +227,7 @@ int32_t xc_groupfreq_xcorr(xc_groupfreq* h, const void* rx, int64_t rxlen, int64
     XC_API_GUARD;
     if (where != XC_HOST && where != XC_DEVICE) return fail(XC_ERR_ARG, "where must be XC_HOST (0) or XC_DEVICE (1)");
     if (!h || !rx) return fail(XC_ERR_ARG, "handle/rx is NULL");
+    XC_TRY(check_handle_device(h->device, "grouped frequency-list correlator"));
     if (K < 0 || shift0 < 0) return fail(XC_ERR_RANGE, "shifts must be >= 0");
     if (K > 0 && shift0 + K - 1 + h->max_end > rxlen)
         return fail(XC_ERR_RANGE, "the last shift reads past the end of rx");            // xcorrRoutines.py:922-925, 1000-1003

@@ -16,6 +16,7 @@ struct xc_mt {
     float2* d_templates;   // [T, L8] zero padded rows, conjugated if requested at create time
     float* d_energies;     // [T]
     xc::MtTcPlan tc;       // tensor-core plan (usable when the templates are exact in BF16)
+    int32_t device;        // the device that owns the arrays of this handle
 };
 
 namespace xc {
@@ -173,6 +174,7 @@ int32_t xc_mt_create(const void* templates, int32_t T, int32_t L, int32_t conj, 
     }
     xc_mt* h = new xc_mt();
     h->T = T; h->L = L; h->L8 = L8;
+    h->device = current_device();
     h->d_templates = nullptr; h->d_energies = nullptr;
     cudaError_t e = cudaMalloc(&h->d_templates, sizeof(float2) * padded.size());
     if (e == cudaSuccess) e = cudaMalloc(&h->d_energies, sizeof(float) * T);
@@ -211,6 +213,7 @@ int32_t xc_mt_correlate(xc_mt* h, const void* x, int64_t xlen, int64_t start, in
     XC_API_GUARD;
     if (where != XC_HOST && where != XC_DEVICE) return fail(XC_ERR_ARG, "where must be XC_HOST (0) or XC_DEVICE (1)");
     if (!h || !x) return fail(XC_ERR_ARG, "handle/x is NULL");
+    XC_TRY(check_handle_device(h->device, "template correlator"));
     if (start < 0) return fail(XC_ERR_RANGE, "startIdx should be >= 0.");                                   // cupyExtensions.py:584-586
     if (K < 0 || start + K - 1 + h->L - 1 >= xlen)
         return fail(XC_ERR_RANGE, "final slide index should be within the bounds of d_x.");                   // cupyExtensions.py:587-591

@@ -230,3 +230,16 @@ def test_fine_search_long_arrays_fft(xr, N):
         xr.fineFreqTimeSearch(dx, dy, [], 0.0, 0.0, 1.0, td)
         torch.cuda.synchronize()
         assert (time.perf_counter() - t0) < 0.05
+
+
+def test_handles_are_bound_to_their_device(xr):
+    """A handle used on another device than the one it was created on is an argument error, not a fault."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two visible devices")
+    c = signals.config_c3(log2_shifts=8)
+    obj = xr.GroupXcorrFFT(c["ygroups"], c["starts"], 1, fftlen=c["F"])          # created on the current device (0)
+    with pytest.raises(ValueError, match="created on device 0"):
+        obj.xcorr(_dev(c["rx"], 1), np.arange(8))
+    q, f = obj.xcorr(_dev(c["rx"], 0), np.arange(8))
+    assert q.shape[0] == 8
