@@ -123,6 +123,21 @@ int32_t xc_cztxcorr_c64(const void* cutout, int32_t N, const void* rx, int64_t r
                         int64_t step, int64_t K, const int64_t* shifts, double f0_cycles, double df_cycles,
                         int32_t nbins, float* qf2, uint32_t* fidx, void* cplx, float* caf, int32_t where,
                         void* stream);
+/* ---- allocation-free variant of the no-frequency-search correlator ------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arithmetic and the
+ * same kernels as xc_fastxcorr_c64(freqsearch = 0) on the contiguous shifts shift0 .. shift0 + K - 1 (all inside rx),
+ * DEVICE pointers only, enqueued on `stream` without synchronising:
+ *     qf2[i] = |sum_n conj(rx[shift0 + i + n]) cutout[n]|^2 / ||cutout||^2 / ||rx[shift0 + i : + N]||^2,  float32[K].
+ * The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine): ||cutout||^2 and the K window
+ * energies live in a static device array of XC_NOALLOC_MAX_SHIFTS + 64 floats (4 MiB + 256 bytes, held by every GPU
+ * that loads the library until the process exits).  K > XC_NOALLOC_MAX_SHIFTS returns XC_ERR_UNSUPPORTED (split the
+ * range or use xc_fastxcorr_c64).  Every call on a device shares that array and fully rewrites the part it uses
+ * (nothing has to start at zero); two calls that overlap on the GPU (different streams of one device) race on it --
+ * keep them in stream order. */
+#define XC_NOALLOC_MAX_SHIFTS 1048576
+int32_t xc_fastxcorr_nofreq_noalloc_c64(const void* cutout, int32_t N, const void* rx, int64_t rxlen, int64_t shift0,
+                                        int64_t K, float* qf2, void* stream);
 /* 1 when the fused frequency-search kernel takes this cutout length: powers of two 2..16384 (one block FFT per
  * shift) and every other length 3..8192 (Bluestein: two block FFTs per shift) */
 int32_t xc_fastxcorr_supported(int32_t N);

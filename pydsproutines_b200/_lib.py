@@ -18,6 +18,7 @@ LIB_PATH = os.path.join(_HERE, "libxcorr_b200.so")
 XC_HOST, XC_DEVICE = 0, 1
 XC_FLAG_ZERO_OOB = 1
 XC_MT_CONJ, XC_MT_FP32 = 1, 2
+XC_NOALLOC_MAX_SHIFTS = 1 << 20
 XC_OK, XC_ERR_ARG, XC_ERR_RANGE, XC_ERR_UNSUPPORTED, XC_ERR_NOMEM, XC_ERR_CUDA = 0, -1, -2, -3, -4, -5
 
 
@@ -48,6 +49,7 @@ SIGNATURES = {
                                 C.POINTER(xc_peak), _i32, _vp]),
     "xc_fastxcorr_caf_c64": (_i32, [_vp, _i32, _vp, _i64, _i64, _i64, _i64, _vp, _vp, _i32, _i32, _vp]),
     "xc_fastxcorr_supported": (_i32, [_i32]),
+    "xc_fastxcorr_nofreq_noalloc_c64": (_i32, [_vp, _i32, _vp, _i64, _i64, _i64, _vp, _vp]),
     "xc_cztxcorr_c64": (_i32, [_vp, _i32, _vp, _i64, _i64, _i64, _i64, _vp, C.c_double, C.c_double, _i32, _vp, _vp, _vp, _vp,
                                _i32, _vp]),
     "xc_group_create": (_i32, [_vp, _i32, _i32, _vp, _i32, _i32, C.POINTER(_vp)]),

@@ -636,3 +636,64 @@ int32_t fastxcorr_nofreq_device(const float2* cutout, int N, const float2* rx, i
 }
 
 }  // namespace xc
+
+// =============================================================================================
+// xc_fastxcorr_nofreq_noalloc_c64: the no-frequency-search correlator for callers that may not allocate
+// (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  Same three kernels as
+// fastxcorr_nofreq_device (||cutout||^2, sliding window energy, nofreq_tiled_kernel); the two normalisation
+// temporaries live in a file-scope device array instead of the cached workspace.  No reference counterpart.
+// =============================================================================================
+namespace xc {
+
+constexpr int64_t NOALLOC_MAX_SHIFTS = XC_NOALLOC_MAX_SHIFTS;
+constexpr int NOALLOC_HEAD = 64;      // floats in front of the energies: [0] = ||cutout||^2, rest padding (256 bytes)
+// 4 MiB + 256 bytes, held by every GPU that loads the library until the process exits
+static __device__ __align__(256) float g_noalloc_scratch[NOALLOC_HEAD + NOALLOC_MAX_SHIFTS];
+// In host code `g_noalloc_scratch` is only a handle for the runtime, not a device address: the address is looked up
+// once per device (with that device current) and cached here.
+static float* g_noalloc_ptr[XC_MAX_DEVICES] = {};
+
+static int32_t noalloc_scratch(float** out) {
+    int dev = 0;
+    XC_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= XC_MAX_DEVICES) return fail(XC_ERR_UNSUPPORTED, "device ordinal %d out of range", dev);
+    if (!g_noalloc_ptr[dev]) {
+        float* p = nullptr;
+        XC_CUDA_TRY(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+        if (!p) return fail(XC_ERR_CUDA, "cudaGetSymbolAddress returned a NULL scratch address on device %d", dev);
+        g_noalloc_ptr[dev] = p;
+    }
+    *out = g_noalloc_ptr[dev];
+    return XC_OK;
+}
+
+}  // namespace xc
+
+extern "C" int32_t xc_fastxcorr_nofreq_noalloc_c64(const void* cutout, int32_t N, const void* rx, int64_t rxlen,
+                                                   int64_t shift0, int64_t K, float* qf2, void* stream) {
+    using namespace xc;
+    XC_API_GUARD;
+    if (!cutout || !rx || !qf2) return fail(XC_ERR_ARG, "cutout/rx/qf2 is NULL");
+    if (N < 1) return fail(XC_ERR_ARG, "cutout length must be >= 1");
+    if (K < 0) return fail(XC_ERR_ARG, "number of shifts must be >= 0");
+    if (K > NOALLOC_MAX_SHIFTS)
+        return fail(XC_ERR_UNSUPPORTED, "xc_fastxcorr_nofreq_noalloc_c64 takes at most %lld shifts per call (the static scratch "
+                    "array), got %lld: split the range or use xc_fastxcorr_c64", (long long)NOALLOC_MAX_SHIFTS, (long long)K);
+    if (K == 0) return XC_OK;
+    if (shift0 < 0 || shift0 + K - 1 + N > rxlen)
+        return fail(XC_ERR_RANGE, "shifts [%lld, %lld] with cutout length %d leave rx of length %lld", (long long)shift0,
+                    (long long)(shift0 + K - 1), N, (long long)rxlen);
+    float* scratch = nullptr;
+    XC_TRY(noalloc_scratch(&scratch));
+    float* d_refn = scratch;                    // fully rewritten by every call: nothing has to start at zero
+    float* d_energy = scratch + NOALLOC_HEAD;
+    cudaStream_t st = (cudaStream_t)stream;
+    const float2* dc = reinterpret_cast<const float2*>(cutout);
+    const float2* drx = reinterpret_cast<const float2*>(rx);
+    XC_TRY(normsq_device(dc, N, 1, N, d_refn, st));
+    XC_TRY(sliding_sum_device(drx + shift0, true, rxlen - shift0, 0, N, K, d_energy, 0, st));
+    const int64_t blocks = (K + ND_TS - 1) / ND_TS;
+    nofreq_tiled_kernel<<<(unsigned)blocks, ND_THREADS, 0, st>>>(dc, N, drx, rxlen, shift0, K, d_energy, d_refn, qf2, nullptr);
+    XC_LAUNCH_CHECK();
+    return XC_OK;
+}
