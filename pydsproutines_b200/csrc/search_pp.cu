@@ -1,7 +1,8 @@
 // search_pp.cu -- instantiations of the ping-pong layout of the frequency search (fused_fft_pp.cuh), kept in their own
 // translation unit: 8192 points (two groups of 128 threads, 64 points per thread), 4096 (four groups of 128 threads, 32
-// points per thread) and 2048 (eight groups of 64 threads).
+// points per thread), 2048 (eight groups of 64 threads) and 1024 (sixteen warps, one FFT per warp).
 #include "fused_fft_pp.cuh"
+#include "fused_fft_warp.cuh"
 
 #ifndef XC_PP_B4096
 #define XC_PP_B4096 4
@@ -9,10 +10,13 @@
 #ifndef XC_PP_B2048
 #define XC_PP_B2048 8
 #endif
+#ifndef XC_PP_B1024
+#define XC_PP_B1024 16
+#endif
 
 namespace xc {
 
-bool search_pp_takes(int N) { return N == 8192 || N == 4096 || N == 2048; }
+bool search_pp_takes(int N) { return N == 8192 || N == 4096 || N == 2048 || N == 1024; }
 
 int32_t search_pp_device(const StagedArgs& a, const FusedOut& out, int64_t K, int N, int fold, cudaStream_t stream) {
 #ifdef XC_EXPERIMENTS
@@ -22,6 +26,7 @@ int32_t search_pp_device(const StagedArgs& a, const FusedOut& out, int64_t K, in
     if (N == 8192) return launch_fused_pp<FftPlan<13, 128, 8, 32, 32>, 2, true>(a, out, K, stream);
     if (N == 4096) return launch_fused_pp<FftPlan<12, 128, 4, 32, 32>, XC_PP_B4096, true>(a, out, K, stream);
     if (N == 2048) return launch_fused_pp<FftPlan<11, 64, 2, 32, 32>, XC_PP_B2048, true>(a, out, K, stream);
+    if (N == 1024) return launch_fused_warp<XC_PP_B1024>(a, out, K, stream);      // one warp per FFT (fused_fft_warp.cuh)
     return fail(XC_ERR_UNSUPPORTED, "no ping-pong layout for %d points", N);
 }
 

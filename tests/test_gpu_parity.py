@@ -866,10 +866,10 @@ def test_czt_run_golden(xr, name, d, space):
         c.runMany(x.astype(np.complex128))
 
 
-@pytest.mark.parametrize("N", [2048, 4096])
+@pytest.mark.parametrize("N", [1024, 2048, 4096])
 def test_pingpong_layout_other_lengths(xr, N):
-    """The ping-pong layout at 2048 points (eight groups of 64 threads per SM) and 4096 points (four groups of 128): one
-    contiguous call against calls of < 16 shifts per SM (B-groups-per-CTA layout) and against the oracle."""
+    """The ping-pong layout at 1024 points (sixteen warps per SM, one FFT per warp: csrc/fused_fft_warp.cuh), 2048 points
+    (eight groups of 64 threads per SM) and 4096 points (four groups of 128): one contiguous call against calls of < 16 shifts per SM (B-groups-per-CTA layout) and against the oracle."""
     K = 40000
     cutout, rx = signals.make_fastxcorr_case(31 + N, N, N + K - 1, 23456, N - 5, amp=0.7)
     q, f = xr.fastXcorr(_dev(cutout), _dev(rx), freqsearch=True)
@@ -922,6 +922,31 @@ def test_pingpong_layout_matches_b2_layout(xr):
     assert_qf2(q[idx + 50], rq)
     assert_bins(f[idx + 50], rf, lambda i: _spec64(cutout, rx, int(idx[i])))
     assert f[123456 + 50] == rf[60]
+
+
+def test_warp_layout_windows_leaving_rx(xr):
+    """N = 1024 (one warp per FFT over a staged window): windows that leave rx on either side give 0 / 0
+    (IppXcorrFFT.cpp:125-130), the rest agrees with short calls (B-groups-per-CTA layout) and the oracle; several refills."""
+    cutout, rx = signals.make_fastxcorr_case(77, 1024, 1024 + 90000, 54321, 1000, amp=0.8)
+    obj = xr.CyIppXcorrFFT(cutout)
+    a, b = -37, 90000 + 1 + 41
+    q, f = obj.xcorr(rx, a, b, 1)
+    assert q.size == b - a and not q[:37].any() and not f[:37].any() and not q[-41:].any() and not f[-41:].any()
+    assert q[37] > 0 and q[-42] > 0
+    i = int(np.argmax(q))
+    assert i == 54321 + 37 and f[i] == 1000
+    qs, fs = [], []
+    for lo in range(a, b, 2000):
+        qq, ff = obj.xcorr(rx, lo, min(lo + 2000, b), 1)
+        qs.append(qq)
+        fs.append(ff)
+    q2, f2 = np.concatenate(qs), np.concatenate(fs)
+    np.testing.assert_allclose(q, q2, rtol=2e-6, atol=1e-9)
+    assert_bins(f[37:-41], f2[37:-41], lambda i: _spec64(cutout, rx, int(i)))
+    idx = np.r_[np.arange(0, 48), np.arange(54321 - 24, 54321 + 24), np.arange(90000 - 47, 90001)]
+    rq, rf = orc.fastXcorr(cutout, rx, freqsearch=True, shifts=idx)
+    assert_qf2(q[idx + 37], rq)
+    assert_bins(f[idx + 37], rf, lambda i: _spec64(cutout, rx, int(idx[i])))
 
 
 def test_groupfreq_large_planted_and_sampled(xr):
