@@ -4,6 +4,9 @@
 #include "fused_fft_pp.cuh"
 #include "fused_fft_warp.cuh"
 
+#ifndef XC_PP_TG8192
+#define XC_PP_TG8192 128
+#endif
 #ifndef XC_PP_B4096
 #define XC_PP_B4096 4
 #endif
@@ -23,7 +26,7 @@ int32_t search_pp_device(const StagedArgs& a, const FusedOut& out, int64_t K, in
     if (!fold && N == 8192) return launch_fused_pp<FftPlan<13, 128, 8, 32, 32>, 2, false>(a, out, K, stream);
 #endif
     (void)fold;
-    if (N == 8192) return launch_fused_pp<FftPlan<13, 128, 8, 32, 32>, 2, true>(a, out, K, stream);
+    if (N == 8192) return launch_fused_pp<FftPlan<13, XC_PP_TG8192, 8, 32, 32>, 2, true>(a, out, K, stream);
     if (N == 4096) return launch_fused_pp<FftPlan<12, 128, 4, 32, 32>, XC_PP_B4096, true>(a, out, K, stream);
     if (N == 2048) return launch_fused_pp<FftPlan<11, 64, 2, 32, 32>, XC_PP_B2048, true>(a, out, K, stream);
     if (N == 1024) return launch_fused_warp<XC_PP_B1024>(a, out, K, stream);      // one warp per FFT (fused_fft_warp.cuh)
