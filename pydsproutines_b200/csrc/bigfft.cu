@@ -27,6 +27,13 @@ namespace xc {
 constexpr int BIG_MIN_LOG2 = 6;          // smallest block plan with an exchange buffer (64 points)
 constexpr int BIG_MAX_LOG2L = 2 * MAX_LOG2N;
 constexpr int TWB_BITS = 10;             // W_L^x = twA[x >> 10] * twB[x & 1023]
+// CTAs per SM the kernels are compiled for: these passes wait on memory (ncu: long_scoreboard 7 per issue with one CTA of
+// 172 registers per SM), so two CTAs of <= 128 registers beat one (benchmark_xcorrs 1e6: 9.1 -> 6.6 ms); three spill
+#ifndef XC_BIG_MINB
+#define XC_BIG_MINB 2
+#endif
+template <int THREADS>
+constexpr int big_minb() { return THREADS <= 256 ? XC_BIG_MINB : 1; }
 
 // ---------------------------------------------------------------------------------------------
 // plans: twiddle tables per (device, log2 L); Bluestein tables per (device, N, bins, a, w)
@@ -90,7 +97,7 @@ struct BigColsArgs {
 };
 
 template <class PL, int B, int MODE>
-__global__ void __launch_bounds__(PL::TG* B) big_cols_kernel(const BigColsArgs a) {
+__global__ void __launch_bounds__(PL::TG* B, big_minb<PL::TG * B>()) big_cols_kernel(const BigColsArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int TG = PL::TG, V = PL::V;
     const int g = threadIdx.x / TG, t = threadIdx.x % TG;
@@ -184,7 +191,7 @@ struct BigRowsArgs {
 };
 
 template <class PL, int B, int EPI>
-__global__ void __launch_bounds__(PL::TG* B) big_rows_kernel(const BigRowsArgs a) {
+__global__ void __launch_bounds__(PL::TG* B, big_minb<PL::TG * B>()) big_rows_kernel(const BigRowsArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int TG = PL::TG, V = PL::V, LR = PL::N;
     const int g = threadIdx.x / TG, t = threadIdx.x % TG;

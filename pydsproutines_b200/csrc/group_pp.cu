@@ -1,4 +1,5 @@
 // group_pp.cu -- plan builder and launcher of the ping-pong GroupXcorrFFT kernel (group_pp.cuh).
+#include <algorithm>
 #include <vector>
 
 #include "group_pp.cuh"
@@ -17,6 +18,52 @@ void group_pp_release(GroupPPPlan* p) {
     if (p->d_w) cudaFree(p->d_w);
     if (p->d_off) cudaFree(p->d_off);
     memset(p, 0, sizeof(*p));
+}
+
+// Rotated-row plan (group_pp.cuh, ROT): every group is cut into sub-groups of TG samples, sorted by the row their first
+// cell lies in; thread t holds the weight of sample (t - r) mod TG of each sub-group.
+static int32_t group_rot_build(const float2* y, const int64_t* starts, int G, int L, int F, int W, GroupPPPlan* p) {
+    constexpr int TG = GPPL::TG;
+    static_assert(GR_MAX_E == sizeof(p->rdesc) / sizeof(p->rdesc[0]), "descriptor table size");
+    const int per = (L + TG - 1) / TG;
+    const int E = G * per;
+    if (E + 1 > GR_MAX_E) return XC_OK;
+    // the stage keeps TG zero cells behind the last window
+    while (W >= 4 * GP_B && GroupPPLayout<GPPL, GP_B, true>::bytes(G, L, W) + sizeof(float2) * TG > (size_t)max_smem_optin()) W -= GP_B;
+    if (W < 4 * GP_B) return XC_OK;
+    const int SW = L + W;
+    struct Sub { int row, r, g, i; };
+    std::vector<Sub> subs;
+    for (int g = 0; g < G; ++g)
+        for (int i = 0; i < per; ++i) {
+            const int64_t a = (((starts[g] + (int64_t)TG * i) % F) + F) % F;
+            subs.push_back(Sub{(int)(a / TG), (int)(a % TG), g, i});
+        }
+    std::stable_sort(subs.begin(), subs.end(), [](const Sub& x, const Sub& z) { return x.row < z.row; });
+    const int NC = (E + 1 + GP_CH - 1) / GP_CH * GP_CH;   // one padding entry (the gather prefetches one ahead), whole st16 chunks
+    std::vector<float2> hw((size_t)NC * TG, make_float2(0.f, 0.f));
+    memset(p->rcnt, 0, sizeof(p->rcnt));
+    for (int e = 0; e < E; ++e) {
+        const Sub& sb = subs[(size_t)e];
+        if (p->rcnt[sb.row] == 255) return XC_OK;
+        ++p->rcnt[sb.row];
+        p->rdesc[e] = (uint32_t)sb.r | ((uint32_t)(sb.g * SW + TG * sb.i) << 7);
+        for (int t = 0; t < TG; ++t) {
+            const int n = TG * sb.i + ((t - sb.r) & (TG - 1));
+            if (n < L) hw[(size_t)e * TG + t] = y[(size_t)sb.g * L + n];
+        }
+    }
+    for (int e = E; e < GR_MAX_E; ++e) p->rdesc[e] = 0;
+    XC_CUDA_TRY(cudaMalloc(&p->d_w, sizeof(float2) * hw.size()));
+    XC_CUDA_TRY(cudaMemcpy(p->d_w, hw.data(), sizeof(float2) * hw.size(), cudaMemcpyHostToDevice));
+    p->G = G;
+    p->L = L;
+    p->W = W;
+    p->NC = NC;
+    p->nq_live = GPPL::V / GPPL::R1;
+    p->rot = 1;
+    p->usable = 1;
+    return XC_OK;
 }
 
 // y: host weights [G][L] (conjugation already applied); the plan is usable when the fold fits the kernel's limits
@@ -49,7 +96,10 @@ int32_t group_pp_build(const float2* y, const int64_t* starts, int G, int L, int
             if (cells[m].size() > len) len = cells[m].size();
         }
         len = (len + 2 * GP_CH - 1) / (2 * GP_CH) * (2 * GP_CH);
-        if (len > 248) return XC_OK;
+        if (len > 248) {
+            memset(p, 0, sizeof(*p));
+            return group_rot_build(y, starts, G, L, F, W, p);
+        }
         if (len > 0) qtop = q;
         p->lens[c] = (unsigned char)len;
         base[c + 1] = base[c] + (int)len;
@@ -57,7 +107,7 @@ int32_t group_pp_build(const float2* y, const int64_t* starts, int G, int L, int
     const int NC = base[V] + GP_CH;                       // one chunk of padding: the gather prefetches one chunk ahead
     if (base[V] == 0 || NC > GP_MAX_NC) {
         memset(p, 0, sizeof(*p));
-        return XC_OK;
+        return group_rot_build(y, starts, G, L, F, W, p);
     }
     int nq = 1;
     while (nq < qtop + 1) nq <<= 1;
@@ -89,16 +139,20 @@ int32_t group_pp_build(const float2* y, const int64_t* starts, int G, int L, int
 int32_t group_pp_run(const GroupPPPlan& p, const int64_t* d_starts, const float2* rx, int64_t rxlen, int64_t shift0, int64_t K,
                      int64_t lo, int64_t hi, const FusedOut& out, cudaStream_t stream) {
     using LY = GroupPPLayout<GPPL, GP_B>;
-    void (*kern)(const GroupPPArgs, const GroupPPLens, const FusedOut, const int64_t, const int) =
-        p.nq_live == 1 ? group_pp_kernel<GPPL, GP_B, 1> : p.nq_live == 2 ? group_pp_kernel<GPPL, GP_B, 2>
-        : p.nq_live == 4 ? group_pp_kernel<GPPL, GP_B, 4> : group_pp_kernel<GPPL, GP_B, 8>;
-    const size_t smem = LY::bytes(p.G, p.L, p.W);
+    void (*kern)(const GroupPPArgs, const GroupPPLens, const GroupRotPlan, const FusedOut, const int64_t, const int) =
+        p.rot ? group_pp_kernel<GPPL, GP_B, 8, true>
+        : p.nq_live == 1 ? group_pp_kernel<GPPL, GP_B, 1, false> : p.nq_live == 2 ? group_pp_kernel<GPPL, GP_B, 2, false>
+        : p.nq_live == 4 ? group_pp_kernel<GPPL, GP_B, 4, false> : group_pp_kernel<GPPL, GP_B, 8, false>;
+    const size_t smem = LY::bytes(p.G, p.L, p.W) + (p.rot ? sizeof(float2) * GPPL::TG : 0);
     if ((int)smem > max_smem_optin()) return fail(XC_ERR_UNSUPPORTED, "group search kernel needs %zu B of shared memory", smem);
-    static KernelOnce once[4];
-    XC_TRY(once[p.nq_live == 1 ? 0 : p.nq_live == 2 ? 1 : p.nq_live == 4 ? 2 : 3].configure(kern, max_smem_optin()));
+    static KernelOnce once[5];
+    XC_TRY(once[p.rot ? 4 : p.nq_live == 1 ? 0 : p.nq_live == 2 ? 1 : p.nq_live == 4 ? 2 : 3].configure(kern, max_smem_optin()));
     GroupPPArgs a{rx, rxlen, shift0, lo, hi, d_starts, p.d_w, p.d_off, p.G, p.L, p.NC, p.nq_live, p.W};
     GroupPPLens lens;
     memcpy(lens.len, p.lens, sizeof(lens.len));
+    GroupRotPlan rp;
+    memcpy(rp.cnt, p.rcnt, sizeof(rp.cnt));
+    memcpy(rp.desc, p.rdesc, sizeof(rp.desc));
     const int64_t per = (K + GP_B - 1) / GP_B;
     int64_t ctas = (int64_t)sm_count();
     if (ctas > per) ctas = per;
@@ -106,7 +160,7 @@ int32_t group_pp_run(const GroupPPPlan& p, const int64_t* d_starts, const float2
     const int64_t chunk = (per + ctas - 1) / ctas;
     if (chunk >= (1ll << 29)) return fail(XC_ERR_UNSUPPORTED, "too many shifts per thread group");
     profile_begin(stream);
-    kern<<<(unsigned)ctas, GPPL::TG * GP_B, smem, stream>>>(a, lens, out, K, (int)chunk);
+    kern<<<(unsigned)ctas, GPPL::TG * GP_B, smem, stream>>>(a, lens, rp, out, K, (int)chunk);
     profile_end(stream);
     XC_LAUNCH_CHECK();
     return XC_OK;

@@ -20,6 +20,20 @@ namespace xc {
 constexpr int GP_MAX_NC = 96;      // padded contributors per thread incl. one chunk of padding (tensor-memory columns: 3 each)
 constexpr int GP_CH = 8;           // contributors per tcgen05.ld pair (lists are padded to 2 GP_CH)
 
+// ROT variant (group starts that are not aligned to the 128-cell rows of the transform: ragged spacings, starts 1000 g, ...).
+// The per-cell lists above are padded to the longest list of a register slot, which a ragged fold blows up (2 contributors
+// per cell on average become 16 per slot).  Here every group is cut into sub-groups of TG = 128 samples; sub-group (a = first
+// cell mod F, r = a mod 128, A = a / 128) lands on rows A (cells r .. 127) and A + 1 (cells 0 .. r - 1) with the SAME thread
+// rotation: thread t multiplies sample l = (t - r) mod 128 of the sub-group by its weight (one tensor-memory column pair per
+// sub-group and thread, no duplicates) and adds the product to row A when t >= r, else to a carry that opens row A + 1.
+// Sub-groups are sorted by row; the row loop is unrolled (static register index), the sub-group loop of a row is a run-time
+// loop whose trip count is the same for every thread.  Capacity: GR_MAX_E sub-groups (2 tensor-memory columns each).
+constexpr int GR_MAX_E = 192;
+struct GroupRotPlan {
+    unsigned char cnt[32];         // sub-groups whose first cell lies in row rho (sorted by row)
+    uint32_t desc[GR_MAX_E];       // r | (first stage cell of the sub-group << 7)
+};
+
 struct GroupPPLens {
     unsigned char len[32];         // padded list length of register slot c (multiple of GP_CH), uniform over the threads
 };
@@ -45,6 +59,12 @@ __device__ __forceinline__ void tmem_ld8_issue(uint32_t taddr, uint32_t* u) {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
                  : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7])
                  : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld2_issue(uint32_t taddr, uint32_t* u) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=r"(u[0]), "=r"(u[1]) : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait2(uint32_t* u) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(u[0]), "+r"(u[1]));
 }
 __device__ __forceinline__ void tmem_ld_wait8(uint32_t* u) {
     asm volatile("tcgen05.wait::ld.sync.aligned;"
@@ -73,7 +93,7 @@ __device__ __forceinline__ void codelet_fft_pruned(float2* a) {
     }
 }
 
-template <class PL, int B>
+template <class PL, int B, bool ROT = false>
 struct GroupPPLayout {
     static_assert(PL::P == 3 && PL::R2 == 32 && PL::R3 == 32 && PL::V == 32 && PL::TG == 128, "4096-point plan: 128 threads x 32 points");
     static constexpr size_t OFF_BUF = 0;
@@ -85,7 +105,7 @@ struct GroupPPLayout {
     // tensor-memory columns of one thread
     static constexpr int COL_W = 0;                       // weights, 2 columns per contributor
     static constexpr int COL_O = 2 * GP_MAX_NC;           // stage byte offsets
-    static constexpr int COL_T1 = 3 * GP_MAX_NC;          // pass-2 input twiddles, chunk layout of fused_fft_pp.cuh
+    static constexpr int COL_T1 = ROT ? 2 * GR_MAX_E : 3 * GP_MAX_NC;   // pass-2 input twiddles, chunk layout of fused_fft_pp.cuh
     static constexpr int COL_T2 = COL_T1 + 64;            // pass-3 input twiddles
     static constexpr int TMEM_COLS = 512;
     static_assert(COL_T2 + 64 <= 512, "tensor memory holds 512 columns");
@@ -129,11 +149,13 @@ __device__ __forceinline__ void gp_pass2(float2* v, float2* buf, const int o2, c
 
 // NQ = number of live pass-1 columns (1, 2, 4 or 8 = all): a template parameter, so that the gather is only unrolled
 // over the 4 NQ register slots that can have contributors and the code of one variant stays inside the instruction cache
-template <class PL, int B, int NQ>
-__global__ void __launch_bounds__(PL::TG* B, 1) group_pp_kernel(const GroupPPArgs a, const GroupPPLens lens, const FusedOut out,
+template <class PL, int B, int NQ, bool ROT>
+__global__ void __launch_bounds__(PL::TG* B, 1) group_pp_kernel(const GroupPPArgs a, const GroupPPLens lens,
+                                                                const __grid_constant__ GroupRotPlan rp, const FusedOut out,
                                                                 const int64_t K, const int chunk) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    using LY = GroupPPLayout<PL, B>;
+    static_assert(!ROT || NQ == PL::V / PL::R1, "the rotated fold reaches every row");
+    using LY = GroupPPLayout<PL, B, ROT>;
     const int W = a.W;                    // extra samples behind every group window (a multiple of B)
     constexpr int TG = PL::TG, V = PL::V, RL = PL::RL, ROW = PL::ROW, R1 = PL::R1;
     const int g = threadIdx.x / TG;       // thread group within the CTA
@@ -165,10 +187,10 @@ __global__ void __launch_bounds__(PL::TG* B, 1) group_pp_kernel(const GroupPPArg
                 const float2 w = a.w[(size_t)(e0 + i) * TG + t];
                 r[2 * i] = w.x;
                 r[2 * i + 1] = w.y;
-                o[i] = a.off[(size_t)(e0 + i) * TG + t];
+                if (!ROT) o[i] = a.off[(size_t)(e0 + i) * TG + t];
             }
             tc::tmem_st16(tb + LY::COL_W + 2 * e0, r);
-            tc::tmem_st8(tb + LY::COL_O + e0, o);
+            if (!ROT) tc::tmem_st8(tb + LY::COL_O + e0, o);
         }
         float r[16];
         const int k1 = t / PL::M2, d = t % PL::M2;
@@ -211,6 +233,9 @@ __global__ void __launch_bounds__(PL::TG* B, 1) group_pp_kernel(const GroupPPArg
     const GroupBar<TG, B> bar{1 + g};
     const int SW = a.L + W;
     const int nstage = a.G * SW;
+    if (ROT) {   // sub-groups of a length that is not a multiple of TG read (with weight zero) up to TG cells behind the last window
+        for (int i = threadIdx.x; i < TG; i += TG * B) stage[nstage + i] = make_float2(0.f, 0.f);
+    }
     const uint32_t stage_s = tc::smem_u32(stage);
     constexpr int K1STEP = (PL::M1 / RL) * ROW;
     constexpr int QSTEP1 = (TG / RL) * ROW;
@@ -238,48 +263,85 @@ __global__ void __launch_bounds__(PL::TG* B, 1) group_pp_kernel(const GroupPPArg
         const bool ok = e < n_act && s + a.lo >= 0 && s + a.hi <= a.rxlen;
         const uint32_t xs = stage_s + 8u * (uint32_t)(o + g);
         o += B;
-        // ---- gather: v[c] = sum_j w[c][j] x[off[c][j]] over the contributor list of register slot c; the chunk of 8
-        // (weights, offsets) after the current one is already on its way from tensor memory, four partial sums ----
-        {
-            uint32_t cw = tb + LY::COL_W, co = tb + LY::COL_O;
-            uint32_t wv[2][16], ov[2][8];
-            tc::tmem_ld16_issue(cw, wv[0]);
-            tc::tmem_ld8_issue(co, ov[0]);
-            int par = 0;                               // runtime parity of the chunk ring: kept uniform by two code copies
+        if constexpr (ROT) {
+            // ---- rotated gather: sub-groups sorted by row; thread t takes sample (t - r) mod TG of each ----
+            static_assert(TG == 128, "rows of 128 cells");
+            uint32_t wn[2];
+            tc::tmem_ld2_issue(tb + LY::COL_W, wn);
+            uint32_t cw = tb + LY::COL_W;
+            int e = 0;
+            float2 carry = make_float2(0.f, 0.f);
 #pragma unroll
-            for (int c = 0; c < R1 * NQ; ++c) {
-                float2 acc[4];
-#pragma unroll
-                for (int i = 0; i < 4; ++i) acc[i] = make_float2(0.f, 0.f);
-                const int n_c = lens.len[c];
+            for (int rho = 0; rho < V; ++rho) {
+                // row rho = cells [128 rho, 128 rho + 128) = (n1, q) with 128 rho = n1 M1 + TG q
+                constexpr int QPR = PL::M1 / TG;                 // rows per n1 block
+                const int c = (rho % QPR) * R1 + rho / QPR;
+                float2 acc = carry;
+                carry = make_float2(0.f, 0.f);
+                const int n = rp.cnt[rho];
 #pragma unroll 1
-                for (int j = 0; j < n_c; j += 2 * GP_CH) {
-                    // lists are padded to a multiple of 16 contributors: two chunks per trip, static register parity
+                for (int i = 0; i < n; ++i) {
+                    const uint32_t d = rp.desc[e];
+                    const int r = (int)(d & 127u);
+                    float2 x;
+                    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(x.x), "=f"(x.y) : "r"(xs + 8u * ((d >> 7) + (uint32_t)((t - r) & 127))));
+                    tc::tmem_ld_wait2(wn);
+                    const float2 y = make_float2(__uint_as_float(wn[0]), __uint_as_float(wn[1]));
+                    ++e;
+                    cw += 2;
+                    tc::tmem_ld2_issue(cw, wn);                  // one padding entry follows the last sub-group
+                    const float2 p = pcmul(x, y);
+                    if (t >= r) acc = padd(acc, p);
+                    else carry = padd(carry, p);
+                }
+                v[c] = acc;
+            }
+            v[0] = padd(v[0], carry);                            // row 31 wraps to row 0 (cells mod F)
+            tc::tmem_ld_wait2(wn);
+        } else {
+        // ---- gather: v[c] = sum_j w[c][j] x[off[c][j]] over the contributor list of register slot c; the chunk of 8
+            // (weights, offsets) after the current one is already on its way from tensor memory, four partial sums ----
+            {
+                uint32_t cw = tb + LY::COL_W, co = tb + LY::COL_O;
+                uint32_t wv[2][16], ov[2][8];
+                tc::tmem_ld16_issue(cw, wv[0]);
+                tc::tmem_ld8_issue(co, ov[0]);
+                int par = 0;                               // runtime parity of the chunk ring: kept uniform by two code copies
 #pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        tc::tmem_ld_wait8(ov[h]);
-                        float2 x[GP_CH];
+                for (int c = 0; c < R1 * NQ; ++c) {
+                    float2 acc[4];
 #pragma unroll
-                        for (int u = 0; u < GP_CH; ++u)
-                            asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(x[u].x), "=f"(x[u].y) : "r"(xs + ov[h][u]));
-                        tc::tmem_ld_wait16(wv[h]);
-                        cw += 2 * GP_CH;
-                        co += GP_CH;
-                        tc::tmem_ld16_issue(cw, wv[h ^ 1]);      // the next chunk (one chunk of padding follows the last list)
-                        tc::tmem_ld8_issue(co, ov[h ^ 1]);
+                    for (int i = 0; i < 4; ++i) acc[i] = make_float2(0.f, 0.f);
+                    const int n_c = lens.len[c];
+#pragma unroll 1
+                    for (int j = 0; j < n_c; j += 2 * GP_CH) {
+                        // lists are padded to a multiple of 16 contributors: two chunks per trip, static register parity
 #pragma unroll
-                        for (int u = 0; u < GP_CH; ++u) {
-                            const float2 y = make_float2(__uint_as_float(wv[h][2 * u]), __uint_as_float(wv[h][2 * u + 1]));
-                            acc[u & 3] = pfma(make_float2(x[u].y, x[u].x), make_float2(-y.y, y.y), pfma(x[u], make_float2(y.x, y.x), acc[u & 3]));
+                        for (int h = 0; h < 2; ++h) {
+                            tc::tmem_ld_wait8(ov[h]);
+                            float2 x[GP_CH];
+#pragma unroll
+                            for (int u = 0; u < GP_CH; ++u)
+                                asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(x[u].x), "=f"(x[u].y) : "r"(xs + ov[h][u]));
+                            tc::tmem_ld_wait16(wv[h]);
+                            cw += 2 * GP_CH;
+                            co += GP_CH;
+                            tc::tmem_ld16_issue(cw, wv[h ^ 1]);      // the next chunk (one chunk of padding follows the last list)
+                            tc::tmem_ld8_issue(co, ov[h ^ 1]);
+#pragma unroll
+                            for (int u = 0; u < GP_CH; ++u) {
+                                const float2 y = make_float2(__uint_as_float(wv[h][2 * u]), __uint_as_float(wv[h][2 * u + 1]));
+                                acc[u & 3] = pfma(make_float2(x[u].y, x[u].x), make_float2(-y.y, y.y), pfma(x[u], make_float2(y.x, y.x), acc[u & 3]));
+                            }
                         }
                     }
+                    v[c] = padd(padd(acc[0], acc[1]), padd(acc[2], acc[3]));
                 }
-                v[c] = padd(padd(acc[0], acc[1]), padd(acc[2], acc[3]));
-            }
-            (void)par;
-            tc::tmem_ld_wait8(ov[0]);                  // drain the last prefetch
+                (void)par;
+                tc::tmem_ld_wait8(ov[0]);                  // drain the last prefetch
 #pragma unroll
-            for (int c = R1 * NQ; c < V; ++c) v[c] = make_float2(0.f, 0.f);
+                for (int c = R1 * NQ; c < V; ++c) v[c] = make_float2(0.f, 0.f);
+            }
         }
         // ---- pass 1: radix-4 columns q < nq_live (the others are all zero), raw stores ----
 #pragma unroll

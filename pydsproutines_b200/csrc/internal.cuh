@@ -46,6 +46,10 @@ struct GroupPPPlan {
     unsigned char lens[32];
     float2* d_w;
     uint32_t* d_off;
+    // rotated-row variant (starts that are not aligned to the 128-cell rows): sub-groups sorted by row
+    int rot;
+    unsigned char rcnt[32];
+    uint32_t rdesc[192];
 };
 int32_t group_pp_build(const float2* y, const int64_t* starts, int G, int L, int F, GroupPPPlan* p);
 void group_pp_release(GroupPPPlan* p);

@@ -949,6 +949,47 @@ def test_warp_layout_windows_leaving_rx(xr):
     assert_bins(f[idx + 37], rf, lambda i: _spec64(cutout, rx, int(idx[i])))
 
 
+@pytest.mark.parametrize("G,L,kind", [(64, 128, "1000g"), (64, 128, "ragged"), (40, 100, "ragged"), (24, 200, "ragged"),
+                                       (64, 128, "dense"), (3, 700, "ragged")])
+def test_group_rotated_rows_vs_oracle_and_ell_layout(xr, G, L, kind):
+    """GroupXcorrFFT, fftlen 4096, contiguous shifts, group starts that are NOT aligned to the 128-cell rows of the transform
+    (csrc/group_pp.cuh, ROT variant: sub-groups of 128 samples sorted by row, rotated thread mapping, carry into the next
+    row): against the same search in short calls (per-cell gather lists, csrc/group.cu) and against the oracle; group
+    lengths that are not a multiple of 128, folds that wrap around fftlen and overlap each other."""
+    F, K = 4096, 1 << 14
+    rng = np.random.default_rng(G * 1000 + L)
+    if kind == "1000g":
+        starts = np.arange(G) * 1000
+    elif kind == "dense":
+        starts = np.sort(rng.integers(0, 3000, G))             # heavily overlapping cells
+    else:
+        starts = np.cumsum(rng.integers(L, 3 * L + 777, G))
+    starts = (starts - starts[0]).astype(np.int64)
+    y = signals.qpsk(rng, G * L).reshape(G, L)
+    span = int(starts[-1]) + F
+    rx = signals.cnoise(rng, K + span)
+    p0, k0 = 9876, 1501
+    for g in range(G):
+        a = p0 + int(starts[g])
+        rx[a:a + L] += np.complex64(0.8) * y[g] * signals.tone(L, k0, F, offset=int(starts[g]))
+    obj = xr.GroupXcorrFFT(y, starts, 1, fftlen=F)
+    q, f, peak = obj.xcorrPeak(_dev(rx), np.arange(K))
+    q, f = q.cpu().numpy(), f.cpu().numpy()
+    assert (peak.shift, peak.fidx) == (p0, k0) and int(np.argmax(q)) == p0 and int(f[p0]) == k0
+    qs, fs = [], []
+    for lo in range(0, K, 2048):                               # < 16 shifts per SM: the gather-list layout
+        qq, ff = obj.xcorr(_dev(rx), np.arange(lo, lo + 2048))
+        qs.append(qq.cpu().numpy())
+        fs.append(ff.cpu().numpy())
+    q2, f2 = np.concatenate(qs), np.concatenate(fs)
+    np.testing.assert_allclose(q, q2, rtol=2e-5, atol=1e-7 * float(q.max()))
+    assert_bins(f, f2, lambda i: _group_spec64(y, starts, rx, F, int(i)), what="group bin")
+    idx = np.r_[np.arange(0, 12), np.arange(p0 - 6, p0 + 6), np.arange(K - 12, K)]
+    qr, fr = orc.GroupXcorrFFT(y, starts, 1, fftlen=F).xcorr(rx, idx)
+    assert_qf2(q[idx], qr)
+    assert_bins(f[idx], fr, lambda i: _group_spec64(y, starts, rx, F, int(idx[i])), what="group bin")
+
+
 def test_groupfreq_large_planted_and_sampled(xr):
     """C3's groups (64 x 128 at 1024 g) against 256 frequencies over 2^17 shifts: the planted (shift, frequency) is the
     global peak, and 48 randomly sampled shifts agree with the oracle (size-independent checks at bench-like size)."""
