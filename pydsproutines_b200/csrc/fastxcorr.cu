@@ -23,6 +23,7 @@ namespace xc {
 // search_pp.cu: the ping-pong layout of the N = 8192 search (fused_fft_pp.cuh); fold = 1 is the shipped variant
 int32_t search_pp_device(const StagedArgs& a, const FusedOut& out, int64_t K, int N, int fold, cudaStream_t stream);
 bool search_pp_takes(int N);
+constexpr int PP_MAX_STEP = 16;       // (groups per SM - 1) * step stays well inside the 2048 samples of window slack
 
 // ---------------------------------------------------------------------------------------------
 // loader of the fused kernel: v[n] = rx[s + n] * conj(cutout[n])
@@ -216,17 +217,18 @@ struct FreqRunner {
             // over one staged rx window, constants in tensor memory (fused_fft_pp.cuh).  Short ranges, shift lists with
             // a step or a gather table and the CAF / complex outputs stay on the B-groups-per-CTA layout below.
             const int layout = search_layout();
-            const bool plain = !out.caf && !out.cplx;
-            const bool contiguous = !sl.shifts && sl.step == 1 && sl.K >= 16 * (int64_t)sm_count();
+            const bool plain = !out.caf;          // (max, arg max) and, optionally, the complex QF at the arg max
+            // a shift range with a small step runs from the same staged window (it is refilled more often)
+            const bool contiguous = !sl.shifts && sl.step >= 1 && sl.step <= PP_MAX_STEP && sl.K >= 16 * (int64_t)sm_count();
             if (layout == LAYOUT_PP && plain && contiguous)
-                return search_pp_device(StagedArgs{rx, rxlen, cutout, sl.shift0}, out, sl.K, 1 << LOG2N, 1, stream);
+                return search_pp_device(StagedArgs{rx, rxlen, cutout, sl.shift0, (int)sl.step}, out, sl.K, 1 << LOG2N, 1, stream);
 #ifdef XC_EXPERIMENTS
             if constexpr (LOG2N == 13) {
-                if (layout == LAYOUT_PP_CHAIN && plain && contiguous)
+                if (layout == LAYOUT_PP_CHAIN && plain && !out.cplx && contiguous)
                     return search_pp_device(StagedArgs{rx, rxlen, cutout, sl.shift0}, out, sl.K, 1 << LOG2N, 0, stream);
-                if (layout == LAYOUT_STAGED && plain && contiguous)
+                if (layout == LAYOUT_STAGED && plain && !out.cplx && contiguous)
                     return launch_fused_staged<typename PF::PL>(StagedArgs{rx, rxlen, cutout, sl.shift0}, out, sl.K, stream);
-                if (layout == LAYOUT_DUAL && plain) return launch_fused_dual<typename PF::PL, LD>(ld, out, sl.K, stream);
+                if (layout == LAYOUT_DUAL && plain && !out.cplx) return launch_fused_dual<typename PF::PL, LD>(ld, out, sl.K, stream);
             }
 #endif
         }
@@ -431,6 +433,11 @@ struct BlueRunner {
     }
 };
 
+__global__ void pick_stride_kernel(const float* __restrict__ in, int64_t step, int64_t K, float* __restrict__ out) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < K; i += stride) out[i] = in[i * step];
+}
+
 int32_t fastxcorr_freq_device(const float2* cutout, int N, const float2* rx, int64_t rxlen, const ShiftList& sl,
                               float* qf2, uint32_t* fidx, float2* cplx, void* caf, int caf_complex,
                               cudaStream_t stream, const CztSpec* czt) {
@@ -452,6 +459,17 @@ int32_t fastxcorr_freq_device(const float2* cutout, int N, const float2* rx, int
     XC_TRY(normsq_device(cutout, N, 1, N, d_refn, stream));
     if (!sl.shifts && sl.step == 1 && sl.shift0 >= 0 && sl.shift0 + sl.K - 1 + N <= rxlen) {
         XC_TRY(sliding_sum_device(rx + sl.shift0, true, rxlen - sl.shift0, 0, N, sl.K, d_energy, 0, stream));
+    } else if (!sl.shifts && sl.step >= 2 && sl.step <= PP_MAX_STEP && sl.shift0 >= 0 && sl.shift0 + (sl.K - 1) * sl.step + N <= rxlen && N >= 256) {
+        // a small step: the sliding sum over the covered range, then every step-th value (one warp per window would read
+        // K N samples instead of K step)
+        const int64_t nall = (sl.K - 1) * sl.step + 1;
+        float* d_all = reinterpret_cast<float*>(workspace(SLOT_TMP2, sizeof(float) * (size_t)nall));
+        if (!d_all) return XC_ERR_NOMEM;
+        XC_TRY(sliding_sum_device(rx + sl.shift0, true, rxlen - sl.shift0, 0, N, nall, d_all, 0, stream));
+        int64_t blocks = (sl.K + 255) / 256;
+        if (blocks > (int64_t)sm_count() * 16) blocks = (int64_t)sm_count() * 16;
+        pick_stride_kernel<<<(unsigned)blocks, 256, 0, stream>>>(d_all, sl.step, sl.K, d_energy);
+        XC_LAUNCH_CHECK();
     } else {
         XC_TRY(window_energy_device(rx, rxlen, N, sl.shift0, sl.step, sl.shifts, sl.K, d_energy, stream));
     }

@@ -41,7 +41,8 @@ struct StagedArgs {
     const float2* rx;
     int64_t rxlen;
     const float2* cutout;
-    int64_t shift0;       // the shift of entry i is shift0 + i
+    int64_t shift0;       // the shift of entry i is shift0 + i * step
+    int step = 1;         // 1 <= step, (B - 1) step <= the window slack of the layout
 };
 
 // Loader concept (all const; the kernel argument is never copied into registers):

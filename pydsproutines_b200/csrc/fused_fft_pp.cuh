@@ -75,7 +75,7 @@ struct PPLayout {
     static constexpr size_t OFF_STAGE = sizeof(float2) * (size_t)PL::BUF * B;
     static constexpr size_t OFF_GMAX = OFF_STAGE + sizeof(float2) * (size_t)(PL::N + W);   // [B][2] bit patterns
     static constexpr size_t OFF_BIN = OFF_GMAX + sizeof(unsigned int) * 2 * B;             // [B]
-    static constexpr size_t OFF_TADDR = OFF_BIN + sizeof(unsigned int) * B;
+    static constexpr size_t OFF_TADDR = OFF_BIN + sizeof(unsigned int) * 2 * B;            // OFF_BIN: [B][2]
     static constexpr size_t BYTES = OFF_TADDR + 16;
     // tensor-memory columns of one thread (32-bit each)
     static constexpr int NQ1 = PL::V / PL::R1;                            // pass-1 columns per thread
@@ -268,7 +268,10 @@ __device__ __forceinline__ void pp_block_fft_fold(float2* v, const float2* x, co
     for (int q = 0; q < NQ2; ++q) codelet_fft<RL, 2>(v + q * RL);
 }
 
-template <class PL, int B, bool FOLD>
+// CPLX: also writes the complex QF X[bin] / (||cutout|| ||window||) of the absResult = False variants
+// (xcorrRoutines.py:533-548): a thread that reaches the group maximum keeps its candidate (bin, value) in registers until the
+// winning bin is known (one FFT later); the bin slots alternate so that the reset never races with those reads.
+template <class PL, int B, bool FOLD, bool CPLX = false>
 __global__ void __launch_bounds__(PL::TG* B, 1) fused_fft_pp_kernel(const StagedArgs a, const FusedOut out, const int64_t K,
                                                                     const int chunk) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -280,11 +283,12 @@ __global__ void __launch_bounds__(PL::TG* B, 1) fused_fft_pp_kernel(const Staged
     float2* const buf = reinterpret_cast<float2*>(smem_raw + L::OFF_BUF) + (size_t)g * PL::BUF;
     float2* const stage = reinterpret_cast<float2*>(smem_raw + L::OFF_STAGE);
     unsigned int* const gmax = reinterpret_cast<unsigned int*>(smem_raw + L::OFF_GMAX) + 2 * g;
-    unsigned int* const binmin = reinterpret_cast<unsigned int*>(smem_raw + L::OFF_BIN) + g;
+    unsigned int* const binmin = reinterpret_cast<unsigned int*>(smem_raw + L::OFF_BIN) + 2 * g;
     uint32_t* const taddr_slot = reinterpret_cast<uint32_t*>(smem_raw + L::OFF_TADDR);
     if (warp_cta == 0) tc::tmem_alloc(tc::smem_u32(taddr_slot), L::TMEM_COLS);
     if (t == 0) {
-        *binmin = 0xffffffffu;
+        binmin[0] = 0xffffffffu;
+        binmin[1] = 0xffffffffu;
         gmax[0] = 0u;
         gmax[1] = 0u;
     }
@@ -367,19 +371,22 @@ __global__ void __launch_bounds__(PL::TG* B, 1) fused_fft_pp_kernel(const Staged
     if (n_left < 0) n_left = 0;
     if (n_left > B * (int64_t)chunk) n_left = B * (int64_t)chunk;
     const int n_act = (int)n_left;
-    const int64_t s_first = a.shift0 + i0;
+    const int step = a.step;
+    const int64_t s_first = a.shift0 + i0 * step;
     const GroupBar<TG, B> bar{1 + g};
     float2 v[V];
     float pend = 0.f;                                  // thread 0 of the group: QF^2 of the previous FFT
-    int o = W;                                         // offset of the current B shifts inside the stage
+    float2 cand = make_float2(0.f, 0.f);               // CPLX: this thread's candidate for the previous FFT
+    unsigned int cand_bin = 0xffffffffu;
+    int o = W + 1;                                     // offset of the current B shifts inside the stage
 
     for (int it = 0; it < chunk; ++it) {
         const int e = B * it + g;
-        if (o == W) {
+        if (o + (B - 1) * step > W) {
             // refill: stage[j] = rx[s + j], j < N + W (zero outside the record).  The first barrier makes sure no
             // group still reads the old window.
             __syncthreads();
-            const int64_t base = s_first + (int64_t)B * it;
+            const int64_t base = s_first + (int64_t)B * it * step;
             for (int j = threadIdx.x; j < PL::N + W; j += TG * B) {
                 const int64_t gi = base + j;
                 stage[j] = (gi >= 0 && gi < a.rxlen) ? __ldg(a.rx + gi) : make_float2(0.f, 0.f);
@@ -387,24 +394,32 @@ __global__ void __launch_bounds__(PL::TG* B, 1) fused_fft_pp_kernel(const Staged
             o = 0;
             __syncthreads();
         }
-        const int64_t s = s_first + e;
+        const int64_t s = s_first + (int64_t)e * step;
         // windows that leave the record still run (the stage is zero filled there); their results are dropped
         const bool ok = e < n_act && s >= 0 && s + PL::N <= a.rxlen;
-        const float2* const xw = stage + o + g + t;
-        o += B;
+        const float2* const xw = stage + o + g * step + t;
+        o += B * step;
         // the barrier inside also orders the previous FFT's bin-minimum atomics before thread 0 reads them
         if constexpr (FOLD)
             pp_block_fft_fold<PL, B>(v, xw, tb, buf, t, bar);
         else
             pp_block_fft<PL, B>(v, xw, tb, buf, t, bar);
+        unsigned int* const bslot = binmin + (CPLX ? (it & 1) : 0);          // this FFT's bin slot
         if (t == 0 && it > 0) {                        // results of the previous FFT of this group
             const int p = e - B;
             if (p < n_act) {
-                const unsigned int b = *binmin;
+                const unsigned int b = CPLX ? binmin[(it & 1) ^ 1] : *binmin;
                 if (out.qf2) out.qf2[i0 + p] = pend;
                 if (out.fidx) out.fidx[i0 + p] = (b == 0xffffffffu) ? 0u : b;
             }
-            *binmin = 0xffffffffu;
+            if (!CPLX) *binmin = 0xffffffffu;
+        }
+        if constexpr (CPLX) {
+            if (cand_bin != 0xffffffffu && cand_bin == binmin[(it & 1) ^ 1]) {
+                const float sc = 1.f / (sqrtf(*out.refnormsq) * sqrtf(out.energy[i0 + e - B]));
+                out.cplx[i0 + e - B] = make_float2(cand.x * sc, cand.y * sc);
+            }
+            cand_bin = 0xffffffffu;
         }
         // ---- |X|^2 and the group maximum: |X|^2 >= +0, so the float order is the order of the bit patterns:
         // one REDUX per warp, one shared atomic per warp into the slot of this iteration's parity ----
@@ -424,7 +439,7 @@ __global__ void __launch_bounds__(PL::TG* B, 1) fused_fft_pp_kernel(const Staged
 #pragma unroll
                 for (int j = 0; j < PL::RL; ++j)
                     if (cnorm2(v[q * PL::RL + j]) == m) mybin = min(mybin, (unsigned int)output_bin<PL>(t, q, j));
-            atomicMin(binmin, mybin);
+            atomicMin(bslot, mybin);
         }
 #else
         // maxima of chunks of 8 registers first: the one thread that holds the group maximum then only searches the
@@ -444,6 +459,7 @@ __global__ void __launch_bounds__(PL::TG* B, 1) fused_fft_pp_kernel(const Staged
         bar();   // all last-pass loads done (buffer free) + group maximum complete
         const float m = __uint_as_float(gmax[it & 1]);
         if (t == 0) gmax[(it & 1) ^ 1] = 0u;
+        if (CPLX && t == 0) binmin[(it & 1) ^ 1] = 0xffffffffu;       // read for the last time before this barrier
         if (ok && tmax == m) {
             unsigned int mybin = 0xffffffffu;
 #pragma unroll
@@ -452,22 +468,36 @@ __global__ void __launch_bounds__(PL::TG* B, 1) fused_fft_pp_kernel(const Staged
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
                         const int j = 8 * c + i;
-                        if (nv[j] == m) mybin = min(mybin, (unsigned int)output_bin<PL>(t, j / PL::RL, j % PL::RL));
+                        if (nv[j] == m) {
+                            const unsigned int bj = (unsigned int)output_bin<PL>(t, j / PL::RL, j % PL::RL);
+                            if (bj < mybin) {
+                                mybin = bj;
+                                if (CPLX) cand = v[j];
+                            }
+                        }
                     }
                 }
             }
-            atomicMin(binmin, mybin);
+            atomicMin(bslot, mybin);
+            if (CPLX) cand_bin = mybin;
         }
 #endif
         if (t == 0) pend = (ok) ? m / *out.refnormsq / out.energy[i0 + e] : 0.f;
+        if (CPLX && t == 0 && e < n_act && !ok) out.cplx[i0 + e] = make_float2(0.f, 0.f);
     }
     bar();
-    if (t == 0 && chunk > 0) {                         // the last FFT of this group
+    if (chunk > 0) {                                   // the last FFT of this group
         const int p = B * (chunk - 1) + g;
-        if (p < n_act) {
-            const unsigned int b = *binmin;
+        const unsigned int b = binmin[CPLX ? ((chunk - 1) & 1) : 0];
+        if (t == 0 && p < n_act) {
             if (out.qf2) out.qf2[i0 + p] = pend;
             if (out.fidx) out.fidx[i0 + p] = (b == 0xffffffffu) ? 0u : b;
+        }
+        if constexpr (CPLX) {
+            if (cand_bin != 0xffffffffu && cand_bin == b) {
+                const float sc = 1.f / (sqrtf(*out.refnormsq) * sqrtf(out.energy[i0 + p]));
+                out.cplx[i0 + p] = make_float2(cand.x * sc, cand.y * sc);
+            }
         }
     }
     tc::tc_fence_before();
@@ -477,11 +507,11 @@ __global__ void __launch_bounds__(PL::TG* B, 1) fused_fft_pp_kernel(const Staged
 
 template <class PL, int B, bool FOLD>
 int32_t launch_fused_pp(const StagedArgs& a, const FusedOut& out, int64_t K, cudaStream_t stream) {
-    auto kern = fused_fft_pp_kernel<PL, B, FOLD>;
+    auto kern = (FOLD && out.cplx) ? fused_fft_pp_kernel<PL, B, FOLD, FOLD> : fused_fft_pp_kernel<PL, B, FOLD, false>;
     constexpr size_t smem = PPLayout<PL, B, FOLD>::BYTES;
     if ((int)smem > max_smem_optin()) return fail(XC_ERR_UNSUPPORTED, "ping-pong fused kernel needs %zu B of shared memory", smem);
-    static KernelOnce once;
-    XC_TRY(once.configure(kern, max_smem_optin()));
+    static KernelOnce once[2];
+    XC_TRY(once[(FOLD && out.cplx) ? 1 : 0].configure(kern, max_smem_optin()));
     const int64_t per = (K + B - 1) / B;               // iterations if one CTA did everything
     int64_t ctas = (int64_t)sm_count();
     if (ctas > per) ctas = per;

@@ -28,7 +28,8 @@ struct WarpLayout {
     static constexpr int COL_CUT = 0, COL_T2 = 64, TMEM_COLS = 128;
 };
 
-template <int B>
+// CPLX: also writes the complex QF X[bin] / (||cutout|| ||window||) of the absResult = False variants (xcorrRoutines.py:533-548)
+template <int B, bool CPLX>
 __global__ void __launch_bounds__(32 * B, 1) fused_fft_warp_kernel(const StagedArgs a, const FusedOut out, const int64_t K,
                                                                    const int chunk) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -79,17 +80,18 @@ __global__ void __launch_bounds__(32 * B, 1) fused_fft_warp_kernel(const StagedA
     if (n_left < 0) n_left = 0;
     if (n_left > B * (int64_t)chunk) n_left = B * (int64_t)chunk;
     const int n_act = (int)n_left;
-    const int64_t s_first = a.shift0 + i0;
+    const int step = a.step;
+    const int64_t s_first = a.shift0 + i0 * step;
     const float refn = *out.refnormsq;
     float2 v[32];
     uint32_t cu[2][16];
-    int o = W;
+    int o = W + 1;
 
     for (int it = 0; it < chunk; ++it) {
         const int e = B * it + g;
-        if (o == W) {
+        if (o + (B - 1) * step > W) {
             __syncthreads();               // no warp still reads the old window
-            const int64_t base = s_first + (int64_t)B * it;
+            const int64_t base = s_first + (int64_t)B * it * step;
             for (int j = threadIdx.x; j < N + W; j += 32 * B) {
                 const int64_t gi = base + j;
                 stage[j] = (gi >= 0 && gi < a.rxlen) ? __ldg(a.rx + gi) : make_float2(0.f, 0.f);
@@ -97,10 +99,10 @@ __global__ void __launch_bounds__(32 * B, 1) fused_fft_warp_kernel(const StagedA
             o = 0;
             __syncthreads();
         }
-        const int64_t s = s_first + e;
+        const int64_t s = s_first + (int64_t)e * step;
         const bool ok = e < n_act && s >= 0 && s + N <= a.rxlen;
-        const float2* const x = stage + o + g + t;
-        o += B;
+        const float2* const x = stage + o + g * step + t;
+        o += B * step;
         float en = 1.f;
         if (t == 0 && ok) en = __ldg(out.energy + i0 + e);     // in flight under the FFT
         // ---- pass 1: column c = t, product folded into the first stage ----
@@ -164,6 +166,20 @@ __global__ void __launch_bounds__(32 * B, 1) fused_fft_warp_kernel(const StagedA
             if (out.qf2) out.qf2[i0 + e] = ok ? mx / refn / en : 0.f;
             if (out.fidx) out.fidx[i0 + e] = (ok && bin != 0xffffffffu) ? bin : 0u;
         }
+        if constexpr (CPLX) {
+            const float enb = __shfl_sync(0xffffffffu, en, 0);
+            if (e < n_act && t == (int)(ok ? (bin & 31u) : 0u)) {        // the lane that holds the winning bin
+                float2 z = make_float2(0.f, 0.f);
+                if (ok) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if ((unsigned int)(t + 32 * bitrev(j, 5)) == bin) z = v[j];
+                    const float sc = 1.f / (sqrtf(refn) * sqrtf(enb));
+                    z = make_float2(z.x * sc, z.y * sc);
+                }
+                out.cplx[i0 + e] = z;
+            }
+        }
     }
     tc::tc_fence_before();
     __syncthreads();
@@ -172,11 +188,11 @@ __global__ void __launch_bounds__(32 * B, 1) fused_fft_warp_kernel(const StagedA
 
 template <int B>
 int32_t launch_fused_warp(const StagedArgs& a, const FusedOut& out, int64_t K, cudaStream_t stream) {
-    auto kern = fused_fft_warp_kernel<B>;
+    auto kern = out.cplx ? fused_fft_warp_kernel<B, true> : fused_fft_warp_kernel<B, false>;
     constexpr size_t smem = WarpLayout<B>::BYTES;
     if ((int)smem > max_smem_optin()) return fail(XC_ERR_UNSUPPORTED, "warp-per-FFT kernel needs %zu B of shared memory", smem);
-    static KernelOnce once;
-    XC_TRY(once.configure(kern, max_smem_optin()));
+    static KernelOnce once[2];
+    XC_TRY(once[out.cplx ? 1 : 0].configure(kern, max_smem_optin()));
     const int64_t per = (K + B - 1) / B;
     int64_t ctas = (int64_t)sm_count();
     if (ctas > per) ctas = per;

@@ -22,15 +22,31 @@ void group_pp_release(GroupPPPlan* p) {
 
 // Rotated-row plan (group_pp.cuh, ROT): every group is cut into sub-groups of TG samples, sorted by the row their first
 // cell lies in; thread t holds the weight of sample (t - r) mod TG of each sub-group.
-static int32_t group_rot_build(const float2* y, const int64_t* starts, int G, int L, int F, int W, GroupPPPlan* p) {
+template <int B>
+static int rot_window_slack(int G, int L) {
+    using LY = GroupPPLayout<GPPL, B, true>;
+    // the stage keeps TG zero cells behind the last window
+    const int64_t room = (int64_t)max_smem_optin() - (int64_t)LY::OFF_STAGE - (int64_t)sizeof(float2) * GPPL::TG;
+    int W = ((int)(room / (int64_t)(sizeof(float2) * (size_t)G)) - L) / B * B;
+    if (W > 252 / B * B) W = 252 / B * B;
+    return W;
+}
+#ifndef XC_GR_B
+#define XC_GR_B 3
+#endif
+static int32_t group_rot_build(const float2* y, const int64_t* starts, int G, int L, int F, GroupPPPlan* p) {
     constexpr int TG = GPPL::TG;
     static_assert(GR_MAX_E == sizeof(p->rdesc) / sizeof(p->rdesc[0]), "descriptor table size");
     const int per = (L + TG - 1) / TG;
     const int E = G * per;
-    if (E + 1 > GR_MAX_E) return XC_OK;
-    // the stage keeps TG zero cells behind the last window
-    while (W >= 4 * GP_B && GroupPPLayout<GPPL, GP_B, true>::bytes(G, L, W) + sizeof(float2) * TG > (size_t)max_smem_optin()) W -= GP_B;
-    if (W < 4 * GP_B) return XC_OK;
+    if (E + 2 > GR_MAX_E) return XC_OK;
+    // four thread groups per SM when their exchange buffers leave at least 16 samples of window slack, else three
+    int B = XC_GR_B, W = (XC_GR_B == 4) ? rot_window_slack<4>(G, L) : rot_window_slack<GP_B>(G, L);
+    if (B == 4 && W < 16) {
+        B = GP_B;
+        W = rot_window_slack<GP_B>(G, L);
+    }
+    if (W < 4 * B) return XC_OK;
     const int SW = L + W;
     struct Sub { int row, r, g, i; };
     std::vector<Sub> subs;
@@ -40,7 +56,7 @@ static int32_t group_rot_build(const float2* y, const int64_t* starts, int G, in
             subs.push_back(Sub{(int)(a / TG), (int)(a % TG), g, i});
         }
     std::stable_sort(subs.begin(), subs.end(), [](const Sub& x, const Sub& z) { return x.row < z.row; });
-    const int NC = (E + 1 + GP_CH - 1) / GP_CH * GP_CH;   // one padding entry (the gather prefetches one ahead), whole st16 chunks
+    const int NC = (E + 2 + GP_CH - 1) / GP_CH * GP_CH;   // padding entries (the gather prefetches ahead), whole st16 chunks
     std::vector<float2> hw((size_t)NC * TG, make_float2(0.f, 0.f));
     memset(p->rcnt, 0, sizeof(p->rcnt));
     for (int e = 0; e < E; ++e) {
@@ -62,6 +78,7 @@ static int32_t group_rot_build(const float2* y, const int64_t* starts, int G, in
     p->NC = NC;
     p->nq_live = GPPL::V / GPPL::R1;
     p->rot = 1;
+    p->B = B;
     p->usable = 1;
     return XC_OK;
 }
@@ -98,7 +115,7 @@ int32_t group_pp_build(const float2* y, const int64_t* starts, int G, int L, int
         len = (len + 2 * GP_CH - 1) / (2 * GP_CH) * (2 * GP_CH);
         if (len > 248) {
             memset(p, 0, sizeof(*p));
-            return group_rot_build(y, starts, G, L, F, W, p);
+            return group_rot_build(y, starts, G, L, F, p);
         }
         if (len > 0) qtop = q;
         p->lens[c] = (unsigned char)len;
@@ -107,7 +124,7 @@ int32_t group_pp_build(const float2* y, const int64_t* starts, int G, int L, int
     const int NC = base[V] + GP_CH;                       // one chunk of padding: the gather prefetches one chunk ahead
     if (base[V] == 0 || NC > GP_MAX_NC) {
         memset(p, 0, sizeof(*p));
-        return group_rot_build(y, starts, G, L, F, W, p);
+        return group_rot_build(y, starts, G, L, F, p);
     }
     int nq = 1;
     while (nq < qtop + 1) nq <<= 1;
@@ -132,17 +149,19 @@ int32_t group_pp_build(const float2* y, const int64_t* starts, int G, int L, int
     p->W = W;
     p->NC = NC;
     p->nq_live = nq;
+    p->B = GP_B;
     p->usable = 1;
     return XC_OK;
 }
 
-int32_t group_pp_run(const GroupPPPlan& p, const int64_t* d_starts, const float2* rx, int64_t rxlen, int64_t shift0, int64_t K,
-                     int64_t lo, int64_t hi, const FusedOut& out, cudaStream_t stream) {
-    using LY = GroupPPLayout<GPPL, GP_B>;
+template <int B>
+static int32_t group_pp_launch(const GroupPPPlan& p, const int64_t* d_starts, const float2* rx, int64_t rxlen, int64_t shift0,
+                               int64_t K, int64_t lo, int64_t hi, const FusedOut& out, cudaStream_t stream) {
+    using LY = GroupPPLayout<GPPL, B>;
     void (*kern)(const GroupPPArgs, const GroupPPLens, const GroupRotPlan, const FusedOut, const int64_t, const int) =
-        p.rot ? group_pp_kernel<GPPL, GP_B, 8, true>
-        : p.nq_live == 1 ? group_pp_kernel<GPPL, GP_B, 1, false> : p.nq_live == 2 ? group_pp_kernel<GPPL, GP_B, 2, false>
-        : p.nq_live == 4 ? group_pp_kernel<GPPL, GP_B, 4, false> : group_pp_kernel<GPPL, GP_B, 8, false>;
+        p.rot ? group_pp_kernel<GPPL, B, 8, true>
+        : p.nq_live == 1 ? group_pp_kernel<GPPL, B, 1, false> : p.nq_live == 2 ? group_pp_kernel<GPPL, B, 2, false>
+        : p.nq_live == 4 ? group_pp_kernel<GPPL, B, 4, false> : group_pp_kernel<GPPL, B, 8, false>;
     const size_t smem = LY::bytes(p.G, p.L, p.W) + (p.rot ? sizeof(float2) * GPPL::TG : 0);
     if ((int)smem > max_smem_optin()) return fail(XC_ERR_UNSUPPORTED, "group search kernel needs %zu B of shared memory", smem);
     static KernelOnce once[5];
@@ -153,17 +172,23 @@ int32_t group_pp_run(const GroupPPPlan& p, const int64_t* d_starts, const float2
     GroupRotPlan rp;
     memcpy(rp.cnt, p.rcnt, sizeof(rp.cnt));
     memcpy(rp.desc, p.rdesc, sizeof(rp.desc));
-    const int64_t per = (K + GP_B - 1) / GP_B;
+    const int64_t per = (K + B - 1) / B;
     int64_t ctas = (int64_t)sm_count();
     if (ctas > per) ctas = per;
     if (ctas < 1) ctas = 1;
     const int64_t chunk = (per + ctas - 1) / ctas;
     if (chunk >= (1ll << 29)) return fail(XC_ERR_UNSUPPORTED, "too many shifts per thread group");
     profile_begin(stream);
-    kern<<<(unsigned)ctas, GPPL::TG * GP_B, smem, stream>>>(a, lens, rp, out, K, (int)chunk);
+    kern<<<(unsigned)ctas, GPPL::TG * B, smem, stream>>>(a, lens, rp, out, K, (int)chunk);
     profile_end(stream);
     XC_LAUNCH_CHECK();
     return XC_OK;
+}
+
+int32_t group_pp_run(const GroupPPPlan& p, const int64_t* d_starts, const float2* rx, int64_t rxlen, int64_t shift0, int64_t K,
+                     int64_t lo, int64_t hi, const FusedOut& out, cudaStream_t stream) {
+    if (p.B == 4) return group_pp_launch<4>(p, d_starts, rx, rxlen, shift0, K, lo, hi, out, stream);
+    return group_pp_launch<GP_B>(p, d_starts, rx, rxlen, shift0, K, lo, hi, out, stream);
 }
 
 }  // namespace xc

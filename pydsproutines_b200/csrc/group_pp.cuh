@@ -266,10 +266,16 @@ __global__ void __launch_bounds__(PL::TG* B, 1) group_pp_kernel(const GroupPPArg
         if constexpr (ROT) {
             // ---- rotated gather: sub-groups sorted by row; thread t takes sample (t - r) mod TG of each ----
             static_assert(TG == 128, "rows of 128 cells");
+            // software pipeline over the sorted sub-group list, independent of the row structure: descriptor two entries
+            // ahead, sample and weight one entry ahead (the loop body would otherwise be one serial chain
+            // LDC -> address -> LDS -> FMA per sub-group; two zero entries follow the last sub-group)
             uint32_t wn[2];
             tc::tmem_ld2_issue(tb + LY::COL_W, wn);
             uint32_t cw = tb + LY::COL_W;
             int e = 0;
+            uint32_t d_n = rp.desc[0], d_nn = rp.desc[1];
+            float2 x_n;
+            asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(x_n.x), "=f"(x_n.y) : "r"(xs + 8u * ((d_n >> 7) + (uint32_t)((t - (int)(d_n & 127u)) & 127))));
             float2 carry = make_float2(0.f, 0.f);
 #pragma unroll
             for (int rho = 0; rho < V; ++rho) {
@@ -281,15 +287,17 @@ __global__ void __launch_bounds__(PL::TG* B, 1) group_pp_kernel(const GroupPPArg
                 const int n = rp.cnt[rho];
 #pragma unroll 1
                 for (int i = 0; i < n; ++i) {
-                    const uint32_t d = rp.desc[e];
-                    const int r = (int)(d & 127u);
-                    float2 x;
-                    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(x.x), "=f"(x.y) : "r"(xs + 8u * ((d >> 7) + (uint32_t)((t - r) & 127))));
+                    const int r = (int)(d_n & 127u);
                     tc::tmem_ld_wait2(wn);
                     const float2 y = make_float2(__uint_as_float(wn[0]), __uint_as_float(wn[1]));
-                    ++e;
+                    const float2 x = x_n;
+                    // next entry on its way
+                    d_n = d_nn;
+                    e += 1;
+                    d_nn = rp.desc[e + 1];
                     cw += 2;
-                    tc::tmem_ld2_issue(cw, wn);                  // one padding entry follows the last sub-group
+                    tc::tmem_ld2_issue(cw, wn);
+                    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(x_n.x), "=f"(x_n.y) : "r"(xs + 8u * ((d_n >> 7) + (uint32_t)((t - (int)(d_n & 127u)) & 127))));
                     const float2 p = pcmul(x, y);
                     if (t >= r) acc = padd(acc, p);
                     else carry = padd(carry, p);

@@ -47,7 +47,7 @@ struct GroupPPPlan {
     float2* d_w;
     uint32_t* d_off;
     // rotated-row variant (starts that are not aligned to the 128-cell rows): sub-groups sorted by row
-    int rot;
+    int rot, B;                  // B = thread groups per SM of the kernel variant
     unsigned char rcnt[32];
     uint32_t rdesc[192];
 };

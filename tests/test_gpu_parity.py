@@ -924,6 +924,63 @@ def test_pingpong_layout_matches_b2_layout(xr):
     assert f[123456 + 50] == rf[60]
 
 
+@pytest.mark.parametrize("N,step", [(1024, 3), (2048, 2), (4096, 16), (8192, 5)])
+def test_staged_layouts_stepped_ranges(xr, N, step):
+    """Shift ranges with a small step (CyIppXcorrFFT.xcorr(rx, start, end, step), fastXcorr(shifts=arange(a, b, step))) run
+    the staged-window layouts too: against the contiguous search at the same shifts and against the oracle."""
+    K = 60000
+    cutout, rx = signals.make_fastxcorr_case(50 + N + step, N, N + K - 1, 30000 - 30000 % step + 0, N // 3, amp=0.7)
+    p0 = 30000 - 30000 % step
+    q1, f1 = xr.fastXcorr(_dev(cutout), _dev(rx), freqsearch=True)
+    q1, f1 = q1.cpu().numpy(), f1.cpu().numpy()
+    sh = np.arange(7, K, step)
+    q, f = xr.fastXcorr(_dev(cutout), _dev(rx), freqsearch=True, shifts=sh)
+    q, f = q.cpu().numpy(), f.cpu().numpy()
+    np.testing.assert_allclose(q, q1[sh], rtol=2e-6, atol=1e-9)
+    assert_bins(f, f1[sh], lambda i: _spec64(cutout, rx, int(sh[i])))
+    obj = xr.CyIppXcorrFFT(cutout)
+    a, b = -3 * step, K + 2 * step                              # windows leaving rx on both sides
+    qc, fc = obj.xcorr(rx, a, b, step)
+    shc = np.arange(a, b, step)
+    inside = (shc >= 0) & (shc + N <= rx.size)
+    assert not qc[~inside].any() and not fc[~inside].any()
+    np.testing.assert_allclose(qc[inside], q1[shc[inside]], rtol=2e-6, atol=1e-9)
+    j = int(np.argmax(qc))
+    assert shc[j] == p0 and fc[j] == N // 3
+    idx = np.r_[0:16, sh.size - 16:sh.size]
+    rq, rf = orc.fastXcorr(cutout, rx, freqsearch=True, shifts=sh[idx])
+    assert_qf2(q[idx], rq)
+    assert_bins(f[idx], rf, lambda i: _spec64(cutout, rx, int(sh[idx[i]])))
+
+
+@pytest.mark.parametrize("N,step", [(1024, 1), (2048, 1), (4096, 3), (8192, 1)])
+def test_staged_layouts_complex_qf(xr, N, step):
+    """absResult=False (complex QF at the arg max, xcorrRoutines.py:533-548) from the staged-window layouts: against short
+    calls (B-groups-per-CTA layout) and the oracle; the squared magnitude equals the QF^2 of the same call."""
+    K = 20000
+    cutout, rx = signals.make_fastxcorr_case(90 + N, N, N + K - 1, 12345 - 12345 % step, 17, amp=0.6)
+    sh = np.arange(0, K, step)
+    z, f = xr.fastXcorr(_dev(cutout), _dev(rx), freqsearch=True, absResult=False, shifts=sh)
+    z, f = z.cpu().numpy(), f.cpu().numpy()
+    q, f1 = xr.fastXcorr(_dev(cutout), _dev(rx), freqsearch=True, shifts=sh)
+    np.testing.assert_allclose(np.abs(z) ** 2, q.cpu().numpy(), rtol=3e-6, atol=1e-10)
+    assert np.array_equal(f, f1.cpu().numpy())
+    zs, fs = [], []
+    for lo in range(0, sh.size, 2000):
+        zz, ff = xr.fastXcorr(_dev(cutout), _dev(rx), freqsearch=True, absResult=False, shifts=sh[lo:lo + 2000])
+        zs.append(zz.cpu().numpy())
+        fs.append(ff.cpu().numpy())
+    z2, f2 = np.concatenate(zs), np.concatenate(fs)
+    assert_bins(f, f2, lambda i: _spec64(cutout, rx, int(sh[i])))
+    same = f == f2
+    np.testing.assert_allclose(z[same], z2[same], rtol=0, atol=3e-6 * float(np.abs(z2).max()))
+    idx = np.r_[0:12, sh.size - 12:sh.size, (12345 - 12345 % step) // step]
+    rz, rf = orc.fastXcorr(cutout, rx, freqsearch=True, shifts=sh[idx], absResult=False)
+    ok = f[idx] == rf
+    assert ok.sum() >= idx.size - 1
+    np.testing.assert_allclose(z[idx][ok], rz[ok], rtol=0, atol=1e-5 * float(np.abs(rz).max()))
+
+
 def test_warp_layout_windows_leaving_rx(xr):
     """N = 1024 (one warp per FFT over a staged window): windows that leave rx on either side give 0 / 0
     (IppXcorrFFT.cpp:125-130), the rest agrees with short calls (B-groups-per-CTA layout) and the oracle; several refills."""
