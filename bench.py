@@ -358,7 +358,9 @@ def config_line(which, lib, peaks, p32, p32src, steps):
         ms = float(np.median(wall[2:]))
         log2l = int(np.ceil(np.log2(2 * N - 1)))
         L = 1 << log2l
-        form_bytes = K * (8.0 * N + 6 * 8.0 * L)                # one read of the window + six passes over the 8 L-byte work array
+        # window + conj(cutout) chirp read, column pass writes 8 L, the fused middle step reads 8 L + FFT_L(chirp) and writes 8 L,
+        # the last row pass reads 8 L (round 2, first half: six passes over the work array)
+        form_bytes = K * (2 * 8.0 * N + 5 * 8.0 * L)
         pub = {"bx": {"numpy_s": 15.9, "cython_ipp_4thr_s": 3.9, "cupy_s": 0.29}, "bx10": {"numpy_s": 192.0, "cython_ipp_4thr_s": 62.0, "cupy_s": 3.0}}[which]
         ach = form_bytes / (ms * 1e-3) / 1e9
         return {"workload": "benchmark_xcorrs.py %d 128 (reference's published benchmark): %d-sample cutout, 128 shifts, cp_fastXcorr "
@@ -368,7 +370,7 @@ def config_line(which, lib, peaks, p32, p32src, steps):
                 "roofline": {"bound": "hbm", "achieved": ach, "peak": float(peaks["hbm_gbs"]), "unit": "GB/s", "frac": ach / float(peaks["hbm_gbs"]),
                              "peak_source": peaks["_source"], "kernel": "big_cols_kernel / big_rows_kernel (four-step Bluestein, L = 2^%d)" % log2l,
                              "kernel_ms": ms, "formulation_bytes_per_call": form_bytes, "traffic": None,
-                             "note": "bytes of the four-step formulation (window read + 6 passes over 8 L bytes per shift); the "
+                             "note": "bytes of the four-step formulation (window and chirped cutout read + 5 passes over 8 L bytes per shift, the Bluestein middle step fused with the second transform's column pass); the "
                                      "work arrays of a batch (about 1 GB) do not stay in the 126 MB L2 -- an L2-sized batch measured "
                                      "slower (12.5 vs 9.9 ms at N = 1e6), see bigfft.cu"}}
     raise SystemExit("unknown workload %r" % which)

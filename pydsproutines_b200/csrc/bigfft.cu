@@ -94,8 +94,13 @@ struct BigColsArgs {
     int NC;                    // number of columns
     const float2* twa;
     const float2* twb;
+    const float2* bp;          // MODE 2: FFT_L(chirp) in the register layout a PL-point row transform leaves ([row][slot][t])
 };
 
+// MODE 2 (Bluestein middle step fused with the second transform's column pass): the input "column" is a contiguous row of
+// the first transform's column pass; it is transformed (PL points), multiplied by FFT_L(chirp), conjugated and brought back
+// to input order through the exchange buffer, and then takes the ordinary path below (second PL-point transform, twiddle,
+// transposed store).  Saves one write and one read of the 8 L bytes per shift against separate row / column passes.
 template <class PL, int B, int MODE>
 __global__ void __launch_bounds__(PL::TG* B, big_minb<PL::TG * B>()) big_cols_kernel(const BigColsArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -121,6 +126,33 @@ __global__ void __launch_bounds__(PL::TG* B, big_minb<PL::TG * B>()) big_cols_ke
         const int col = tile * B + g;
         const bool act = col < a.NC && in_range;
         constexpr int NQ = V / PL::R1;
+        if (MODE == 1) {
+            // slab load: the B adjacent columns of a row are 8 B contiguous bytes, so the CTA reads row by row with the
+            // lanes along the columns (full sectors; one lane per row touched 32 sectors per load instruction and the
+            // pass ran at the L1 tag rate) and hands the samples to the groups through their exchange buffers
+            float2* const bufs = reinterpret_cast<float2*>(smem_raw + PL::TABLE_BYTES);
+            const int ncol = (a.NC - tile * B < B) ? (a.NC - tile * B) : B;
+            const float2* const xr = a.rx + s + (int64_t)tile * B;
+            const float2* const cr = a.cc + (int64_t)tile * B;
+#pragma unroll 4
+            for (int i = threadIdx.x; i < PL::N * B; i += TG * B) {
+                const int n = i / B, gg = i % B;
+                const int64_t idx = (int64_t)n * a.sn + gg;
+                float2 x = make_float2(0.f, 0.f);
+                if (in_range && gg < ncol && (int64_t)tile * B + idx < a.nvalid) x = cmul(__ldg(xr + idx), __ldg(cr + idx));
+                const int nr = (n + 2 * gg) & (PL::N - 1);       // rotated by 2 cells per column: the B stores of a row hit B banks
+                bufs[(size_t)gg * PL::BUF + nr + ((nr >> 5) << 1)] = x;
+            }
+            __syncthreads();
+#pragma unroll
+            for (int n1 = 0; n1 < PL::R1; ++n1)
+#pragma unroll
+                for (int q = 0; q < NQ; ++q) {
+                    const int n = (input_index<PL>(t, q, n1) + 2 * g) & (PL::N - 1);
+                    v[q * PL::R1 + n1] = buf[n + ((n >> 5) << 1)];
+                }
+            bar();                                                 // reads done before the pass-1 stores of the transform
+        } else {
 #pragma unroll
         for (int n1 = 0; n1 < PL::R1; ++n1)
 #pragma unroll
@@ -129,14 +161,37 @@ __global__ void __launch_bounds__(PL::TG* B, big_minb<PL::TG * B>()) big_cols_ke
                 float2 x = make_float2(0.f, 0.f);
                 if (act) {
                     const int64_t idx = n * a.sn + (int64_t)col * a.sc;
-                    if (MODE == 0) {
-                        x = __ldg(a.in + (int64_t)b * a.in_batch + idx);
-                    } else if (idx < a.nvalid) {
-                        x = cmul(__ldg(a.rx + s + idx), __ldg(a.cc + idx));
-                    }
+                    x = __ldg(a.in + (int64_t)b * a.in_batch + idx);
                 }
                 v[q * PL::R1 + n1] = x;
             }
+        }
+        if (MODE == 2) {
+            block_fft<PL>(v, th, tab, buf, t, bar);
+            const float2* const bpr = a.bp + (int64_t)(col < a.NC ? col : 0) * PL::N + t;
+#pragma unroll
+            for (int sl = 0; sl < V; ++sl) {
+                const float2 p = cmul(v[sl], __ldg(bpr + sl * TG));
+                v[sl] = make_float2(p.x, -p.y);
+            }
+            bar();                                                 // last-pass loads done: the buffer is free
+#pragma unroll
+            for (int q = 0; q < V / PL::RL; ++q)
+#pragma unroll
+                for (int j = 0; j < PL::RL; ++j) {
+                    const int i = output_bin<PL>(t, q, j);
+                    buf[i + ((i >> 5) << 1)] = v[q * PL::RL + j];
+                }
+            bar();
+#pragma unroll
+            for (int n1 = 0; n1 < PL::R1; ++n1)
+#pragma unroll
+                for (int q = 0; q < NQ; ++q) {
+                    const int i = input_index<PL>(t, q, n1);
+                    v[q * PL::R1 + n1] = buf[i + ((i >> 5) << 1)];
+                }
+            bar();
+        }
         block_fft<PL>(v, th, tab, buf, t, bar);
         // ---- twiddle, then the transposed store through the exchange buffers: group g leaves its R outputs in natural
         // order in its own buffer (skewed by SK g cells against bank conflicts), and the whole CTA writes, for every k,
@@ -680,23 +735,24 @@ int32_t bigfft_freq_device(const float2* cutout, int64_t N, const float2* rx, in
             if (out.caf) XC_TRY((big_forward<1, EPI_CAF>(ca, ra, log2R, log2C, nb, stream)));
             else XC_TRY((big_forward<1, EPI_ARGMAX>(ca, ra, log2R, log2C, nb, stream)));
         } else {
-            // first transform: product -> columns(R) -> rows(C) times FFT_L(chirp), conjugated, row-local natural order
-            ra.out = d_z;
-            ra.bp = blue->d_bp;
-            XC_TRY((big_forward<1, EPI_BLUE_MID>(ca, ra, log2R, log2C, nb, stream)));
-            // second transform over k = k2 R + k1: its columns are the rows of Z (contiguous), C-point FFTs over k2
+            // first transform's column pass: product -> columns(R), transposed store Y[k1][c]
+            XC_TRY(dispatch_log2(log2R, ColsRunner<1>{ca, nb, stream}));
+            // its row pass (C points, times FFT_L(chirp), conjugated) fused with the column pass of the second transform
+            // over k = k2 R + k1 (the same C-point rows): Y[k1][.] -> Z[j1][k1]
             BigColsArgs cb{};
-            cb.in = d_z;
+            cb.in = d_y;
             cb.in_batch = L;
             cb.sn = 1;
             cb.sc = C;
-            cb.out = d_y;
+            cb.out = d_z;
             cb.L = L;
             cb.NC = R;
             cb.twa = tw->d_a;
             cb.twb = tw->d_b;
+            cb.bp = blue->d_bp;
+            XC_TRY(dispatch_log2(log2C, ColsRunner<2>{cb, nb, stream}));
             BigRowsArgs rb = ra;
-            rb.in = d_y;
+            rb.in = d_z;
             rb.NR = C;
             rb.out = nullptr;
             rb.bp = nullptr;
@@ -704,8 +760,8 @@ int32_t bigfft_freq_device(const float2* cutout, int64_t N, const float2* rx, in
             rb.pc = out.cplx ? d_pc : nullptr;
             rb.post = blue->d_post;
             NRfinal = C;
-            if (out.caf) XC_TRY((big_forward<0, EPI_CAF>(cb, rb, log2C, log2R, nb, stream)));
-            else XC_TRY((big_forward<0, EPI_ARGMAX>(cb, rb, log2C, log2R, nb, stream)));
+            if (out.caf) XC_TRY(dispatch_log2(log2R, RowsRunner<EPI_CAF>{rb, nb, stream}));
+            else XC_TRY(dispatch_log2(log2R, RowsRunner<EPI_ARGMAX>{rb, nb, stream}));
         }
         if (!out.caf) {
             big_finalize_kernel<<<nb, 256, 0, stream>>>(d_pmax, out.cplx ? d_pc : nullptr, NRfinal, first, sl.shift0, sl.step,

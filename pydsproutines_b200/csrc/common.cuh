@@ -68,6 +68,7 @@ enum Slot {
     SLOT_TMP2,
     SLOT_TMP3,
     SLOT_BIG,      // work arrays of the four-step frequency search (bigfft.cu)
+    SLOT_SCAN,     // chunk sums of the energy kernels for very long windows (energy.cu)
     SLOT_COUNT
 };
 // returns a device pointer of at least `bytes` bytes (256-byte aligned), NULL + error on failure

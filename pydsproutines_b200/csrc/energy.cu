@@ -31,10 +31,60 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
+// Very long windows (the reference's benchmark correlates a 1e6-sample cutout at 128 shifts): the first window of a tile is
+// not summed sample by sample by one CTA, but taken from cumulative sums at chunk boundaries (cum[j] = sum of p[0 .. j SE_CHUNK),
+// double) plus the two ragged edges.
+constexpr int SE_CHUNK = 4096;
+constexpr int SE_LONG_L = 4 * SE_CHUNK;    // windows from this length on use the chunk sums
+
+template <bool COMPLEX_IN>
+__global__ void __launch_bounds__(256) chunk_sum_kernel(const void* __restrict__ x, int64_t n_in, double* __restrict__ part) {
+    __shared__ double s_part[8];
+    const int64_t j0 = (int64_t)blockIdx.x * SE_CHUNK;
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < SE_CHUNK; i += 256) acc += (double)load_p<COMPLEX_IN>(x, j0 + i, 0, n_in);
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double w = 0.0;
+        for (int i = 0; i < 8; ++i) w += s_part[i];
+        part[blockIdx.x] = w;
+    }
+}
+// cum[0] = 0, cum[j + 1] = cum[j] + part[j], in place over part shifted by one (one block; n <= a few 10^4 chunks)
+__global__ void __launch_bounds__(1024) chunk_scan_kernel(const double* __restrict__ part, int64_t n, double* __restrict__ cum) {
+    __shared__ double s_tot[32];
+    __shared__ double s_carry;
+    if (threadIdx.x == 0) {
+        s_carry = 0.0;
+        cum[0] = 0.0;
+    }
+    __syncthreads();
+    for (int64_t base = 0; base < n; base += 1024) {
+        const int64_t i = base + threadIdx.x;
+        double v = i < n ? part[i] : 0.0;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const double y = __shfl_up_sync(0xffffffffu, v, o);
+            if ((threadIdx.x & 31) >= o) v += y;
+        }
+        if ((threadIdx.x & 31) == 31) s_tot[threadIdx.x >> 5] = v;
+        __syncthreads();
+        double off = s_carry;
+        for (int w = 0; w < (int)(threadIdx.x >> 5); ++w) off += s_tot[w];
+        if (i < n) cum[i + 1] = off + v;
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry = off + v;
+        __syncthreads();
+    }
+}
+
 template <bool COMPLEX_IN>
 __global__ void __launch_bounds__(SE_THREADS) sliding_sum_kernel(const void* __restrict__ x, int64_t n_in,
                                                                  int64_t front_pad, int L, int64_t n_out,
-                                                                 float* __restrict__ out, int average) {
+                                                                 float* __restrict__ out, int average,
+                                                                 const double* __restrict__ cum) {
     __shared__ double s_part[SE_THREADS / 32];
     __shared__ double s_w0;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -42,7 +92,16 @@ __global__ void __launch_bounds__(SE_THREADS) sliding_sum_kernel(const void* __r
 
     // (1) first window of the tile
     double acc = 0.0;
-    for (int n = tid; n < L; n += SE_THREADS) acc += (double)load_p<COMPLEX_IN>(x, s0 + n, front_pad, n_in);
+    if (cum) {
+        // whole chunks [c0, c1) from the cumulative sums, the ragged edges [s0, c0 CHUNK) and [c1 CHUNK, s0 + L) directly
+        const int64_t c0 = (s0 + SE_CHUNK - 1) / SE_CHUNK, c1 = (s0 + L) / SE_CHUNK;
+        const int64_t e0 = c0 * SE_CHUNK, e1 = c1 * SE_CHUNK;
+        for (int64_t n = s0 + tid; n < e0; n += SE_THREADS) acc += (double)load_p<COMPLEX_IN>(x, n, 0, n_in);
+        for (int64_t n = e1 + tid; n < s0 + L; n += SE_THREADS) acc += (double)load_p<COMPLEX_IN>(x, n, 0, n_in);
+        if (tid == 0) acc += cum[c1] - cum[c0];
+    } else {
+        for (int n = tid; n < L; n += SE_THREADS) acc += (double)load_p<COMPLEX_IN>(x, s0 + n, front_pad, n_in);
+    }
     acc = warp_sum(acc);
     if (lane == 0) s_part[warp] = acc;
     __syncthreads();
@@ -92,13 +151,30 @@ __global__ void __launch_bounds__(SE_THREADS) sliding_sum_kernel(const void* __r
 }
 
 int32_t sliding_sum_device(const void* x, bool complex_in, int64_t n_in, int64_t front_pad, int L, int64_t n_out,
-                           float* out, int average, cudaStream_t stream) {
+                           float* out, int average, cudaStream_t stream, bool scratch) {
     if (n_out <= 0) return XC_OK;
     const int64_t blocks = (n_out + SE_TILE - 1) / SE_TILE;
+    const double* cum = nullptr;
+    if (scratch && L >= SE_LONG_L && front_pad == 0 && n_out - 1 + (int64_t)L <= n_in) {
+        // chunk sums of everything the windows cover, then their running totals
+        int64_t cover = n_out - 1 + L;
+        if (cover > n_in) cover = n_in;
+        const int64_t nch = cover / SE_CHUNK;          // whole chunks only (c1 <= (s0 + L) / CHUNK <= cover / CHUNK)
+        double* d = reinterpret_cast<double*>(workspace(SLOT_SCAN, sizeof(double) * (size_t)(2 * nch + 2)));
+        if (!d) return XC_ERR_NOMEM;
+        if (nch > 0) {
+            if (complex_in) chunk_sum_kernel<true><<<(unsigned)nch, 256, 0, stream>>>(x, n_in, d + nch + 1);
+            else chunk_sum_kernel<false><<<(unsigned)nch, 256, 0, stream>>>(x, n_in, d + nch + 1);
+            XC_LAUNCH_CHECK();
+        }
+        chunk_scan_kernel<<<1, 1024, 0, stream>>>(d + nch + 1, nch, d);
+        XC_LAUNCH_CHECK();
+        cum = d;
+    }
     if (complex_in)
-        sliding_sum_kernel<true><<<(unsigned)blocks, SE_THREADS, 0, stream>>>(x, n_in, front_pad, L, n_out, out, average);
+        sliding_sum_kernel<true><<<(unsigned)blocks, SE_THREADS, 0, stream>>>(x, n_in, front_pad, L, n_out, out, average, cum);
     else
-        sliding_sum_kernel<false><<<(unsigned)blocks, SE_THREADS, 0, stream>>>(x, n_in, front_pad, L, n_out, out, average);
+        sliding_sum_kernel<false><<<(unsigned)blocks, SE_THREADS, 0, stream>>>(x, n_in, front_pad, L, n_out, out, average, cum);
     XC_LAUNCH_CHECK();
     return XC_OK;
 }
@@ -157,7 +233,37 @@ __global__ void normsq_kernel(const float2* __restrict__ x, int64_t n, int64_t r
     }
 }
 
-int32_t normsq_device(const float2* x, int64_t n, int64_t rows, int64_t row_stride, float* out, cudaStream_t stream) {
+// one long vector: chunk sums by many CTAs, then their total in a fixed order
+__global__ void __launch_bounds__(256) normsq_final_kernel(const double* __restrict__ part, int64_t n, const float2* __restrict__ tail,
+                                                           int64_t ntail, float* __restrict__ out) {
+    __shared__ double s_part[8];
+    double acc = 0.0;
+    for (int64_t i = threadIdx.x; i < n; i += 256) acc += part[i];
+    for (int64_t i = threadIdx.x; i < ntail; i += 256) {
+        const float2 v = tail[i];
+        acc += (double)v.x * v.x + (double)v.y * v.y;
+    }
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double w = 0.0;
+        for (int i = 0; i < 8; ++i) w += s_part[i];
+        out[0] = (float)w;
+    }
+}
+
+int32_t normsq_device(const float2* x, int64_t n, int64_t rows, int64_t row_stride, float* out, cudaStream_t stream, bool scratch) {
+    if (scratch && rows == 1 && n >= 16 * SE_CHUNK) {
+        const int64_t nch = n / SE_CHUNK;
+        double* d = reinterpret_cast<double*>(workspace(SLOT_SCAN, sizeof(double) * (size_t)(2 * nch + 2)));
+        if (!d) return XC_ERR_NOMEM;
+        chunk_sum_kernel<true><<<(unsigned)nch, 256, 0, stream>>>(x, n, d);
+        XC_LAUNCH_CHECK();
+        normsq_final_kernel<<<1, 256, 0, stream>>>(d, nch, x + nch * SE_CHUNK, n - nch * SE_CHUNK, out);
+        XC_LAUNCH_CHECK();
+        return XC_OK;
+    }
     normsq_kernel<<<(unsigned)rows, 256, 0, stream>>>(x, n, row_stride, out);
     XC_LAUNCH_CHECK();
     return XC_OK;

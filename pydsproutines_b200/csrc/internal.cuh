@@ -6,11 +6,12 @@
 namespace xc {
 
 // energy.cu
+// scratch = false keeps the call allocation free (very long windows then pay a serial first-window sum per tile)
 int32_t sliding_sum_device(const void* x, bool complex_in, int64_t n_in, int64_t front_pad, int L, int64_t n_out,
-                           float* out, int average, cudaStream_t stream);
+                           float* out, int average, cudaStream_t stream, bool scratch = true);
 int32_t window_energy_device(const float2* x, int64_t xlen, int L, int64_t shift0, int64_t step, const int64_t* shifts,
                              int64_t K, float* out, cudaStream_t stream);
-int32_t normsq_device(const float2* x, int64_t n, int64_t rows, int64_t row_stride, float* out, cudaStream_t stream);
+int32_t normsq_device(const float2* x, int64_t n, int64_t rows, int64_t row_stride, float* out, cudaStream_t stream, bool scratch = true);
 int32_t magnsq_device(const float2* x, int64_t n, void* out, int out_f64, cudaStream_t stream);
 
 // fastxcorr.cu

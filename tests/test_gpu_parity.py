@@ -430,6 +430,18 @@ def test_moving_average_known_answers():
         np.testing.assert_allclose(fr.slidingEnergy(z, L), orc.slidingEnergy(z, L), rtol=2e-6)
         ref = np.array([np.linalg.norm(z[s:s + L].astype(np.complex128)) ** 2 for s in (0, (50000 - L) // 2, 50000 - L)])
         np.testing.assert_allclose(fr.slidingEnergy(z, L)[[0, (50000 - L) // 2, 50000 - L]], ref, rtol=1e-6)
+    # very long windows take the first window of a tile from cumulative chunk sums (csrc/energy.cu): several tiles, a window
+    # that starts on / off a chunk boundary, the multi-block cutout norm of the no-frequency-search correlator
+    z = signals.cnoise(rng, 400000)
+    for L in (16384, 100001, 393217):
+        got = fr.slidingEnergy(_dev(z), L).cpu().numpy()
+        c = np.concatenate([[0.0], np.cumsum(np.abs(z.astype(np.complex128)) ** 2)])
+        np.testing.assert_allclose(got, c[L:] - c[:-L], rtol=2e-6)
+    from pydsproutines_b200 import xcorrRoutines as xr
+    cut = z[1000:1000 + 70001].copy()
+    q = xr.fastXcorr(_dev(cut), _dev(z[:80000])).cpu().numpy()
+    assert int(np.argmax(q)) == 1000 and abs(q[1000] - 1.0) < 2e-5
+    np.testing.assert_allclose(q[[0, 5000]], orc.fastXcorr(cut, z[:80000], shifts=np.array([0, 5000])), rtol=1e-4, atol=1e-9)
 
 
 def test_magnsq_argmax_local_maxima():
