@@ -20,32 +20,29 @@ void group_pp_release(GroupPPPlan* p) {
     memset(p, 0, sizeof(*p));
 }
 
+using GPPL2K = FftPlan<11, 64, 2, 32, 32>;     // fftlen 2048: six groups of 64 threads, rows of 64 cells (ROT variant only)
+constexpr int GP_B2K = 6;
+
 // Rotated-row plan (group_pp.cuh, ROT): every group is cut into sub-groups of TG samples, sorted by the row their first
 // cell lies in; thread t holds the weight of sample (t - r) mod TG of each sub-group.
-template <int B>
+template <class PL, int B>
 static int rot_window_slack(int G, int L) {
-    using LY = GroupPPLayout<GPPL, B, true>;
+    using LY = GroupPPLayout<PL, B, true>;
     // the stage keeps TG zero cells behind the last window
-    const int64_t room = (int64_t)max_smem_optin() - (int64_t)LY::OFF_STAGE - (int64_t)sizeof(float2) * GPPL::TG;
+    const int64_t room = (int64_t)max_smem_optin() - (int64_t)LY::OFF_STAGE - (int64_t)sizeof(float2) * PL::TG;
     int W = ((int)(room / (int64_t)(sizeof(float2) * (size_t)G)) - L) / B * B;
     if (W > 252 / B * B) W = 252 / B * B;
     return W;
 }
-#ifndef XC_GR_B
-#define XC_GR_B 3
-#endif
-static int32_t group_rot_build(const float2* y, const int64_t* starts, int G, int L, int F, GroupPPPlan* p) {
-    constexpr int TG = GPPL::TG;
+template <class PL, int B>
+static int32_t group_rot_build(const float2* y, const int64_t* starts, int G, int L, GroupPPPlan* p) {
+    constexpr int TG = PL::TG, F = PL::N;
     static_assert(GR_MAX_E == sizeof(p->rdesc) / sizeof(p->rdesc[0]), "descriptor table size");
+    static_assert(F / TG == 32, "32 rows");
     const int per = (L + TG - 1) / TG;
     const int E = G * per;
     if (E + 2 > GR_MAX_E) return XC_OK;
-    // four thread groups per SM when their exchange buffers leave at least 16 samples of window slack, else three
-    int B = XC_GR_B, W = (XC_GR_B == 4) ? rot_window_slack<4>(G, L) : rot_window_slack<GP_B>(G, L);
-    if (B == 4 && W < 16) {
-        B = GP_B;
-        W = rot_window_slack<GP_B>(G, L);
-    }
+    const int W = rot_window_slack<PL, B>(G, L);
     if (W < 4 * B) return XC_OK;
     const int SW = L + W;
     struct Sub { int row, r, g, i; };
@@ -76,9 +73,10 @@ static int32_t group_rot_build(const float2* y, const int64_t* starts, int G, in
     p->L = L;
     p->W = W;
     p->NC = NC;
-    p->nq_live = GPPL::V / GPPL::R1;
+    p->nq_live = PL::V / PL::R1;
     p->rot = 1;
     p->B = B;
+    p->F = F;
     p->usable = 1;
     return XC_OK;
 }
@@ -86,6 +84,7 @@ static int32_t group_rot_build(const float2* y, const int64_t* starts, int G, in
 // y: host weights [G][L] (conjugation already applied); the plan is usable when the fold fits the kernel's limits
 int32_t group_pp_build(const float2* y, const int64_t* starts, int G, int L, int F, GroupPPPlan* p) {
     memset(p, 0, sizeof(*p));
+    if (F == GPPL2K::N) return group_rot_build<GPPL2K, GP_B2K>(y, starts, G, L, p);
     if (F != GPPL::N) return XC_OK;
     using LY = GroupPPLayout<GPPL, GP_B>;
     // window slack: the largest multiple of B (at most 252) that fits shared memory
@@ -115,7 +114,7 @@ int32_t group_pp_build(const float2* y, const int64_t* starts, int G, int L, int
         len = (len + 2 * GP_CH - 1) / (2 * GP_CH) * (2 * GP_CH);
         if (len > 248) {
             memset(p, 0, sizeof(*p));
-            return group_rot_build(y, starts, G, L, F, p);
+            return group_rot_build<GPPL, GP_B>(y, starts, G, L, p);
         }
         if (len > 0) qtop = q;
         p->lens[c] = (unsigned char)len;
@@ -124,7 +123,7 @@ int32_t group_pp_build(const float2* y, const int64_t* starts, int G, int L, int
     const int NC = base[V] + GP_CH;                       // one chunk of padding: the gather prefetches one chunk ahead
     if (base[V] == 0 || NC > GP_MAX_NC) {
         memset(p, 0, sizeof(*p));
-        return group_rot_build(y, starts, G, L, F, p);
+        return group_rot_build<GPPL, GP_B>(y, starts, G, L, p);
     }
     int nq = 1;
     while (nq < qtop + 1) nq <<= 1;
@@ -150,22 +149,32 @@ int32_t group_pp_build(const float2* y, const int64_t* starts, int G, int L, int
     p->NC = NC;
     p->nq_live = nq;
     p->B = GP_B;
+    p->F = F;
     p->usable = 1;
     return XC_OK;
 }
 
-template <int B>
+template <class PL, int B, bool ROT_ONLY>
 static int32_t group_pp_launch(const GroupPPPlan& p, const int64_t* d_starts, const float2* rx, int64_t rxlen, int64_t shift0,
                                int64_t K, int64_t lo, int64_t hi, const FusedOut& out, cudaStream_t stream) {
-    using LY = GroupPPLayout<GPPL, B>;
+    using LY = GroupPPLayout<PL, B, ROT_ONLY>;
+    constexpr int NQA = PL::V / PL::R1;
     void (*kern)(const GroupPPArgs, const GroupPPLens, const GroupRotPlan, const FusedOut, const int64_t, const int) =
-        p.rot ? group_pp_kernel<GPPL, B, 8, true>
-        : p.nq_live == 1 ? group_pp_kernel<GPPL, B, 1, false> : p.nq_live == 2 ? group_pp_kernel<GPPL, B, 2, false>
-        : p.nq_live == 4 ? group_pp_kernel<GPPL, B, 4, false> : group_pp_kernel<GPPL, B, 8, false>;
-    const size_t smem = LY::bytes(p.G, p.L, p.W) + (p.rot ? sizeof(float2) * GPPL::TG : 0);
+        group_pp_kernel<PL, B, NQA, true>;
+    int slot = 4;
+    if constexpr (!ROT_ONLY) {
+        if (!p.rot) {
+            kern = p.nq_live == 1 ? group_pp_kernel<PL, B, 1, false> : p.nq_live == 2 ? group_pp_kernel<PL, B, 2, false>
+                 : p.nq_live == 4 ? group_pp_kernel<PL, B, 4, false> : group_pp_kernel<PL, B, 8, false>;
+            slot = p.nq_live == 1 ? 0 : p.nq_live == 2 ? 1 : p.nq_live == 4 ? 2 : 3;
+        }
+    } else if (!p.rot) {
+        return fail(XC_ERR_UNSUPPORTED, "no per-cell list variant for fftlen %d", PL::N);
+    }
+    const size_t smem = LY::bytes(p.G, p.L, p.W) + (p.rot ? sizeof(float2) * PL::TG : 0);
     if ((int)smem > max_smem_optin()) return fail(XC_ERR_UNSUPPORTED, "group search kernel needs %zu B of shared memory", smem);
     static KernelOnce once[5];
-    XC_TRY(once[p.rot ? 4 : p.nq_live == 1 ? 0 : p.nq_live == 2 ? 1 : p.nq_live == 4 ? 2 : 3].configure(kern, max_smem_optin()));
+    XC_TRY(once[slot].configure(kern, max_smem_optin()));
     GroupPPArgs a{rx, rxlen, shift0, lo, hi, d_starts, p.d_w, p.d_off, p.G, p.L, p.NC, p.nq_live, p.W};
     GroupPPLens lens;
     memcpy(lens.len, p.lens, sizeof(lens.len));
@@ -179,7 +188,7 @@ static int32_t group_pp_launch(const GroupPPPlan& p, const int64_t* d_starts, co
     const int64_t chunk = (per + ctas - 1) / ctas;
     if (chunk >= (1ll << 29)) return fail(XC_ERR_UNSUPPORTED, "too many shifts per thread group");
     profile_begin(stream);
-    kern<<<(unsigned)ctas, GPPL::TG * B, smem, stream>>>(a, lens, rp, out, K, (int)chunk);
+    kern<<<(unsigned)ctas, PL::TG * B, smem, stream>>>(a, lens, rp, out, K, (int)chunk);
     profile_end(stream);
     XC_LAUNCH_CHECK();
     return XC_OK;
@@ -187,8 +196,8 @@ static int32_t group_pp_launch(const GroupPPPlan& p, const int64_t* d_starts, co
 
 int32_t group_pp_run(const GroupPPPlan& p, const int64_t* d_starts, const float2* rx, int64_t rxlen, int64_t shift0, int64_t K,
                      int64_t lo, int64_t hi, const FusedOut& out, cudaStream_t stream) {
-    if (p.B == 4) return group_pp_launch<4>(p, d_starts, rx, rxlen, shift0, K, lo, hi, out, stream);
-    return group_pp_launch<GP_B>(p, d_starts, rx, rxlen, shift0, K, lo, hi, out, stream);
+    if (p.F == GPPL2K::N) return group_pp_launch<GPPL2K, GP_B2K, true>(p, d_starts, rx, rxlen, shift0, K, lo, hi, out, stream);
+    return group_pp_launch<GPPL, GP_B, false>(p, d_starts, rx, rxlen, shift0, K, lo, hi, out, stream);
 }
 
 }  // namespace xc

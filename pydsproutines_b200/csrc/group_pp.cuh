@@ -95,7 +95,8 @@ __device__ __forceinline__ void codelet_fft_pruned(float2* a) {
 
 template <class PL, int B, bool ROT = false>
 struct GroupPPLayout {
-    static_assert(PL::P == 3 && PL::R2 == 32 && PL::R3 == 32 && PL::V == 32 && PL::TG == 128, "4096-point plan: 128 threads x 32 points");
+    static_assert(PL::P == 3 && PL::R2 == 32 && PL::R3 == 32 && PL::V == 32 && (PL::TG == 128 || (ROT && PL::TG == 64)),
+                  "4096-point plan (128 threads x 32 points); 2048 points (64 threads) in the rotated-row variant");
     static constexpr size_t OFF_BUF = 0;
     static constexpr size_t OFF_GMAX = sizeof(float2) * (size_t)PL::BUF * B;          // [B][2]
     static constexpr size_t OFF_BIN = OFF_GMAX + sizeof(unsigned int) * 2 * B;        // [B]
@@ -177,7 +178,8 @@ __global__ void __launch_bounds__(PL::TG* B, 1) group_pp_kernel(const GroupPPArg
     tc::tc_fence_after();
     const uint32_t tmem0 = *taddr_slot;
     const uint32_t tb = tmem0 + (((uint32_t)(warp_cta & 3) * 32u) << 16);
-    if (g == 0) {
+    // groups whose warps cover the four lane quarters between them write (one group of 128 threads, two of 64)
+    if (g < (TG >= 128 ? 1 : 128 / TG)) {
         // ---- per-thread constants -> tensor memory (read by the same in-group thread of every group) ----
         for (int e0 = 0; e0 < a.NC; e0 += GP_CH) {
             float r[16];
@@ -265,7 +267,6 @@ __global__ void __launch_bounds__(PL::TG* B, 1) group_pp_kernel(const GroupPPArg
         o += B;
         if constexpr (ROT) {
             // ---- rotated gather: sub-groups sorted by row; thread t takes sample (t - r) mod TG of each ----
-            static_assert(TG == 128, "rows of 128 cells");
             // software pipeline over the sorted sub-group list, independent of the row structure: descriptor two entries
             // ahead, sample and weight one entry ahead (the loop body would otherwise be one serial chain
             // LDC -> address -> LDS -> FMA per sub-group; two zero entries follow the last sub-group)
@@ -275,7 +276,7 @@ __global__ void __launch_bounds__(PL::TG* B, 1) group_pp_kernel(const GroupPPArg
             int e = 0;
             uint32_t d_n = rp.desc[0], d_nn = rp.desc[1];
             float2 x_n;
-            asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(x_n.x), "=f"(x_n.y) : "r"(xs + 8u * ((d_n >> 7) + (uint32_t)((t - (int)(d_n & 127u)) & 127))));
+            asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(x_n.x), "=f"(x_n.y) : "r"(xs + 8u * ((d_n >> 7) + (uint32_t)((t - (int)(d_n & 127u)) & (TG - 1)))));
             float2 carry = make_float2(0.f, 0.f);
 #pragma unroll
             for (int rho = 0; rho < V; ++rho) {
@@ -297,7 +298,7 @@ __global__ void __launch_bounds__(PL::TG* B, 1) group_pp_kernel(const GroupPPArg
                     d_nn = rp.desc[e + 1];
                     cw += 2;
                     tc::tmem_ld2_issue(cw, wn);
-                    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(x_n.x), "=f"(x_n.y) : "r"(xs + 8u * ((d_n >> 7) + (uint32_t)((t - (int)(d_n & 127u)) & 127))));
+                    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(x_n.x), "=f"(x_n.y) : "r"(xs + 8u * ((d_n >> 7) + (uint32_t)((t - (int)(d_n & 127u)) & (TG - 1)))));
                     const float2 p = pcmul(x, y);
                     if (t >= r) acc = padd(acc, p);
                     else carry = padd(carry, p);
@@ -362,7 +363,7 @@ __global__ void __launch_bounds__(PL::TG* B, 1) group_pp_kernel(const GroupPPArg
         }
         bar();
         // ---- pass 2 (in place, warp local from here on) ----
-        gp_pass2<PL, 4 * NQ>(v, buf, o2, tb + LY::COL_T1);
+        gp_pass2<PL, ROT ? PL::R2 : 4 * NQ>(v, buf, o2, tb + LY::COL_T1);
         __syncwarp();
         // ---- pass 3 ----
         {

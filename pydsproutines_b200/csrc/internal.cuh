@@ -48,7 +48,7 @@ struct GroupPPPlan {
     float2* d_w;
     uint32_t* d_off;
     // rotated-row variant (starts that are not aligned to the 128-cell rows): sub-groups sorted by row
-    int rot, B;                  // B = thread groups per SM of the kernel variant
+    int rot, B, F;               // B = thread groups per SM of the kernel variant, F = transform length
     unsigned char rcnt[32];
     uint32_t rdesc[192];
 };

@@ -1018,17 +1018,20 @@ def test_warp_layout_windows_leaving_rx(xr):
     assert_bins(f[idx + 37], rf, lambda i: _spec64(cutout, rx, int(idx[i])))
 
 
-@pytest.mark.parametrize("G,L,kind", [(64, 128, "1000g"), (64, 128, "ragged"), (40, 100, "ragged"), (24, 200, "ragged"),
-                                       (64, 128, "dense"), (3, 700, "ragged")])
-def test_group_rotated_rows_vs_oracle_and_ell_layout(xr, G, L, kind):
-    """GroupXcorrFFT, fftlen 4096, contiguous shifts, group starts that are NOT aligned to the 128-cell rows of the transform
+@pytest.mark.parametrize("G,L,kind,F", [(64, 128, "1000g", 4096), (64, 128, "ragged", 4096), (40, 100, "ragged", 4096),
+                                         (24, 200, "ragged", 4096), (64, 128, "dense", 4096), (3, 700, "ragged", 4096),
+                                         (16, 64, "128g", 2048), (50, 100, "ragged", 2048), (64, 128, "dense", 2048)])
+def test_group_rotated_rows_vs_oracle_and_ell_layout(xr, G, L, kind, F):
+    """GroupXcorrFFT, fftlen 4096 (and 2048: rows of 64 cells), contiguous shifts, group starts that are NOT aligned to the 128-cell rows of the transform
     (csrc/group_pp.cuh, ROT variant: sub-groups of 128 samples sorted by row, rotated thread mapping, carry into the next
     row): against the same search in short calls (per-cell gather lists, csrc/group.cu) and against the oracle; group
     lengths that are not a multiple of 128, folds that wrap around fftlen and overlap each other."""
-    F, K = 4096, 1 << 14
-    rng = np.random.default_rng(G * 1000 + L)
+    K = 1 << 14
+    rng = np.random.default_rng(G * 1000 + L + F)
     if kind == "1000g":
         starts = np.arange(G) * 1000
+    elif kind == "128g":
+        starts = np.arange(G) * 128
     elif kind == "dense":
         starts = np.sort(rng.integers(0, 3000, G))             # heavily overlapping cells
     else:
@@ -1037,7 +1040,7 @@ def test_group_rotated_rows_vs_oracle_and_ell_layout(xr, G, L, kind):
     y = signals.qpsk(rng, G * L).reshape(G, L)
     span = int(starts[-1]) + F
     rx = signals.cnoise(rng, K + span)
-    p0, k0 = 9876, 1501
+    p0, k0 = 9876, 1501 % F
     for g in range(G):
         a = p0 + int(starts[g])
         rx[a:a + L] += np.complex64(0.8) * y[g] * signals.tone(L, k0, F, offset=int(starts[g]))
