@@ -3,6 +3,7 @@
 #include <vector>
 
 #include "group_pp.cuh"
+#include "group_warp.cuh"
 #include "internal.cuh"
 
 namespace xc {
@@ -25,16 +26,18 @@ constexpr int GP_B2K = 6;
 
 // Rotated-row plan (group_pp.cuh, ROT): every group is cut into sub-groups of TG samples, sorted by the row their first
 // cell lies in; thread t holds the weight of sample (t - r) mod TG of each sub-group.
-template <class PL, int B>
+using GPPL1K = FftPlan<10, 32, 32, 32, 1>;     // fftlen 1024: sixteen warps, one shift per warp (group_warp.cuh)
+constexpr int GP_B1K = 16;
+
+template <class PL, int B, class LY>
 static int rot_window_slack(int G, int L) {
-    using LY = GroupPPLayout<PL, B, true>;
     // the stage keeps TG zero cells behind the last window
     const int64_t room = (int64_t)max_smem_optin() - (int64_t)LY::OFF_STAGE - (int64_t)sizeof(float2) * PL::TG;
     int W = ((int)(room / (int64_t)(sizeof(float2) * (size_t)G)) - L) / B * B;
     if (W > 252 / B * B) W = 252 / B * B;
     return W;
 }
-template <class PL, int B>
+template <class PL, int B, class LY = GroupPPLayout<PL, B, true>>
 static int32_t group_rot_build(const float2* y, const int64_t* starts, int G, int L, GroupPPPlan* p) {
     constexpr int TG = PL::TG, F = PL::N;
     static_assert(GR_MAX_E == sizeof(p->rdesc) / sizeof(p->rdesc[0]), "descriptor table size");
@@ -42,7 +45,7 @@ static int32_t group_rot_build(const float2* y, const int64_t* starts, int G, in
     const int per = (L + TG - 1) / TG;
     const int E = G * per;
     if (E + 2 > GR_MAX_E) return XC_OK;
-    const int W = rot_window_slack<PL, B>(G, L);
+    const int W = rot_window_slack<PL, B, LY>(G, L);
     if (W < 4 * B) return XC_OK;
     const int SW = L + W;
     struct Sub { int row, r, g, i; };
@@ -85,6 +88,7 @@ static int32_t group_rot_build(const float2* y, const int64_t* starts, int G, in
 int32_t group_pp_build(const float2* y, const int64_t* starts, int G, int L, int F, GroupPPPlan* p) {
     memset(p, 0, sizeof(*p));
     if (F == GPPL2K::N) return group_rot_build<GPPL2K, GP_B2K>(y, starts, G, L, p);
+    if (F == GPPL1K::N) return group_rot_build<GPPL1K, GP_B1K, GroupWarpLayout<GP_B1K>>(y, starts, G, L, p);
     if (F != GPPL::N) return XC_OK;
     using LY = GroupPPLayout<GPPL, GP_B>;
     // window slack: the largest multiple of B (at most 252) that fits shared memory
@@ -194,8 +198,35 @@ static int32_t group_pp_launch(const GroupPPPlan& p, const int64_t* d_starts, co
     return XC_OK;
 }
 
+static int32_t group_warp_launch(const GroupPPPlan& p, const int64_t* d_starts, const float2* rx, int64_t rxlen, int64_t shift0,
+                                 int64_t K, int64_t lo, int64_t hi, const FusedOut& out, cudaStream_t stream) {
+    constexpr int B = GP_B1K;
+    using LY = GroupWarpLayout<B>;
+    auto kern = group_warp_kernel<B>;
+    const size_t smem = LY::bytes(p.G, p.L, p.W);
+    if ((int)smem > max_smem_optin()) return fail(XC_ERR_UNSUPPORTED, "group search kernel needs %zu B of shared memory", smem);
+    static KernelOnce once;
+    XC_TRY(once.configure(kern, max_smem_optin()));
+    GroupPPArgs a{rx, rxlen, shift0, lo, hi, d_starts, p.d_w, p.d_off, p.G, p.L, p.NC, p.nq_live, p.W};
+    GroupRotPlan rp;
+    memcpy(rp.cnt, p.rcnt, sizeof(rp.cnt));
+    memcpy(rp.desc, p.rdesc, sizeof(rp.desc));
+    const int64_t per = (K + B - 1) / B;
+    int64_t ctas = (int64_t)sm_count();
+    if (ctas > per) ctas = per;
+    if (ctas < 1) ctas = 1;
+    const int64_t chunk = (per + ctas - 1) / ctas;
+    if (chunk >= (1ll << 26)) return fail(XC_ERR_UNSUPPORTED, "too many shifts per warp");
+    profile_begin(stream);
+    kern<<<(unsigned)ctas, 32 * B, smem, stream>>>(a, rp, out, K, (int)chunk);
+    profile_end(stream);
+    XC_LAUNCH_CHECK();
+    return XC_OK;
+}
+
 int32_t group_pp_run(const GroupPPPlan& p, const int64_t* d_starts, const float2* rx, int64_t rxlen, int64_t shift0, int64_t K,
                      int64_t lo, int64_t hi, const FusedOut& out, cudaStream_t stream) {
+    if (p.F == GPPL1K::N) return group_warp_launch(p, d_starts, rx, rxlen, shift0, K, lo, hi, out, stream);
     if (p.F == GPPL2K::N) return group_pp_launch<GPPL2K, GP_B2K, true>(p, d_starts, rx, rxlen, shift0, K, lo, hi, out, stream);
     return group_pp_launch<GPPL, GP_B, false>(p, d_starts, rx, rxlen, shift0, K, lo, hi, out, stream);
 }
