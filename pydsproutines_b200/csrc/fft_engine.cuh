@@ -85,25 +85,6 @@ __device__ __forceinline__ void codelet_fft(float2* a) {
 template <>
 __device__ __forceinline__ void codelet_fft<1, 1>(float2*) {}
 
-// NC codelets side by side (a + c * STRIDE, c < NC), butterfly by butterfly: the independent chains of the columns sit next
-// to each other in the instruction stream
-template <int R, int H0, int NC, int STRIDE>
-__device__ __forceinline__ void codelet_fft_multi(float2* a) {
-    constexpr int LG = ilog2(R);
-#pragma unroll
-    for (int h = H0; h < R; h <<= 1) {
-#pragma unroll
-        for (int blk = 0; blk < R; blk += 2 * h) {
-#pragma unroll
-            for (int j = 0; j < h; ++j) {
-#pragma unroll
-                for (int c = 0; c < NC; ++c)
-                    dit_butterfly(a[c * STRIDE + bitrev(blk + j, LG)], a[c * STRIDE + bitrev(blk + j + h, LG)], j * (16 / h));
-            }
-        }
-    }
-}
-
 // First stage (h = 1) of codelet_fft<R> with a pending twiddle on every input: the stage pairs a[i] with a[i + R/2]
 // (w = 1), so (a[i], a[i + R/2]) <- (wu a[i] + wv a[i + R/2], wu a[i] - wv a[i + R/2]) costs five packed
 // instructions (P = wu u; S = P + wv v; D = 2 P - S) instead of two complex multiplies and a butterfly (six).

@@ -239,20 +239,12 @@ __device__ __forceinline__ void pp_block_fft_fold(float2* v, const float2* x, co
         if (c + 1 < 4 * NQ2) tc::tmem_ld16_issue(tb + L::COL_TW1 + 16 * (c + 1), cu[(c + 1) & 1]);
         folded_stage_chunk(v + (c / 4) * R2, c % 4, cu[c & 1]);
     }
-#ifdef XC_PP_INTERLEAVE
-    codelet_fft_multi<R2, 2, NQ2, R2>(v);
-#pragma unroll
-    for (int q = 0; q < NQ2; ++q)
-#pragma unroll
-        for (int j = 0; j < R2; ++j) buf[o2 + q * QSTEP2 + bitrev(j, ilog2(R2)) * ROW] = v[q * R2 + j];
-#else
 #pragma unroll
     for (int q = 0; q < NQ2; ++q) {
         codelet_fft<R2, 2>(v + q * R2);
 #pragma unroll
         for (int j = 0; j < R2; ++j) buf[o2 + q * QSTEP2 + bitrev(j, ilog2(R2)) * ROW] = v[q * R2 + j];
     }
-#endif
     tc::tmem_ld16_issue(tb + L::COL_TW2, cu[0]);      // first chunk of T2
     __syncwarp();   // the rows a warp wrote are exactly the rows it reads next
     // ---- last pass ----
@@ -272,12 +264,8 @@ __device__ __forceinline__ void pp_block_fft_fold(float2* v, const float2* x, co
 #pragma unroll
         for (int q = 0; q < NQ2; ++q) folded_stage_chunk(v + q * RL, m, cu[m & 1]);
     }
-#ifdef XC_PP_INTERLEAVE
-    codelet_fft_multi<RL, 2, NQ2, RL>(v);
-#else
 #pragma unroll
     for (int q = 0; q < NQ2; ++q) codelet_fft<RL, 2>(v + q * RL);
-#endif
 }
 
 // CPLX: also writes the complex QF X[bin] / (||cutout|| ||window||) of the absResult = False variants
