@@ -101,27 +101,65 @@ __global__ void __launch_bounds__(PL::TG* B) fused_fft_kernel(const Loader loade
             if (out.fidx) out.fidx[i0 + it - 1] = (b == 0xffffffffu) ? 0u : b;
         }
         if (GENERAL && out.caf) {
-            // ---- CAF row: write all bins (natural order) ----
-            if (active) {
+            // ---- CAF row: all bins in natural order.  The registers hold bins at a stride of R1 across the lanes, so the row
+            // goes through the (now free) exchange buffer and leaves as coalesced runs (4-byte stores at a stride of R1
+            // floats reached 0.13 of the HBM write rate) ----
+            if (PL::P == 1) {
+                if (active) {
+                    const float refn = *out.refnormsq;
+                    const float denom_e = ok ? out.energy[i0 + it] : 1.f;
+                    const float sc = ok ? 1.f / (sqrtf(refn) * sqrtf(denom_e)) : 0.f;
+#pragma unroll
+                    for (int j = 0; j < PL::RL; ++j) {
+                        const float2 x = v[j];
+                        if (out.caf_complex)
+                            reinterpret_cast<float2*>(out.caf)[(size_t)(i0 + it) * PL::N + output_bin<PL>(t, 0, j)] = make_float2(x.x * sc, x.y * sc);
+                        else
+                            out.caf[(size_t)(i0 + it) * PL::N + output_bin<PL>(t, 0, j)] = ok ? cnorm2(x) / refn / denom_e : 0.f;
+                    }
+                }
+            } else {
+                bar();   // every thread has finished the last-pass loads: the buffer is free
                 const float refn = *out.refnormsq;
-                const float denom_e = ok ? out.energy[i0 + it] : 1.f;
+                const float denom_e = (active && ok) ? out.energy[i0 + it] : 1.f;
                 if (out.caf_complex) {
-                    float2* row = reinterpret_cast<float2*>(out.caf) + (size_t)(i0 + it) * PL::N;
                     const float sc = ok ? 1.f / (sqrtf(refn) * sqrtf(denom_e)) : 0.f;
 #pragma unroll
                     for (int q = 0; q < V / PL::RL; ++q)
 #pragma unroll
                         for (int j = 0; j < PL::RL; ++j) {
+                            const int bn = output_bin<PL>(t, q, j);
                             const float2 x = v[q * PL::RL + j];
-                            row[output_bin<PL>(t, q, j)] = make_float2(x.x * sc, x.y * sc);
+                            buf[bn + ((bn / PL::RL) << 1)] = make_float2(x.x * sc, x.y * sc);      // rows of RL cells are ROW = RL + 2 apart
                         }
+                    bar();
+                    if (active) {
+                        float2* row = reinterpret_cast<float2*>(out.caf) + (size_t)(i0 + it) * PL::N;
+#pragma unroll
+                        for (int i = 0; i < V; ++i) {
+                            const int bn = i * TG + t;
+                            row[bn] = buf[bn + ((bn / PL::RL) << 1)];
+                        }
+                    }
                 } else {
-                    float* row = out.caf + (size_t)(i0 + it) * PL::N;
+                    float* const fb = reinterpret_cast<float*>(buf);
+                    const float sc2 = ok ? (1.f / refn) / denom_e : 0.f;       // one reciprocal per row, not two divisions per bin
 #pragma unroll
                     for (int q = 0; q < V / PL::RL; ++q)
 #pragma unroll
-                        for (int j = 0; j < PL::RL; ++j)
-                            row[output_bin<PL>(t, q, j)] = ok ? cnorm2(v[q * PL::RL + j]) / refn / denom_e : 0.f;
+                        for (int j = 0; j < PL::RL; ++j) {
+                            const int bn = output_bin<PL>(t, q, j);
+                            fb[bn + (bn >> 5)] = cnorm2(v[q * PL::RL + j]) * sc2;
+                        }
+                    bar();
+                    if (active) {
+                        float* row = out.caf + (size_t)(i0 + it) * PL::N;
+#pragma unroll
+                        for (int i = 0; i < V; ++i) {
+                            const int bn = i * TG + t;
+                            row[bn] = fb[bn + (bn >> 5)];
+                        }
+                    }
                 }
             }
             bar();   // buffer free for the next iteration
