@@ -308,7 +308,7 @@ def config_line(which, lib, peaks, p32, p32src, steps):
                              "peak_source": peaks["_source"] + " (cuBLAS bf16 burst)", "precision_passes": passes,
                              "algorithmic_frac": flops / (ms * 1e-3) / 1e12 / peak, "kernel": "mt_tc_kernel",
                              "kernel_ms": ms, "traffic": None}}
-    if which in ("n1024", "n2048", "n4096", "n16384"):
+    if which in ("n256", "n512", "n1024", "n2048", "n4096", "n16384"):
         # the frequency search at the other power-of-two lengths (2^20 shifts each, planted peak checked)
         N = int(which[1:])
         c = signals.config_c2(log2_shifts=20, N=N)
@@ -325,7 +325,8 @@ def config_line(which, lib, peaks, p32, p32src, steps):
         ms = float(np.median(kms[2:]))
         cells = float(c["K"]) * N
         flops = cells * (5.0 * np.log2(N) + 10.0)
-        layout = ("fused_fft_warp_kernel (one warp per FFT, staged window, constants in tensor memory)" if N == 1024 else
+        layout = ("fused_fft_subwarp_kernel (%d lanes per FFT, %d FFTs per warp, staged window, constants in tensor memory)" % (N // 32, 1024 // N) if N < 1024 else
+                  "fused_fft_warp_kernel (one warp per FFT, staged window, constants in tensor memory)" if N == 1024 else
                   "fused_fft_pp_kernel (ping-pong layout)" if N in (2048, 4096) else "fused_fft_kernel (B groups per CTA, round 1)")
         return {"workload": "fastXcorr freqsearch: %d-sample cutout, 2^20 shifts, %d-bin FFT per shift" % (N, N), "ms": ms,
                 "cells_per_s": cells / (ms * 1e-3), "peak_checked": [c["p0"], c["k0"]],
@@ -566,7 +567,7 @@ def run_ours(args, rank, world, local_rank):
                                               % (n, os.cpu_count() or 1, CPU_NOTE)}
         if world == 1 and not args.no_configs:
             line["configs"] = []
-            for w in ("c1", "c3", "c4", "c6", "bx", "n1024", "n2048", "n4096", "n16384"):
+            for w in ("c1", "c3", "c4", "c6", "bx", "n256", "n512", "n1024", "n2048", "n4096", "n16384"):
                 try:
                     line["configs"].append(config_line(w, lib, peaks, p32, p32src, 3))
                 except Exception as e:                      # a config failure must not hide the headline
@@ -583,7 +584,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=["c2", "c1", "c3", "c4", "c6", "bx", "bx10", "n1024", "n2048", "n4096", "n16384"],
+    ap.add_argument("--workload", default="c2", choices=["c2", "c1", "c3", "c4", "c6", "bx", "bx10", "n256", "n512", "n1024", "n2048", "n4096", "n16384"],
                     help="single-GPU headline config (default C2, BASELINE.json's metric config)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-configs", action="store_true", help="skip the C1 / C3 / C4 / C6 lines of the N = 1 run")

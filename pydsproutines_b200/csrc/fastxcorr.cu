@@ -212,8 +212,8 @@ struct FreqRunner {
         using PF = PlanFor<LOG2N>;
         using LD = CutoutLoader<typename PF::PL, PF::CS>;
         LD ld{rx, rxlen, cutout, sl.shift0, sl.step, sl.shifts};
-        if constexpr (LOG2N >= 10 && LOG2N <= 13) {
-            // contiguous shift range, (max, arg max) outputs, 1024 / 2048 / 4096 / 8192 points: free-running thread groups per SM
+        if constexpr (LOG2N >= 7 && LOG2N <= 13) {
+            // contiguous shift range, (max, arg max) outputs, 128 ... 8192 points (at 64 points the round-1 layout is faster): free-running thread groups per SM
             // over one staged rx window, constants in tensor memory (fused_fft_pp.cuh).  Short ranges, shift lists with
             // a step or a gather table and the CAF / complex outputs stay on the B-groups-per-CTA layout below.
             const int layout = search_layout();

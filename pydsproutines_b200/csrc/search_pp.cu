@@ -3,6 +3,7 @@
 // points per thread), 2048 (eight groups of 64 threads) and 1024 (sixteen warps, one FFT per warp).
 #include "fused_fft_pp.cuh"
 #include "fused_fft_warp.cuh"
+#include "fused_fft_subwarp.cuh"
 
 #ifndef XC_PP_TG8192
 #define XC_PP_TG8192 128
@@ -19,7 +20,7 @@
 
 namespace xc {
 
-bool search_pp_takes(int N) { return N == 8192 || N == 4096 || N == 2048 || N == 1024; }
+bool search_pp_takes(int N) { return N == 8192 || N == 4096 || N == 2048 || N == 1024 || N == 512 || N == 256 || N == 128; }
 
 int32_t search_pp_device(const StagedArgs& a, const FusedOut& out, int64_t K, int N, int fold, cudaStream_t stream) {
 #ifdef XC_EXPERIMENTS
@@ -30,6 +31,9 @@ int32_t search_pp_device(const StagedArgs& a, const FusedOut& out, int64_t K, in
     if (N == 4096) return launch_fused_pp<FftPlan<12, 128, 4, 32, 32>, XC_PP_B4096, true>(a, out, K, stream);
     if (N == 2048) return launch_fused_pp<FftPlan<11, 64, 2, 32, 32>, XC_PP_B2048, true>(a, out, K, stream);
     if (N == 1024) return launch_fused_warp<XC_PP_B1024>(a, out, K, stream);      // one warp per FFT (fused_fft_warp.cuh)
+    if (N == 512) return launch_fused_subwarp<4, 16>(a, out, K, stream);          // 16 lanes per FFT, two FFTs per warp (fused_fft_subwarp.cuh)
+    if (N == 256) return launch_fused_subwarp<3, 16>(a, out, K, stream);          // 8 lanes per FFT, four per warp
+    if (N == 128) return launch_fused_subwarp<2, 16>(a, out, K, stream);          // 4 lanes per FFT, eight per warp
     return fail(XC_ERR_UNSUPPORTED, "no ping-pong layout for %d points", N);
 }
 

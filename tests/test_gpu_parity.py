@@ -878,7 +878,7 @@ def test_czt_run_golden(xr, name, d, space):
         c.runMany(x.astype(np.complex128))
 
 
-@pytest.mark.parametrize("N", [1024, 2048, 4096])
+@pytest.mark.parametrize("N", [64, 128, 256, 512, 1024, 2048, 4096])
 def test_pingpong_layout_other_lengths(xr, N):
     """The ping-pong layout at 1024 points (sixteen warps per SM, one FFT per warp: csrc/fused_fft_warp.cuh), 2048 points
     (eight groups of 64 threads per SM) and 4096 points (four groups of 128): one contiguous call against calls of < 16 shifts per SM (B-groups-per-CTA layout) and against the oracle."""
@@ -936,7 +936,7 @@ def test_pingpong_layout_matches_b2_layout(xr):
     assert f[123456 + 50] == rf[60]
 
 
-@pytest.mark.parametrize("N,step", [(1024, 3), (2048, 2), (4096, 16), (8192, 5)])
+@pytest.mark.parametrize("N,step", [(64, 16), (128, 2), (256, 16), (512, 7), (1024, 3), (2048, 2), (4096, 16), (8192, 5)])
 def test_staged_layouts_stepped_ranges(xr, N, step):
     """Shift ranges with a small step (CyIppXcorrFFT.xcorr(rx, start, end, step), fastXcorr(shifts=arange(a, b, step))) run
     the staged-window layouts too: against the contiguous search at the same shifts and against the oracle."""
@@ -965,7 +965,7 @@ def test_staged_layouts_stepped_ranges(xr, N, step):
     assert_bins(f[idx], rf, lambda i: _spec64(cutout, rx, int(sh[idx[i]])))
 
 
-@pytest.mark.parametrize("N,step", [(1024, 1), (2048, 1), (4096, 3), (8192, 1)])
+@pytest.mark.parametrize("N,step", [(64, 3), (128, 1), (256, 1), (512, 5), (1024, 1), (2048, 1), (4096, 3), (8192, 1)])
 def test_staged_layouts_complex_qf(xr, N, step):
     """absResult=False (complex QF at the arg max, xcorrRoutines.py:533-548) from the staged-window layouts: against short
     calls (B-groups-per-CTA layout) and the oracle; the squared magnitude equals the QF^2 of the same call."""

@@ -84,7 +84,7 @@ def main():
             ms = timed(lambda: xr._caf_call(cu, rx, dsh, True), steps)
             line("CAF rows N=%d complex64 (%d shifts)" % (N, Kc), ms, Kc * N, Kc * N * fft_flops(N), bytes_=8.0 * Kc * N)
     # ---- shorter powers of two ----
-    for N in (512, 256, 64):
+    for N in (512, 256, 128, 64):
         if want("plain%d" % N):
             K = 1 << 20
             c = signals.config_c2(log2_shifts=20, N=N)
