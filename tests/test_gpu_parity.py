@@ -1063,6 +1063,31 @@ def test_group_rotated_rows_vs_oracle_and_ell_layout(xr, G, L, kind, F):
     assert_bins(f[idx], fr, lambda i: _group_spec64(y, starts, rx, F, int(idx[i])), what="group bin")
 
 
+def test_group_rotated_rows_nonzero_first_start(xr):
+    """autoZeroStarts=False with a first start of 333 samples (xcorrRoutines.py:1058-1060): the fold is rotated by the first
+    start as well; fftlen 4096 and 1024, against the oracle and the gather-list layout."""
+    for F, G, L in ((4096, 20, 128), (1024, 12, 96)):
+        rng = np.random.default_rng(F + G)
+        starts = (np.cumsum(rng.integers(L, 900, G)) + 333).astype(np.int64)
+        y = signals.qpsk(rng, G * L).reshape(G, L)
+        K = 1 << 13
+        rx = signals.cnoise(rng, K + int(starts[-1]) + F)
+        p0, k0 = 4000, 77
+        for g in range(G):
+            a = p0 + int(starts[g])
+            rx[a:a + L] += y[g] * signals.tone(L, k0, F, offset=int(starts[g]))
+        obj = xr.GroupXcorrFFT(y, starts, 1, fftlen=F, autoZeroStarts=False)
+        q, f = obj.xcorr(_dev(rx), np.arange(K))
+        q, f = q.cpu().numpy(), f.cpu().numpy()
+        assert int(np.argmax(q)) == p0 and int(f[p0]) == k0
+        q2, f2 = obj.xcorr(_dev(rx), np.arange(1000, 3000))
+        np.testing.assert_allclose(q[1000:3000], q2.cpu().numpy(), rtol=2e-5, atol=1e-7)
+        idx = np.r_[np.arange(0, 8), np.arange(p0 - 4, p0 + 4), np.arange(K - 8, K)]
+        qr, fr = orc.GroupXcorrFFT(y, starts, 1, fftlen=F, autoZeroStarts=False).xcorr(rx, idx)
+        assert_qf2(q[idx], qr)
+        assert_bins(f[idx], fr, lambda i: _group_spec64(y, starts, rx, F, int(idx[i])), what="group bin")
+
+
 def test_groupfreq_large_planted_and_sampled(xr):
     """C3's groups (64 x 128 at 1024 g) against 256 frequencies over 2^17 shifts: the planted (shift, frequency) is the
     global peak, and 48 randomly sampled shifts agree with the oracle (size-independent checks at bench-like size)."""
