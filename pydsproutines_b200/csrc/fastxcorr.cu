@@ -23,6 +23,9 @@ namespace xc {
 // search_pp.cu: the ping-pong layout of the N = 8192 search (fused_fft_pp.cuh); fold = 1 is the shipped variant
 int32_t search_pp_device(const StagedArgs& a, const FusedOut& out, int64_t K, int N, int fold, cudaStream_t stream);
 bool search_pp_takes(int N);
+bool search_blue_pp_takes(int M);
+int32_t search_blue_pp_device(const StagedArgs& a, const float2* bhat, int nvalid, int nbins, const FusedOut& out, int64_t K, int M,
+                              cudaStream_t stream);
 constexpr int PP_MAX_STEP = 16;       // (groups per SM - 1) * step stays well inside the 2048 samples of window slack
 
 // ---------------------------------------------------------------------------------------------
@@ -248,6 +251,7 @@ struct BluePlan {
     int N = 0, nbins = 0, log2m = 0;
     float2* d_b = nullptr;          // [M]: pre-chirp conj(aa[n]) = exp(+i 2 pi (a n + w n^2 / 2)) for n < N, 0 beyond
     float2* d_bhat_perm = nullptr;  // [M]: FFT_M(W^(-d^2/2) wrapped)[output_bin(t, slot)] at slot * TG + t
+    float2* d_bhat_nat = nullptr;   // [M]: the same in natural bin order (the ping-pong layout lays it out itself)
     float2* d_post = nullptr;       // [nbins]: exp(+i 2 pi w k^2 / 2); X[k] = conj(d_post[k] v) / M
 };
 // keyed by (device, length, bins, start frequency a, frequency step w) -- a, w in cycles per sample
@@ -259,6 +263,7 @@ constexpr size_t BLUE_CACHE_MAX = 16;
 static void blue_free(BluePlan& p) {
     if (p.d_b) cudaFree(p.d_b);
     if (p.d_bhat_perm) cudaFree(p.d_bhat_perm);
+    if (p.d_bhat_nat) cudaFree(p.d_bhat_nat);
     if (p.d_post) cudaFree(p.d_post);
     p = BluePlan();
 }
@@ -371,9 +376,13 @@ static int32_t blue_plan_for(int N, const CztSpec* spec, const BluePlan** out) {
     }
     fft_host_radix2(ext);
     XC_TRY(dispatch_log2(p.log2m, BluePermute{ext, perm}));
+    std::vector<float2> nat(M);
+    for (int i = 0; i < M; ++i) nat[i] = make_float2((float)ext[i].re, (float)ext[i].im);
     XC_CUDA_TRY(cudaMalloc(&p.d_b, sizeof(float2) * M));
     XC_CUDA_TRY(cudaMalloc(&p.d_bhat_perm, sizeof(float2) * M));
     XC_CUDA_TRY(cudaMalloc(&p.d_post, sizeof(float2) * nbins));
+    XC_CUDA_TRY(cudaMalloc(&p.d_bhat_nat, sizeof(float2) * M));
+    XC_CUDA_TRY(cudaMemcpy(p.d_bhat_nat, nat.data(), sizeof(float2) * M, cudaMemcpyHostToDevice));
     XC_CUDA_TRY(cudaMemcpy(p.d_b, hb.data(), sizeof(float2) * M, cudaMemcpyHostToDevice));
     XC_CUDA_TRY(cudaMemcpy(p.d_bhat_perm, perm.data(), sizeof(float2) * M, cudaMemcpyHostToDevice));
     XC_CUDA_TRY(cudaMemcpy(p.d_post, post.data(), sizeof(float2) * nbins, cudaMemcpyHostToDevice));
@@ -484,6 +493,11 @@ int32_t fastxcorr_freq_device(const float2* cutout, int N, const float2* rx, int
         if (!d_cutb) return XC_ERR_NOMEM;
         chirp_cutout_kernel<<<(M + 255) / 256, 256, 0, stream>>>(cutout, plan->d_b, N, M, d_cutb);
         XC_LAUNCH_CHECK();
+        // shift ranges with (max, arg max) outputs: thread groups over one staged window, constants in tensor memory
+        if (search_blue_pp_takes(M) && !out.caf && !out.cplx && !sl.shifts && sl.step >= 1 && sl.step <= PP_MAX_STEP &&
+            sl.K >= 16 * (int64_t)sm_count() && search_layout() == LAYOUT_PP)
+            return search_blue_pp_device(StagedArgs{rx, rxlen, d_cutb, sl.shift0, (int)sl.step}, plan->d_bhat_nat, N, plan->nbins, out,
+                                         sl.K, M, stream);
         return dispatch_log2(plan->log2m, BlueRunner{d_cutb, N, plan, rx, rxlen, sl, out, stream});
     }
     return dispatch_log2(ilog2(N), FreqRunner{cutout, rx, rxlen, sl, out, stream});

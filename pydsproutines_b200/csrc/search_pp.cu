@@ -2,6 +2,7 @@
 // translation unit: 8192 points (two groups of 128 threads, 64 points per thread), 4096 (four groups of 128 threads, 32
 // points per thread), 2048 (eight groups of 64 threads) and 1024 (sixteen warps, one FFT per warp).
 #include "fused_fft_pp.cuh"
+#include "fused_blue_pp.cuh"
 #include "fused_fft_warp.cuh"
 #include "fused_fft_subwarp.cuh"
 
@@ -35,6 +36,23 @@ int32_t search_pp_device(const StagedArgs& a, const FusedOut& out, int64_t K, in
     if (N == 256) return launch_fused_subwarp<3, 16>(a, out, K, stream);          // 8 lanes per FFT, four per warp
     if (N == 128) return launch_fused_subwarp<2, 16>(a, out, K, stream);          // 4 lanes per FFT, eight per warp
     return fail(XC_ERR_UNSUPPORTED, "no ping-pong layout for %d points", N);
+}
+
+// Bluestein (cutout lengths that are not a power of two, chirp-z grids) over a padded length M = 2048 / 4096 / 8192
+#ifdef XC_NO_BLUE_PP
+bool search_blue_pp_takes(int) { return false; }
+#else
+// at M = 8192 (two groups of four warps, six group barriers per shift) the layout measured no faster than bluestein.cuh
+bool search_blue_pp_takes(int M) { return M == 4096 || M == 2048; }
+#endif
+int32_t search_blue_pp_device(const StagedArgs& a, const float2* bhat, int nvalid, int nbins, const FusedOut& out, int64_t K, int M,
+                              cudaStream_t stream) {
+    const double m = (double)M;
+    const BlueArgs ba{bhat, nvalid, nbins, (float)(1.0 / (m * m))};
+    if (M == 8192) return launch_blue_pp<FftPlan<13, 128, 8, 32, 32>, 2>(a, ba, out, K, stream);
+    if (M == 4096) return launch_blue_pp<FftPlan<12, 128, 4, 32, 32>, XC_PP_B4096>(a, ba, out, K, stream);
+    if (M == 2048) return launch_blue_pp<FftPlan<11, 64, 2, 32, 32>, XC_PP_B2048>(a, ba, out, K, stream);
+    return fail(XC_ERR_UNSUPPORTED, "no ping-pong Bluestein layout for %d points", M);
 }
 
 }  // namespace xc

@@ -993,6 +993,38 @@ def test_staged_layouts_complex_qf(xr, N, step):
     np.testing.assert_allclose(z[idx][ok], rz[ok], rtol=0, atol=1e-5 * float(np.abs(rz).max()))
 
 
+@pytest.mark.parametrize("N,step", [(1000, 1), (777, 4), (1500, 1), (2049, 2), (3000, 1), (4095, 3)])
+def test_pingpong_bluestein_lengths(xr, N, step):
+    """Cutout lengths that are not a power of two over shift ranges: Bluestein in the ping-pong layout
+    (csrc/fused_blue_pp.cuh; padded lengths 2048 / 4096 / 8192) against short calls (csrc/bluestein.cuh) and the oracle;
+    windows that leave rx through CyIppXcorrFFT's zero rule."""
+    K = 9000
+    p0 = 4321 - 4321 % step
+    cutout, rx = signals.make_fastxcorr_case(7 * N + step, N, N + K - 1, p0, N // 5, amp=0.7)
+    sh = np.arange(0, K, step)
+    q, f = xr.fastXcorr(_dev(cutout), _dev(rx), freqsearch=True, shifts=sh)
+    q, f = q.cpu().numpy(), f.cpu().numpy()
+    assert int(np.argmax(q)) == p0 // step and int(f[p0 // step]) == N // 5
+    qs, fs = [], []
+    for lo in range(0, sh.size, 1500):
+        qq, ff = xr.fastXcorr(_dev(cutout), _dev(rx), freqsearch=True, shifts=sh[lo:lo + 1500])
+        qs.append(qq.cpu().numpy())
+        fs.append(ff.cpu().numpy())
+    q2, f2 = np.concatenate(qs), np.concatenate(fs)
+    np.testing.assert_allclose(q, q2, rtol=5e-6, atol=1e-9)
+    assert_bins(f, f2, lambda i: _spec64(cutout, rx, int(sh[i])))
+    idx = np.r_[0:10, sh.size - 10:sh.size, p0 // step]
+    rq, rf = orc.fastXcorr(cutout, rx, freqsearch=True, shifts=sh[idx])
+    assert_qf2(q[idx], rq)
+    assert_bins(f[idx], rf, lambda i: _spec64(cutout, rx, int(sh[idx[i]])))
+    a, b = -5 * step, K + 3 * step
+    qc, fc = xr.CyIppXcorrFFT(cutout).xcorr(rx, a, b, step)
+    shc = np.arange(a, b, step)
+    inside = (shc >= 0) & (shc + N <= rx.size)
+    assert not qc[~inside].any() and not fc[~inside].any()
+    np.testing.assert_allclose(qc[inside], q[shc[inside] // step], rtol=5e-6, atol=1e-9)
+
+
 def test_warp_layout_windows_leaving_rx(xr):
     """N = 1024 (one warp per FFT over a staged window): windows that leave rx on either side give 0 / 0
     (IppXcorrFFT.cpp:125-130), the rest agrees with short calls (B-groups-per-CTA layout) and the oracle; several refills."""

@@ -92,7 +92,7 @@ def main():
             ms = timed(lambda: xr._fastxcorr_call(cu, rx, xr._Shifts(None, rx.shape[0], N, rx), True, want_fidx=True), steps)
             line("freqsearch N=%d contiguous, 2^20 shifts" % N, ms, K * N, K * N * fft_flops(N))
     # ---- lengths that are not a power of two (Bluestein inside one SM); flops counted for the true length ----
-    for N in (1000, 3000, 5000, 8191):
+    for N in (1000, 2000, 3000, 5000, 8191):
         if want("blue%d" % N):
             K = 1 << 17
             cutout, rxa = signals.make_fastxcorr_case(5, N, N + K - 1, 4321, 77)
