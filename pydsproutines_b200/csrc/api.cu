@@ -417,8 +417,13 @@ static int32_t fastxcorr_host_pipelined(const float2* cutout, int32_t N, const f
     XC_CUDA_TRY(cudaStreamWaitEvent(d.s_in, d.ev_k[0], 0));
     XC_CUDA_TRY(cudaStreamWaitEvent(d.s_out, d.ev_k[0], 0));
     XC_CUDA_TRY(cudaMemcpyAsync(dc, cutout, sizeof(float2) * (size_t)N, cudaMemcpyHostToDevice, d.s_in));
+    // short first and last chunks (a quarter of an even share): only the first copy-in and the last copy-out are exposed
+    if (nch < 3) nch = 3;
     int64_t k0[PIPE_MAX + 1];
-    for (int c = 0; c <= nch; ++c) k0[c] = (K * c) / nch;
+    const int64_t edge = K / (4 * (int64_t)nch);
+    k0[0] = 0;
+    k0[nch] = K;
+    for (int c = 1; c < nch; ++c) k0[c] = edge + ((K - 2 * edge) * (c - 1)) / (nch - 2);
     int64_t copied = shift0;                     // rx[shift0, copied) is on its way
     for (int c = 0; c < nch; ++c) {
         const int64_t need = shift0 + k0[c + 1] + N - 1;     // chunk c reads rx[shift0 + k0[c], need)
