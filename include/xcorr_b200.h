@@ -116,7 +116,8 @@ int32_t xc_fastxcorr_caf_c64(const void* cutout, int32_t N, const void* rx, int6
  * xcorrRoutines.cztXcorr (xcorrRoutines.py:413-457) with spectralRoutines.CZTCached (spectralRoutines.py:239-309):
  * per shift the product rx[s:s+N] * conj(cutout) is evaluated on the frequency grid
  *     f_k = (f0_cycles + k * df_cycles) cycles per sample,  k < nbins      (f / fs in the reference's units)
- * by the same fused kernel (Bluestein with a general chirp; N + nbins - 1 <= 16384).  qf2[i] = max_k |X[k]|^2 /
+ * by the same fused kernel (Bluestein with a general chirp) while N + nbins - 1 <= 16384, by the four-step path up to
+ * 2^28 points.  qf2[i] = max_k |X[k]|^2 /
  * ||cutout||^2 / ||rx slice||^2, fidx[i] = arg max, cplx[i] = X[arg max] / ||cutout|| / ||rx slice||,
  * caf (optional float32 (K, nbins)) = all bins.  Any of the outputs may be NULL. */
 int32_t xc_cztxcorr_c64(const void* cutout, int32_t N, const void* rx, int64_t rxlen, int64_t shift0,
@@ -134,12 +135,14 @@ int32_t xc_cztxcorr_c64(const void* cutout, int32_t N, const void* rx, int64_t r
  * that loads the library until the process exits).  K > XC_NOALLOC_MAX_SHIFTS returns XC_ERR_UNSUPPORTED (split the
  * range or use xc_fastxcorr_c64).  Every call on a device shares that array and fully rewrites the part it uses
  * (nothing has to start at zero); two calls that overlap on the GPU (different streams of one device) race on it --
- * keep them in stream order. */
+ * keep them in stream order.  (Cutouts of 65536 samples and more: xc_fastxcorr_c64 sums ||cutout||^2 and the first window
+ * of a tile through a small scratch allocation; this entry keeps the serial sums, the results agree to rounding.) */
 #define XC_NOALLOC_MAX_SHIFTS 1048576
 int32_t xc_fastxcorr_nofreq_noalloc_c64(const void* cutout, int32_t N, const void* rx, int64_t rxlen, int64_t shift0,
                                         int64_t K, float* qf2, void* stream);
-/* 1 when the fused frequency-search kernel takes this cutout length: powers of two 2..16384 (one block FFT per
- * shift) and every other length 3..8192 (Bluestein: two block FFTs per shift) */
+/* 1 when the frequency search takes this cutout length: powers of two 2..16384 (one block FFT per shift on one SM), every
+ * other length 3..8192 (Bluestein: two block FFTs per shift), and beyond that the four-step path: powers of two up to 2^28
+ * points, any other length while 2 N - 1 <= 2^28 */
 int32_t xc_fastxcorr_supported(int32_t N);
 
 /* ---- a7, a8: GroupXcorrFFT ----------------------------------------------------------------
