@@ -4,6 +4,7 @@
 
 #include "group_pp.cuh"
 #include "group_warp.cuh"
+#include "group_dense.cuh"
 #include "internal.cuh"
 
 namespace xc {
@@ -84,9 +85,80 @@ static int32_t group_rot_build(const float2* y, const int64_t* starts, int G, in
     return XC_OK;
 }
 
+// Dense-fold plan for short transforms (group_dense.cuh): per (group, cell pair) the two weights and the sample offsets
+template <int LF>
+static int32_t group_dense_build(const float2* y, const int64_t* starts, int G, int L, GroupPPPlan* p) {
+    using LY = GroupDenseLayout<LF>;
+    constexpr int F = LY::F, CB = LY::CB;
+    const int G4 = (G + 3) / 4 * 4;
+    if (G4 + 1 > GD_MAX_G - 1 || L > F) return XC_OK;
+    if (LY::bytes(G4, L) > (size_t)max_smem_optin()) return XC_OK;
+    std::vector<float4> hw((size_t)G4 * CB, make_float4(0.f, 0.f, 0.f, 0.f));
+    std::vector<uint32_t> hd((size_t)G4 * CB, 0u | (1u << 14));
+    for (int g = 0; g < G; ++g) {
+        const int r = (int)(((starts[g] % F) + F) % F);
+        for (int cb = 0; cb < CB; ++cb) {
+            int l0 = ((2 * cb - r) % F + F) % F, l1 = ((2 * cb + 1 - r) % F + F) % F;
+            const bool v0 = l0 < L, v1 = l1 < L;
+            float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (v0) { w.x = y[(size_t)g * L + l0].x; w.y = y[(size_t)g * L + l0].y; }
+            if (v1) { w.z = y[(size_t)g * L + l1].x; w.w = y[(size_t)g * L + l1].y; }
+            uint32_t mode;
+            if (!v0 && !v1) {
+                l0 = r & 1;                    // any window of the right parity
+                l1 = l0 + 1;
+                mode = (uint32_t)(l0 & 1);
+            } else if (v0 && (l1 == l0 + 1)) {
+                mode = (uint32_t)(l0 & 1);     // one sliding window (cell 1 may lie behind the group: weight zero)
+            } else {
+                if (!v0) l0 = 0;               // cell 1 opens the group (l1 = 0) or cell 0 closes it at the wrap-around point
+                if (!v1) l1 = 0;
+                mode = 2u;
+            }
+            hw[(size_t)g * CB + cb] = w;
+            hd[(size_t)g * CB + cb] = (uint32_t)l0 | ((uint32_t)l1 << 14) | (mode << 28);
+        }
+    }
+    XC_CUDA_TRY(cudaMalloc(&p->d_w, sizeof(float4) * hw.size()));
+    XC_CUDA_TRY(cudaMalloc(&p->d_off, sizeof(uint32_t) * hd.size()));
+    XC_CUDA_TRY(cudaMemcpy(p->d_w, hw.data(), sizeof(float4) * hw.size(), cudaMemcpyHostToDevice));
+    XC_CUDA_TRY(cudaMemcpy(p->d_off, hd.data(), sizeof(uint32_t) * hd.size(), cudaMemcpyHostToDevice));
+    p->G = G;
+    p->G4 = G4;
+    p->L = L;
+    p->F = F;
+    p->dense = 1;
+    p->usable = 1;
+    return XC_OK;
+}
+
+template <int LF>
+static int32_t group_dense_launch(const GroupPPPlan& p, const int64_t* d_starts, const float2* rx, int64_t rxlen, int64_t shift0,
+                                  int64_t K, int64_t lo, int64_t hi, const FusedOut& out, cudaStream_t stream) {
+    using LY = GroupDenseLayout<LF>;
+    auto kern = group_dense_kernel<LF>;
+    const size_t smem = LY::bytes(p.G4, p.L);
+    if ((int)smem > max_smem_optin()) return fail(XC_ERR_UNSUPPORTED, "group search kernel needs %zu B of shared memory", smem);
+    static KernelOnce once;
+    XC_TRY(once.configure(kern, max_smem_optin()));
+    GroupDenseArgs a{rx, rxlen, shift0, lo, hi, d_starts, reinterpret_cast<const float4*>(p.d_w), p.d_off, p.G, p.G4, p.L};
+    const int64_t ntiles = (K + LY::ST - 1) / LY::ST;
+    int64_t ctas = (int64_t)sm_count();
+    if (ctas > ntiles) ctas = ntiles;
+    if (ctas < 1) ctas = 1;
+    profile_begin(stream);
+    kern<<<(unsigned)ctas, 512, smem, stream>>>(a, out, K);
+    profile_end(stream);
+    XC_LAUNCH_CHECK();
+    return XC_OK;
+}
+
 // y: host weights [G][L] (conjugation already applied); the plan is usable when the fold fits the kernel's limits
 int32_t group_pp_build(const float2* y, const int64_t* starts, int G, int L, int F, GroupPPPlan* p) {
     memset(p, 0, sizeof(*p));
+    if (F == 256) return group_dense_build<8>(y, starts, G, L, p);
+    if (F == 128) return group_dense_build<7>(y, starts, G, L, p);
+    if (F == 64) return group_dense_build<6>(y, starts, G, L, p);
     if (F == GPPL2K::N) return group_rot_build<GPPL2K, GP_B2K>(y, starts, G, L, p);
     if (F == GPPL1K::N) return group_rot_build<GPPL1K, GP_B1K, GroupWarpLayout<GP_B1K>>(y, starts, G, L, p);
     if (F != GPPL::N) return XC_OK;
@@ -226,6 +298,9 @@ static int32_t group_warp_launch(const GroupPPPlan& p, const int64_t* d_starts, 
 
 int32_t group_pp_run(const GroupPPPlan& p, const int64_t* d_starts, const float2* rx, int64_t rxlen, int64_t shift0, int64_t K,
                      int64_t lo, int64_t hi, const FusedOut& out, cudaStream_t stream) {
+    if (p.dense && p.F == 256) return group_dense_launch<8>(p, d_starts, rx, rxlen, shift0, K, lo, hi, out, stream);
+    if (p.dense && p.F == 128) return group_dense_launch<7>(p, d_starts, rx, rxlen, shift0, K, lo, hi, out, stream);
+    if (p.dense && p.F == 64) return group_dense_launch<6>(p, d_starts, rx, rxlen, shift0, K, lo, hi, out, stream);
     if (p.F == GPPL1K::N) return group_warp_launch(p, d_starts, rx, rxlen, shift0, K, lo, hi, out, stream);
     if (p.F == GPPL2K::N) return group_pp_launch<GPPL2K, GP_B2K, true>(p, d_starts, rx, rxlen, shift0, K, lo, hi, out, stream);
     return group_pp_launch<GPPL, GP_B, false>(p, d_starts, rx, rxlen, shift0, K, lo, hi, out, stream);

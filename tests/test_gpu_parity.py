@@ -1120,6 +1120,49 @@ def test_group_rotated_rows_nonzero_first_start(xr):
         assert_bins(f[idx], fr, lambda i: _group_spec64(y, starts, rx, F, int(idx[i])), what="group bin")
 
 
+@pytest.mark.parametrize("G,L,F,kind", [(64, 128, 128, "1024g"), (20, 100, 128, "ragged"), (30, 256, 256, "ragged"),
+                                         (50, 64, 64, "1000g"), (16, 40, 64, "ragged"), (7, 128, 256, "ragged"),
+                                         (100, 128, 128, "dense")])
+def test_group_dense_fold_short_fftlen(xr, G, L, F, kind):
+    """GroupXcorrFFT at short transform lengths (fftlen 64 / 128 / 256, including the reference's default fftlen = group
+    length): the dense-fold kernel (csrc/group_dense.cuh: register-tiled fold of G F products per shift, sub-warp FFT of
+    the tile) against short calls (gather lists, csrc/group.cu) and the oracle; odd and even rotations, groups shorter than
+    fftlen, blocks that straddle a group's wrap-around point."""
+    K = 1 << 13
+    rng = np.random.default_rng(G * 100 + L + F)
+    if kind == "1024g":
+        starts = np.arange(G) * 1024
+    elif kind == "1000g":
+        starts = np.arange(G) * 1000 + 3
+    elif kind == "dense":
+        starts = np.sort(rng.integers(0, 5000, G))
+    else:
+        starts = np.cumsum(rng.integers(L, 3 * L + 77, G))
+    starts = (starts - starts[0]).astype(np.int64)
+    y = signals.qpsk(rng, G * L).reshape(G, L)
+    rx = signals.cnoise(rng, K + int(starts[-1]) + F)
+    p0, k0 = 5005, (F // 3) | 1
+    for g in range(G):
+        a = p0 + int(starts[g])
+        rx[a:a + L] += np.complex64(0.8) * y[g] * signals.tone(L, k0, F, offset=int(starts[g]))
+    obj = xr.GroupXcorrFFT(y, starts, 1, fftlen=F)
+    q, f, peak = obj.xcorrPeak(_dev(rx), np.arange(K))
+    q, f = q.cpu().numpy(), f.cpu().numpy()
+    assert (peak.shift, peak.fidx) == (p0, k0) and int(np.argmax(q)) == p0 and int(f[p0]) == k0
+    qs, fs = [], []
+    for lo in range(0, K, 2048):
+        qq, ff = obj.xcorr(_dev(rx), np.arange(lo, lo + 2048))
+        qs.append(qq.cpu().numpy())
+        fs.append(ff.cpu().numpy())
+    q2, f2 = np.concatenate(qs), np.concatenate(fs)
+    np.testing.assert_allclose(q, q2, rtol=2e-5, atol=1e-7 * float(q.max()))
+    assert_bins(f, f2, lambda i: _group_spec64(y, starts, rx, F, int(i)), what="group bin")
+    idx = np.r_[np.arange(0, 12), np.arange(p0 - 6, p0 + 6), np.arange(K - 12, K)]
+    qr, fr = orc.GroupXcorrFFT(y, starts, 1, fftlen=F).xcorr(rx, idx)
+    assert_qf2(q[idx], qr)
+    assert_bins(f[idx], fr, lambda i: _group_spec64(y, starts, rx, F, int(idx[i])), what="group bin")
+
+
 def test_groupfreq_large_planted_and_sampled(xr):
     """C3's groups (64 x 128 at 1024 g) against 256 frequencies over 2^17 shifts: the planted (shift, frequency) is the
     global peak, and 48 randomly sampled shifts agree with the oracle (size-independent checks at bench-like size)."""
