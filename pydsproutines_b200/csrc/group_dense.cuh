@@ -16,6 +16,10 @@
 
 namespace xc {
 
+#ifndef XC_GD_UNROLL
+#define XC_GD_UNROLL 4
+#endif
+constexpr int GD_UNROLL = XC_GD_UNROLL;   // groups per trip of the fold loop
 constexpr int GD_MAX_G = 112;          // groups (4 tensor-memory columns each beside the 64 twiddle columns)
 
 namespace tc {
@@ -39,7 +43,8 @@ struct GroupDenseLayout {
     static constexpr size_t OFF_U = 0;
     static constexpr size_t OFF_TADDR = sizeof(float2) * (size_t)ST * UP;
     static constexpr size_t OFF_DESC = OFF_TADDR + 16;                 // [G4][CB] uint32
-    __host__ __device__ static constexpr size_t off_stage(int G4) { return (OFF_DESC + sizeof(uint32_t) * (size_t)G4 * CB + 15) / 16 * 16; }
+    __host__ __device__ static constexpr size_t off_starts(int G4) { return (OFF_DESC + sizeof(uint32_t) * (size_t)G4 * CB + 15) / 16 * 16; }   // int64 [G4]
+    __host__ __device__ static constexpr size_t off_stage(int G4) { return off_starts(G4) + sizeof(int64_t) * (size_t)G4; }
     __host__ __device__ static constexpr int sw(int L) { return (L + ST + 16 + 1) / 2 * 2; }    // staged samples per group
     __host__ __device__ static constexpr size_t bytes(int G4, int L) { return off_stage(G4) + sizeof(float2) * (size_t)G4 * sw(L); }
 };
@@ -59,6 +64,34 @@ __device__ __forceinline__ float2 gd_mac(float2 acc, float2 x, float wr, float w
     return pfma(make_float2(x.y, x.x), make_float2(-wi, wi), pfma(x, make_float2(wr, wr), acc));
 }
 
+// stage[g SW + j] = rx[s0 + s_g + j], j < L + ST (zero outside the record, behind the window and for the padding groups);
+// sst = the group starts in shared memory; eight independent loads in flight per thread
+template <int LF>
+__device__ __forceinline__ void gd_stage(const GroupDenseArgs& a, float2* stage, const int64_t* sst, const int SW, const int nstage,
+                                         const int64_t s0, const int tid, const int nthreads) {
+    constexpr int ST = GroupDenseLayout<LF>::ST;
+    for (int i0 = tid; i0 < nstage; i0 += 8 * nthreads) {
+        float2 val[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int i = i0 + k * nthreads;
+            val[k] = make_float2(0.f, 0.f);
+            if (i < nstage) {
+                const int gi = i / SW, j = i - gi * SW;
+                if (gi < a.G && j < a.L + ST) {
+                    const int64_t p = s0 + sst[gi] + j;
+                    if (p >= 0 && p < a.rxlen) val[k] = __ldg(a.rx + p);
+                }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int i = i0 + k * nthreads;
+            if (i < nstage) stage[i] = val[k];
+        }
+    }
+}
+
 template <int LF>
 __global__ void __launch_bounds__(512, 1) group_dense_kernel(const GroupDenseArgs a, const FusedOut out, const int64_t K) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -71,7 +104,9 @@ __global__ void __launch_bounds__(512, 1) group_dense_kernel(const GroupDenseArg
     float2* const stage = reinterpret_cast<float2*>(smem_raw + LY::off_stage(a.G4));
     const int SW = LY::sw(a.L);
     if (warp == 0) tc::tmem_alloc(tc::smem_u32(taddr_slot), LY::TMEM_COLS);
+    int64_t* const sst = reinterpret_cast<int64_t*>(smem_raw + LY::off_starts(a.G4));
     for (int i = threadIdx.x; i < a.G4 * CB; i += 512) desc[i] = a.desc[i];
+    for (int i = threadIdx.x; i < a.G4; i += 512) sst[i] = i < a.G ? a.starts[i] : 0;
     tc::tc_fence_before();
     __syncthreads();
     tc::tc_fence_after();
@@ -120,24 +155,18 @@ __global__ void __launch_bounds__(512, 1) group_dense_kernel(const GroupDenseArg
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int64_t i0 = tile * ST;                          // first shift-list entry of the tile
         const int64_t s0 = a.shift0 + i0;
-        // ---- stage the group windows rx[s0 + s_g, + L + ST) (zero outside the record and behind them) ----
-        for (int i = threadIdx.x; i < nstage; i += 512) {
-            const int gi = i / SW, j = i - gi * SW;
-            float2 val = make_float2(0.f, 0.f);
-            if (gi < a.G && j < a.L + ST) {
-                const int64_t p = s0 + __ldg(a.starts + gi) + j;
-                if (p >= 0 && p < a.rxlen) val = __ldg(a.rx + p);
-            }
-            stage[i] = val;
+        if (tile == (int64_t)blockIdx.x) {
+            // the first tile: every warp stages (later tiles are staged by warps 8 .. 15 under the previous transform phase)
+            gd_stage<LF>(a, stage, sst, SW, nstage, s0, threadIdx.x, 512);
+            __syncthreads();
         }
-        __syncthreads();
         // ---- fold: two cells x eight shifts per thread ----
         float2 acc0[8], acc1[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc0[j] = acc1[j] = make_float2(0.f, 0.f);
         uint32_t wn[4];
         tc::tmem_ld4_issue(tb + LY::COL_W, wn);
-#pragma unroll 1
+#pragma unroll GD_UNROLL
         for (int g = 0; g < a.G4; ++g) {
             const uint32_t d = desc[g * CB + cb];
             const int l0 = (int)(d & 0x3fffu), l1 = (int)((d >> 14) & 0x3fffu), mode = (int)(d >> 28);
@@ -250,8 +279,11 @@ __global__ void __launch_bounds__(512, 1) group_dense_kernel(const GroupDenseArg
                 if (out.qf2) out.qf2[e] = ok ? mx / refn / en : 0.f;
                 if (out.fidx) out.fidx[e] = (ok && bin != 0xffffffffu) ? bin : 0u;
             }
+        } else if (tile + gridDim.x < ntiles) {
+            // the fold is done with the stage: the other warps fetch the windows of this CTA's next tile meanwhile
+            gd_stage<LF>(a, stage, sst, SW, nstage, a.shift0 + (tile + gridDim.x) * ST, (int)threadIdx.x - 32 * (ST / FPW), 512 - 32 * (ST / FPW));
         }
-        __syncthreads();     // u and the stage are free for the next tile
+        __syncthreads();     // u is free and the stage holds the next tile
     }
     tc::tc_fence_before();
     __syncthreads();
