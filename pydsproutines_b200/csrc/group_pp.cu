@@ -161,6 +161,12 @@ int32_t group_pp_build(const float2* y, const int64_t* starts, int G, int L, int
     if (F == 64) return group_dense_build<6>(y, starts, G, L, p);
     if (F == GPPL2K::N) return group_rot_build<GPPL2K, GP_B2K>(y, starts, G, L, p);
     if (F == GPPL1K::N) return group_rot_build<GPPL1K, GP_B1K, GroupWarpLayout<GP_B1K>>(y, starts, G, L, p);
+    if (F == 512 || F == 32) {
+        // X_F[k] = X_1024[k 1024 / F]: the 1024-point kernel, every (1024 / F)-th bin
+        XC_TRY((group_rot_build<GPPL1K, GP_B1K, GroupWarpLayout<GP_B1K>>(y, starts, G, L, p)));
+        if (p->usable) p->bin_shift = F == 512 ? 1 : 5;
+        return XC_OK;
+    }
     if (F != GPPL::N) return XC_OK;
     using LY = GroupPPLayout<GPPL, GP_B>;
     // window slack: the largest multiple of B (at most 252) that fits shared memory
@@ -279,7 +285,7 @@ static int32_t group_warp_launch(const GroupPPPlan& p, const int64_t* d_starts, 
     if ((int)smem > max_smem_optin()) return fail(XC_ERR_UNSUPPORTED, "group search kernel needs %zu B of shared memory", smem);
     static KernelOnce once;
     XC_TRY(once.configure(kern, max_smem_optin()));
-    GroupPPArgs a{rx, rxlen, shift0, lo, hi, d_starts, p.d_w, p.d_off, p.G, p.L, p.NC, p.nq_live, p.W};
+    GroupPPArgs a{rx, rxlen, shift0, lo, hi, d_starts, p.d_w, p.d_off, p.G, p.L, p.NC, p.nq_live, p.W, p.bin_shift};
     GroupRotPlan rp;
     memcpy(rp.cnt, p.rcnt, sizeof(rp.cnt));
     memcpy(rp.desc, p.rdesc, sizeof(rp.desc));

@@ -47,6 +47,7 @@ struct GroupPPArgs {
     const float2* w;               // [NC][TG] weights (conj applied), device
     const uint32_t* off;           // [NC][TG] byte offsets into the stage at iteration offset 0
     int G, L, NC, nq_live, W;
+    int bin_shift = 0;             // group_warp_kernel: report bin >> bin_shift of the bins that are multiples of 2^bin_shift
 };
 
 namespace tc {

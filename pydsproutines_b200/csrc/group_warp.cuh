@@ -171,9 +171,13 @@ __global__ void __launch_bounds__(32 * B, 1) group_warp_kernel(const GroupPPArgs
                           fmaxf(fmaxf(nv[8 * c + 4], nv[8 * c + 5]), fmaxf(nv[8 * c + 6], nv[8 * c + 7])));
             tmax = fmaxf(tmax, m8[c]);
         }
+        // a transform twice (2^bs times) the requested fftlen holds the requested bins at the multiples of 2^bs (the DFT of
+        // the products does not care where the fold wraps): lane t owns bins t + 32 k2
+        const bool lane_on = (t & ((1 << a.bin_shift) - 1)) == 0;
+        if (!lane_on) tmax = 0.f;
         const float mx = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(tmax)));
         unsigned int mybin = 0xffffffffu;
-        if (tmax == mx) {
+        if (lane_on && tmax == mx) {
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
                 if (m8[c] == mx) {
@@ -188,7 +192,7 @@ __global__ void __launch_bounds__(32 * B, 1) group_warp_kernel(const GroupPPArgs
         const unsigned int bin = __reduce_min_sync(0xffffffffu, mybin);
         if (t == 0 && e < n_act) {
             if (out.qf2) out.qf2[i0 + e] = ok ? mx / refn / en : 0.f;
-            if (out.fidx) out.fidx[i0 + e] = (ok && bin != 0xffffffffu) ? bin : 0u;
+            if (out.fidx) out.fidx[i0 + e] = (ok && bin != 0xffffffffu) ? (bin >> a.bin_shift) : 0u;
         }
     }
     tc::tc_fence_before();

@@ -49,6 +49,7 @@ struct GroupPPPlan {
     uint32_t* d_off;
     // rotated-row variant (starts that are not aligned to the 128-cell rows): sub-groups sorted by row
     int rot, B, F;               // B = thread groups per SM of the kernel variant, F = transform length
+    int bin_shift;               // the kernel's transform is 2^bin_shift times the requested fftlen: only every 2^bin_shift-th bin counts
     int dense, G4;               // dense-fold variant for short transforms (group_dense.cuh): d_w = float4 [G4][F / 2], d_off = descriptors
     unsigned char rcnt[32];
     uint32_t rdesc[192];

@@ -108,7 +108,7 @@ def main():
         line("cztXcorr N=4096, 1001 bins, 2^17 shifts", t0, K * 1001)
     # ---- GroupXcorrFFT at other transform lengths ----
     for F, G, L, sp in ((2048, 16, 64, 0), (8192, 64, 128, 0), (4096, 8, 512, 0), (4096, 64, 128, 1000), (4096, 64, 128, -1),
-                        (128, 64, 128, 1024), (128, 64, 128, -1), (256, 32, 256, -1), (64, 32, 64, 1000),
+                        (512, 16, 128, 1000), (128, 64, 128, 1024), (128, 64, 128, -1), (256, 32, 256, -1), (64, 32, 64, 1000),
                         (1024, 16, 128, 2000), (4096, 64, 128, 1024)):
         if want("group%d" % F):
             K = 1 << 18
