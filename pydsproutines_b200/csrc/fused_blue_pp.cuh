@@ -14,9 +14,8 @@ struct BluePPLayout {
     using L = PPLayout<PL, B, true>;
     static constexpr int COL_BH = L::CW;                                  // FFT_M(chirp)[output_bin(t, slot)], slot < V
     static constexpr int CW = L::CW + 2 * PL::V;
-    static_assert(L::COPIES == 1, "one warp of a group per lane quarter");
-    static_assert(CW <= 512, "tensor memory holds 512 columns");
-    static constexpr int TMEM_COLS = (CW <= 256) ? 256 : 512;
+    static_assert(CW * L::COPIES <= 512, "tensor memory holds 512 columns");
+    static constexpr int TMEM_COLS = (CW * L::COPIES <= 256) ? 256 : 512;
 };
 
 // second transform: the inputs are already in the registers in input_index order (no product), raw stores
@@ -107,7 +106,8 @@ __global__ void __launch_bounds__(PL::TG* B, 1) fused_blue_pp_kernel(const Stage
     __syncthreads();
     tc::tc_fence_after();
     const uint32_t tmem0 = *taddr_slot;
-    const uint32_t tb = tmem0 + (((uint32_t)(warp_cta & 3) * 32u) << 16);
+    // lane quarter of this warp, column block of the warps of a group that share a quarter
+    const uint32_t tb = tmem0 + (((uint32_t)(warp_cta & 3) * 32u) << 16) + (uint32_t)((t >> 7) * BL::CW);
     if (g < L::WRITERS) {
         float r[16];
 #pragma unroll
