@@ -155,11 +155,9 @@ __global__ void __launch_bounds__(512, 1) group_dense_kernel(const GroupDenseArg
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int64_t i0 = tile * ST;                          // first shift-list entry of the tile
         const int64_t s0 = a.shift0 + i0;
-        if (tile == (int64_t)blockIdx.x) {
-            // the first tile: every warp stages (later tiles are staged by warps 8 .. 15 under the previous transform phase)
-            gd_stage<LF>(a, stage, sst, SW, nstage, s0, threadIdx.x, 512);
-            __syncthreads();
-        }
+        // (staging the next tile by the eight warps that do not transform measured slower: it outlasts the transform)
+        gd_stage<LF>(a, stage, sst, SW, nstage, s0, threadIdx.x, 512);
+        __syncthreads();
         // ---- fold: two cells x eight shifts per thread ----
         float2 acc0[8], acc1[8];
 #pragma unroll
@@ -279,11 +277,8 @@ __global__ void __launch_bounds__(512, 1) group_dense_kernel(const GroupDenseArg
                 if (out.qf2) out.qf2[e] = ok ? mx / refn / en : 0.f;
                 if (out.fidx) out.fidx[e] = (ok && bin != 0xffffffffu) ? bin : 0u;
             }
-        } else if (tile + gridDim.x < ntiles) {
-            // the fold is done with the stage: the other warps fetch the windows of this CTA's next tile meanwhile
-            gd_stage<LF>(a, stage, sst, SW, nstage, a.shift0 + (tile + gridDim.x) * ST, (int)threadIdx.x - 32 * (ST / FPW), 512 - 32 * (ST / FPW));
         }
-        __syncthreads();     // u is free and the stage holds the next tile
+        __syncthreads();     // u and the stage are free for the next tile
     }
     tc::tc_fence_before();
     __syncthreads();
