@@ -24,8 +24,8 @@ namespace xc {
 int32_t search_pp_device(const StagedArgs& a, const FusedOut& out, int64_t K, int N, int fold, cudaStream_t stream);
 bool search_pp_takes(int N);
 bool search_blue_pp_takes(int M);
-int32_t search_blue_pp_device(const StagedArgs& a, const float2* bhat, int nvalid, int nbins, const FusedOut& out, int64_t K, int M,
-                              cudaStream_t stream);
+int32_t search_blue_pp_device(const StagedArgs& a, const float2* bhat, const float2* post, int nvalid, int nbins, const FusedOut& out,
+                              int64_t K, int M, cudaStream_t stream);
 constexpr int PP_MAX_STEP = 16;       // (groups per SM - 1) * step stays well inside the 2048 samples of window slack
 
 // ---------------------------------------------------------------------------------------------
@@ -494,10 +494,10 @@ int32_t fastxcorr_freq_device(const float2* cutout, int N, const float2* rx, int
         chirp_cutout_kernel<<<(M + 255) / 256, 256, 0, stream>>>(cutout, plan->d_b, N, M, d_cutb);
         XC_LAUNCH_CHECK();
         // shift ranges with (max, arg max) outputs: thread groups over one staged window, constants in tensor memory
-        if (search_blue_pp_takes(M) && !out.caf && !out.cplx && !sl.shifts && sl.step >= 1 && sl.step <= PP_MAX_STEP &&
+        if (search_blue_pp_takes(M) && !out.caf && !sl.shifts && sl.step >= 1 && sl.step <= PP_MAX_STEP &&
             sl.K >= 16 * (int64_t)sm_count() && search_layout() == LAYOUT_PP)
-            return search_blue_pp_device(StagedArgs{rx, rxlen, d_cutb, sl.shift0, (int)sl.step}, plan->d_bhat_nat, N, plan->nbins, out,
-                                         sl.K, M, stream);
+            return search_blue_pp_device(StagedArgs{rx, rxlen, d_cutb, sl.shift0, (int)sl.step}, plan->d_bhat_nat, plan->d_post, N, plan->nbins,
+                                         out, sl.K, M, stream);
         return dispatch_log2(plan->log2m, BlueRunner{d_cutb, N, plan, rx, rxlen, sl, out, stream});
     }
     return dispatch_log2(ilog2(N), FreqRunner{cutout, rx, rxlen, sl, out, stream});

@@ -80,9 +80,12 @@ struct BlueArgs {
     int nvalid;           // true cutout length N (samples of the window that must lie inside rx)
     int nbins;            // bins k < nbins count
     float inv_m2;         // 1 / M^2
+    const float2* post;   // [nbins] post-chirp exp(+i 2 pi w k^2 / 2): X[k] = conj(post[k] v[k]) / M (complex QF only)
 };
 
-template <class PL, int B>
+// CPLX: also the complex QF at the arg max (cztXcorr's default output, xcorrRoutines.py:413-457): candidate (bin, value) kept in
+// registers until the winning bin is known one FFT later, alternating bin slots (as fused_fft_pp_kernel)
+template <class PL, int B, bool CPLX>
 __global__ void __launch_bounds__(PL::TG* B, 1) fused_blue_pp_kernel(const StagedArgs a, const BlueArgs ba, const FusedOut out,
                                                                      const int64_t K, const int chunk) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -99,6 +102,7 @@ __global__ void __launch_bounds__(PL::TG* B, 1) fused_blue_pp_kernel(const Stage
     if (warp_cta == 0) tc::tmem_alloc(tc::smem_u32(taddr_slot), BL::TMEM_COLS);
     if (t == 0) {
         binmin[0] = 0xffffffffu;
+        binmin[1] = 0xffffffffu;
         gmax[0] = 0u;
         gmax[1] = 0u;
     }
@@ -173,6 +177,8 @@ __global__ void __launch_bounds__(PL::TG* B, 1) fused_blue_pp_kernel(const Stage
     const unsigned int bbase = (unsigned int)output_bin_base<PL>(t);
     float2 v[V];
     float pend = 0.f;
+    float2 cand = make_float2(0.f, 0.f);
+    unsigned int cand_bin = 0xffffffffu;
     int o = W + 1;
 
     for (int it = 0; it < chunk; ++it) {
@@ -193,14 +199,23 @@ __global__ void __launch_bounds__(PL::TG* B, 1) fused_blue_pp_kernel(const Stage
         o += B * step;
         // ---- FFT #1 of the chirped product (the barrier inside also orders the previous shift's bin atomics) ----
         pp_block_fft_fold<PL, B>(v, xw, tb, buf, t, bar);
+        unsigned int* const bslot = binmin + (CPLX ? (it & 1) : 0);
         if (t == 0 && it > 0) {
             const int p = e - B;
             if (p < n_act) {
-                const unsigned int b = *binmin;
+                const unsigned int b = CPLX ? binmin[(it & 1) ^ 1] : *binmin;
                 if (out.qf2) out.qf2[i0 + p] = pend;
                 if (out.fidx) out.fidx[i0 + p] = (b == 0xffffffffu) ? 0u : b;
             }
-            *binmin = 0xffffffffu;
+            if (!CPLX) *binmin = 0xffffffffu;
+        }
+        if constexpr (CPLX) {
+            if (cand_bin != 0xffffffffu && cand_bin == binmin[(it & 1) ^ 1]) {
+                const float sc = sqrtf(ba.inv_m2) / (sqrtf(*out.refnormsq) * sqrtf(out.energy[i0 + e - B]));
+                const float2 pz = cmul(__ldg(ba.post + cand_bin), cand);
+                out.cplx[i0 + e - B] = make_float2(pz.x * sc, -pz.y * sc);
+            }
+            cand_bin = 0xffffffffu;
         }
         // ---- times FFT_M(chirp), conjugated for the inverse transform ----
         {
@@ -252,6 +267,7 @@ __global__ void __launch_bounds__(PL::TG* B, 1) fused_blue_pp_kernel(const Stage
         bar();
         const float m = __uint_as_float(gmax[it & 1]);
         if (t == 0) gmax[(it & 1) ^ 1] = 0u;
+        if (CPLX && t == 0) binmin[(it & 1) ^ 1] = 0xffffffffu;       // read for the last time before this barrier
         if (ok && tmax == m) {
             unsigned int mybin = 0xffffffffu;
 #pragma unroll
@@ -261,21 +277,33 @@ __global__ void __launch_bounds__(PL::TG* B, 1) fused_blue_pp_kernel(const Stage
                     for (int i = 0; i < 8; ++i) {
                         const int j = 8 * c + i;
                         const unsigned int bj = bbase + (unsigned int)output_bin_off<PL>(j / PL::RL, j % PL::RL);
-                        if (nv[j] == m && bj < (unsigned int)ba.nbins) mybin = min(mybin, bj);
+                        if (nv[j] == m && bj < (unsigned int)ba.nbins && bj < mybin) {
+                            mybin = bj;
+                            if (CPLX) cand = v[j];
+                        }
                     }
                 }
             }
-            atomicMin(binmin, mybin);
+            atomicMin(bslot, mybin);
+            if (CPLX) cand_bin = mybin;
         }
         if (t == 0) pend = ok ? m * ba.inv_m2 / *out.refnormsq / out.energy[i0 + e] : 0.f;
+        if (CPLX && t == 0 && e < n_act && !ok) out.cplx[i0 + e] = make_float2(0.f, 0.f);
     }
     bar();
-    if (t == 0 && chunk > 0) {
+    if (chunk > 0) {
         const int p = B * (chunk - 1) + g;
-        if (p < n_act) {
-            const unsigned int b = *binmin;
+        const unsigned int b = binmin[CPLX ? ((chunk - 1) & 1) : 0];
+        if (t == 0 && p < n_act) {
             if (out.qf2) out.qf2[i0 + p] = pend;
             if (out.fidx) out.fidx[i0 + p] = (b == 0xffffffffu) ? 0u : b;
+        }
+        if constexpr (CPLX) {
+            if (cand_bin != 0xffffffffu && cand_bin == b) {
+                const float sc = sqrtf(ba.inv_m2) / (sqrtf(*out.refnormsq) * sqrtf(out.energy[i0 + p]));
+                const float2 pz = cmul(__ldg(ba.post + cand_bin), cand);
+                out.cplx[i0 + p] = make_float2(pz.x * sc, -pz.y * sc);
+            }
         }
     }
     tc::tc_fence_before();
@@ -285,11 +313,11 @@ __global__ void __launch_bounds__(PL::TG* B, 1) fused_blue_pp_kernel(const Stage
 
 template <class PL, int B>
 int32_t launch_blue_pp(const StagedArgs& a, const BlueArgs& ba, const FusedOut& out, int64_t K, cudaStream_t stream) {
-    auto kern = fused_blue_pp_kernel<PL, B>;
+    auto kern = out.cplx ? fused_blue_pp_kernel<PL, B, true> : fused_blue_pp_kernel<PL, B, false>;
     constexpr size_t smem = PPLayout<PL, B, true>::BYTES;
     if ((int)smem > max_smem_optin()) return fail(XC_ERR_UNSUPPORTED, "ping-pong Bluestein kernel needs %zu B of shared memory", smem);
-    static KernelOnce once;
-    XC_TRY(once.configure(kern, max_smem_optin()));
+    static KernelOnce once[2];
+    XC_TRY(once[out.cplx ? 1 : 0].configure(kern, max_smem_optin()));
     const int64_t per = (K + B - 1) / B;
     int64_t ctas = (int64_t)sm_count();
     if (ctas > per) ctas = per;

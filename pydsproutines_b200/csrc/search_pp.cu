@@ -44,10 +44,10 @@ bool search_blue_pp_takes(int) { return false; }
 #else
 bool search_blue_pp_takes(int M) { return M == 8192 || M == 4096 || M == 2048; }
 #endif
-int32_t search_blue_pp_device(const StagedArgs& a, const float2* bhat, int nvalid, int nbins, const FusedOut& out, int64_t K, int M,
-                              cudaStream_t stream) {
+int32_t search_blue_pp_device(const StagedArgs& a, const float2* bhat, const float2* post, int nvalid, int nbins, const FusedOut& out,
+                              int64_t K, int M, cudaStream_t stream) {
     const double m = (double)M;
-    const BlueArgs ba{bhat, nvalid, nbins, (float)(1.0 / (m * m))};
+    const BlueArgs ba{bhat, nvalid, nbins, (float)(1.0 / (m * m)), post};
     if (M == 8192) return launch_blue_pp<FftPlan<13, 256, 8, 32, 32>, 2>(a, ba, out, K, stream);     // 16 warps: 32 points per thread
     if (M == 4096) return launch_blue_pp<FftPlan<12, 128, 4, 32, 32>, XC_PP_B4096>(a, ba, out, K, stream);
     if (M == 2048) return launch_blue_pp<FftPlan<11, 64, 2, 32, 32>, XC_PP_B2048>(a, ba, out, K, stream);

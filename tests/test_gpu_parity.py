@@ -1025,6 +1025,46 @@ def test_pingpong_bluestein_lengths(xr, N, step):
     np.testing.assert_allclose(qc[inside], q[shc[inside] // step], rtol=5e-6, atol=1e-9)
 
 
+@pytest.mark.parametrize("N,nb", [(1500, 301), (3000, 1001), (700, 64)])
+def test_pingpong_bluestein_complex_outputs(xr, N, nb):
+    """The complex QF of the Bluestein searches from the ping-pong layout: cztXcorr's default output (complex QF at the best
+    bin of a chirp-z grid, xcorrRoutines.py:413-457) and fastXcorr(absResult=False) at a length that is not a power of two,
+    over shift ranges long enough for that layout, against short calls (csrc/bluestein.cuh) and the oracle."""
+    K = 6000
+    df = 2.0
+    fs = 4.0 * N * df                         # grid step = a quarter of the resolution fs / N: adjacent bins differ clearly
+    cutout, rx = signals.make_fastxcorr_case(3 * N + nb, N, N + K - 1, 2500, 0, amp=0.8)
+    f1, f2 = -df * (nb // 2), df * (nb // 2) - (0 if nb % 2 else df)
+    rx[2500:2500 + N] *= np.exp(2j * np.pi * (f1 + 7 * df) * np.arange(N) / fs).astype(np.complex64)      # a tone on grid point 7
+    z, fr = xr.cztXcorr(_dev(cutout), _dev(rx), f1, f2, fs, cztStep=df)
+    z = z.cpu().numpy()
+    fr = fr.cpu().numpy() if hasattr(fr, "cpu") else np.asarray(fr)
+    assert int(np.argmax(np.abs(z))) == 2500 and abs(fr[2500] - (f1 + 7 * df)) < 1e-9
+    zs, fs_ = [], []
+    for lo in range(0, K, 1500):
+        zz, ff = xr.cztXcorr(_dev(cutout), _dev(rx), f1, f2, fs, cztStep=df, shifts=np.arange(lo, lo + 1500))
+        zs.append(zz.cpu().numpy())
+        fs_.append(ff.cpu().numpy() if hasattr(ff, "cpu") else np.asarray(ff))
+    z2, f2_ = np.concatenate(zs), np.concatenate(fs_)
+    same = fr == f2_
+    assert same.sum() >= K - K // 200
+    np.testing.assert_allclose(z[same], z2[same], rtol=0, atol=5e-6 * float(np.abs(z2).max()))
+    idx = np.r_[0:6, 2497:2503, K - 6:K]
+    rz, rf = orc.cztXcorr(cutout, rx, f1, f2, fs, cztStep=df, shifts=idx)
+    ok = fr[idx] == rf
+    assert ok.sum() >= idx.size - 1 and ok[8]
+    np.testing.assert_allclose(z[idx][ok], rz[ok], rtol=0, atol=2e-5 * float(np.abs(rz).max()))
+    # fastXcorr(absResult=False) at the same length (DFT grid)
+    zc, fc = xr.fastXcorr(_dev(cutout), _dev(rx), freqsearch=True, absResult=False)
+    qc, fq = xr.fastXcorr(_dev(cutout), _dev(rx), freqsearch=True)
+    np.testing.assert_allclose(np.abs(zc.cpu().numpy()) ** 2, qc.cpu().numpy(), rtol=5e-6, atol=1e-10)
+    assert np.array_equal(fc.cpu().numpy(), fq.cpu().numpy())
+    rz, rf = orc.fastXcorr(cutout, rx, freqsearch=True, shifts=idx, absResult=False)
+    okb = fc.cpu().numpy()[idx] == rf
+    assert okb.sum() >= idx.size - 1
+    np.testing.assert_allclose(zc.cpu().numpy()[idx][okb], rz[okb], rtol=0, atol=2e-5 * float(np.abs(rz).max()))
+
+
 def test_warp_layout_windows_leaving_rx(xr):
     """N = 1024 (one warp per FFT over a staged window): windows that leave rx on either side give 0 / 0
     (IppXcorrFFT.cpp:125-130), the rest agrees with short calls (B-groups-per-CTA layout) and the oracle; several refills."""
