@@ -325,7 +325,8 @@ def config_line(which, lib, peaks, p32, p32src, steps):
         ms = float(np.median(kms[2:]))
         cells = float(c["K"]) * N
         flops = cells * (5.0 * np.log2(N) + 10.0)
-        layout = ("fused_fft_subwarp_kernel (%d lanes per FFT, %d FFTs per warp, staged window, constants in tensor memory)" % (N // 32, 1024 // N) if N < 1024 else
+        layout = ("fused_fft_kernel (one group of 512 threads, conj(cutout) in tensor memory)" if N == 16384 else
+                  "fused_fft_subwarp_kernel (%d lanes per FFT, %d FFTs per warp, staged window, constants in tensor memory)" % (N // 32, 1024 // N) if N < 1024 else
                   "fused_fft_warp_kernel (one warp per FFT, staged window, constants in tensor memory)" if N == 1024 else
                   "fused_fft_pp_kernel (ping-pong layout)" if N in (2048, 4096) else "fused_fft_kernel (B groups per CTA, round 1)")
         return {"workload": "fastXcorr freqsearch: %d-sample cutout, 2^20 shifts, %d-bin FFT per shift" % (N, N), "ms": ms,

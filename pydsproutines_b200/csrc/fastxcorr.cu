@@ -11,6 +11,7 @@
 
 #include "bluestein.cuh"
 #include "fused_fft_kernel.cuh"
+#include "fused_fft_pp.cuh"
 #ifdef XC_EXPERIMENTS   // earlier layouts of the N = 8192 search, kept for A/B runs only (tools/staged_check.py)
 #include "fused_fft_dual.cuh"
 #include "fused_fft_staged.cuh"
@@ -109,6 +110,76 @@ struct CutoutLoader {
     __device__ __forceinline__ bool load(float2* v, int t, int64_t i, const unsigned char* smem) const {
         if (!issue(v, t, i, smem)) return false;
         finish(v, t, smem);
+        return true;
+    }
+};
+
+// CutoutLoader with conj(cutout) in TENSOR MEMORY (one group of 512 threads: four warps per lane quarter, 64 columns each):
+// for 16384 points the cutout is 128 KB, fits neither shared memory beside the exchange buffer nor the L1, and was re-read from
+// the L2 for every shift.
+template <class PL>
+struct CutoutLoaderTmem {
+    static_assert(PL::V == 32 && PL::TG % 128 == 0 && PL::TG <= 1024, "32 points per thread");
+    static constexpr bool USES_TMEM = true;
+    static constexpr int COPIES = PL::TG / 128;
+    static constexpr int COLS = (64 * COPIES <= 64) ? 64 : (64 * COPIES <= 128) ? 128 : (64 * COPIES <= 256) ? 256 : 512;
+    const float2* rx;
+    int64_t rxlen;
+    const float2* cutout;
+    int64_t shift0, step;
+    const int64_t* shifts;
+
+    __host__ __device__ static constexpr size_t smem_bytes() { return 16; }
+    size_t dyn_smem() const { return 0; }
+    __device__ __forceinline__ void prepare(int tid, int, unsigned char* smem) const {
+        if (tid < 32) tc::tmem_alloc(tc::smem_u32(smem), COLS);
+        tc::tc_fence_before();
+    }
+    __device__ __forceinline__ uint32_t base(int t, const unsigned char* smem) const {
+        return *reinterpret_cast<const uint32_t*>(smem) + ((((uint32_t)(t >> 5) & 3u) * 32u) << 16) + (uint32_t)((t >> 7) * 64);
+    }
+    __device__ __forceinline__ void prepare2(int t, unsigned char* smem) const {      // one group per CTA: t = thread in the group
+        tc::tc_fence_after();
+        const uint32_t tb = base(t, smem);
+        float r[16];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int j = 8 * c + i;
+                const float2 cv = cutout[input_index<PL>(t, j / PL::R1, j % PL::R1)];
+                r[2 * i] = cv.x;
+                r[2 * i + 1] = -cv.y;
+            }
+            tc::tmem_st16(tb + 16 * c, r);
+        }
+        tc::tmem_st_wait();
+        tc::tc_fence_before();
+    }
+    __device__ __forceinline__ void release(int tid, unsigned char* smem) const {
+        tc::tc_fence_after();
+        if (tid < 32) tc::tmem_dealloc(*reinterpret_cast<const uint32_t*>(smem), COLS);
+    }
+    __device__ __forceinline__ bool load(float2* v, int t, int64_t i, const unsigned char* smem) const {
+        const int64_t s = shifts ? shifts[i] : shift0 + i * step;
+        if (s < 0 || s + PL::N > rxlen) return false;
+        const float2* x = rx + s + t;
+        constexpr int NQ = PL::V / PL::R1;
+        uint32_t cu[2][16];
+        const uint32_t tb = base(t, smem);
+        tc::tmem_ld16_issue(tb, cu[0]);
+#pragma unroll
+        for (int n1 = 0; n1 < PL::R1; ++n1)
+#pragma unroll
+            for (int q = 0; q < NQ; ++q) v[q * PL::R1 + n1] = __ldg(x + input_index<PL>(0, q, n1));
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            tc::tmem_ld_wait16(cu[c & 1]);
+            if (c + 1 < 4) tc::tmem_ld16_issue(tb + 16 * (c + 1), cu[(c + 1) & 1]);
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                v[8 * c + i] = pcmul(v[8 * c + i], make_float2(__uint_as_float(cu[c & 1][2 * i]), __uint_as_float(cu[c & 1][2 * i + 1])));
+        }
         return true;
     }
 };
@@ -235,6 +306,16 @@ struct FreqRunner {
             }
 #endif
         }
+#ifndef XC_NO_TMEM_CUTOUT
+        if constexpr (LOG2N == 14) {
+            // (max, arg max) searches at 16384 points: conj(cutout) from tensor memory instead of the L2
+            if (!out.caf && !out.cplx) {
+                using LT = CutoutLoaderTmem<typename PF::PL>;
+                static_assert(PF::B == 1, "one group per CTA");
+                return launch_fused<typename PF::PL, 1, LT>(LT{rx, rxlen, cutout, sl.shift0, sl.step, sl.shifts}, out, sl.K, stream);
+            }
+        }
+#endif
         return launch_fused<typename PF::PL, PF::B, LD>(ld, out, sl.K, stream);
     }
 };

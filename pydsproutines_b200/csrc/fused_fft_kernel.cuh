@@ -10,9 +10,18 @@
 // stay in the constant bank, pending results stay in shared memory, and the rarely used outputs
 // (complex QF, CAF rows) are compiled into a separate GENERAL instantiation.
 #pragma once
+#include <type_traits>
+
 #include "fft_engine.cuh"
 
 namespace xc {
+
+// loaders that keep their constants in tensor memory declare USES_TMEM and add prepare2() (after the first CTA barrier: the
+// allocation is visible) and release() (after the last one)
+template <class T, class = void>
+struct loader_uses_tmem : std::false_type {};
+template <class T>
+struct loader_uses_tmem<T, std::void_t<decltype(T::USES_TMEM)>> : std::bool_constant<T::USES_TMEM> {};
 
 template <int TG, int B>
 struct GroupBar {
@@ -71,6 +80,10 @@ __global__ void __launch_bounds__(PL::TG* B) fused_fft_kernel(const Loader loade
     float* const pend = reinterpret_cast<float*>(smem_raw + OFF_PEND) + g;
     if (t == 0) *binmin = 0xffffffffu;
     __syncthreads();
+    if constexpr (loader_uses_tmem<Loader>::value) {
+        loader.prepare2(threadIdx.x, smem_raw);
+        __syncthreads();
+    }
 
     FftThread<PL> th;
     th.init(t);
@@ -212,6 +225,10 @@ __global__ void __launch_bounds__(PL::TG* B) fused_fft_kernel(const Loader loade
         const unsigned int b = *binmin;
         if (out.qf2) out.qf2[i0 + chunk - 1] = *pend;
         if (out.fidx) out.fidx[i0 + chunk - 1] = (b == 0xffffffffu) ? 0u : b;
+    }
+    if constexpr (loader_uses_tmem<Loader>::value) {
+        __syncthreads();
+        loader.release(threadIdx.x, smem_raw);
     }
 }
 
