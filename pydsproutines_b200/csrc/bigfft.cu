@@ -423,7 +423,9 @@ __global__ void __launch_bounds__(256) big_finalize_kernel(const unsigned long l
 template <int LOG2N>
 struct BigGeom {
     using PL = typename PlanFor<LOG2N>::PL;
-    static constexpr int B = (PL::TG >= 256) ? 1 : 256 / PL::TG;
+    // 4096- and 8192-point passes run 512 threads per CTA, so that the transposed store / slab load still sees 4 (2) adjacent
+    // columns (benchmark_xcorrs 1e7, L = 4096 x 8192: 144 -> 122 ms)
+    static constexpr int B = (PL::TG >= 512) ? 1 : (PL::TG >= 128) ? 512 / PL::TG : 256 / PL::TG;
     static constexpr size_t SMEM = PL::TABLE_BYTES + sizeof(float2) * (size_t)PL::BUF * B + sizeof(unsigned long long) * B + 16;
 };
 
