@@ -5,6 +5,7 @@
 #include "group_pp.cuh"
 #include "group_warp.cuh"
 #include "group_dense.cuh"
+#include "group_rot2.cuh"
 #include "internal.cuh"
 
 namespace xc {
@@ -38,14 +39,17 @@ static int rot_window_slack(int G, int L) {
     if (W > 252 / B * B) W = 252 / B * B;
     return W;
 }
-template <class PL, int B, class LY = GroupPPLayout<PL, B, true>>
+using GPPL8K = FftPlan<13, 128, 8, 32, 32>;    // fftlen 8192: two groups of 128 threads, 64 rows of 128 cells (group_rot2.cuh)
+constexpr int GP_B8K = 2;
+
+template <class PL, int B, class LY = GroupPPLayout<PL, B, true>, int MAXE = GR_MAX_E>
 static int32_t group_rot_build(const float2* y, const int64_t* starts, int G, int L, GroupPPPlan* p) {
     constexpr int TG = PL::TG, F = PL::N;
-    static_assert(GR_MAX_E == sizeof(p->rdesc) / sizeof(p->rdesc[0]), "descriptor table size");
-    static_assert(F / TG == 32, "32 rows");
+    static_assert(GR_MAX_E == sizeof(p->rdesc) / sizeof(p->rdesc[0]) && MAXE <= GR_MAX_E, "descriptor table size");
+    static_assert(F / TG <= (int)sizeof(p->rcnt), "row counters");
     const int per = (L + TG - 1) / TG;
     const int E = G * per;
-    if (E + 2 > GR_MAX_E) return XC_OK;
+    if (E + 2 > MAXE) return XC_OK;
     const int W = rot_window_slack<PL, B, LY>(G, L);
     if (W < 4 * B) return XC_OK;
     const int SW = L + W;
@@ -159,6 +163,7 @@ int32_t group_pp_build(const float2* y, const int64_t* starts, int G, int L, int
     if (F == 256) return group_dense_build<8>(y, starts, G, L, p);
     if (F == 128) return group_dense_build<7>(y, starts, G, L, p);
     if (F == 64) return group_dense_build<6>(y, starts, G, L, p);
+    if (F == GPPL8K::N) return group_rot_build<GPPL8K, GP_B8K, GroupRot2Layout<GPPL8K, GP_B8K>, GR2_MAX_E>(y, starts, G, L, p);
     if (F == GPPL2K::N) return group_rot_build<GPPL2K, GP_B2K>(y, starts, G, L, p);
     if (F == GPPL1K::N) return group_rot_build<GPPL1K, GP_B1K, GroupWarpLayout<GP_B1K>>(y, starts, G, L, p);
     if (F == 512 || F == 32) {
@@ -302,8 +307,35 @@ static int32_t group_warp_launch(const GroupPPPlan& p, const int64_t* d_starts, 
     return XC_OK;
 }
 
+static int32_t group_rot2_launch(const GroupPPPlan& p, const int64_t* d_starts, const float2* rx, int64_t rxlen, int64_t shift0,
+                                 int64_t K, int64_t lo, int64_t hi, const FusedOut& out, cudaStream_t stream) {
+    constexpr int B = GP_B8K;
+    using LY = GroupRot2Layout<GPPL8K, B>;
+    auto kern = group_rot2_kernel<GPPL8K, B>;
+    const size_t smem = LY::bytes(p.G, p.L, p.W);
+    if ((int)smem > max_smem_optin()) return fail(XC_ERR_UNSUPPORTED, "group search kernel needs %zu B of shared memory", smem);
+    static KernelOnce once;
+    XC_TRY(once.configure(kern, max_smem_optin()));
+    GroupPPArgs a{rx, rxlen, shift0, lo, hi, d_starts, p.d_w, p.d_off, p.G, p.L, p.NC, p.nq_live, p.W};
+    GroupRot2Plan rp;
+    memcpy(rp.cnt, p.rcnt, sizeof(rp.cnt));
+    memcpy(rp.desc, p.rdesc, sizeof(rp.desc));
+    const int64_t per = (K + B - 1) / B;
+    int64_t ctas = (int64_t)sm_count();
+    if (ctas > per) ctas = per;
+    if (ctas < 1) ctas = 1;
+    const int64_t chunk = (per + ctas - 1) / ctas;
+    if (chunk >= (1ll << 29)) return fail(XC_ERR_UNSUPPORTED, "too many shifts per thread group");
+    profile_begin(stream);
+    kern<<<(unsigned)ctas, GPPL8K::TG * B, smem, stream>>>(a, rp, out, K, (int)chunk);
+    profile_end(stream);
+    XC_LAUNCH_CHECK();
+    return XC_OK;
+}
+
 int32_t group_pp_run(const GroupPPPlan& p, const int64_t* d_starts, const float2* rx, int64_t rxlen, int64_t shift0, int64_t K,
                      int64_t lo, int64_t hi, const FusedOut& out, cudaStream_t stream) {
+    if (p.F == GPPL8K::N) return group_rot2_launch(p, d_starts, rx, rxlen, shift0, K, lo, hi, out, stream);
     if (p.dense && p.F == 256) return group_dense_launch<8>(p, d_starts, rx, rxlen, shift0, K, lo, hi, out, stream);
     if (p.dense && p.F == 128) return group_dense_launch<7>(p, d_starts, rx, rxlen, shift0, K, lo, hi, out, stream);
     if (p.dense && p.F == 64) return group_dense_launch<6>(p, d_starts, rx, rxlen, shift0, K, lo, hi, out, stream);

@@ -51,7 +51,7 @@ struct GroupPPPlan {
     int rot, B, F;               // B = thread groups per SM of the kernel variant, F = transform length
     int bin_shift;               // the kernel's transform is 2^bin_shift times the requested fftlen: only every 2^bin_shift-th bin counts
     int dense, G4;               // dense-fold variant for short transforms (group_dense.cuh): d_w = float4 [G4][F / 2], d_off = descriptors
-    unsigned char rcnt[32];
+    unsigned char rcnt[64];
     uint32_t rdesc[192];
 };
 int32_t group_pp_build(const float2* y, const int64_t* starts, int G, int L, int F, GroupPPPlan* p);

@@ -1094,7 +1094,8 @@ def test_warp_layout_windows_leaving_rx(xr):
                                          (24, 200, "ragged", 4096), (64, 128, "dense", 4096), (3, 700, "ragged", 4096),
                                          (16, 64, "128g", 2048), (50, 100, "ragged", 2048), (64, 128, "dense", 2048),
                                          (16, 128, "1000g", 1024), (30, 50, "ragged", 1024), (5, 1000, "ragged", 1024),
-                                         (16, 128, "1000g", 512), (8, 300, "ragged", 512), (10, 20, "ragged", 32)])
+                                         (16, 128, "1000g", 512), (8, 300, "ragged", 512), (10, 20, "ragged", 32),
+                                         (64, 128, "1000g", 8192), (20, 300, "ragged", 8192), (64, 128, "128g", 8192)])
 def test_group_rotated_rows_vs_oracle_and_ell_layout(xr, G, L, kind, F):
     """GroupXcorrFFT, fftlen 4096 (and 2048: rows of 64 cells), contiguous shifts, group starts that are NOT aligned to the 128-cell rows of the transform
     (csrc/group_pp.cuh, ROT variant: sub-groups of 128 samples sorted by row, rotated thread mapping, carry into the next
