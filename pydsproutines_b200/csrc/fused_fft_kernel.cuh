@@ -117,19 +117,22 @@ __global__ void __launch_bounds__(PL::TG* B) fused_fft_kernel(const Loader loade
             // ---- CAF row: all bins in natural order.  The registers hold bins at a stride of R1 across the lanes, so the row
             // goes through the (now free) exchange buffer and leaves as coalesced runs (4-byte stores at a stride of R1
             // floats reached 0.13 of the HBM write rate) ----
-            if (PL::P == 1) {
+            if (PL::P <= 2) {
+                // one- and two-pass plans: lane t holds bins t + TG q + R1 k, i.e. the lanes already write consecutive bins
                 if (active) {
                     const float refn = *out.refnormsq;
                     const float denom_e = ok ? out.energy[i0 + it] : 1.f;
                     const float sc = ok ? 1.f / (sqrtf(refn) * sqrtf(denom_e)) : 0.f;
+                    const float sc2 = ok ? (1.f / refn) / denom_e : 0.f;
 #pragma unroll
-                    for (int j = 0; j < PL::RL; ++j) {
-                        const float2 x = v[j];
-                        if (out.caf_complex)
-                            reinterpret_cast<float2*>(out.caf)[(size_t)(i0 + it) * PL::N + output_bin<PL>(t, 0, j)] = make_float2(x.x * sc, x.y * sc);
-                        else
-                            out.caf[(size_t)(i0 + it) * PL::N + output_bin<PL>(t, 0, j)] = ok ? cnorm2(x) / refn / denom_e : 0.f;
-                    }
+                    for (int q = 0; q < V / PL::RL; ++q)
+#pragma unroll
+                        for (int j = 0; j < PL::RL; ++j) {
+                            const float2 x = v[q * PL::RL + j];
+                            const size_t o = (size_t)(i0 + it) * PL::N + output_bin<PL>(t, q, j);
+                            if (out.caf_complex) reinterpret_cast<float2*>(out.caf)[o] = make_float2(x.x * sc, x.y * sc);
+                            else out.caf[o] = cnorm2(x) * sc2;
+                        }
                 }
             } else {
                 bar();   // every thread has finished the last-pass loads: the buffer is free
