@@ -1205,6 +1205,33 @@ def test_group_dense_fold_short_fftlen(xr, G, L, F, kind):
     assert_bins(f[idx], fr, lambda i: _group_spec64(y, starts, rx, F, int(idx[i])), what="group bin")
 
 
+def test_group_kernels_ragged_shift_counts(xr):
+    """Shift counts that are not a multiple of the kernels' tiles (64 shifts per CTA tile in the dense-fold kernel, groups x
+    chunk in the rotated-row kernels), a first shift that is not zero, and windows that run past the end of rx for the last
+    shifts are not requested (the reference asserts them out): every fftlen family against the oracle at both ends."""
+    for F, G, L in ((128, 30, 128), (256, 9, 200), (1024, 12, 128), (2048, 20, 64), (4096, 40, 128), (8192, 30, 128)):
+        rng = np.random.default_rng(F + 7)
+        starts = np.cumsum(rng.integers(L, 700, G)).astype(np.int64)
+        starts -= starts[0]
+        y = signals.qpsk(rng, G * L).reshape(G, L)
+        K = 5000 + 37
+        first = 11
+        rx = signals.cnoise(rng, first + K + int(starts[-1]) + F + 5)
+        p0, k0 = 3333, F // 2 + 3
+        for g in range(G):
+            a = p0 + int(starts[g])
+            rx[a:a + L] += y[g] * signals.tone(L, k0, F, offset=int(starts[g]))
+        obj = xr.GroupXcorrFFT(y, starts, 1, fftlen=F)
+        sh = np.arange(first, first + K)
+        q, f = obj.xcorr(_dev(rx), sh)
+        q, f = q.cpu().numpy(), f.cpu().numpy()
+        assert q.shape == (K,) and int(np.argmax(q)) == p0 - first and int(f[p0 - first]) == k0
+        idx = np.r_[0:10, K - 10:K]
+        qr, fr = orc.GroupXcorrFFT(y, starts, 1, fftlen=F).xcorr(rx, sh[idx])
+        assert_qf2(q[idx], qr)
+        assert_bins(f[idx], fr, lambda i: _group_spec64(y, starts, rx, F, int(sh[idx[i]])), what="group bin")
+
+
 def test_groupfreq_large_planted_and_sampled(xr):
     """C3's groups (64 x 128 at 1024 g) against 256 frequencies over 2^17 shifts: the planted (shift, frequency) is the
     global peak, and 48 randomly sampled shifts agree with the oracle (size-independent checks at bench-like size)."""
