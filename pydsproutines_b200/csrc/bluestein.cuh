@@ -39,6 +39,10 @@ fused_bluestein_kernel(const Loader loader, const FusedOut out, const int64_t K,
     float* const pend = reinterpret_cast<float*>(smem_raw + OFF_PEND) + g;
     if (t == 0) *binmin = 0xffffffffu;
     __syncthreads();
+    if constexpr (loader_uses_tmem<Loader>::value) {
+        loader.prepare2(threadIdx.x, smem_raw);
+        __syncthreads();
+    }
 
     FftThread<PL> th;
     th.init(t);
@@ -168,6 +172,10 @@ fused_bluestein_kernel(const Loader loader, const FusedOut out, const int64_t K,
         const unsigned int b = *binmin;
         if (out.qf2) out.qf2[i0 + chunk - 1] = *pend;
         if (out.fidx) out.fidx[i0 + chunk - 1] = (b == 0xffffffffu) ? 0u : b;
+    }
+    if constexpr (loader_uses_tmem<Loader>::value) {
+        __syncthreads();
+        loader.release(threadIdx.x, smem_raw);
     }
 }
 

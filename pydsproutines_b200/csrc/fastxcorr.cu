@@ -128,6 +128,7 @@ struct CutoutLoaderTmem {
     const float2* cutout;
     int64_t shift0, step;
     const int64_t* shifts;
+    int nvalid = PL::N;            // Bluestein: only the first nvalid points of the padded window exist in rx
 
     __host__ __device__ static constexpr size_t smem_bytes() { return 16; }
     size_t dyn_smem() const { return 0; }
@@ -162,7 +163,7 @@ struct CutoutLoaderTmem {
     }
     __device__ __forceinline__ bool load(float2* v, int t, int64_t i, const unsigned char* smem) const {
         const int64_t s = shifts ? shifts[i] : shift0 + i * step;
-        if (s < 0 || s + PL::N > rxlen) return false;
+        if (s < 0 || s + nvalid > rxlen) return false;
         const float2* x = rx + s + t;
         constexpr int NQ = PL::V / PL::R1;
         uint32_t cu[2][16];
@@ -171,7 +172,10 @@ struct CutoutLoaderTmem {
 #pragma unroll
         for (int n1 = 0; n1 < PL::R1; ++n1)
 #pragma unroll
-            for (int q = 0; q < NQ; ++q) v[q * PL::R1 + n1] = __ldg(x + input_index<PL>(0, q, n1));
+            for (int q = 0; q < NQ; ++q) {
+                const int n = input_index<PL>(0, q, n1);
+                v[q * PL::R1 + n1] = (n + t < nvalid) ? __ldg(x + n) : make_float2(0.f, 0.f);
+            }
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
             tc::tmem_ld_wait16(cu[c & 1]);
@@ -514,6 +518,14 @@ struct BlueRunner {
         using PF = PlanFor<LOG2N>;
         using PL = typename PF::PL;
         if constexpr (PL::P >= 2) {
+#ifndef XC_NO_TMEM_CUTOUT
+            if constexpr (LOG2N == 14) {
+                // the chirped cutout (128 KB) from tensor memory instead of the L2
+                using LT = CutoutLoaderTmem<PL>;
+                return launch_bluestein<PL, 1, LT>(LT{rx, rxlen, cutb, sl.shift0, sl.step, sl.shifts, N}, out, sl.K, plan->d_bhat_perm, plan->d_post,
+                                                   plan->nbins, stream);
+            }
+#endif
             using LD = ChirpLoader<PL, PF::CS>;
             LD ld{rx, rxlen, cutb, sl.shift0, sl.step, sl.shifts, N};
             return launch_bluestein<PL, PF::B, LD>(ld, out, sl.K, plan->d_bhat_perm, plan->d_post, plan->nbins, stream);
