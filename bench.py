@@ -274,6 +274,47 @@ def config_line(which, lib, peaks, p32, p32src, steps):
         return {"workload": "C3 GroupXcorrFFT: 64 groups x 128, fftlen 4096, 2^22 shifts", "ms": ms,
                 "cells_per_s": c["K"] * c["F"] / (ms * 1e-3), "peak_checked": [c["p0"], c["k0"]],
                 "roofline": fp32_roofline(flops, ms, p32, p32src, "group_pp_kernel<4096> (staged group windows, contributor lists in tensor memory, pruned transform)", 16.0 * c["K"], peaks)}
+    if which in ("c3r", "g128"):
+        # C3's groups with a spacing that is not a multiple of the transform's 128-cell rows (starts 1000 g: the rotated-row
+        # kernel), and the reference's default fftlen = group length (dense-fold kernel); 2^20 shifts each
+        if which == "c3r":
+            c = signals.config_c3(log2_shifts=20, spacing=1000)
+            kern, name = "group_pp_kernel<4096, ROT> (rotated-row fold)", "GroupXcorrFFT: 64 groups x 128 at starts 1000 g, fftlen 4096, 2^20 shifts"
+        else:
+            c = signals.config_c3(log2_shifts=20, F=128)
+            kern, name = "group_dense_kernel<128> (register-tiled fold, sub-warp FFT)", "GroupXcorrFFT: 64 groups x 128, fftlen 128 (default fftlen = group length), 2^20 shifts"
+        obj = xr.GroupXcorrFFT(c["ygroups"], c["starts"], 1, fftlen=c["F"])
+        rx = dev(c["rx"])
+        shl = xr._group_shifts(np.arange(c["K"]), rx)
+        q, f = obj._handle.run(rx, shl, True, False)[:2]
+        p = int(torch.argmax(q))
+        assert p == c["p0"] and int(f[p]) == c["k0"], "%s lost the planted peak" % which
+        ms = float(np.median(event_times(lambda: obj._handle.run(rx, shl, True, False), steps, 2, flush)))
+        flops = c["K"] * (c["F"] * (5.0 * np.log2(c["F"]) + 10.0) + 8.0 * 64 * 128)      # transform + fold
+        return {"workload": name, "ms": ms, "cells_per_s": c["K"] * c["F"] / (ms * 1e-3), "peak_checked": [c["p0"], c["k0"]],
+                "roofline": fp32_roofline(flops, ms, p32, p32src, kern, 16.0 * c["K"], peaks)}
+    if which == "b1000":
+        # a cutout length that is not a power of two (the default of the reference's benchmark_xcorrs.py): Bluestein, M = 2048
+        N, K = 1000, 1 << 20
+        cutout, rxa = signals.make_fastxcorr_case(1007, N, N + K - 1, 600001, 123)
+        cu, rx = dev(cutout), dev(rxa)
+        q, f, peak = xr.fastXcorrPeak(cu, rx, freqsearch=True)
+        assert (peak.shift, peak.fidx) == (600001, 123), "lost the planted peak at N = 1000"
+        lib.xc_profile_enable(1)
+        kms = []
+        for i in range(2 + steps):
+            flush.zero_()
+            xr.fastXcorrPeak(cu, rx, freqsearch=True)
+            kms.append(lib.xc_profile_last_ms())
+        lib.xc_profile_enable(0)
+        ms = float(np.median(kms[2:]))
+        cells = float(K) * N
+        flops = cells * (5.0 * np.log2(N) + 10.0)
+        r = fp32_roofline(flops, ms, p32, p32src, "fused_blue_pp_kernel<2048> (Bluestein, both transforms in the ping-pong layout)", 16.0 * K, peaks)
+        r["executed_flops_per_launch"] = float(K) * 2 * 2048 * (5.0 * 11 + 10.0)
+        r["note"] = "flops counted for the true length; Bluestein executes two 2048-point transforms per shift (4.5 x)"
+        return {"workload": "fastXcorr freqsearch: 1000-sample cutout (not a power of two), 2^20 shifts", "ms": ms,
+                "cells_per_s": cells / (ms * 1e-3), "peak_checked": [600001, 123], "roofline": r}
     if which in ("c4", "c6"):
         if which == "c4":
             c = signals.config_c4()
@@ -568,7 +609,7 @@ def run_ours(args, rank, world, local_rank):
                                               % (n, os.cpu_count() or 1, CPU_NOTE)}
         if world == 1 and not args.no_configs:
             line["configs"] = []
-            for w in ("c1", "c3", "c4", "c6", "bx", "n256", "n512", "n1024", "n2048", "n4096", "n16384"):
+            for w in ("c1", "c3", "c3r", "g128", "c4", "c6", "bx", "b1000", "n256", "n512", "n1024", "n2048", "n4096", "n16384"):
                 try:
                     line["configs"].append(config_line(w, lib, peaks, p32, p32src, 3))
                 except Exception as e:                      # a config failure must not hide the headline
@@ -585,7 +626,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=["c2", "c1", "c3", "c4", "c6", "bx", "bx10", "n256", "n512", "n1024", "n2048", "n4096", "n16384"],
+    ap.add_argument("--workload", default="c2", choices=["c2", "c1", "c3", "c3r", "g128", "c4", "c6", "bx", "bx10", "b1000", "n256", "n512", "n1024", "n2048", "n4096", "n16384"],
                     help="single-GPU headline config (default C2, BASELINE.json's metric config)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-configs", action="store_true", help="skip the C1 / C3 / C4 / C6 lines of the N = 1 run")
