@@ -257,10 +257,17 @@ def config_line(which, lib, peaks, p32, p32src, steps):
         q = xr._fastxcorr_call(cu, rx, sh, False)[0]
         assert int(torch.argmax(q)) == c["p0"], "C1 lost the planted peak"
         ms = float(np.median(event_times(lambda: xr._fastxcorr_call(cu, rx, sh, False), steps, 2, flush)))
-        flops = K * (8.0 * 4096 + 10)
+        flops = K * (8.0 * 4096 + 10)                          # the sliding dot product
+        # executed: fast correlation through 8192-point blocks (ovs.cuh): two transforms + the spectrum product per block of 4097 shifts
+        nblk = -(-K // (8192 - 4096 + 1))
+        executed = nblk * (2 * 8192 * (5.0 * 13 + 10) + 8.0 * 8192)
+        r = fp32_roofline(executed, ms, p32, p32src, "ovs_kernel<8192> (overlap-save fast correlation, one wave of 128 CTAs)", 16.0 * K, peaks)
+        r["algorithmic_flops_sliding_dot_product"] = flops
+        r["frac_in_sliding_dot_product_flops"] = flops / (ms * 1e-3) / 1e12 / p32
+        r["note"] = ("executed flops of the fast correlation (110 x fewer than the 8 N + 10 per shift of SURVEY 8d's accounting, which "
+                     "this time would put at several times the FP32 peak); the call is one wave of 128 CTAs plus two small kernels: latency bound")
         return {"workload": "C1 fastXcorr no freqsearch: 4096-sample cutout, 2^20-sample rx, step 1", "ms": ms,
-                "cells_per_s": K / (ms * 1e-3), "peak_checked": [c["p0"]],
-                "roofline": fp32_roofline(flops, ms, p32, p32src, "nofreq_tiled_kernel", 16.0 * K, peaks)}
+                "cells_per_s": K / (ms * 1e-3), "peak_checked": [c["p0"]], "roofline": r}
     if which == "c3":
         c = signals.config_c3()
         obj = xr.GroupXcorrFFT(c["ygroups"], c["starts"], 1, fftlen=c["F"])

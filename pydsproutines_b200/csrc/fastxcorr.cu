@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "bluestein.cuh"
+#include "ovs.cuh"
 #include "fused_fft_kernel.cuh"
 #include "fused_fft_pp.cuh"
 #ifdef XC_EXPERIMENTS   // earlier layouts of the N = 8192 search, kept for A/B runs only (tools/staged_check.py)
@@ -603,6 +604,8 @@ int32_t fastxcorr_freq_device(const float2* cutout, int N, const float2* rx, int
 // =============================================================================================
 namespace xc {
 
+constexpr int OVS_MIN_N = 1024;    // overlap-save from this cutout length ...
+constexpr int64_t OVS_MIN_K = 8192; // ... and this many shifts on
 constexpr int ND_THREADS = 128;   // threads per CTA
 constexpr int ND_R = 8;           // consecutive shifts per thread
 constexpr int ND_TS = ND_THREADS * ND_R;   // shifts per CTA tile
@@ -752,6 +755,13 @@ int32_t fastxcorr_nofreq_device(const float2* cutout, int N, const float2* rx, i
     const bool contiguous = !sl.shifts && sl.step == 1 && sl.shift0 >= 0 && sl.shift0 + sl.K - 1 + N <= rxlen;
     if (contiguous) {
         XC_TRY(sliding_sum_device(rx + sl.shift0, true, rxlen - sl.shift0, 0, N, sl.K, d_energy, 0, stream));
+#ifndef XC_NO_OVS
+        // long cutouts over many shifts: fast correlation through 8192- / 16384-point blocks (ovs.cuh) instead of 8 N flops per shift
+        if (N >= OVS_MIN_N && N <= 8192 && sl.K >= OVS_MIN_K) {
+            if (N <= 4096) return ovs_run<13>(cutout, N, rx, rxlen, sl.shift0, sl.K, d_energy, d_refn, qf2, cplx, stream);
+            return ovs_run<14>(cutout, N, rx, rxlen, sl.shift0, sl.K, d_energy, d_refn, qf2, cplx, stream);
+        }
+#endif
         const int64_t blocks = (sl.K + ND_TS - 1) / ND_TS;
         nofreq_tiled_kernel<<<(unsigned)blocks, ND_THREADS, 0, stream>>>(cutout, N, rx, rxlen, sl.shift0, sl.K, d_energy,
                                                                           d_refn, qf2, cplx);

@@ -1065,6 +1065,35 @@ def test_pingpong_bluestein_complex_outputs(xr, N, nb):
     np.testing.assert_allclose(zc.cpu().numpy()[idx][okb], rz[okb], rtol=0, atol=2e-5 * float(np.abs(rz).max()))
 
 
+@pytest.mark.parametrize("N", [1024, 1500, 4096, 6000, 8192])
+def test_nofreq_overlap_save_vs_direct_and_oracle(xr, N):
+    """fastXcorr without frequency search over many shifts runs as a fast correlation through 8192- / 16384-point blocks
+    (csrc/ovs.cuh) from 1024-sample cutouts on: against the sliding dot product (the allocation-free entry point still runs
+    it) on every shift, and against the oracle, QF^2 and the complex result (absResult=False)."""
+    import ctypes as C
+    import torch
+    from pydsproutines_b200 import _lib
+    K = 30011
+    p0 = 12345
+    cutout, rx = signals.make_fastxcorr_case(400 + N, N, N + K - 1 + 100, p0, 0, amp=0.9)
+    dc, drx = _dev(cutout), _dev(rx)
+    sh = np.arange(5, 5 + K)
+    q = xr.fastXcorr(dc, drx, shifts=sh).cpu().numpy()
+    assert q.shape == (K,) and int(np.argmax(q)) == p0 - 5
+    lib = _lib.load()
+    qd = torch.empty(K, dtype=torch.float32, device="cuda")
+    _lib.check(lib.xc_fastxcorr_nofreq_noalloc_c64(C.c_void_p(dc.data_ptr()), N, C.c_void_p(drx.data_ptr()), drx.numel(), 5, K,
+                                                   C.c_void_p(qd.data_ptr()), None))
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(q, qd.cpu().numpy(), rtol=2e-5, atol=1e-7 * float(q.max()))
+    idx = np.r_[0:8, p0 - 5 - 4:p0 - 5 + 4, K - 8:K]
+    assert_qf2(q[idx], orc.fastXcorr(cutout, rx, shifts=sh[idx]))
+    z = xr.fastXcorr(dc, drx, shifts=sh, absResult=False).cpu().numpy()
+    rz = orc.fastXcorr(cutout, rx, shifts=sh[idx], absResult=False)
+    np.testing.assert_allclose(z[idx], rz, rtol=0, atol=2e-5 * float(np.abs(rz).max()))
+    np.testing.assert_allclose(np.abs(z) ** 2, q, rtol=1e-5, atol=1e-9)
+
+
 def test_warp_layout_windows_leaving_rx(xr):
     """N = 1024 (one warp per FFT over a staged window): windows that leave rx on either side give 0 / 0
     (IppXcorrFFT.cpp:125-130), the rest agrees with short calls (B-groups-per-CTA layout) and the oracle; several refills."""
