@@ -348,6 +348,23 @@ def config_line(which, lib, peaks, p32, p32src, steps):
             cells, flops, passes = c["K"] * NFQ, c["K"] * NFQ * 8.0 * 64 * 128, 3
             name = "C6 GroupXcorr (frequency list, SURVEY 8f): 64 groups x 128, 256 frequencies, 2^20 shifts"
             checked, tcores = None, True
+        if which == "c4":
+            # the shipped path for (best, template) at this template length is the fast correlation (mt_ovs.cuh, FP32); the
+            # tensor-core contraction it replaces is timed beside it (XC_MT_DIRECT)
+            hd = xr._MtHandle(c["templates"].conj(), False, direct=True)
+            ms_tc = float(np.median(event_times(lambda: hd.run(x, 0, c["K"], True, False, False), steps, 1, flush)))
+            S = 8192 - 1024 + 1
+            nblk = -(-c["K"] // S)
+            executed = nblk * ((1 + 256) * 8192 * (5.0 * 13 + 10) + 256 * 8.0 * 8192)
+            r = fp32_roofline(executed, ms, p32, p32src, "mt_ovs_kernel<8192> (overlap-save: one transform of the x block for all templates)", 16.0 * c["K"], peaks)
+            r["note"] = ("executed flops of the fast correlation; SURVEY 8d counts the dense contraction (8 L flops per template and "
+                         "shift = %.3g flop), which the tensor-core kernel runs in %.1f ms" % (flops, ms_tc))
+            peak = float(peaks.get("bf16_tflops", 1590.0))
+            return {"workload": name, "ms": ms, "cells_per_s": cells / (ms * 1e-3), "peak_checked": checked, "tensor_cores": False,
+                    "roofline": r,
+                    "tensor_core_contraction": {"ms": ms_tc, "bound": "tensor", "achieved": passes * flops / (ms_tc * 1e-3) / 1e12, "peak": peak,
+                                                "frac": passes * flops / (ms_tc * 1e-3) / 1e12 / peak, "precision_passes": passes,
+                                                "kernel": "mt_tc_kernel (XC_MT_DIRECT)"}}
         peak = float(peaks.get("bf16_tflops", 1590.0))
         ach = passes * flops / (ms * 1e-3) / 1e12
         return {"workload": name, "ms": ms, "cells_per_s": cells / (ms * 1e-3), "peak_checked": checked,

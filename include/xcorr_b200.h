@@ -226,9 +226,13 @@ int32_t xc_time_scan_c128(const void* x, const void* y, int64_t N, double shift_
  * (TemplateCrossCorrelator semantics; without it they are used as given, multiTemplateSlidingDotProduct semantics),
  * XC_MT_FP32 keeps the contraction on the FP32 SIMT kernel instead of the tensor cores (BF16 hi/lo split, FP32
  * accumulate; both agree to 1e-5 -- the flag exists for callers who want plain FP32 products and for A/B runs).
- * energies: optional float32[T] template energies (NULL = computed inside). */
+ * energies: optional float32[T] template energies (NULL = computed inside).
+ * (best, template index) requests for templates of 512 ... 4096 samples over at least four blocks of 8193 - L shifts run as a fast
+ * correlation (overlap-save through 8192-point FFT blocks, one transform of the x block for all templates, FP32); XC_MT_DIRECT
+ * keeps the contraction.  Both agree with the reference to 1e-5. */
 #define XC_MT_CONJ 1
 #define XC_MT_FP32 2
+#define XC_MT_DIRECT 4   /* keep the dense contraction (tensor cores) also where the fast-correlation path would run */
 typedef struct xc_mt xc_mt;
 int32_t xc_mt_create(const void* templates, int32_t T, int32_t L, int32_t conj, const float* energies,
                      xc_mt** handle);

@@ -17,7 +17,7 @@ LIB_PATH = os.path.join(_HERE, "libxcorr_b200.so")
 
 XC_HOST, XC_DEVICE = 0, 1
 XC_FLAG_ZERO_OOB = 1
-XC_MT_CONJ, XC_MT_FP32 = 1, 2
+XC_MT_CONJ, XC_MT_FP32, XC_MT_DIRECT = 1, 2, 4
 XC_NOALLOC_MAX_SHIFTS = 1 << 20
 XC_OK, XC_ERR_ARG, XC_ERR_RANGE, XC_ERR_UNSUPPORTED, XC_ERR_NOMEM, XC_ERR_CUDA = 0, -1, -2, -3, -4, -5
 

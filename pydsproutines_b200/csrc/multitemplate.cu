@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "internal.cuh"
+#include "mt_ovs.cuh"
 
 struct xc_mt {
     int32_t T, L, L8;
@@ -17,10 +18,13 @@ struct xc_mt {
     float* d_energies;     // [T]
     xc::MtTcPlan tc;       // tensor-core plan (usable when the templates are exact in BF16)
     int32_t device;        // the device that owns the arrays of this handle
+    float2* d_H;           // [T][8192] spectra of the templates for the fast-correlation path (mt_ovs.cuh), made at first use
+    int32_t fp32_only;     // XC_MT_FP32 at create time: plain FP32 products wanted, no fast correlation either
 };
 
 namespace xc {
 
+constexpr int MT_OVS_MIN_L = 512;      // templates from this length on take the fast-correlation path over long records
 constexpr int MT_THREADS = 128;
 constexpr int MT_R = 8;
 constexpr int MT_TS = MT_THREADS * MT_R;
@@ -176,6 +180,8 @@ int32_t xc_mt_create(const void* templates, int32_t T, int32_t L, int32_t conj, 
     h->T = T; h->L = L; h->L8 = L8;
     h->device = current_device();
     h->d_templates = nullptr; h->d_energies = nullptr;
+    h->d_H = nullptr;
+    h->fp32_only = (conj & (XC_MT_FP32 | XC_MT_DIRECT)) ? 1 : 0;
     cudaError_t e = cudaMalloc(&h->d_templates, sizeof(float2) * padded.size());
     if (e == cudaSuccess) e = cudaMalloc(&h->d_energies, sizeof(float) * T);
     if (e == cudaSuccess) e = cudaMemcpy(h->d_templates, padded.data(), sizeof(float2) * padded.size(), cudaMemcpyHostToDevice);
@@ -202,6 +208,7 @@ int32_t xc_mt_destroy(xc_mt* h) {
     mt_tc_release(&h->tc);
     cudaFree(h->d_templates);
     cudaFree(h->d_energies);
+    cudaFree(h->d_H);
     delete h;
     return XC_OK;
 }
@@ -243,7 +250,32 @@ int32_t xc_mt_correlate(xc_mt* h, const void* x, int64_t xlen, int64_t start, in
     float* d_energy = (float*)workspace(SLOT_TMP1, sizeof(float) * (size_t)K);
     if (!d_energy) return XC_ERR_NOMEM;
     XC_TRY(sliding_sum_device(dx + start, true, xlen - start, 0, h->L, K, d_energy, 0, st));
-    if (h->tc.usable) {
+    using OPL = PlanFor<13>::PL;                       // 8192-point blocks, one group of 256 threads per CTA
+    constexpr int64_t OM = OPL::N;
+    if (!dfull && !h->fp32_only && h->L >= MT_OVS_MIN_L && h->L <= OM / 2 && K >= 4 * (OM - h->L + 1)) {
+        // (best, template) over a long record: fast correlation through 8192-point blocks (mt_ovs.cuh)
+        constexpr size_t osmem = OPL::TABLE_BYTES + sizeof(float2) * (size_t)OPL::BUF;
+        if (!h->d_H) {
+            XC_CUDA_TRY(cudaMalloc(&h->d_H, sizeof(float2) * (size_t)h->T * OM));
+            auto tk = mt_ovs_table_kernel<OPL>;
+            static KernelOnce tonce;
+            XC_TRY(tonce.configure(tk, max_smem_optin()));
+            tk<<<(unsigned)h->T, OPL::TG, osmem, st>>>(h->d_templates, h->L, h->L8, h->d_H);
+            XC_LAUNCH_CHECK();
+        }
+        auto kern = mt_ovs_kernel<OPL>;
+        static KernelOnce once;
+        XC_TRY(once.configure(kern, max_smem_optin()));
+        const int S = (int)(OM - h->L + 1);
+        const int64_t nblocks = (K + S - 1) / S;
+        int64_t ctas = nblocks < (int64_t)sm_count() ? nblocks : (int64_t)sm_count();
+        MtOvsArgs oa{dx, xlen, start, K, S, h->T, h->d_H, h->d_energies, d_energy, db, dt, sqrt_out ? 1 : 0,
+                     (float)(1.0 / ((double)OM * (double)OM))};
+        profile_begin(st);
+        kern<<<(unsigned)ctas, OPL::TG, osmem, st>>>(oa, nblocks);
+        profile_end(st);
+        XC_LAUNCH_CHECK();
+    } else if (h->tc.usable) {
         // dense complex contraction on the tensor cores (tcgen05); the full (T, K) complex QF comes out of the same
         // kernel's complex epilogue (flag 2), normalised and template-major
         XC_TRY(mt_tc_run(h->tc, dx, xlen, start, K, d_energy, db, dt, (sqrt_out ? 1 : 0) | (dfull ? 2 : 0), st, nullptr, dfull));

@@ -970,7 +970,7 @@ class CyGroupXcorrFFT:
 # a9: TemplateCrossCorrelator  (xcorrRoutines.py:277-371)
 # ------------------------------------------------------------------------------------------------
 class _MtHandle:
-    def __init__(self, templates, conj, energies=None, fp32=False):
+    def __init__(self, templates, conj, energies=None, fp32=False, direct=False):
         lib = _lib.load()
         if _lib.is_torch(templates):
             templates = templates.detach().cpu().numpy()
@@ -982,7 +982,7 @@ class _MtHandle:
             e = np.ascontiguousarray(energies, dtype=np.float32)
         self.T, self.L = t.shape
         self._h = C.c_void_p()
-        flags = (_lib.XC_MT_CONJ if conj else 0) | (_lib.XC_MT_FP32 if fp32 else 0)
+        flags = (_lib.XC_MT_CONJ if conj else 0) | (_lib.XC_MT_FP32 if fp32 else 0) | (_lib.XC_MT_DIRECT if direct else 0)
         check(lib.xc_mt_create(_lib.ptr(t), self.T, self.L, flags, _lib.ptr(e), C.byref(self._h)))
 
     @property

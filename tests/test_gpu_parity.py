@@ -545,6 +545,38 @@ def test_mt_inexact_templates_split_hi_lo(xr):
     np.testing.assert_allclose(full_tc, full_32, rtol=0, atol=2e-5 * np.abs(full_32).max())
 
 
+@pytest.mark.parametrize("T,L", [(6, 700), (3, 4096), (20, 512)])
+def test_mt_fast_correlation_vs_fp32_and_oracle(xr, T, L):
+    """Templates of 512 ... 4096 samples over a long record: (best, template) come from the overlap-save path
+    (csrc/mt_ovs.cuh: one transform of the x block for all templates); against the FP32 SIMT kernel (XC_MT_FP32) on every
+    shift, against the oracle on windows, start offset and the sqrt output included."""
+    rng = np.random.default_rng(T * 10 + L)
+    templates = signals.qpsk(rng, T * L).reshape(T, L) * np.linspace(0.7, 1.3, T, dtype=np.float32)[:, None]
+    templates = templates.astype(np.complex64)
+    K, start = 4 * (8192 - L + 1) + 777, 13
+    x = signals.cnoise(rng, start + K + L - 1 + 50)
+    plants = [(5000, 1 % T), (start + K - 3000, (T - 1))]
+    for pos, t in plants:
+        x[pos:pos + L] += np.complex64(1.5) * templates[t].conj()
+    h = xr._MtHandle(templates, False)
+    best, tidx, _, _ = h.run(_dev(x), start, K, True, False, False)
+    best, tidx = best.cpu().numpy(), tidx.cpu().numpy()
+    for pos, t in plants:
+        assert tidx[pos - start] == t and best[pos - start] > 0.5
+    h32 = xr._MtHandle(templates, False, fp32=True)
+    b32, t32, _, _ = h32.run(_dev(x), start, K, True, False, False)
+    b32, t32 = b32.cpu().numpy(), t32.cpu().numpy()
+    np.testing.assert_allclose(best, b32, rtol=3e-5, atol=1e-7 * float(b32.max()))
+    assert_templates(tidx, t32, templates, x, start)
+    for a in (0, plants[0][0] - start - 8, K - 16):
+        ti_ref, q_ref = orc.multiTemplateSlidingDotProduct(x, templates, start + a, 16)
+        assert_qf2(best[a:a + 16], q_ref)
+        assert_templates(tidx[a:a + 16], ti_ref, templates, x, start + a)
+    bs, ts, _, _ = h.run(_dev(x), start, K, True, False, True)
+    np.testing.assert_allclose(bs.cpu().numpy(), np.sqrt(best), rtol=1e-6)
+    assert np.array_equal(ts.cpu().numpy(), tidx)
+
+
 # ---------------------------------------------------------------------------------------------
 # a14: gather / copy helpers
 # ---------------------------------------------------------------------------------------------
