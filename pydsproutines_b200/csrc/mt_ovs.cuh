@@ -60,6 +60,7 @@ __global__ void __launch_bounds__(PL::TG) mt_ovs_kernel(const MtOvsArgs a, const
     float2* const tab = reinterpret_cast<float2*>(smem_raw);
     build_fft_tables<PL>(tab, t, TG);
     float2* const buf = reinterpret_cast<float2*>(smem_raw + PL::TABLE_BYTES);
+    float2* const rbuf = buf + PL::BUF;                 // M + M / 8 cells
     __syncthreads();
     FftThread<PL> th;
     th.init(t);
@@ -93,17 +94,25 @@ __global__ void __launch_bounds__(PL::TG) mt_ovs_kernel(const MtOvsArgs a, const
                 const float2 p = pcmul(X[sl], __ldg(Ht + (size_t)sl * TG));
                 v[sl] = make_float2(p.x, -p.y);
             }
-            bar();    // last-pass loads of the previous transform are done: the buffer is free
+            // reorder from output bins to input order through a buffer of its own, one pad cell per 8 cells: the stores (bins at
+            // a stride of R1 = 8 cells across the lanes) and the loads (consecutive cells) are both conflict free, and the
+            // transform's exchange buffer needs no barrier of its own (the previous reads of rbuf are behind the barrier
+            // inside the previous transform; the barrier below also says that everyone is done with the last pass of it)
 #pragma unroll
             for (int q = 0; q < V / PL::RL; ++q)
 #pragma unroll
-                for (int j = 0; j < PL::RL; ++j) buf[blue_cell(output_bin<PL>(t, q, j))] = v[q * PL::RL + j];
+                for (int j = 0; j < PL::RL; ++j) {
+                    const int i = output_bin<PL>(t, q, j);
+                    rbuf[i + (i >> 3)] = v[q * PL::RL + j];
+                }
             bar();
 #pragma unroll
             for (int n1 = 0; n1 < PL::R1; ++n1)
 #pragma unroll
-                for (int q = 0; q < NQ; ++q) v[q * PL::R1 + n1] = buf[blue_cell(input_index<PL>(t, q, n1))];
-            bar();
+                for (int q = 0; q < NQ; ++q) {
+                    const int i = input_index<PL>(t, q, n1);
+                    v[q * PL::R1 + n1] = rbuf[i + (i >> 3)];
+                }
             block_fft<PL>(v, th, tab, buf, t, bar);
             const float ie = 1.f / __ldg(a.tenergy + tt);
 #pragma unroll

@@ -254,7 +254,7 @@ int32_t xc_mt_correlate(xc_mt* h, const void* x, int64_t xlen, int64_t start, in
     constexpr int64_t OM = OPL::N;
     if (!dfull && !h->fp32_only && h->L >= MT_OVS_MIN_L && h->L <= OM / 2 && K >= 4 * (OM - h->L + 1)) {
         // (best, template) over a long record: fast correlation through 8192-point blocks (mt_ovs.cuh)
-        constexpr size_t osmem = OPL::TABLE_BYTES + sizeof(float2) * (size_t)OPL::BUF;
+        constexpr size_t osmem = OPL::TABLE_BYTES + sizeof(float2) * (size_t)(OPL::BUF + OM + OM / 8);    // + the reorder buffer
         if (!h->d_H) {
             XC_CUDA_TRY(cudaMalloc(&h->d_H, sizeof(float2) * (size_t)h->T * OM));
             auto tk = mt_ovs_table_kernel<OPL>;
