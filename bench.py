@@ -356,7 +356,7 @@ def config_line(which, lib, peaks, p32, p32src, steps):
             S = 8192 - 1024 + 1
             nblk = -(-c["K"] // S)
             executed = nblk * ((1 + 256) * 8192 * (5.0 * 13 + 10) + 256 * 8.0 * 8192)
-            r = fp32_roofline(executed, ms, p32, p32src, "mt_ovs_kernel<8192> (overlap-save: one transform of the x block for all templates)", 16.0 * c["K"], peaks)
+            r = fp32_roofline(executed, ms, p32, p32src, "mt_ovs2_kernel<8192> (overlap-save: one transform of the x block for all templates; X and the running maxima in tensor memory)", 16.0 * c["K"], peaks)
             r["note"] = ("executed flops of the fast correlation; SURVEY 8d counts the dense contraction (8 L flops per template and "
                          "shift = %.3g flop), which the tensor-core kernel runs in %.1f ms" % (flops, ms_tc))
             peak = float(peaks.get("bf16_tflops", 1590.0))

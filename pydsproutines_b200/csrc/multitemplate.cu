@@ -263,16 +263,25 @@ int32_t xc_mt_correlate(xc_mt* h, const void* x, int64_t xlen, int64_t start, in
             tk<<<(unsigned)h->T, OPL::TG, osmem, st>>>(h->d_templates, h->L, h->L8, h->d_H);
             XC_LAUNCH_CHECK();
         }
-        auto kern = mt_ovs_kernel<OPL>;
-        static KernelOnce once;
-        XC_TRY(once.configure(kern, max_smem_optin()));
         const int S = (int)(OM - h->L + 1);
         const int64_t nblocks = (K + S - 1) / S;
-        int64_t ctas = nblocks < (int64_t)sm_count() ? nblocks : (int64_t)sm_count();
         MtOvsArgs oa{dx, xlen, start, K, S, h->T, h->d_H, h->d_energies, d_energy, db, dt, sqrt_out ? 1 : 0,
                      (float)(1.0 / ((double)OM * (double)OM))};
+#ifndef XC_MT_OVS1      // the shipped variant: two groups per SM, X and the running maxima in tensor memory (15.4 -> 12.9 ms at C4)
+        auto kern = mt_ovs2_kernel<OPL, 2>;
+        constexpr size_t ksmem = OPL::TABLE_BYTES + sizeof(float2) * (size_t)OPL::BUF * 2 + 16;
+        constexpr int kthreads = OPL::TG * 2;
+        int64_t ctas = (nblocks + 1) / 2 < (int64_t)sm_count() ? (nblocks + 1) / 2 : (int64_t)sm_count();
+#else
+        auto kern = mt_ovs_kernel<OPL>;
+        constexpr size_t ksmem = osmem;
+        constexpr int kthreads = OPL::TG;
+        int64_t ctas = nblocks < (int64_t)sm_count() ? nblocks : (int64_t)sm_count();
+#endif
+        static KernelOnce once;
+        XC_TRY(once.configure(kern, max_smem_optin()));
         profile_begin(st);
-        kern<<<(unsigned)ctas, OPL::TG, osmem, st>>>(oa, nblocks);
+        kern<<<(unsigned)ctas, kthreads, ksmem, st>>>(oa, nblocks);
         profile_end(st);
         XC_LAUNCH_CHECK();
     } else if (h->tc.usable) {
