@@ -262,6 +262,7 @@ int32_t xc_mt_correlate(xc_mt* h, const void* x, int64_t xlen, int64_t start, in
             XC_TRY(tonce.configure(tk, max_smem_optin()));
             tk<<<(unsigned)h->T, OPL::TG, osmem, st>>>(h->d_templates, h->L, h->L8, h->d_H);
             XC_LAUNCH_CHECK();
+            XC_CUDA_TRY(cudaStreamSynchronize(st));      // the handle may be used from another stream next time
         }
         const int S = (int)(OM - h->L + 1);
         const int64_t nblocks = (K + S - 1) / S;
