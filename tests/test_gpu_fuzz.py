@@ -10,7 +10,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("tool,cases,seed", [("fuzz_paths.py", 60, 101), ("fuzz_groups.py", 40, 102)])
+@pytest.mark.parametrize("tool,cases,seed", [("fuzz_paths.py", 60, 101), ("fuzz_groups.py", 40, 102), ("fuzz_mt.py", 10, 103)])
 def test_dispatch_fuzz(tool, cases, seed):
     r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", tool), str(cases), str(seed)], cwd=ROOT, capture_output=True,
                        text=True, timeout=900)
